@@ -1,0 +1,72 @@
+/*
+ * libsgnn_b200 -- C ABI of the B200 (sm_100a) kernels behind the sgnn learned-simulator path.
+ *
+ * The reference (xrkong/sgnn) is pure Python: it has no FFI.  Its hot path bottoms out in
+ * third-party Python/C++ entry points; each function below names the call it replaces
+ * (paths relative to the reference tree).  Host code (sgnn_b200/*.py) binds these with ctypes.
+ *
+ * Conventions: every entry returns 0 on success or a negative code (message through
+ * sgnn_last_error()); pointers are DEVICE pointers unless stated; the caller owns all
+ * buffers incl. workspaces; every call is asynchronous on `stream` (a cudaStream_t passed
+ * as void*), allocates nothing and never synchronises with the host.
+ */
+#ifndef SGNN_B200_H
+#define SGNN_B200_H
+#include <stddef.h>
+#include "../sgnn_b200/csrc/params.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* sgnn_last_error(void);
+int sgnn_version(void);
+int sgnn_sm_arch(void);                               /* 100: built for sm_100a only */
+int sgnn_device_info(int* sm_count, int* cc_major, int* cc_minor);
+
+/* Neighbour search -> receiver-sorted CSR, bit-exact to
+ *   torch_geometric.nn.radius_graph(pos, r, batch, loop, max_num_neighbors)
+ * as called at sgnn/single_scale/learned_simulator.py:116-117 (K=20) and
+ * sgnn/multi_scale/multi_scale_graph.py:222-227,269-274 (K=24).
+ *   pos/pos_stride : particle i at pos + i*pos_stride (floats); dim in [1,3]
+ *   example_ptr    : [n_examples+1] int32 boundaries (replaces the `batch` vector built at
+ *                    learned_simulator.py:104-106)
+ *   rowptr [n+1], src/tgt [n*(K + !loop)] : outputs; E = rowptr[n] stays on the device     */
+size_t sgnn_radius_graph_workspace_bytes(int n, int max_neighbors);
+int sgnn_radius_graph_csr(const float* pos, long pos_stride, int n, int dim, const int* example_ptr,
+                          int n_examples, double r, int max_neighbors, int loop, void* workspace,
+                          size_t workspace_bytes, int* rowptr, int* src, int* tgt, void* stream);
+
+/* nn.Linear weight block -> tensor-core operand image (K-major SWIZZLE_128B); replaces the
+ * implicit cuBLAS operand handling of every nn.Linear at graph_network.py:41-42.           */
+int sgnn_pack_weight(const float* w, int ld, int row0, int n, int col0, int k, int kpad, float scale,
+                     int round_tf32, float* dst, void* stream);
+/* row-major latents <-> 128-row operand tiles (module-level API of InteractionNetwork)      */
+int sgnn_pack_rows_to_tiles(const float* rows, long ld, const int* perm, int n_rows, int width,
+                            int round_tf32, float* tiles, void* stream);
+int sgnn_unpack_tiles_to_rows(const float* tiles, const int* perm, int n_rows, int width, float scale,
+                              float* rows, long ld, void* stream);
+
+/* Edge features + Encoder.edge_fn: learned_simulator.py:299-312, graph_network.py:92-96,
+ * multi_scale_simulator.py:203-238, multi_scale_gnn.py:248-259.                             */
+size_t sgnn_edge_encoder_smem_bytes(int blob_bytes, int hidden, int out, int tc);
+int sgnn_edge_encoder_fwd(const SgnnEdgeEncoderParams* p, int use_tensor_cores, int grid, void* stream);
+
+/* InteractionNetwork.message + PyG aggregate (index_select x2, cat, edge MLP, LayerNorm,
+ * scatter_add): graph_network.py:173,178-199; multi_scale_gnn.py:84-110,132-157,179-205.   */
+size_t sgnn_edge_layer_smem_bytes(int blob_bytes, int he, int hidden, int out, int tc);
+int sgnn_edge_layer_fwd(const SgnnEdgeLayerParams* p, int use_tensor_cores, int grid, void* stream);
+
+/* Node features + Encoder.node_fn (learned_simulator.py:257-290, graph_network.py:86-90);
+ * InteractionNetwork.update + residual (graph_network.py:176,201-222); Decoder + Euler
+ * integrator (graph_network.py:321-333, learned_simulator.py:381-411).                      */
+size_t sgnn_node_smem_bytes(const SgnnNodeParams* p, int tc);
+int sgnn_node_fwd(const SgnnNodeParams* p, int use_tensor_cores, int grid, void* stream);
+
+/* self-test of the GEMM tile primitive (tests/test_gemm_tile_gpu.py)                        */
+int sgnn_debug_gemm(const float* a, const float* wimg, int k, int n, float* d, int tc, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

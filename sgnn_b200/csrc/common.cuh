@@ -1,0 +1,215 @@
+// Common device/host helpers for libsgnn_b200 (sm_100a only).
+//
+// Tensor-core GEMMs in this library are tcgen05.mma kind::tf32 with both operands in shared
+// memory in the canonical K-major SWIZZLE_128B layout and fp32 accumulators in TMEM:
+//   * a K-block is 32 fp32 (128 bytes) wide; a tile of R rows x 32 floats is R*128 bytes,
+//     rows grouped by 8 (1024-byte swizzle atoms); inside an atom the 16-byte chunk index is
+//     XORed with (row & 7)  [Swizzle<3,4,3> on byte addresses]
+//   * a wider operand is a sequence of K-blocks, each its own [R x 128 B] tile
+//   * one tcgen05.mma consumes K = 8 fp32 (32 bytes); stepping K inside a K-block advances
+//     the descriptor start address by 32 bytes
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define SGNN_OK 0
+#define SGNN_ERR_ARG -1
+#define SGNN_ERR_CUDA -2
+#define SGNN_ERR_UNSUPPORTED -3
+
+void sgnn_set_error(const char* fmt, ...);
+
+#define SGNN_CHECK_ARG(cond, ...)        \
+  do {                                   \
+    if (!(cond)) {                       \
+      sgnn_set_error(__VA_ARGS__);       \
+      return SGNN_ERR_ARG;               \
+    }                                    \
+  } while (0)
+
+#define SGNN_CUDA(expr)                                                         \
+  do {                                                                          \
+    cudaError_t _e = (expr);                                                    \
+    if (_e != cudaSuccess) {                                                    \
+      sgnn_set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e),    \
+                     __FILE__, __LINE__);                                       \
+      return SGNN_ERR_CUDA;                                                     \
+    }                                                                           \
+  } while (0)
+
+#define SGNN_LAUNCH_CHECK()  SGNN_CUDA(cudaGetLastError())
+
+#ifdef __CUDACC__
+#define SGNN_HD __host__ __device__
+#else
+#define SGNN_HD
+#endif
+SGNN_HD static inline int sgnn_ceil_div(long a, long b) { return (int)((a + b - 1) / b); }
+
+#ifdef __CUDACC__
+namespace sgnn {
+
+constexpr int kTileRows = 128;        // rows (edges or nodes) per tensor-core tile = UMMA M
+constexpr int kKBlock = 32;           // fp32 per 128-byte swizzled row
+constexpr int kKBlockBytes = 128;
+
+// ---- TF32 ---------------------------------------------------------------------------
+// round-to-nearest (ties away) to TF32, kept in an fp32 container. The tensor core ignores
+// the 13 low mantissa bits; rounding first halves the representation error and unbiases it.
+__device__ __forceinline__ float to_tf32(float x) {
+  uint32_t u;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
+  return __uint_as_float(u);
+}
+
+// ---- swizzled K-major tile addressing -------------------------------------------------
+// byte offset of element (row, col) of an operand with `rows` rows; col over the full K.
+__device__ __forceinline__ uint32_t sw128_offset(int row, int col, int rows) {
+  const int kb = col >> 5, c = col & 31;
+  return (uint32_t)(kb * rows * kKBlockBytes + (row >> 3) * 1024 + (row & 7) * 128 +
+                    ((((c >> 2) ^ (row & 7)) & 7) << 4) + ((c & 3) << 2));
+}
+// byte offset of the 16-byte chunk `chunk` (4 floats; chunk index over the full K) of `row`
+__device__ __forceinline__ uint32_t sw128_chunk_offset(int row, int chunk, int rows) {
+  const int kb = chunk >> 3, c = chunk & 7;
+  return (uint32_t)(kb * rows * kKBlockBytes + (row >> 3) * 1024 + (row & 7) * 128 +
+                    (((c ^ (row & 7)) & 7) << 4));
+}
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+
+// ---- mbarrier -----------------------------------------------------------------------
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) {
+  }
+}
+
+// ---- TMA bulk copy (global -> shared, completes on an mbarrier) ------------------------
+__device__ __forceinline__ void tma_bulk_g2s(void* smem_dst, const void* gmem_src, uint32_t bytes,
+                                             uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+          "r"(smem_u32(smem_dst)),
+      "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+// generic-proxy writes to shared memory -> visible to the async proxy (tcgen05.mma, TMA)
+__device__ __forceinline__ void fence_proxy_async_smem() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+
+// ---- tcgen05 / TMEM -------------------------------------------------------------------
+__device__ __forceinline__ void tmem_alloc(uint32_t* smem_result, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                   smem_u32(smem_result)),
+               "r"(ncols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols)
+               : "memory");
+}
+__device__ __forceinline__ void tc_fence_before_sync() {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after_sync() {
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+// all previously issued tcgen05.mma of this thread arrive on `bar` when complete
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                   smem_u32(bar))
+               : "memory");
+}
+
+// shared-memory matrix descriptor: K-major, SWIZZLE_128B, 8-row groups 1024 B apart
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);   // start address  [0,14)
+  d |= (uint64_t)1 << 16;                        // leading byte offset (unused for SW128 K-major)
+  d |= (uint64_t)(1024 >> 4) << 32;              // stride byte offset [32,46)
+  d |= (uint64_t)1 << 46;                        // descriptor version (Blackwell)
+  d |= (uint64_t)2 << 61;                        // layout type: SWIZZLE_128B
+  return d;
+}
+// instruction descriptor: D fp32, A/B tf32, both K-major, shape M x N
+__device__ __forceinline__ uint32_t umma_idesc_tf32(int m, int n) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) |
+         ((uint32_t)(m >> 4) << 24);
+}
+// D[tmem] (+)= A[smem] * B[smem]^T, K = 8 (tf32)
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
+                                          uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// Issue the MMAs of one GEMM: D[128 x n] = A[128 x k] * W[n x k]^T (k multiple of 32).
+// a_base / w_base: shared addresses of the operands (1024-byte aligned K-block tiles).
+__device__ __forceinline__ void umma_gemm_tf32(uint32_t tmem_d, uint32_t a_base, uint32_t w_base,
+                                               int k, int n, bool accumulate_first = false) {
+  const uint32_t idesc = umma_idesc_tf32(kTileRows, n);
+  uint32_t acc = accumulate_first ? 1u : 0u;
+  for (int kb = 0; kb < k / kKBlock; ++kb) {
+    const uint32_t a_kb = a_base + kb * kTileRows * kKBlockBytes;
+    const uint32_t w_kb = w_base + kb * n * kKBlockBytes;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      umma_tf32(tmem_d, umma_desc_sw128(a_kb + j * 32), umma_desc_sw128(w_kb + j * 32), idesc, acc);
+      acc = 1u;
+    }
+  }
+}
+
+// TMEM -> registers: this warp's 32 lanes x 32 consecutive fp32 columns starting at `taddr`
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
+  uint32_t r[32];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n\t"
+      "tcgen05.wait::ld.sync.aligned;"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]),
+        "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]),
+        "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]),
+        "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+        "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+}  // namespace sgnn
+#endif  // __CUDACC__

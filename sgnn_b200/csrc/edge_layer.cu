@@ -1,0 +1,279 @@
+// Edge side of one message-passing layer (InteractionNetwork.message + PyG sum-aggregation,
+// sgnn/single_scale/graph_network.py:178-199; G2M/M2M/M2G blocks, multi_scale_gnn.py:84-205).
+//
+//   m_e   = LN( MLP( [x_tgt | x_src | 2^l e0] ) )          reference: concat then Linear
+//         = LN( MLP'( e0 (2^l W1c)^T + P[tgt] + Q[src] ) )  here: P = x W1a^T + b1, Q = x W1b^T
+//   agg_i = sum_{e : tgt(e) = i} m_e                        (deterministic, CSR row order)
+//
+// One persistent CTA of 128 threads per SM slot walks 128-edge tiles of the receiver-sorted
+// edge array.  Per tile: TMA bulk load of the e0 tile (already in A-operand layout) ->
+// tcgen05 GEMMs with the layer's weights resident in shared memory -> thread-per-row epilogues
+// (gather P/Q, ReLU, LayerNorm) -> segmented column sums -> agg rows.  Neither the [E,3H]
+// concat, nor the hidden activations, nor the per-edge messages ever touch HBM, and because of
+// the reference's e' = 2e quirk (graph_network.py:173-176) no edge latent is written at all.
+//
+// Algorithmic HBM bytes per edge: 4*he (e0) + 8 (src,tgt) ; per node 4*out (agg) ; P/Q rows
+// are gathers that mostly hit L2 (counted once per node: 8*hidden).
+#include "mlp_tile.cuh"
+#include "params.h"
+
+namespace sgnn {
+
+struct EdgeMisc {
+  uint64_t bar_w, bar_e, bar_mma;
+  uint32_t tmem_slot;
+  int n_edges;
+  int tgt_s[kTileRows + 4];     // [0] = receiver of the edge before the tile, [1+r] = row r
+  int piece_tgt[8];
+  int piece_flag[8];            // [2g] head piece of warp g (1 = exists, 3 = runs through), [2g+1] tail
+  float pieces[8 * 128];
+};
+
+struct EdgeLayerSmem {
+  int blob, e_tile, hid, misc, simt, total;
+};
+__host__ __device__ inline EdgeLayerSmem edge_layer_smem(int blob_bytes, int he, int hidden, int out,
+                                                         bool tc) {
+  EdgeLayerSmem s;
+  const int w = hidden > out ? hidden : out;
+  s.blob = 0;
+  s.e_tile = align_up(blob_bytes, 1024);
+  s.hid = s.e_tile + kTileRows * he * 4;
+  s.misc = s.hid + kTileRows * w * 4;
+  s.simt = align_up(s.misc + (int)sizeof(EdgeMisc), 1024);
+  s.total = s.simt + (tc ? 0 : kTileRows * pow2_cols(2 * w) * 4) + 1024;  // +1024: base alignment
+  return s;
+}
+
+__device__ __forceinline__ float m_tile_read(const float* m, int row, int col, int width) {
+  return m[row * width + ((((col >> 2) ^ (row & 7))) << 2) + (col & 3)];
+}
+
+template <bool TC>
+__global__ void __launch_bounds__(kThreads) edge_layer_kernel(const SgnnEdgeLayerParams p) {
+  char* smem = smem_base_1024();
+  const int hidden = p.mlp.hidden, out = p.mlp.out, he = p.he, nh = p.mlp.n_hidden;
+  const int w = hidden > out ? hidden : out;
+  const EdgeLayerSmem L = edge_layer_smem(p.blob_bytes, he, hidden, out, TC);
+  const float* blob_f = reinterpret_cast<const float*>(smem + L.blob);
+  char* e_tile = smem + L.e_tile;
+  char* hid = smem + L.hid;
+  EdgeMisc* misc = reinterpret_cast<EdgeMisc*>(smem + L.misc);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tile_bytes = kTileRows * he * 4;
+
+  const int n_edges = p.rowptr[p.n_nodes];
+  const int n_tiles = (n_edges + kTileRows - 1) / kTileRows;
+  if ((int)blockIdx.x >= n_tiles) return;   // uniform per CTA, before any barrier/TMEM use
+
+  if (tid == 0) {
+    mbar_init(&misc->bar_w, 1);
+    mbar_init(&misc->bar_e, 1);
+    mbar_fence_init();
+    tma_load_span(smem + L.blob, reinterpret_cast<const char*>(p.blob), p.blob_bytes, &misc->bar_w);
+    tma_load_span(e_tile, reinterpret_cast<const char*>(p.e_tiles) + (long)blockIdx.x * tile_bytes,
+                  tile_bytes, &misc->bar_e);
+  }
+  TileAcc<TC> acc;
+  acc_setup<TC>(acc, pow2_cols(2 * w), &misc->bar_mma, &misc->tmem_slot,
+                reinterpret_cast<float*>(smem + L.simt));
+  mbar_wait(&misc->bar_w, 0);
+  uint32_t phase_e = 0;
+
+  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const int e0 = tile * kTileRows;
+    const int nvalid = n_edges - e0 < kTileRows ? n_edges - e0 : kTileRows;
+    const int eidx = e0 + tid;
+    const int s = tid < nvalid ? p.src[eidx] : -1;
+    const int t = tid < nvalid ? p.tgt[eidx] : -3;
+    misc->tgt_s[1 + tid] = t;
+    if (tid == 0) {
+      misc->tgt_s[0] = tile > 0 ? p.tgt[e0 - 1] : -2;
+      misc->tgt_s[1 + kTileRows] = e0 + kTileRows < n_edges ? p.tgt[e0 + kTileRows] : -3;
+    }
+    if (tid < 8) misc->piece_flag[tid] = 0;
+
+    // ---- stage 0: e0 (2^l W1c)^T, then + P[tgt] + Q[src], ReLU ----
+    mbar_wait(&misc->bar_e, phase_e);
+    phase_e ^= 1u;
+    gemm_step<TC>(acc, e_tile, smem + p.mlp.w_off[0], he, hidden, 0, false);
+    gemm_wait<TC>(acc);
+    if constexpr (!TC) __syncthreads();      // every thread has finished reading the e0 tile
+    if (tid == 0 && tile + (int)gridDim.x < n_tiles)
+      tma_load_span(e_tile, reinterpret_cast<const char*>(p.e_tiles) +
+                                (long)(tile + gridDim.x) * tile_bytes, tile_bytes, &misc->bar_e);
+    {
+      const float* prow = p.pq + (long)(t < 0 ? 0 : t) * 2 * hidden;
+      const float* qrow = p.pq + (long)(s < 0 ? 0 : s) * 2 * hidden + hidden;
+      for (int c = 0; c < hidden; c += 32) {
+        float v[32];
+        acc_load32<TC>(acc, c, v);
+        if (tid < nvalid) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 a = __ldg(reinterpret_cast<const float4*>(prow + c) + j);
+            const float4 b = __ldg(reinterpret_cast<const float4*>(qrow + c) + j);
+            v[4 * j] += a.x + b.x; v[4 * j + 1] += a.y + b.y;
+            v[4 * j + 2] += a.z + b.z; v[4 * j + 3] += a.w + b.w;
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+        a_tile_store32<TC>(hid, c, v);
+      }
+    }
+    // ---- hidden -> hidden stages (nmlp_layers > 1) ----
+    int region = 0;
+    for (int l = 1; l < nh; ++l) {
+      a_tile_publish<TC>();
+      region ^= 1;
+      gemm_step<TC>(acc, hid, smem + p.mlp.w_off[l], hidden, hidden, region * w, false);
+      gemm_wait<TC>(acc);
+      const float* b = blob_f + p.mlp.b_off[l];
+      for (int c = 0; c < hidden; c += 32) {
+        float v[32];
+        acc_load32<TC>(acc, region * w + c, v);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j] + b[c + j], 0.f);
+        a_tile_store32<TC>(hid, c, v);
+      }
+    }
+    // ---- output stage + LayerNorm -> message tile M (aliases hid) ----
+    a_tile_publish<TC>();
+    region ^= 1;
+    gemm_step<TC>(acc, hid, smem + p.mlp.w_off[nh], hidden, out, region * w, false);
+    gemm_wait<TC>(acc);
+    float* m_tile = reinterpret_cast<float*>(hid);
+    {
+      const float* b = blob_f + p.mlp.b_off[nh];
+      const float* gam = blob_f + p.mlp.gamma_off;
+      const float* bet = blob_f + p.mlp.beta_off;
+      float mean, rstd;
+      row_ln_stats<TC>(acc, region * w, out, b, mean, rstd);
+      for (int c = 0; c < out; c += 32) {
+        float v[32];
+        acc_load32<TC>(acc, region * w + c, v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float4 y;
+          y.x = (v[4 * j] + b[c + 4 * j] - mean) * rstd * gam[c + 4 * j] + bet[c + 4 * j];
+          y.y = (v[4 * j + 1] + b[c + 4 * j + 1] - mean) * rstd * gam[c + 4 * j + 1] + bet[c + 4 * j + 1];
+          y.z = (v[4 * j + 2] + b[c + 4 * j + 2] - mean) * rstd * gam[c + 4 * j + 2] + bet[c + 4 * j + 2];
+          y.w = (v[4 * j + 3] + b[c + 4 * j + 3] - mean) * rstd * gam[c + 4 * j + 3] + bet[c + 4 * j + 3];
+          const int chunk = (c >> 2) + j;
+          *reinterpret_cast<float4*>(m_tile + tid * out + ((chunk ^ (tid & 7)) << 2)) = y;
+        }
+      }
+    }
+    if constexpr (TC) tc_fence_before_sync();
+    __syncthreads();   // tgt_s / piece_flag visible; all TMEM reads of this tile retired
+
+    // ---- segmented sums over the receiver-sorted rows: warp g owns rows 32g..32g+31, lane
+    //      owns out/32 consecutive columns; control flow is warp-uniform ----
+    const int cpl = out >> 5;                  // columns per lane: 1, 2 or 4
+    const int r0 = warp * 32;
+    if (r0 < nvalid) {
+      const int rend = r0 + 32 < nvalid ? r0 + 32 : nvalid;
+      int cur = misc->tgt_s[1 + r0];
+      const bool first_cont = misc->tgt_s[r0] == cur;
+      bool first_seg = true;
+      float sum[4] = {0.f, 0.f, 0.f, 0.f};
+      for (int row = r0; row < rend; ++row) {
+        const int tr = misc->tgt_s[1 + row];
+        if (tr != cur) {
+          if (first_seg && first_cont) {
+            for (int j = 0; j < cpl; ++j) misc->pieces[(2 * warp) * 128 + lane * cpl + j] = sum[j];
+            if (lane == 0) { misc->piece_tgt[2 * warp] = cur; misc->piece_flag[2 * warp] = 1; }
+          } else {
+            for (int j = 0; j < cpl; ++j) p.agg[(long)cur * out + lane * cpl + j] = sum[j];
+          }
+          first_seg = false;
+          cur = tr;
+          sum[0] = sum[1] = sum[2] = sum[3] = 0.f;
+        }
+        for (int j = 0; j < cpl; ++j) sum[j] += m_tile_read(m_tile, row, lane * cpl + j, out);
+      }
+      const bool cont_next = misc->tgt_s[1 + rend] == cur;
+      if (first_seg && first_cont) {
+        for (int j = 0; j < cpl; ++j) misc->pieces[(2 * warp) * 128 + lane * cpl + j] = sum[j];
+        if (lane == 0) { misc->piece_tgt[2 * warp] = cur; misc->piece_flag[2 * warp] = cont_next ? 3 : 1; }
+      } else if (cont_next) {
+        for (int j = 0; j < cpl; ++j) misc->pieces[(2 * warp + 1) * 128 + lane * cpl + j] = sum[j];
+        if (lane == 0) { misc->piece_tgt[2 * warp + 1] = cur; misc->piece_flag[2 * warp + 1] = 1; }
+      } else {
+        for (int j = 0; j < cpl; ++j) p.agg[(long)cur * out + lane * cpl + j] = sum[j];
+      }
+    }
+    __syncthreads();
+    // ---- stitch the pieces of rows that straddle warp groups / tiles (warp 0) ----
+    if (warp == 0) {
+      float carry[4] = {0.f, 0.f, 0.f, 0.f};
+      bool has = false, from_prev = false;
+      int ctgt = -1;
+      for (int g = 0; g < 4; ++g) {
+        const int f0 = misc->piece_flag[2 * g];
+        if (f0) {
+          if (!has) { has = true; from_prev = true; ctgt = misc->piece_tgt[2 * g];
+                      carry[0] = carry[1] = carry[2] = carry[3] = 0.f; }
+          for (int j = 0; j < cpl; ++j) carry[j] += misc->pieces[(2 * g) * 128 + lane * cpl + j];
+          if (!(f0 & 2)) {
+            float* dst = from_prev ? p.head + (long)tile * out : p.agg + (long)ctgt * out;
+            for (int j = 0; j < cpl; ++j) dst[lane * cpl + j] = carry[j];
+            has = false;
+          }
+        }
+        if (misc->piece_flag[2 * g + 1]) {
+          has = true; from_prev = false; ctgt = misc->piece_tgt[2 * g + 1];
+          for (int j = 0; j < cpl; ++j) carry[j] = misc->pieces[(2 * g + 1) * 128 + lane * cpl + j];
+        }
+      }
+      if (has) {   // the row continues into the next tile: its remainder arrives as that tile's head
+        float* dst = from_prev ? p.head + (long)tile * out : p.agg + (long)ctgt * out;
+        for (int j = 0; j < cpl; ++j) dst[lane * cpl + j] = carry[j];
+      }
+    }
+    // next iteration's first __syncthreads (a_tile_publish) orders the piece buffers
+  }
+  acc_teardown<TC>(acc);
+}
+
+}  // namespace sgnn
+
+using namespace sgnn;
+
+static int check_mlp(const SgnnMlp& m, const char* who) {
+  SGNN_CHECK_ARG(m.n_hidden >= 1 && m.n_hidden <= SGNN_MAX_HIDDEN, "%s: n_hidden=%d unsupported", who, m.n_hidden);
+  SGNN_CHECK_ARG(m.hidden % 32 == 0 && m.hidden >= 32 && m.hidden <= 128,
+                 "%s: hidden width %d must be a multiple of 32 in [32,128]", who, m.hidden);
+  return SGNN_OK;
+}
+
+extern "C" size_t sgnn_edge_layer_smem_bytes(int blob_bytes, int he, int hidden, int out, int tc) {
+  return (size_t)edge_layer_smem(blob_bytes, he, hidden, out, tc != 0).total;
+}
+
+extern "C" int sgnn_edge_layer_fwd(const SgnnEdgeLayerParams* p, int use_tensor_cores, int grid,
+                                   void* stream) {
+  int rc = check_mlp(p->mlp, "edge_layer");
+  if (rc) return rc;
+  SGNN_CHECK_ARG(p->mlp.out % 32 == 0 && p->mlp.out >= 32 && p->mlp.out <= 128,
+                 "edge_layer: message width %d must be a multiple of 32 in [32,128]", p->mlp.out);
+  SGNN_CHECK_ARG(p->he % 32 == 0 && p->he >= 32 && p->he <= 128, "edge_layer: he=%d unsupported", p->he);
+  SGNN_CHECK_ARG(p->blob_bytes % 16 == 0, "edge_layer: blob size must be a multiple of 16");
+  SGNN_CHECK_ARG(p->mlp.has_ln, "edge_layer: the edge MLP ends in a LayerNorm in the reference");
+  if (p->max_tiles <= 0 || p->n_nodes <= 0) return SGNN_OK;
+  const int smem = edge_layer_smem(p->blob_bytes, p->he, p->mlp.hidden, p->mlp.out, use_tensor_cores).total;
+  SGNN_CHECK_ARG(smem <= 227 * 1024, "edge_layer: needs %d bytes of shared memory (> 227 KB); "
+                 "this layer shape is not supported by the resident-weight kernel", smem);
+  if (grid > p->max_tiles) grid = p->max_tiles;
+  if (grid < 1) grid = 1;
+  if (use_tensor_cores) {
+    SGNN_CUDA(cudaFuncSetAttribute(edge_layer_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    edge_layer_kernel<true><<<grid, kThreads, smem, (cudaStream_t)stream>>>(*p);
+  } else {
+    SGNN_CUDA(cudaFuncSetAttribute(edge_layer_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    edge_layer_kernel<false><<<grid, kThreads, smem, (cudaStream_t)stream>>>(*p);
+  }
+  SGNN_LAUNCH_CHECK();
+  return SGNN_OK;
+}

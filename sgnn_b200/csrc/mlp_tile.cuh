@@ -1,0 +1,297 @@
+// Row-tile MLP machinery shared by the encoder / message-passing / decoder kernels.
+//
+// A CTA of 128 threads owns a tile of 128 rows (edges or nodes); thread t owns row t in every
+// epilogue (TMEM lane t <-> accumulator row t, so LayerNorm and bias/ReLU are thread-local).
+// A GEMM step is  D[128 x n] (+)= A[128 x k] * W[n x k]^T  with A and W in shared memory in
+// the K-major SWIZZLE_128B layout of common.cuh.
+//
+// Two arithmetic modes, selected at compile time, share every line of prologue/epilogue code:
+//   TC = true  : tcgen05.mma kind::tf32, accumulators in TMEM (the product path)
+//   TC = false : fp32 FFMA by the row-owning thread, accumulators in shared memory
+//                (precision="fp32": tight-tolerance parity mode, ~30x slower)
+#pragma once
+#include "common.cuh"
+#include "params.h"
+
+namespace sgnn {
+
+constexpr int kThreads = 128;
+
+template <bool TC>
+struct TileAcc {
+  uint32_t tmem_base;   // TC: TMEM base address (lane 0, column 0 of this CTA's allocation)
+  float* simt_acc;      // !TC: [128][acc_cols] fp32, XOR-swizzled in 16-byte chunks
+  int acc_cols;         // total accumulator columns (power of two >= 32 for TMEM)
+  uint64_t* bar;        // TC: mbarrier signalled by tcgen05.commit
+  uint32_t phase;
+};
+
+// ---- fp32 SIMT accumulator addressing (thread == row; conflict-free 16-byte accesses) ----
+__device__ __forceinline__ float4* simt_acc_chunk(float* base, int row, int chunk, int acc_cols) {
+  return reinterpret_cast<float4*>(base + (size_t)row * acc_cols) + (chunk ^ (row & 7));
+}
+
+// One GEMM step.  Called by ALL threads of the CTA (uniform control flow).
+//   a_tile / w_img : shared-memory operands (1024-byte aligned), k multiple of 32, n multiple of 16
+//   acc_col        : first accumulator column of D
+// TC: thread 0 issues the MMAs; completion is observed with gemm_wait().
+template <bool TC>
+__device__ __forceinline__ void gemm_step(TileAcc<TC>& acc, const void* a_tile, const void* w_img,
+                                          int k, int n, int acc_col, bool accumulate) {
+  if constexpr (TC) {
+    if (threadIdx.x == 0) {
+      tc_fence_after_sync();
+      umma_gemm_tf32(acc.tmem_base + acc_col, smem_u32(a_tile), smem_u32(w_img), k, n, accumulate);
+    }
+  } else {
+    const int row = threadIdx.x;
+    const char* a = reinterpret_cast<const char*>(a_tile);
+    const char* w = reinterpret_cast<const char*>(w_img);
+    for (int n0 = 0; n0 < n; n0 += 16) {
+      float d[16];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float4 v = accumulate ? *simt_acc_chunk(acc.simt_acc, row, (acc_col + n0) / 4 + j, acc.acc_cols)
+                              : make_float4(0.f, 0.f, 0.f, 0.f);
+        d[4 * j] = v.x; d[4 * j + 1] = v.y; d[4 * j + 2] = v.z; d[4 * j + 3] = v.w;
+      }
+      for (int kc = 0; kc < k / 4; ++kc) {
+        const float4 av = *reinterpret_cast<const float4*>(a + sw128_chunk_offset(row, kc, kTileRows));
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const float4 wv = *reinterpret_cast<const float4*>(w + sw128_chunk_offset(n0 + j, kc, n));
+          d[j] = fmaf(av.x, wv.x, d[j]);
+          d[j] = fmaf(av.y, wv.y, d[j]);
+          d[j] = fmaf(av.z, wv.z, d[j]);
+          d[j] = fmaf(av.w, wv.w, d[j]);
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        *simt_acc_chunk(acc.simt_acc, row, (acc_col + n0) / 4 + j, acc.acc_cols) =
+            make_float4(d[4 * j], d[4 * j + 1], d[4 * j + 2], d[4 * j + 3]);
+    }
+  }
+}
+
+// Make all GEMM steps issued so far visible to the epilogue (all threads call).
+template <bool TC>
+__device__ __forceinline__ void gemm_wait(TileAcc<TC>& acc) {
+  if constexpr (TC) {
+    if (threadIdx.x == 0) tc_commit(acc.bar);
+    mbar_wait(acc.bar, acc.phase);
+    acc.phase ^= 1u;
+    tc_fence_after_sync();
+  }
+}
+
+// Load 32 consecutive accumulator columns of this thread's row.
+template <bool TC>
+__device__ __forceinline__ void acc_load32(const TileAcc<TC>& acc, int col, float* v) {
+  if constexpr (TC) {
+    const uint32_t lane_base = (uint32_t)((threadIdx.x >> 5) * 32) << 16;
+    tmem_ld32(acc.tmem_base + lane_base + (uint32_t)col, v);
+  } else {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float4 t = *simt_acc_chunk(acc.simt_acc, threadIdx.x, col / 4 + j, acc.acc_cols);
+      v[4 * j] = t.x; v[4 * j + 1] = t.y; v[4 * j + 2] = t.z; v[4 * j + 3] = t.w;
+    }
+  }
+}
+
+// Epilogue -> next GEMM's A operand.  After the writers finish: generic->async proxy fence,
+// tcgen05 fence, CTA barrier.  (All threads call.)
+template <bool TC>
+__device__ __forceinline__ void a_tile_publish() {
+  if constexpr (TC) {
+    fence_proxy_async_smem();
+    tc_fence_before_sync();
+  }
+  __syncthreads();
+}
+
+// Store 32 columns [col, col+32) of this thread's row into an A tile (rounded to TF32 for TC).
+template <bool TC>
+__device__ __forceinline__ void a_tile_store32(void* a_tile, int col, const float* v) {
+  char* a = reinterpret_cast<char*>(a_tile);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    float4 t;
+    if constexpr (TC) {
+      t = make_float4(to_tf32(v[4 * j]), to_tf32(v[4 * j + 1]), to_tf32(v[4 * j + 2]), to_tf32(v[4 * j + 3]));
+    } else {
+      t = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    }
+    *reinterpret_cast<float4*>(a + sw128_chunk_offset(threadIdx.x, col / 4 + j, kTileRows)) = t;
+  }
+}
+
+// Cooperative, coalesced load of `rows_valid` fp32 rows of width `width` (multiple of 4) from
+// global memory into columns [col0, col0 + width) of an A tile.  Row r of the tile comes from
+// src + row_index(r) * ld.  Rows >= rows_valid are zero-filled.  A warp covers a row with
+// 16-byte lanes, so each global request is one contiguous row segment.
+template <bool TC, class RowIndex>
+__device__ __forceinline__ void a_tile_load_rows(void* a_tile, int col0, const float* __restrict__ src,
+                                                 long ld, int width, int rows_valid, RowIndex row_index,
+                                                 float scale = 1.0f) {
+  char* a = reinterpret_cast<char*>(a_tile);
+  const int chunks = width >> 2;                   // 16-byte chunks per row
+  const int total = kTileRows * chunks;
+  for (int idx = threadIdx.x; idx < total; idx += kThreads) {
+    const int r = idx / chunks, c = idx - r * chunks;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (r < rows_valid) {
+      const long g = row_index(r);
+      if (g >= 0) v = __ldg(reinterpret_cast<const float4*>(src + g * ld) + c);
+    }
+    v.x *= scale; v.y *= scale; v.z *= scale; v.w *= scale;
+    if constexpr (TC) v = make_float4(to_tf32(v.x), to_tf32(v.y), to_tf32(v.z), to_tf32(v.w));
+    *reinterpret_cast<float4*>(a + sw128_chunk_offset(r, (col0 >> 2) + c, kTileRows)) = v;
+  }
+}
+
+// LayerNorm statistics of this thread's row over accumulator columns [col, col+n), after
+// adding bias (torch semantics: biased variance, eps inside the sqrt).
+template <bool TC>
+__device__ __forceinline__ void row_ln_stats(const TileAcc<TC>& acc, int col, int n,
+                                             const float* __restrict__ bias, float& mean, float& rstd) {
+  float s = 0.f;
+  for (int c = 0; c < n; c += 32) {
+    float v[32];
+    acc_load32<TC>(acc, col + c, v);
+#pragma unroll
+    for (int j = 0; j < 32; ++j) s += v[j] + bias[c + j];
+  }
+  mean = s / (float)n;
+  float q = 0.f;
+  for (int c = 0; c < n; c += 32) {
+    float v[32];
+    acc_load32<TC>(acc, col + c, v);
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      const float d = v[j] + bias[c + j] - mean;
+      q = fmaf(d, d, q);
+    }
+  }
+  rstd = 1.0f / sqrtf(q / (float)n + 1e-5f);   // IEEE sqrt and divide, as torch
+}
+
+// Layers 1 .. n_hidden of an MLP whose layer-0 activations (after ReLU) already sit in `hid`
+// (A-operand layout, width m.hidden).  Hidden layers: bias + ReLU written back into `hid`.
+// Returns the accumulator column where the last Linear's output (bias not yet added) starts.
+// `w` = accumulator region width, `region` = region used by layer 0.  All threads call.
+template <bool TC>
+__device__ __forceinline__ int mlp_run_rest(TileAcc<TC>& acc, char* hid, const char* smem_blob,
+                                            const SgnnMlp& m, int w, int region) {
+  const float* blob_f = reinterpret_cast<const float*>(smem_blob);
+  for (int l = 1; l < m.n_hidden; ++l) {
+    a_tile_publish<TC>();
+    region ^= 1;
+    gemm_step<TC>(acc, hid, smem_blob + m.w_off[l], m.hidden, m.hidden, region * w, false);
+    gemm_wait<TC>(acc);
+    const float* b = blob_f + m.b_off[l];
+    for (int c = 0; c < m.hidden; c += 32) {
+      float v[32];
+      acc_load32<TC>(acc, region * w + c, v);
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j] + b[c + j], 0.f);
+      a_tile_store32<TC>(hid, c, v);
+    }
+  }
+  a_tile_publish<TC>();
+  region ^= 1;
+  const int n_out = (m.out + 15) & ~15;      // UMMA N granularity at M = 128
+  gemm_step<TC>(acc, hid, smem_blob + m.w_off[m.n_hidden], m.hidden, n_out, region * w, false);
+  gemm_wait<TC>(acc);
+  return region * w;
+}
+
+// 32 output columns [c, c+32) of this thread's row: bias, then LayerNorm affine if has_ln
+template <bool TC>
+__device__ __forceinline__ void mlp_out_chunk(const TileAcc<TC>& acc, int acc_col, int c,
+                                              const float* blob_f, const SgnnMlp& m, float mean,
+                                              float rstd, float* v) {
+  acc_load32<TC>(acc, acc_col + c, v);
+  const float* b = blob_f + m.b_off[m.n_hidden];
+  if (m.has_ln) {
+    const float* gam = blob_f + m.gamma_off;
+    const float* bet = blob_f + m.beta_off;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = (v[j] + b[c + j] - mean) * rstd * gam[c + j] + bet[c + j];
+  } else {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] += b[c + j];
+  }
+}
+
+// ---- TMA bulk store shared -> global ----------------------------------------------------
+__device__ __forceinline__ void tma_bulk_s2g(void* gmem_dst, const void* smem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gmem_dst),
+               "r"(smem_u32(smem_src)), "r"(bytes)
+               : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void tma_store_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+__device__ __forceinline__ void tma_store_wait_all() {
+  asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
+// stage `bytes` (multiple of 16) from global to shared with TMA bulk copies on one mbarrier
+__device__ __forceinline__ void tma_load_span(char* dst, const char* src, int bytes, uint64_t* bar) {
+  mbar_arrive_expect_tx(bar, (uint32_t)bytes);
+  for (int off = 0; off < bytes; off += 32768) {
+    const int n = bytes - off < 32768 ? bytes - off : 32768;
+    tma_bulk_g2s(dst + off, src + off, (uint32_t)n, bar);
+  }
+}
+
+__host__ __device__ inline int align_up(int x, int a) { return (x + a - 1) / a * a; }
+__host__ __device__ inline int pow2_cols(int c) {
+  int p = 32;
+  while (p < c) p <<= 1;
+  return p;
+}
+
+// ---- per-CTA setup / teardown of the accumulator --------------------------------------
+template <bool TC>
+__device__ __forceinline__ void acc_setup(TileAcc<TC>& acc, int acc_cols, uint64_t* bar,
+                                          uint32_t* tmem_slot, float* simt_acc) {
+  acc.acc_cols = acc_cols;
+  acc.bar = bar;
+  acc.phase = 0;
+  acc.simt_acc = simt_acc;
+  acc.tmem_base = 0;
+  if constexpr (TC) {
+    if (threadIdx.x == 0) {
+      mbar_init(bar, 1);
+      mbar_fence_init();
+    }
+    if (threadIdx.x < 32) tmem_alloc(tmem_slot, (uint32_t)acc_cols);
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    acc.tmem_base = *tmem_slot;
+  } else {
+    __syncthreads();
+  }
+}
+template <bool TC>
+__device__ __forceinline__ void acc_teardown(TileAcc<TC>& acc) {
+  if constexpr (TC) {
+    tc_fence_before_sync();
+    __syncthreads();
+    if (threadIdx.x < 32) tmem_dealloc(acc.tmem_base, (uint32_t)acc.acc_cols);
+  }
+}
+
+// dynamic shared memory base, aligned to 1024 bytes (SWIZZLE_128B atoms)
+__device__ __forceinline__ char* smem_base_1024() {
+  extern __shared__ char sgnn_dyn_smem[];
+  uintptr_t p = reinterpret_cast<uintptr_t>(sgnn_dyn_smem);
+  return reinterpret_cast<char*>((p + 1023) & ~(uintptr_t)1023);
+}
+
+}  // namespace sgnn

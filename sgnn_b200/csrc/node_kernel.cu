@@ -1,0 +1,322 @@
+// Node side of the Encode-Process-Decode network: one kernel, three prologues, three tails.
+//
+//   prologue FEATURES : node features from the position window (time_diff, velocity
+//                       normalisation, wall distance, type embedding) -- learned_simulator.py:
+//                       257-290,540-550 / multi_scale_simulator.py:173-201   -> Encoder.node_fn
+//            AGG_X    : [aggregate | x] of InteractionNetwork.update (graph_network.py:201-222);
+//                       the aggregate is agg[i] (+ the head partials of CSR rows that straddle
+//                       edge tiles), or 0 for receivers without edges
+//            ROWS     : explicit input rows (module-level API: Encoder / Decoder called directly)
+//   body              : Linear-ReLU-...-Linear (tcgen05 GEMMs, weights resident in shared memory)
+//                       -> LayerNorm -> (+ x residual) -> x_out
+//   tail     PQ       : P = x_out W1a^T + b1, Q = x_out W1b^T for the NEXT layer's edge kernel
+//            DECODE   : Decoder MLP (graph_network.py:321-333) with the last dim+1-wide Linear in
+//                       FFMA, then the Euler integrator (_decoder_postprocessor, :381-411)
+// A persistent CTA of 128 threads walks 128-node tiles; thread t owns row t in all epilogues.
+// Algorithmic HBM bytes per node and layer: 4*(agg_w + x_w) read + 4*out + 8*pq_hidden written.
+#include "mlp_tile.cuh"
+
+namespace sgnn {
+
+struct NodeMisc {
+  uint64_t bar_w, bar_mma;
+  uint32_t tmem_slot;
+  int pad;
+};
+
+struct NodeSmem {
+  int a, misc, simt, acc_cols, total;
+};
+__host__ __device__ inline int imax(int a, int b) { return a > b ? a : b; }
+
+__host__ __device__ inline NodeSmem node_smem(const SgnnNodeParams& p, bool tc) {
+  NodeSmem s;
+  int ka = p.k_pad, wacc = 32;
+  if (p.has_mlp) {
+    ka = imax(ka, imax(p.mlp.hidden, p.mlp.out));
+    wacc = imax(p.mlp.hidden, (p.mlp.out + 15) & ~15);
+  }
+  int cols = 2 * wacc;
+  if (p.tail == SGNN_TAIL_PQ) cols = imax(cols, 2 * p.pq_hidden);
+  if (p.tail == SGNN_TAIL_DECODE) {
+    ka = imax(ka, p.dec.hidden);
+    cols = imax(cols, 2 * p.dec.hidden);
+  }
+  s.acc_cols = pow2_cols(cols);
+  s.a = align_up(p.blob_bytes, 1024);
+  s.misc = s.a + kTileRows * ka * 4;
+  s.simt = align_up(s.misc + (int)sizeof(NodeMisc), 1024);
+  s.total = s.simt + (tc ? 0 : kTileRows * s.acc_cols * 4) + 1024;
+  return s;
+}
+
+template <bool TC>
+__device__ __forceinline__ void a_store_scalar(char* a_tile, int row, int col, float v) {
+  if constexpr (TC) v = to_tf32(v);
+  *reinterpret_cast<float*>(a_tile + sw128_offset(row, col, kTileRows)) = v;
+}
+
+// FEATURES prologue: thread == row
+template <bool TC>
+__device__ __forceinline__ void prologue_features(const SgnnNodeParams& p, char* a_tile, long i, bool valid) {
+  const int row = threadIdx.x;
+  int k = 0;
+  if (valid) {
+    const float* ps = p.pos_seq + i * p.pos_seq_stride;
+    for (int t = 0; t + 1 < p.seq_len; ++t)
+      for (int d = 0; d < p.dim; ++d) {
+        const float vel = __fsub_rn(ps[(t + 1) * p.dim + d], ps[t * p.dim + d]);
+        const float f = __fdiv_rn(__fsub_rn(vel, p.vel_mean[d]), p.vel_std[d]);
+        if (p.feat_out) p.feat_out[i * p.k_in + k] = f;
+        a_store_scalar<TC>(a_tile, row, k++, f);
+      }
+    float wd = __fadd_rn(ps[(p.seq_len - 1) * p.dim], p.wall_offset);
+    wd = fminf(fmaxf(wd, 0.f), p.wall_max);
+    wd = __fdiv_rn(wd, p.wall_div);
+    if (p.feat_out) p.feat_out[i * p.k_in + k] = wd;
+    a_store_scalar<TC>(a_tile, row, k++, wd);
+    if (p.emb) {
+      const float* e = p.emb + p.types[i] * p.emb_dim;
+      for (int j = 0; j < p.emb_dim; ++j) {
+        if (p.feat_out) p.feat_out[i * p.k_in + k] = e[j];
+        a_store_scalar<TC>(a_tile, row, k++, e[j]);
+      }
+    }
+  }
+  for (; k < p.k_pad; ++k) a_store_scalar<TC>(a_tile, row, k, 0.f);
+}
+
+// AGG_X prologue: cooperative, coalesced row segments
+template <bool TC>
+__device__ __forceinline__ void prologue_agg_x(const SgnnNodeParams& p, char* a_tile, long row0, int nvalid) {
+  const int chunks = p.agg_w >> 2;
+  for (int idx = threadIdx.x; idx < kTileRows * chunks; idx += kThreads) {
+    const int r = idx / chunks, c = idx - r * chunks;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (r < nvalid) {
+      const long i = row0 + r;
+      const int beg = p.rowptr[i], end = p.rowptr[i + 1];
+      if (end > beg) {
+        v = __ldg(reinterpret_cast<const float4*>(p.agg + i * p.agg_w) + c);
+        const int t0 = beg >> 7, t1 = (end - 1) >> 7;
+        for (int t = t0 + 1; t <= t1; ++t) {
+          const float4 h = __ldg(reinterpret_cast<const float4*>(p.head + (long)t * p.agg_w) + c);
+          v.x += h.x; v.y += h.y; v.z += h.z; v.w += h.w;
+        }
+      }
+    }
+    if constexpr (TC) v = make_float4(to_tf32(v.x), to_tf32(v.y), to_tf32(v.z), to_tf32(v.w));
+    *reinterpret_cast<float4*>(a_tile + sw128_chunk_offset(r, c, kTileRows)) = v;
+  }
+  a_tile_load_rows<TC>(a_tile, p.agg_w, p.x_in, p.x_w, p.x_w, nvalid, [row0](int r) { return row0 + r; });
+}
+
+// ROWS prologue: arbitrary width / leading dimension (scalar, coalesced along the row)
+template <bool TC>
+__device__ __forceinline__ void prologue_rows(const SgnnNodeParams& p, char* a_tile, long row0, int nvalid) {
+  for (int idx = threadIdx.x; idx < kTileRows * p.k_pad; idx += kThreads) {
+    const int r = idx / p.k_pad, c = idx - r * p.k_pad;
+    float v = 0.f;
+    if (r < nvalid && c < p.k_in) v = __ldg(p.rows_in + (row0 + r) * p.rows_ld + c);
+    a_store_scalar<TC>(a_tile, r, c, v);
+  }
+}
+
+template <bool TC>
+__global__ void __launch_bounds__(kThreads) node_kernel(const SgnnNodeParams p) {
+  char* smem = smem_base_1024();
+  const NodeSmem L = node_smem(p, TC);
+  const float* blob_f = reinterpret_cast<const float*>(smem);
+  char* a_tile = smem + L.a;
+  NodeMisc* misc = reinterpret_cast<NodeMisc*>(smem + L.misc);
+  const int tid = threadIdx.x;
+  const int n_tiles = (p.n_rows + kTileRows - 1) / kTileRows;
+  if ((int)blockIdx.x >= n_tiles) return;
+
+  if (tid == 0) {
+    mbar_init(&misc->bar_w, 1);
+    mbar_fence_init();
+    tma_load_span(smem, reinterpret_cast<const char*>(p.blob), p.blob_bytes, &misc->bar_w);
+  }
+  TileAcc<TC> acc;
+  acc_setup<TC>(acc, L.acc_cols, &misc->bar_mma, &misc->tmem_slot, reinterpret_cast<float*>(smem + L.simt));
+  mbar_wait(&misc->bar_w, 0);
+  const int w = p.has_mlp ? imax(p.mlp.hidden, (p.mlp.out + 15) & ~15) : 32;
+
+  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const long row0 = (long)tile * kTileRows;
+    const int nvalid = p.n_rows - row0 < kTileRows ? (int)(p.n_rows - row0) : kTileRows;
+    const long i = row0 + tid;
+    const bool valid = tid < nvalid;
+    // previous tile's MMAs (async proxy) have completed (gemm_wait); its TMEM reads retired below
+    if (p.prologue == SGNN_PRO_FEATURES) prologue_features<TC>(p, a_tile, i, valid);
+    else if (p.prologue == SGNN_PRO_AGG_X) prologue_agg_x<TC>(p, a_tile, row0, nvalid);
+    else prologue_rows<TC>(p, a_tile, row0, nvalid);
+
+    int x_width = p.k_pad;       // width of the tail's input held in the A tile
+    if (p.has_mlp) {
+      const int hidden = p.mlp.hidden, out = p.mlp.out;
+      a_tile_publish<TC>();
+      gemm_step<TC>(acc, a_tile, smem + p.mlp.w_off[0], p.k_pad, hidden, 0, false);
+      gemm_wait<TC>(acc);
+      {
+        const float* b = blob_f + p.mlp.b_off[0];
+        for (int c = 0; c < hidden; c += 32) {
+          float v[32];
+          acc_load32<TC>(acc, c, v);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j] + b[c + j], 0.f);
+          a_tile_store32<TC>(a_tile, c, v);
+        }
+      }
+      const int acc_col = mlp_run_rest<TC>(acc, a_tile, smem, p.mlp, w, 0);
+      float mean = 0.f, rstd = 1.f;
+      if (p.mlp.has_ln) row_ln_stats<TC>(acc, acc_col, out, blob_f + p.mlp.b_off[p.mlp.n_hidden], mean, rstd);
+      for (int c = 0; c < out; c += 32) {
+        float v[32];
+        mlp_out_chunk<TC>(acc, acc_col, c, blob_f, p.mlp, mean, rstd, v);
+        if (valid) {
+          if (p.residual) {
+            const float4* xr = reinterpret_cast<const float4*>(p.x_in + i * p.x_w + c);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 x = __ldg(xr + j);
+              v[4 * j] += x.x; v[4 * j + 1] += x.y; v[4 * j + 2] += x.z; v[4 * j + 3] += x.w;
+            }
+          }
+          if (p.x_out) {
+            float4* xo = reinterpret_cast<float4*>(p.x_out + i * out + c);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) xo[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          }
+        }
+        if (p.tail != SGNN_TAIL_NONE) a_tile_store32<TC>(a_tile, c, v);
+      }
+      x_width = out;
+    }
+
+    if (p.tail == SGNN_TAIL_PQ) {
+      const int hq = p.pq_hidden;
+      a_tile_publish<TC>();
+      gemm_step<TC>(acc, a_tile, smem + p.wp_off, x_width, hq, 0, false);
+      gemm_step<TC>(acc, a_tile, smem + p.wq_off, x_width, hq, hq, false);
+      gemm_wait<TC>(acc);
+      const float* b1 = blob_f + p.pq_bias_off;
+      for (int c = 0; c < 2 * hq; c += 32) {
+        float v[32];
+        acc_load32<TC>(acc, c, v);
+        if (c < hq) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] += b1[c + j];
+        }
+        if (valid) {
+          float4* dst = reinterpret_cast<float4*>(p.pq_out + i * 2 * hq + c);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) dst[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        }
+      }
+    } else if (p.tail == SGNN_TAIL_DECODE) {
+      const int hd = p.dec.hidden, nout = p.dec.out;
+      int region = 1, kin = x_width;
+      for (int l = 0; l < p.dec.n_hidden; ++l) {
+        a_tile_publish<TC>();
+        region ^= 1;
+        gemm_step<TC>(acc, a_tile, smem + p.dec.w_off[l], kin, hd, region * hd, false);
+        gemm_wait<TC>(acc);
+        kin = hd;
+        if (l + 1 < p.dec.n_hidden) {
+          const float* b = blob_f + p.dec.b_off[l];
+          for (int c = 0; c < hd; c += 32) {
+            float v[32];
+            acc_load32<TC>(acc, region * hd + c, v);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j] + b[c + j], 0.f);
+            a_tile_store32<TC>(a_tile, c, v);
+          }
+        }
+      }
+      // last hidden activation stays in registers; final Linear (hd -> nout <= 8) in FFMA
+      float o[8];
+      const float* bl = blob_f + p.dec.b_off[p.dec.n_hidden];
+      const float* wl = blob_f + p.dec_wlast_off;
+      const float* bh = blob_f + p.dec.b_off[p.dec.n_hidden - 1];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) o[k] = 0.f;
+      for (int c = 0; c < hd; c += 32) {
+        float v[32];
+        acc_load32<TC>(acc, region * hd + c, v);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j] + bh[c + j], 0.f);
+        for (int k = 0; k < nout; ++k) {
+          float a = o[k];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) a = fmaf(v[j], wl[k * hd + c + j], a);
+          o[k] = a;
+        }
+      }
+      if (valid) {
+        for (int k = 0; k < nout; ++k) o[k] += bl[k];
+        if (p.dec_out)
+          for (int k = 0; k < nout; ++k) p.dec_out[i * nout + k] = o[k];
+        if (p.strain_out) p.strain_out[i] = o[nout - 1];
+        if (p.next_pos) {
+          const float* ps = p.pos_seq + i * p.pos_seq_stride;
+          for (int d = 0; d < p.dim; ++d) {
+            const float a = __fadd_rn(__fmul_rn(o[d], p.acc_std[d]), p.acc_mean[d]);
+            const float last = ps[(p.seq_len - 1) * p.dim + d];
+            const float vel = __fsub_rn(last, ps[(p.seq_len - 2) * p.dim + d]);
+            p.next_pos[i * p.next_pos_stride + d] = __fadd_rn(last, __fadd_rn(vel, a));
+          }
+        }
+      }
+    }
+    if constexpr (TC) tc_fence_before_sync();
+    __syncthreads();     // TMEM reads and A-tile reads of this tile retired before the next prologue
+  }
+  acc_teardown<TC>(acc);
+}
+
+}  // namespace sgnn
+
+using namespace sgnn;
+
+extern "C" size_t sgnn_node_smem_bytes(const SgnnNodeParams* p, int tc) {
+  return (size_t)node_smem(*p, tc != 0).total;
+}
+
+extern "C" int sgnn_node_fwd(const SgnnNodeParams* p, int use_tensor_cores, int grid, void* stream) {
+  SGNN_CHECK_ARG(p->k_pad % 32 == 0 && p->k_pad >= 32 && p->k_pad <= 256, "node: k_pad=%d must be a multiple of 32 in [32,256]", p->k_pad);
+  SGNN_CHECK_ARG(p->k_in <= p->k_pad, "node: k_in > k_pad");
+  if (p->has_mlp) {
+    SGNN_CHECK_ARG(p->mlp.n_hidden >= 1 && p->mlp.n_hidden <= SGNN_MAX_HIDDEN, "node: n_hidden=%d", p->mlp.n_hidden);
+    SGNN_CHECK_ARG(p->mlp.hidden % 32 == 0 && p->mlp.hidden >= 32 && p->mlp.hidden <= 128, "node: hidden width %d unsupported", p->mlp.hidden);
+    SGNN_CHECK_ARG(p->mlp.out % 32 == 0 && p->mlp.out >= 32 && p->mlp.out <= 128, "node: output width %d unsupported (use the DECODE tail for narrow outputs)", p->mlp.out);
+    SGNN_CHECK_ARG(!p->residual || p->x_w == p->mlp.out, "node: residual needs x_w == out");
+  }
+  if (p->prologue == SGNN_PRO_AGG_X)
+    SGNN_CHECK_ARG(p->agg_w % 32 == 0 && p->x_w % 32 == 0 && p->k_pad == p->agg_w + p->x_w, "node: AGG_X widths must be multiples of 32");
+  if (p->tail == SGNN_TAIL_PQ)
+    SGNN_CHECK_ARG(p->pq_hidden % 32 == 0 && p->pq_hidden >= 32 && p->pq_hidden <= 128, "node: pq_hidden=%d unsupported", p->pq_hidden);
+  if (p->tail == SGNN_TAIL_DECODE) {
+    SGNN_CHECK_ARG(p->dec.out >= 1 && p->dec.out <= 8, "node: decoder output width %d must be in [1,8]", p->dec.out);
+    SGNN_CHECK_ARG(p->dec.hidden % 32 == 0 && p->dec.hidden <= 128 && p->dec.n_hidden >= 1, "node: decoder hidden width %d unsupported", p->dec.hidden);
+    SGNN_CHECK_ARG(p->next_pos == nullptr || p->dec.out >= p->dim, "node: decoder output narrower than dim");
+  }
+  SGNN_CHECK_ARG(p->blob_bytes % 16 == 0, "node: blob size must be a multiple of 16");
+  if (p->n_rows <= 0) return SGNN_OK;
+  const NodeSmem L = node_smem(*p, use_tensor_cores);
+  SGNN_CHECK_ARG(L.acc_cols <= 512, "node: needs %d TMEM columns (> 512)", L.acc_cols);
+  SGNN_CHECK_ARG(L.total <= 227 * 1024, "node: needs %d bytes of shared memory (> 227 KB); layer shape unsupported", L.total);
+  const int n_tiles = sgnn_ceil_div(p->n_rows, kTileRows);
+  if (grid > n_tiles) grid = n_tiles;
+  if (grid < 1) grid = 1;
+  if (use_tensor_cores) {
+    SGNN_CUDA(cudaFuncSetAttribute(node_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total));
+    node_kernel<true><<<grid, kThreads, L.total, (cudaStream_t)stream>>>(*p);
+  } else {
+    SGNN_CUDA(cudaFuncSetAttribute(node_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total));
+    node_kernel<false><<<grid, kThreads, L.total, (cudaStream_t)stream>>>(*p);
+  }
+  SGNN_LAUNCH_CHECK();
+  return SGNN_OK;
+}

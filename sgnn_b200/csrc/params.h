@@ -1,0 +1,130 @@
+// Plain-C parameter blocks of the network kernels.  They are part of the C ABI
+// (include/sgnn_b200.h re-exports them): the Python host side fills them with ctypes.
+//
+// "blob": one contiguous device buffer per kernel holding every GEMM weight as a K-major
+// SWIZZLE_128B image (sgnn_pack_weight; 1024-byte aligned offsets, in BYTES) followed by the
+// fp32 vectors (biases, LayerNorm gamma/beta, small dense layers; offsets in FLOATS).  It is
+// staged into shared memory once per CTA with TMA bulk copies and stays resident.
+#pragma once
+#include <stdint.h>
+
+#define SGNN_MAX_HIDDEN 3   /* hidden layers per MLP (reference uses 1 and 2) */
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Linear(k_in -> hidden) ReLU [Linear(hidden->hidden) ReLU]* Linear(hidden -> out) [LayerNorm] */
+typedef struct {
+  int n_hidden;                      /* number of hidden layers (nmlp_layers) >= 1              */
+  int hidden;                        /* hidden width, multiple of 32                            */
+  int out;                           /* output width                                            */
+  int has_ln;                        /* LayerNorm(out) after the last Linear                    */
+  int w_off[SGNN_MAX_HIDDEN + 1];    /* byte offsets of the GEMM images, layer 0 .. n_hidden    */
+  int b_off[SGNN_MAX_HIDDEN + 1];    /* float offsets of the biases (-1: no bias / folded)      */
+  int gamma_off, beta_off;           /* float offsets of the LayerNorm affine parameters        */
+} SgnnMlp;
+
+/* Per message-passing layer, edge side:  m_e = LN(MLP(e W1c^T + P[tgt] + Q[src])),
+ * agg[i] = sum of m_e over the CSR row of receiver i.  Reference: InteractionNetwork.message +
+ * PyG aggregate (sgnn/single_scale/graph_network.py:178-199). */
+typedef struct {
+  const float* e_tiles;   /* edge latents e0, 128-row tiles in A-operand layout, width he      */
+  const float* pq;        /* [n_nodes, 2*hidden]: P = x W1a^T + b1 | Q = x W1b^T               */
+  const int* src;         /* [E] sender of each edge (CSR order)                               */
+  const int* tgt;         /* [E] receiver of each edge, ascending                              */
+  const int* rowptr;      /* [n_nodes + 1]; E = rowptr[n_nodes] is read on the device          */
+  int n_nodes;
+  int he;                 /* edge latent width (K of the first GEMM), multiple of 32           */
+  const float* blob;
+  int blob_bytes;
+  SgnnMlp mlp;            /* layer 0 image = W1c * 2^layer (the e' = 2e quirk), no bias        */
+  float* agg;             /* [n_nodes, out]; rows of receivers without edges are NOT written   */
+  float* head;            /* [n_tiles, out]: partial sum of a CSR row continuing from the      */
+                          /* previous tile (added back by the node kernel)                     */
+  int max_tiles;
+} SgnnEdgeLayerParams;
+
+/* Edge encoder: features from positions -> MLP -> LN -> e0 tiles.  Reference:
+ * LearnedSimulator._encoder_preprocessor edge part (learned_simulator.py:299-312) and
+ * Encoder.edge_fn (graph_network.py:92-96). */
+typedef struct {
+  const float* pos;       /* most recent positions: particle i at pos + i * pos_stride         */
+  long pos_stride;
+  int dim;
+  float inv_radius_unused;
+  float radius;           /* displacements are DIVIDED by this (fp32 division, as torch)       */
+  const int* src;
+  const int* tgt;
+  const int* rowptr;
+  int n_nodes;
+  const float* feat;      /* optional explicit edge features [E, k_in] (module API); else NULL */
+  int k_in;               /* dim + 1 when computed from positions                              */
+  const float* blob;
+  int blob_bytes;
+  SgnnMlp mlp;            /* layer 0 is evaluated with FFMA from w0_off (plain [hidden,k_in])  */
+  int w0_off;             /* float offset of the plain row-major first-layer weight            */
+  float* e_tiles;         /* out: tiles, width mlp.out                                         */
+  float* feat_out;        /* optional [E, k_in] copy of the features (tests / module API)      */
+  int max_tiles;
+} SgnnEdgeEncoderParams;
+
+enum { SGNN_PRO_FEATURES = 0, SGNN_PRO_AGG_X = 1, SGNN_PRO_ROWS = 2 };
+enum { SGNN_TAIL_NONE = 0, SGNN_TAIL_PQ = 1, SGNN_TAIL_DECODE = 2 };
+
+/* Node-side kernel: prologue -> MLP (-> LN) (-> + residual) -> x_out, then an optional tail
+ * GEMM on x_out: PQ for the next layer's edge kernel, or the decoder + Euler integrator. */
+typedef struct {
+  int n_rows;
+  int prologue;
+  /* FEATURES: node features from the position window (learned_simulator.py:257-290,
+   * multi_scale_simulator.py:173-201) */
+  const float* pos_seq;   /* window of particle i: pos_seq + i * pos_seq_stride, [S, dim] */
+  long pos_seq_stride;    /* floats between particles (S*dim when contiguous)          */
+  int seq_len, dim;
+  const float* vel_mean;  /* [dim] */
+  const float* vel_std;   /* [dim] */
+  float wall_offset;      /* 2.0: distance to the wall at x = -2 */
+  float wall_max;         /* clamp upper bound (connectivity radius / grid radius) */
+  float wall_div;         /* 1.0 single-scale; grid radius multi-scale (fp32 division) */
+  const int64_t* types;   /* [n] particle types, used when emb != NULL */
+  const float* emb;       /* [n_types, emb_dim] or NULL */
+  int emb_dim;
+  float* feat_out;        /* optional [n, k_in] copy of the features */
+  /* AGG_X: [aggregate | x] of InteractionNetwork.update (graph_network.py:201-222) */
+  const float* agg;       /* [n, agg_w] */
+  const float* head;      /* [n_tiles_e, agg_w] */
+  const int* rowptr;      /* [n + 1] */
+  int agg_w;
+  const float* x_in;      /* [n, x_w] (also the residual) */
+  int x_w;
+  /* ROWS: explicit input rows */
+  const float* rows_in;   /* [n, k_in] */
+  long rows_ld;
+  int k_in;               /* logical input width of the MLP (features / rows) */
+  int k_pad;              /* k_in rounded up to 32 (AGG_X: agg_w + x_w, both multiples of 32) */
+  const float* blob;
+  int blob_bytes;
+  int has_mlp;            /* 0: skip the MLP (tail applied directly to the ROWS input)         */
+  SgnnMlp mlp;
+  int residual;           /* x_out = x_in + LN(MLP(..)) */
+  float* x_out;           /* [n, mlp.out] or NULL */
+  /* tail */
+  int tail;
+  int pq_hidden;          /* PQ: width of P and of Q (next layer's hidden width)               */
+  int wp_off, wq_off;     /* byte offsets of the W1a / W1b images (N = pq_hidden, K = out)     */
+  int pq_bias_off;        /* float offset of b1 (added to P)                                   */
+  float* pq_out;          /* [n, 2*pq_hidden]                                                  */
+  SgnnMlp dec;            /* DECODE: hidden layers as GEMMs; the last Linear (hidden -> out,   */
+  int dec_wlast_off;      /* out <= 8) is a plain row-major [out, hidden] fp32 matrix (floats) */
+  float* dec_out;         /* optional raw network output [n, dec.out]                          */
+  const float* acc_mean;  /* integrator (learned_simulator.py:381-411); NULL = skip            */
+  const float* acc_std;
+  float* next_pos;        /* [n, dim] */
+  long next_pos_stride;
+  float* strain_out;      /* [n] */
+} SgnnNodeParams;
+
+#ifdef __cplusplus
+}
+#endif

@@ -1,0 +1,270 @@
+"""Launch plans for the Encode-Process-Decode forward pass on libsgnn_b200.
+
+A plan is built once from reference-shaped torch modules (same Sequential / "NN-i" structure as
+sgnn/single_scale/graph_network.py and sgnn/multi_scale/multi_scale_gnn.py) and then launched
+with device pointers only -- no allocation, no host sync, capturable in a CUDA graph.
+
+  edge set   : a receiver-sorted CSR edge list + its encoder -> e0 tiles
+  block      : one InteractionNetwork-style layer (edge kernel + node kernel) over an edge set,
+               with the reference's edge-latent doubling folded into the weights (scale 2^l)
+"""
+import ctypes as C
+from typing import Dict, List, Optional
+
+import torch
+
+from . import _lib as L
+from .blob import BlobBuilder, fill_mlp, linears_of, pad32
+
+TILE = 128
+
+
+class Csr:
+    """Receiver-sorted edge set in int32 (src, tgt, rowptr); capacity fixed at construction."""
+
+    def __init__(self, n_nodes: int, max_edges: int, device):
+        self.n_nodes = n_nodes
+        self.max_edges = max(int(max_edges), 1)
+        self.rowptr = torch.zeros(n_nodes + 1, dtype=torch.int32, device=device)
+        self.src = torch.zeros(self.max_edges, dtype=torch.int32, device=device)
+        self.tgt = torch.zeros(self.max_edges, dtype=torch.int32, device=device)
+
+    @property
+    def max_tiles(self) -> int:
+        return (self.max_edges + TILE - 1) // TILE
+
+    @staticmethod
+    def from_edge_index(edge_index: torch.Tensor, n_nodes: int):
+        """Arbitrary (unsorted, duplicated) [2,E] edge list -> CSR by a STABLE sort on the
+        receiver, so each receiver's messages are summed in the caller's edge order.  Returns
+        (csr, perm) with perm[k] = original edge id of CSR slot k.  Host-side setup code."""
+        dev = edge_index.device
+        src, tgt = edge_index[0].long(), edge_index[1].long()
+        perm = torch.sort(tgt, stable=True).indices
+        csr = Csr(n_nodes, max(edge_index.shape[1], 1), dev)
+        e = edge_index.shape[1]
+        csr.src[:e] = src[perm].int()
+        csr.tgt[:e] = tgt[perm].int()
+        counts = torch.bincount(tgt, minlength=n_nodes)
+        csr.rowptr[1:] = torch.cumsum(counts, 0).int()
+        return csr, perm.int()
+
+    def edge_index(self) -> torch.Tensor:
+        """[2,E] int64 (one host sync: reads E)."""
+        e = int(self.rowptr[-1].item())
+        return torch.stack([self.src[:e].long(), self.tgt[:e].long()])
+
+
+class RadiusGraph:
+    """Workspace + output buffers of sgnn_radius_graph_csr for up to n particles."""
+
+    def __init__(self, n: int, max_neighbors: int, loop: bool, device):
+        self.n, self.k, self.loop = n, max_neighbors, loop
+        per_row = max_neighbors if loop else max_neighbors + 1
+        self.csr = Csr(n, n * per_row, device)
+        nbytes = L.lib().sgnn_radius_graph_workspace_bytes(n, max_neighbors)
+        self.ws = torch.empty(nbytes, dtype=torch.uint8, device=device)
+        self.ws_bytes = nbytes
+
+    def build(self, pos: torch.Tensor, pos_stride: int, dim: int, example_ptr: torch.Tensor,
+              radius: float):
+        """pos: tensor whose data_ptr is particle 0's most recent position."""
+        L.check(L.lib().sgnn_radius_graph_csr(
+            C.c_void_p(pos.data_ptr()), C.c_long(pos_stride), self.n, dim, L.ptr(example_ptr),
+            example_ptr.numel() - 1, C.c_double(radius), self.k, int(self.loop), L.ptr(self.ws),
+            C.c_size_t(self.ws_bytes), L.ptr(self.csr.rowptr), L.ptr(self.csr.src),
+            L.ptr(self.csr.tgt), L.stream_ptr()), launches=9)
+        return self.csr
+
+
+def _grid(smem_bytes: int, max_ctas: int) -> int:
+    sm, _, _ = L.device_info()
+    occ = max(1, min(2, (227 * 1024) // max(smem_bytes, 1)))
+    return max(1, min(max_ctas, sm * occ))
+
+
+class EdgeEncoderPlan:
+    def __init__(self, seq: torch.nn.Sequential, k_in: int, tc: bool, device):
+        lins, ln = linears_of(seq[0]), seq[1]
+        b = BlobBuilder(device, tc)
+        self.p = L.EdgeEncoderParams()
+        fill_mlp(b, self.p.mlp, lins, ln, first_as_image=False)
+        self.p.w0_off = b.add_vector(lins[0].weight)      # plain [hidden, k_in]
+        self.blob, nbytes = b.finish()
+        self.p.blob, self.p.blob_bytes, self.p.k_in = self.blob.data_ptr(), nbytes, k_in
+        self.tc = tc
+        self.out = self.p.mlp.out
+        self.smem = L.lib().sgnn_edge_encoder_smem_bytes(nbytes, self.p.mlp.hidden, self.out, int(tc))
+
+    def launch(self, csr: Csr, e_tiles, pos=None, pos_stride=0, dim=0, radius=1.0, feat=None,
+               feat_out=None, n_edges: Optional[int] = None):
+        p = self.p
+        if isinstance(pos, torch.Tensor):
+            pos = pos.data_ptr()
+        p.pos, p.pos_stride, p.dim = pos, pos_stride, dim
+        p.radius = radius
+        p.src, p.tgt = csr.src.data_ptr(), csr.tgt.data_ptr()
+        if n_edges is None:
+            p.rowptr, p.n_nodes = csr.rowptr.data_ptr(), csr.n_nodes
+        else:                       # explicit edge count (no CSR needed: module-level Encoder)
+            p.rowptr, p.n_nodes = None, n_edges
+        p.feat = feat.data_ptr() if feat is not None else None
+        p.feat_out = feat_out.data_ptr() if feat_out is not None else None
+        p.e_tiles, p.max_tiles = e_tiles.data_ptr(), csr.max_tiles
+        L.check(L.lib().sgnn_edge_encoder_fwd(C.byref(p), int(self.tc), _grid(self.smem, csr.max_tiles),
+                                              L.stream_ptr()))
+
+
+class EdgeLayerPlan:
+    """Edge kernel of one block.  edge_fn = Sequential(build_mlp(2*nnode+nedge -> ...), LN);
+    the first Linear's columns are [x_target | x_source | e] (graph_network.py:197)."""
+
+    def __init__(self, edge_fn: torch.nn.Sequential, nnode: int, nedge: int, scale: float, tc: bool,
+                 device):
+        lins, ln = linears_of(edge_fn[0]), edge_fn[1]
+        assert lins[0].in_features == 2 * nnode + nedge
+        b = BlobBuilder(device, tc)
+        self.p = L.EdgeLayerParams()
+        fill_mlp(b, self.p.mlp, lins, ln, first_cols=(2 * nnode, nedge), first_scale=scale,
+                 first_bias=False)
+        self.blob, nbytes = b.finish()
+        self.p.blob, self.p.blob_bytes, self.p.he = self.blob.data_ptr(), nbytes, nedge
+        self.tc, self.hidden, self.out = tc, self.p.mlp.hidden, self.p.mlp.out
+        self.smem = L.lib().sgnn_edge_layer_smem_bytes(nbytes, nedge, self.hidden, self.out, int(tc))
+
+    def launch(self, csr: Csr, e_tiles, pq, agg, head):
+        p = self.p
+        p.e_tiles, p.pq = e_tiles.data_ptr(), pq.data_ptr()
+        p.src, p.tgt, p.rowptr, p.n_nodes = csr.src.data_ptr(), csr.tgt.data_ptr(), csr.rowptr.data_ptr(), csr.n_nodes
+        p.agg, p.head, p.max_tiles = agg.data_ptr(), head.data_ptr(), csr.max_tiles
+        L.check(L.lib().sgnn_edge_layer_fwd(C.byref(p), int(self.tc), _grid(self.smem, csr.max_tiles),
+                                            L.stream_ptr()))
+
+
+class NodePlan:
+    """Node kernel: prologue -> [MLP (+LN) (+residual)] -> tail.
+
+    body       : Sequential(build_mlp, LayerNorm) or None
+    pq_from    : the NEXT block's edge_fn (tail PQ) or None
+    decoder    : build_mlp Sequential without LayerNorm (tail DECODE) or None
+    """
+
+    def __init__(self, prologue: int, k_in: int, body: Optional[torch.nn.Sequential], tc: bool,
+                 device, nnode_next: int = 0, pq_from: Optional[torch.nn.Sequential] = None,
+                 decoder: Optional[torch.nn.Sequential] = None, residual: bool = False,
+                 body_has_ln: bool = True):
+        b = BlobBuilder(device, tc)
+        p = self.p = L.NodeParams()
+        p.prologue, p.k_in, p.k_pad = prologue, k_in, pad32(k_in)
+        p.residual = int(residual)
+        width = p.k_pad
+        if body is not None:
+            if body_has_ln:
+                lins, ln = linears_of(body[0]), body[1]
+            else:
+                lins, ln = linears_of(body), None
+            fill_mlp(b, p.mlp, lins, ln, first_kpad=p.k_pad)
+            p.has_mlp = 1
+            width = p.mlp.out
+        p.tail = L.TAIL_NONE
+        if pq_from is not None:
+            w1 = linears_of(pq_from[0])[0]
+            p.tail, p.pq_hidden = L.TAIL_PQ, w1.out_features
+            p.wp_off = b.add_image(w1.weight, 0, w1.out_features, 0, nnode_next, pad32(width))
+            p.wq_off = b.add_image(w1.weight, 0, w1.out_features, nnode_next, nnode_next, pad32(width))
+            p.pq_bias_off = b.add_vector(w1.bias)
+        elif decoder is not None:
+            lins = linears_of(decoder)
+            p.tail = L.TAIL_DECODE
+            fill_mlp(b, p.dec, lins, None, first_kpad=pad32(width), last_as_image=False)
+            p.dec_wlast_off = b.add_vector(lins[-1].weight)
+        self.blob, nbytes = b.finish()
+        p.blob, p.blob_bytes = self.blob.data_ptr(), nbytes
+        self.tc = tc
+        self.smem = L.lib().sgnn_node_smem_bytes(C.byref(p), int(tc))
+
+    def launch(self, n_rows: int, **kw):
+        p = self.p
+        p.n_rows = n_rows
+        for k, v in kw.items():
+            if isinstance(v, torch.Tensor):
+                v = v.data_ptr()
+            setattr(p, k, v)
+        n_tiles = (n_rows + TILE - 1) // TILE
+        L.check(L.lib().sgnn_node_fwd(C.byref(p), int(self.tc), _grid(self.smem, n_tiles), L.stream_ptr()))
+
+
+class EpdEngine:
+    """Forward pass of an Encode-Process-Decode network over one or more edge sets.
+
+    node_encoder : Sequential(mlp, LN)  on the node features built from the position window
+    edge_encoders: list of Sequential(mlp, LN), one per edge set
+    blocks       : list of (edge_fn, node_fn, edge_set_index, layer_index_within_its_edge_set)
+    decoder      : build_mlp Sequential (no LN)
+    """
+
+    def __init__(self, node_encoder, edge_encoders, blocks, decoder, *, k_node_in: int, dim: int,
+                 latent: int, n_nodes: int, edge_caps: List[int], precision: str, device):
+        if precision not in ("tf32", "fp32"):
+            raise ValueError("precision must be 'tf32' (tensor cores) or 'fp32' (FFMA parity mode)")
+        L.device_info()
+        tc = precision == "tf32"
+        self.tc, self.n, self.dim, self.latent, self.device = tc, n_nodes, dim, latent, device
+        self.edge_enc = [EdgeEncoderPlan(seq, dim + 1, tc, device) for seq in edge_encoders]
+        self.blocks = []
+        for bi, (edge_fn, node_fn, es, layer) in enumerate(blocks):
+            nedge = self.edge_enc[es].out
+            ep = EdgeLayerPlan(edge_fn, latent, nedge, float(2 ** layer), tc, device)
+            nxt = blocks[bi + 1][0] if bi + 1 < len(blocks) else None
+            npn = NodePlan(L.PRO_AGG_X, ep.out + latent, node_fn, tc, device, nnode_next=latent,
+                           pq_from=nxt, decoder=None if nxt is not None else decoder, residual=True)
+            self.blocks.append((ep, npn, es))
+        self.node_enc = NodePlan(L.PRO_FEATURES, k_node_in, node_encoder, tc, device,
+                                 nnode_next=latent, pq_from=blocks[0][0])
+        f32 = dict(dtype=torch.float32, device=device)
+        max_hidden = max(ep.hidden for ep, _, _ in self.blocks)
+        max_out = max(ep.out for ep, _, _ in self.blocks)
+        self.x = [torch.empty(n_nodes, latent, **f32) for _ in range(2)]
+        self.pq = torch.empty(n_nodes, 2 * max_hidden, **f32)
+        self.agg = torch.empty(n_nodes, max_out, **f32)
+        self.head = torch.empty(max(max((c + TILE - 1) // TILE for c in edge_caps), 1), max_out, **f32)
+        self.e_tiles = [torch.empty(((c + TILE - 1) // TILE) * TILE * enc.out + 32, **f32)
+                        for c, enc in zip(edge_caps, self.edge_enc)]
+        self.dec_out = torch.empty(n_nodes, linears_of(decoder)[-1].out_features, **f32)
+
+    def forward(self, *, pos_seq, pos_seq_stride: int, seq_len: int, csrs: List[Csr],
+                radii: List[float], vel_mean, vel_std, wall_max: float, wall_div: float,
+                types=None, emb=None, acc_mean=None, acc_std=None, next_pos=None,
+                next_pos_stride: int = 0, strain_out=None, feat_out=None, edge_feat_out=None):
+        """Launches the whole forward on the current stream.  pos_seq: tensor whose data_ptr is
+        particle 0's oldest frame of the window.  Returns the raw network output buffer."""
+        n, dim = self.n, self.dim
+        last_off = (seq_len - 1) * dim * 4
+        last_pos_ptr = pos_seq.data_ptr() + last_off
+        for k, (enc, csr) in enumerate(zip(self.edge_enc, csrs)):
+            enc.launch(csr, self.e_tiles[k], pos=last_pos_ptr, pos_stride=pos_seq_stride, dim=dim,
+                       radius=radii[k],
+                       feat_out=None if edge_feat_out is None else edge_feat_out[k])
+        x_cur = 0
+        self.node_enc.launch(
+            n, pos_seq=pos_seq, pos_seq_stride=pos_seq_stride, seq_len=seq_len, dim=dim,
+            vel_mean=vel_mean, vel_std=vel_std, wall_offset=2.0, wall_max=wall_max, wall_div=wall_div,
+            types=types if emb is not None else None, emb=emb,
+            emb_dim=0 if emb is None else emb.shape[1], feat_out=feat_out,
+            x_out=self.x[x_cur], pq_out=self.pq)
+        for bi, (ep, npn, es) in enumerate(self.blocks):
+            csr = csrs[es]
+            ep.launch(csr, self.e_tiles[es], self.pq, self.agg, self.head)
+            last = bi == len(self.blocks) - 1
+            kw = dict(agg=self.agg, head=self.head, rowptr=csr.rowptr, agg_w=ep.out,
+                      x_in=self.x[x_cur], x_w=self.latent, x_out=self.x[1 - x_cur])
+            if not last:
+                kw.update(pq_out=self.pq)
+            else:
+                kw.update(dec_out=self.dec_out, pos_seq=pos_seq, pos_seq_stride=pos_seq_stride,
+                          seq_len=seq_len, dim=dim, acc_mean=acc_mean, acc_std=acc_std,
+                          next_pos=next_pos, next_pos_stride=next_pos_stride, strain_out=strain_out)
+            npn.launch(n, **kw)
+            x_cur = 1 - x_cur
+        self.x_final = self.x[x_cur]
+        return self.dec_out

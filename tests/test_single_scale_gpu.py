@@ -1,0 +1,117 @@
+"""GPU parity of the single-scale path (LearnedSimulator + modules) against the golden
+fixtures generated from the unmodified reference and against the CPU oracle.
+
+Tolerances (stated, see DESIGN.md "Tolerance policy"):
+  precision="fp32": FFMA in fp32; differs from the reference only by summation order
+      -> |network output| within 2e-4 abs of the reference's fp32 run
+  precision="tf32": operands rounded to TF32 (rel 2^-11), fp32 accumulate
+      -> |network output (normalised acceleration)| within 3e-2 abs; positions within
+         3e-2 * acc_std per step (the integrator scales the output by acc_std)
+Edge sets are bit-exact in every mode.
+"""
+import numpy as np
+import pytest
+import torch
+
+from tests.util import Fixture
+
+pytestmark = pytest.mark.gpu
+
+TOL = {"fp32": 2e-4, "tf32": 3e-2}
+
+
+def make_sim(f, precision):
+    from sgnn_b200.single_scale import LearnedSimulator
+    nx, ny, S, H, L, nmlp, nsteps, ntypes, emb = f["meta"].tolist()
+    _, radius = f["spacing_radius"].tolist()
+    nnode_in = (S - 1) * 2 + 1 + (emb if ntypes > 1 else 0)
+    sim = LearnedSimulator(2, nnode_in, 3, H, L, nmlp, H, radius, f.stats(), ntypes, emb,
+                           device="cuda", precision=precision)
+    sim.load_state_dict(f.state_dict())
+    return sim.cuda().eval(), S, radius, nsteps
+
+
+@pytest.mark.parametrize("name", ["single_h64", "single_h32_batch"])
+@pytest.mark.parametrize("precision", ["fp32", "tf32"])
+def test_features_and_edges(name, precision):
+    f = Fixture(name)
+    sim, S, radius, _ = make_sim(f, precision)
+    pos, types = f.t("positions").cuda(), f.t("particle_types").cuda()
+    n = pos.shape[0]
+    nf, ei, ef = sim._encoder_preprocessor(pos[:, :S], [torch.tensor(n)], types)
+    assert torch.equal(ei.cpu(), f.t("edge_index/0"))
+    assert torch.equal(nf.cpu(), f.t("node_features_f32"))
+    assert torch.allclose(ef.cpu(), f.t("edge_features_f32"), atol=1e-6, rtol=1e-6)
+    a, b = sim._compute_graph_connectivity(pos[:, S - 1].contiguous(), torch.tensor([n]), radius)
+    assert torch.equal(torch.stack([a, b]).cpu(), f.t("edge_index/0"))
+
+
+@pytest.mark.parametrize("name", ["single_h64", "single_h32_batch"])
+@pytest.mark.parametrize("precision", ["fp32", "tf32"])
+def test_rollout_matches_reference(name, precision):
+    f = Fixture(name)
+    sim, S, radius, nsteps = make_sim(f, precision)
+    pos, types = f.t("positions").cuda(), f.t("particle_types").cuda()
+    n = pos.shape[0]
+    acc_std = f.stats()["acceleration"]["std"].max().item()
+    ref32, ref64 = f.t("rollout_f32"), f.t("rollout_f64")
+    gap = (ref32.double() - ref64).abs().max().item()
+    cur = pos[:, :S].contiguous()
+    worst = 0.0
+    for step in range(nsteps):
+        if precision == "fp32":
+            _, ei, _ = sim._encoder_preprocessor(cur, [torch.tensor(n)], types)
+            assert torch.equal(ei.cpu(), f.t(f"edge_index/{step}")), step
+        nxt, strain = sim.predict_positions(cur, [torch.tensor(n)], types)
+        err = (nxt.cpu().double() - ref64[step]).abs().max().item()
+        worst = max(worst, err)
+        tol = TOL[precision] * acc_std * (step + 1) * 3 + 4 * gap
+        assert err <= tol, (step, err, tol)
+        serr = (strain.cpu() - f.t("rollout_strain_f32")[step]).abs().max().item()
+        assert serr <= TOL[precision] * (step + 1) * 3, (step, serr)
+        cur = torch.cat([cur[:, 1:], nxt[:, None, :]], dim=1)
+    print(f"{name} {precision}: max |pos - ref64| = {worst:.3e} (fp32 ref gap {gap:.3e}, acc_std {acc_std:.3e})")
+
+
+@pytest.mark.parametrize("precision", ["fp32", "tf32"])
+def test_network_output_and_modules(precision):
+    """EncodeProcessDecode.forward on explicit tensors (module-level API) vs the reference,
+    plus the e' = 2e quirk and Encoder / Decoder called on their own."""
+    from sgnn_b200.single_scale import graph_network as G
+    f = Fixture("single_h64")
+    sim, S, radius, _ = make_sim(f, precision)
+    G.set_default_precision(precision)
+    try:
+        nf, ei, ef = f.t("node_features_f32").cuda(), f.t("edge_index/0").cuda(), f.t("edge_features_f32").cuda()
+        epd = sim._encode_process_decode
+        out = epd(nf, ei, ef)
+        err = (out.cpu() - f.t("epd_out_f32")).abs().max().item()
+        print(f"epd module forward {precision}: max abs err {err:.3e}")
+        assert err <= TOL[precision]
+        x0, e0 = epd._encoder(nf, ef)
+        x1, e1 = epd._processor.gnn_stacks[0](x0, ei, e0)
+        assert torch.equal(e1, 2 * e0)
+        # unsorted / duplicated edge list gives the same node update as the sorted one
+        perm = torch.randperm(ei.shape[1], generator=torch.Generator().manual_seed(0)).cuda()
+        x1p, _ = epd._processor.gnn_stacks[0](x0, ei[:, perm], e0[perm])
+        assert torch.allclose(x1, x1p, atol=1e-5 if precision == "fp32" else 5e-3)
+        from oracle import sgnn_oracle as O
+        sd = f.state_dict()
+        xo = O.mlp_ln(sd, "_encode_process_decode._encoder.node_fn.", nf.cpu())
+        eo = O.mlp_ln(sd, "_encode_process_decode._encoder.edge_fn.", ef.cpu())
+        assert (x0.cpu() - xo).abs().max() <= TOL[precision]
+        assert (e0.cpu() - eo).abs().max() <= TOL[precision]
+        x1o, _ = O.interaction_network(sd, "_encode_process_decode._processor.gnn_stacks.0.", xo, ei.cpu(), eo)
+        assert (x1.cpu() - x1o).abs().max() <= TOL[precision]
+    finally:
+        G.set_default_precision("tf32")
+
+
+def test_rejects_cpu_tensors():
+    from sgnn_b200._lib import SgnnError
+    f = Fixture("single_h64")
+    sim, S, _, _ = make_sim(f, "tf32")
+    with pytest.raises(SgnnError):
+        sim.predict_positions(f.t("positions")[:, :S], [torch.tensor(240)], f.t("particle_types"))
+    with pytest.raises(ValueError):
+        sim.predict_positions(f.t("positions")[:, 0].cuda(), [torch.tensor(240)], f.t("particle_types"))
