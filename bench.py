@@ -1,0 +1,337 @@
+"""Benchmark of the sgnn learned-simulator hot path on B200 (contract: see the task brief).
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference] [--workload rollout]
+
+One "step" = one 100-step autoregressive rollout of the single-scale model (H=64, L=5, S=11,
+K=20 neighbours, r=15) over a 120x40 synthetic Taylor bar (N=4800), BASELINE.json configs[1]
+with the connectivity regime SURVEY.md section 8(d) calls the primary perf config
+(spacing 12.5 -> r/s = 1.2, E ~ 23.7k).  metric = particle-steps/s (neighbour search included,
+no D2H inside the rollout).  N>1: one independent trajectory per rank (replicas, weak scaling).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from sgnn_b200 import synthetic  # noqa: E402
+
+NX, NY, S, H, LAYERS, ROLLOUT_STEPS = 120, 40, 11, 64, 5, 100
+REGIME = "A"
+METRIC, UNIT = "rollout_particle_steps_per_s", "particle-steps/s"
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"hbm_gbs": d["hbm_gbs"], "bf16_tflops": d["bf16_tflops"], "source": "measured"}
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "source": "fallback"}
+
+
+def make_case(seed=0, nx=NX, ny=NY, nsteps=ROLLOUT_STEPS):
+    spacing, radius = synthetic.spacing_for(REGIME)
+    traj = synthetic.taylor_trajectory(nx, ny, spacing, nframes=S + nsteps, seed=seed)
+    meta = synthetic.metadata_from(traj["positions"])
+    stats = synthetic.normalization_stats(meta, 0.02 * spacing / 0.5)
+    return traj, stats, radius
+
+
+def make_sim(stats, radius, device, precision="tf32"):
+    from sgnn_b200.single_scale import LearnedSimulator
+    torch.manual_seed(1)
+    sim = LearnedSimulator(2, (S - 1) * 2 + 1, 3, H, LAYERS, 1, H, radius, stats, 1, 9,
+                           device=device, precision=precision)
+    return sim.to(device).eval()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.stop, self.index = [], False, index
+        self.th = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        while not self.stop:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True,
+                                     timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([c.strip() for c in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def __enter__(self):
+        self.th.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop = True
+        self.th.join(timeout=6)
+
+    def summary(self):
+        sm = sorted(float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit())
+        reasons = set()
+        for r in self.rows:
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None,
+                "sm_max_mhz": float(self.rows[0][1]) if self.rows else None,
+                "samples": len(self.rows), "reasons": sorted(reasons)}
+
+
+def cpu_reference_rollout(nsteps, threads):
+    """The reference's algorithm on the host cores: oracle port (torch CPU, fp32) of the same
+    model on the same synthetic workload, `nsteps` rollout steps.  Returns seconds."""
+    from oracle import sgnn_oracle as O
+    torch.set_num_threads(threads)
+    traj, stats, radius = make_case(seed=0, nsteps=nsteps)
+    sim = make_sim(stats, radius, "cpu")
+    sd = {k: v.detach() for k, v in sim.state_dict().items()}
+    t0 = time.perf_counter()
+    with torch.no_grad():
+        O.rollout(sd, traj["positions"], traj["particle_types"], nsteps, radius, stats, S)
+    return time.perf_counter() - t0
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path (oracle port) timed on the host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    nsteps = 5                                        # bounded sample of the 100-step rollout
+    n = NX * NY
+    for _ in range(args.warmup):
+        cpu_reference_rollout(1, threads)
+    times = [cpu_reference_rollout(nsteps, threads) for _ in range(args.steps)]
+    total = sum(times)
+    value = n * nsteps * args.steps / total
+    sample = f"{nsteps} of {ROLLOUT_STEPS} rollout steps per timed step, N={n}, regime {REGIME}"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic", "config": workload_config(),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def workload_config():
+    spacing, radius = synthetic.spacing_for(REGIME)
+    return {"workload": "single-scale GNS 100-step rollout, synthetic Taylor-Impact-2D bar",
+            "particles": NX * NY, "dim": 2, "radius": radius, "spacing": spacing,
+            "max_neighbors": 20, "layers": LAYERS, "hidden": H, "input_sequence_length": S,
+            "rollout_steps": ROLLOUT_STEPS, "batch": 1, "multi_gpu": "replicas (one trajectory per rank)",
+            "l2": "flushed with a 512 MiB write between timed rollouts"}
+
+
+def edge_layer_alg(n, e, he=H, hidden=H, out=H):
+    """Algorithmic bytes / flops of ONE edge-layer launch."""
+    by = e * (4 * he + 8) + n * (8 * hidden + 4 * out)
+    fl = e * 2 * (he * hidden + hidden * out)
+    return by, fl
+
+
+def roofline_entry(ms, n, e, pk, traffic=None):
+    by, fl = edge_layer_alg(n, e)
+    tf32_peak = pk["bf16_tflops"] / 2.0            # TF32 dense = 1/2 BF16 (nominal ratio)
+    t_hbm, t_tc = by / (pk["hbm_gbs"] * 1e9), fl / (tf32_peak * 1e12)
+    achieved = by / (ms * 1e-3) / 1e9
+    return {"kernel": "edge_layer_kernel<tf32>", "bound": "hbm" if t_hbm >= t_tc else "tensor",
+            "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"],
+            "traffic": traffic, "peak_source": pk["source"], "ms_per_launch": ms,
+            "alg_bytes_per_launch": by, "alg_flops_per_launch": fl,
+            "tensor_frac": fl / (ms * 1e-3) / 1e12 / tf32_peak, "edges": e, "nodes": n}
+
+
+def measure_edge_layer(sim, n, dev, reps=50):
+    """Average duration of the layer-0 edge kernel, `reps` launches between two CUDA events on
+    the launching stream, on the buffers left by the last rollout step."""
+    eng, rg = sim._engine(n, dev)
+    ep, _, es = eng.blocks[0]
+    csr = rg.csr
+    e = int(csr.rowptr[-1].item())
+    for _ in range(5):
+        ep.launch(csr, eng.e_tiles[es], eng.pq, eng.agg, eng.head)
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(reps):
+        ep.launch(csr, eng.e_tiles[es], eng.pq, eng.agg, eng.head)
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / reps, e
+
+
+def large_config(pk, dev, nx=2048, ny=512):
+    """BASELINE configs[4] on one GPU: one step over ~1M particles, per-kernel CUDA-event times."""
+    from sgnn_b200 import engine as E
+    from sgnn_b200.single_scale import evaluate as EV
+    traj, stats, radius = make_case(seed=7, nx=nx, ny=ny, nsteps=2)
+    sim = make_sim(stats, radius, dev)
+    n = nx * ny
+    plan = EV.RolloutPlan(sim, n, S + 2, S, 2, "autoregressive", dev, use_graph=False)
+    plan.traj[:, :S].copy_(traj["positions"][:, :S].to(dev))
+    plan.launch_steps(0, 1)                      # warm-up
+    torch.cuda.synchronize()
+    E.PROFILE = {}
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    plan.launch_steps(1, 2)
+    b.record()
+    torch.cuda.synchronize()
+    prof = E.profile_summary()
+    E.PROFILE = None
+    eng, rg = sim._engine(n, dev)
+    e = int(rg.csr.rowptr[-1].item())
+    step_ms = a.elapsed_time(b)
+    out = {"particles": n, "edges": e, "ms_per_step": step_ms, "particle_steps_per_s": n / (step_ms * 1e-3),
+           "kernels_ms": {k: {"launches": v[0], "mean_ms": v[1]} for k, v in prof.items()},
+           "roofline": roofline_entry(prof["edge_layer"][1], n, e, pk)}
+    del plan, sim
+    torch.cuda.empty_cache()
+    return out
+
+
+def run_gpu(args):
+    import torch.distributed as dist
+    from sgnn_b200 import _lib as L
+    from sgnn_b200.single_scale import evaluate as EV
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU path); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    L.lib()
+    EV.VERBOSE = False
+    pk = peaks()
+    traj, stats, radius = make_case(seed=rank)
+    sim = make_sim(stats, radius, dev)
+    n, t, dim = traj["positions"].shape
+    nsteps = t - S
+    pos_dev = traj["positions"].to(dev)
+    plan = EV.get_plan(sim, n, t, S, dim, "autoregressive", dev, True)
+    plan.types.copy_(traj["particle_types"].to(dev))
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        plan.traj[:, :S].copy_(pos_dev[:, :S])
+        plan.run()
+    barrier()
+    launches0 = L.launch_count
+    evs = []
+    with ClockSampler(local) as clk:
+        for _ in range(args.steps):
+            plan.traj[:, :S].copy_(pos_dev[:, :S])      # inputs resident before the timed region
+            flush.fill_(1)                               # L2 flush (untimed)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            plan.run()
+            b.record()
+            evs.append((a, b))
+        barrier()
+        if args.steps * 10 < 1500:                       # keep the sampler alive >= ~1 s under load
+            for _ in range(40):
+                plan.run()
+            torch.cuda.synchronize()
+    gpu_launches = L.launch_count - launches0
+    total_ms = sum(a.elapsed_time(b) for a, b in evs)
+    tt = torch.tensor([total_ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    total_ms = tt.item()
+    value = world * n * nsteps * args.steps / (total_ms * 1e-3)
+
+    # ---- end to end through the public API: pinned host buffers in, numpy out ----
+    pos_pin = traj["positions"].pin_memory()
+    strains_pin = traj["strains"].pin_memory()
+    types_pin = traj["particle_types"].pin_memory()
+    ke = max(3, min(args.steps, 10))
+    res = None
+    for i in range(2 + ke):
+        if i == 2:
+            barrier()
+            t0 = time.perf_counter()
+        res = EV.rollout(sim, pos_pin.to(dev, non_blocking=True), types_pin.to(dev, non_blocking=True),
+                         torch.tensor(n), strains_pin.to(dev, non_blocking=True), nsteps, dim, dev, S)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    te = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_value = world * n * nsteps * ke / te.item()
+    h2d = pos_pin.numel() * 4 + strains_pin.numel() * 4 + types_pin.numel() * 8
+    d2h = sum(v.nbytes for v in res.values() if hasattr(v, "nbytes"))
+
+    line = None
+    if rank == 0:
+        ms_edge, e_edges = measure_edge_layer(sim, n, dev)
+        roof = roofline_entry(ms_edge, n, e_edges, pk)
+        roof["timing"] = "50 back-to-back launches between CUDA events; working set L2-resident at this size"
+        cores = os.cpu_count() or 1
+        cpu_steps = 5
+        cpu_reference_rollout(1, cores)
+        cpu_s = cpu_reference_rollout(cpu_steps, cores)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "tf32", "data": "synthetic",
+            "config": workload_config(), "clocks": clk.summary(),
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "api": "sgnn_b200.single_scale.evaluate.rollout", "rollouts_timed": ke},
+            "gpu_launches": gpu_launches,
+            "roofline": roof,
+            "cpu_baseline": {"value": n * cpu_steps / cpu_s, "unit": UNIT, "cores": cores, "kind": "port",
+                             "sample": f"{cpu_steps} of {ROLLOUT_STEPS} rollout steps, N={n}, regime {REGIME}"},
+        }
+        if world == 1 and not args.no_large:
+            try:
+                line["large"] = large_config(pk, dev)
+            except Exception as ex:           # report, never hide
+                line["large"] = {"error": repr(ex)}
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if line is not None:
+        print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="sgnn_b200", choices=["sgnn_b200", "reference"])
+    ap.add_argument("--no-large", action="store_true", help="skip the 1M-particle single-step section")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -39,6 +39,18 @@ void sgnn_set_error(const char* fmt, ...);
 
 #define SGNN_LAUNCH_CHECK()  SGNN_CUDA(cudaGetLastError())
 
+// Raise a kernel's dynamic shared-memory limit once (never inside a CUDA-graph capture after
+// the first, un-captured call).
+#define SGNN_ENSURE_SMEM(kernel, bytes)                                                     \
+  do {                                                                                      \
+    static int _cur = 0;                                                                    \
+    if ((bytes) > _cur) {                                                                   \
+      SGNN_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,   \
+                                     (bytes)));                                             \
+      _cur = (bytes);                                                                       \
+    }                                                                                       \
+  } while (0)
+
 #ifdef __CUDACC__
 #define SGNN_HD __host__ __device__
 #else

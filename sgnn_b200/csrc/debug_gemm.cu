@@ -43,10 +43,10 @@ extern "C" int sgnn_debug_gemm(const float* a, const float* wimg, int k, int n, 
   const int smem = align_up(kTileRows * k * 4 + n * k * 4 + 64, 1024) + (tc ? 0 : kTileRows * pow2_cols(n) * 4) + 1024;
   SGNN_CHECK_ARG(smem <= 227 * 1024, "debug_gemm: too much shared memory");
   if (tc) {
-    SGNN_CUDA(cudaFuncSetAttribute(debug_gemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    SGNN_ENSURE_SMEM(debug_gemm_kernel<true>, smem);
     debug_gemm_kernel<true><<<1, kThreads, smem, (cudaStream_t)stream>>>(a, wimg, k, n, d);
   } else {
-    SGNN_CUDA(cudaFuncSetAttribute(debug_gemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    SGNN_ENSURE_SMEM(debug_gemm_kernel<false>, smem);
     debug_gemm_kernel<false><<<1, kThreads, smem, (cudaStream_t)stream>>>(a, wimg, k, n, d);
   }
   SGNN_LAUNCH_CHECK();

@@ -146,10 +146,10 @@ extern "C" int sgnn_edge_encoder_fwd(const SgnnEdgeEncoderParams* p, int use_ten
   if (grid > p->max_tiles) grid = p->max_tiles;
   if (grid < 1) grid = 1;
   if (use_tensor_cores) {
-    SGNN_CUDA(cudaFuncSetAttribute(edge_encoder_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    SGNN_ENSURE_SMEM(edge_encoder_kernel<true>, smem);
     edge_encoder_kernel<true><<<grid, kThreads, smem, (cudaStream_t)stream>>>(*p);
   } else {
-    SGNN_CUDA(cudaFuncSetAttribute(edge_encoder_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    SGNN_ENSURE_SMEM(edge_encoder_kernel<false>, smem);
     edge_encoder_kernel<false><<<grid, kThreads, smem, (cudaStream_t)stream>>>(*p);
   }
   SGNN_LAUNCH_CHECK();

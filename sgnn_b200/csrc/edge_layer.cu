@@ -268,10 +268,10 @@ extern "C" int sgnn_edge_layer_fwd(const SgnnEdgeLayerParams* p, int use_tensor_
   if (grid > p->max_tiles) grid = p->max_tiles;
   if (grid < 1) grid = 1;
   if (use_tensor_cores) {
-    SGNN_CUDA(cudaFuncSetAttribute(edge_layer_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    SGNN_ENSURE_SMEM(edge_layer_kernel<true>, smem);
     edge_layer_kernel<true><<<grid, kThreads, smem, (cudaStream_t)stream>>>(*p);
   } else {
-    SGNN_CUDA(cudaFuncSetAttribute(edge_layer_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    SGNN_ENSURE_SMEM(edge_layer_kernel<false>, smem);
     edge_layer_kernel<false><<<grid, kThreads, smem, (cudaStream_t)stream>>>(*p);
   }
   SGNN_LAUNCH_CHECK();

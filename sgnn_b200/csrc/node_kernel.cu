@@ -311,10 +311,10 @@ extern "C" int sgnn_node_fwd(const SgnnNodeParams* p, int use_tensor_cores, int 
   if (grid > n_tiles) grid = n_tiles;
   if (grid < 1) grid = 1;
   if (use_tensor_cores) {
-    SGNN_CUDA(cudaFuncSetAttribute(node_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total));
+    SGNN_ENSURE_SMEM(node_kernel<true>, L.total);
     node_kernel<true><<<grid, kThreads, L.total, (cudaStream_t)stream>>>(*p);
   } else {
-    SGNN_CUDA(cudaFuncSetAttribute(node_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total));
+    SGNN_ENSURE_SMEM(node_kernel<false>, L.total);
     node_kernel<false><<<grid, kThreads, L.total, (cudaStream_t)stream>>>(*p);
   }
   SGNN_LAUNCH_CHECK();

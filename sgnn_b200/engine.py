@@ -69,12 +69,38 @@ class RadiusGraph:
     def build(self, pos: torch.Tensor, pos_stride: int, dim: int, example_ptr: torch.Tensor,
               radius: float):
         """pos: tensor whose data_ptr is particle 0's most recent position."""
-        L.check(L.lib().sgnn_radius_graph_csr(
+        with _timed("radius_graph"):
+          L.check(L.lib().sgnn_radius_graph_csr(
             C.c_void_p(pos.data_ptr()), C.c_long(pos_stride), self.n, dim, L.ptr(example_ptr),
             example_ptr.numel() - 1, C.c_double(radius), self.k, int(self.loop), L.ptr(self.ws),
             C.c_size_t(self.ws_bytes), L.ptr(self.csr.rowptr), L.ptr(self.csr.src),
             L.ptr(self.csr.tgt), L.stream_ptr()), launches=9)
         return self.csr
+
+
+PROFILE = None      # set to a dict to collect (start, end) CUDA events per kernel family
+
+
+class _timed:
+    """Wraps one kernel launch in CUDA events on the launching stream when PROFILE is a dict."""
+
+    def __init__(self, name):
+        self.name = name
+
+    def __enter__(self):
+        if PROFILE is not None:
+            self.ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+            self.ev[0].record()
+
+    def __exit__(self, *a):
+        if PROFILE is not None:
+            self.ev[1].record()
+            PROFILE.setdefault(self.name, []).append(self.ev)
+
+
+def profile_summary():
+    """{name: (launches, mean_ms)} -- call after torch.cuda.synchronize()."""
+    return {k: (len(v), sum(a.elapsed_time(b) for a, b in v) / len(v)) for k, v in (PROFILE or {}).items()}
 
 
 def _grid(smem_bytes: int, max_ctas: int) -> int:
@@ -111,7 +137,8 @@ class EdgeEncoderPlan:
         p.feat = feat.data_ptr() if feat is not None else None
         p.feat_out = feat_out.data_ptr() if feat_out is not None else None
         p.e_tiles, p.max_tiles = e_tiles.data_ptr(), csr.max_tiles
-        L.check(L.lib().sgnn_edge_encoder_fwd(C.byref(p), int(self.tc), _grid(self.smem, csr.max_tiles),
+        with _timed("edge_encoder"):
+          L.check(L.lib().sgnn_edge_encoder_fwd(C.byref(p), int(self.tc), _grid(self.smem, csr.max_tiles),
                                               L.stream_ptr()))
 
 
@@ -137,7 +164,8 @@ class EdgeLayerPlan:
         p.e_tiles, p.pq = e_tiles.data_ptr(), pq.data_ptr()
         p.src, p.tgt, p.rowptr, p.n_nodes = csr.src.data_ptr(), csr.tgt.data_ptr(), csr.rowptr.data_ptr(), csr.n_nodes
         p.agg, p.head, p.max_tiles = agg.data_ptr(), head.data_ptr(), csr.max_tiles
-        L.check(L.lib().sgnn_edge_layer_fwd(C.byref(p), int(self.tc), _grid(self.smem, csr.max_tiles),
+        with _timed("edge_layer"):
+          L.check(L.lib().sgnn_edge_layer_fwd(C.byref(p), int(self.tc), _grid(self.smem, csr.max_tiles),
                                             L.stream_ptr()))
 
 
@@ -191,7 +219,8 @@ class NodePlan:
                 v = v.data_ptr()
             setattr(p, k, v)
         n_tiles = (n_rows + TILE - 1) // TILE
-        L.check(L.lib().sgnn_node_fwd(C.byref(p), int(self.tc), _grid(self.smem, n_tiles), L.stream_ptr()))
+        with _timed("node_" + ("encoder", "layer", "rows")[p.prologue]):
+          L.check(L.lib().sgnn_node_fwd(C.byref(p), int(self.tc), _grid(self.smem, n_tiles), L.stream_ptr()))
 
 
 class EpdEngine:

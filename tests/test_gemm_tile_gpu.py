@@ -21,14 +21,14 @@ def _run(k, n, tc):
     return a, w, d
 
 
-@pytest.mark.parametrize("k,n", [(32, 32), (64, 64), (128, 64), (64, 128), (256, 128)])
+@pytest.mark.parametrize("k,n", [(32, 32), (64, 64), (128, 64), (64, 128), (256, 64)])
 def test_gemm_tile_fp32(k, n):
     a, w, d = _run(k, n, False)
     ref = (a.double() @ w.double().T).float()
     assert torch.allclose(d, ref, atol=2e-5 * k ** 0.5, rtol=1e-5)
 
 
-@pytest.mark.parametrize("k,n", [(32, 32), (64, 64), (128, 64), (64, 128), (256, 128)])
+@pytest.mark.parametrize("k,n", [(32, 32), (64, 64), (128, 64), (64, 128), (256, 64)])
 def test_gemm_tile_tf32(k, n):
     a, w, d = _run(k, n, True)
     ref = (a.double() @ w.double().T).float()

@@ -1,0 +1,78 @@
+"""GPU: device-resident rollout driver (CUDA-graph replay) vs golden fixtures / oracle."""
+import numpy as np
+import pytest
+import torch
+
+from tests.test_single_scale_gpu import TOL, make_sim
+from tests.util import Fixture
+
+pytestmark = pytest.mark.gpu
+
+
+def _run(sim, f, S, mode="autoregressive", graph=True, types=None):
+    from sgnn_b200.single_scale import evaluate as EV
+    EV.VERBOSE = False
+    pos, strains = f.t("positions").cuda(), f.t("strains").cuda()
+    types = f.t("particle_types").cuda() if types is None else types
+    return EV.rollout(sim, pos, types, torch.tensor(pos.shape[0]), strains, 0, 2, "cuda", S, mode,
+                      use_cuda_graph=graph)
+
+
+@pytest.mark.parametrize("precision", ["fp32", "tf32"])
+def test_rollout_golden_and_graph_determinism(precision):
+    f = Fixture("single_h64")
+    sim, S, radius, nsteps = make_sim(f, precision)
+    a = _run(sim, f, S, graph=True)
+    b = _run(sim, f, S, graph=True)          # second call: pure graph replay
+    c = _run(sim, f, S, graph=False)
+    assert np.array_equal(a["predicted_rollout"], b["predicted_rollout"])
+    assert np.array_equal(a["predicted_rollout"], c["predicted_rollout"])   # deterministic kernels
+    assert np.array_equal(a["predicted_strain"], c["predicted_strain"])
+    ref64 = f["rollout_f64"]
+    acc_std = f.stats()["acceleration"]["std"].max().item()
+    assert a["predicted_rollout"].shape == ref64.shape
+    for step in range(nsteps):
+        err = np.abs(a["predicted_rollout"][step] - ref64[step]).max()
+        assert err <= TOL[precision] * acc_std * (step + 1) * 3 + 2e-4, (step, err)
+    if precision == "fp32":
+        assert np.allclose(a["rmse_position"], f["rmse_position_f32"], rtol=1e-3)
+    for k in ("initial_positions", "initial_strains", "ground_truth_rollout", "ground_truth_strain",
+              "predicted_strain", "particle_types", "rmse_strain", "run_time", "inference_mode"):
+        assert k in a
+    assert a["initial_positions"].shape == (S, 240, 2)
+
+
+def test_one_step_mode_matches_oracle():
+    from oracle import sgnn_oracle as O
+    f = Fixture("single_h64")
+    sim, S, radius, nsteps = make_sim(f, "fp32")
+    out = _run(sim, f, S, mode="one_step")
+    pred, _, _ = O.rollout(f.state_dict(), f.t("positions"), f.t("particle_types"), nsteps, radius,
+                           f.stats(), S, mode="one_step")
+    assert np.abs(out["predicted_rollout"] - pred.numpy()).max() <= 2e-4
+    with pytest.raises(ValueError):
+        _run(sim, f, S, mode="bogus")
+
+
+def test_erosional_particles_follow_ground_truth():
+    f = Fixture("single_h64")
+    sim, S, radius, nsteps = make_sim(f, "fp32")
+    types = f.t("particle_types").clone()
+    types[::7] = -1
+    out = _run(sim, f, S, types=types.cuda())
+    gt = f["positions"][:, S:].transpose(1, 0, 2)
+    assert np.array_equal(out["predicted_rollout"][:, ::7], gt[:, ::7])
+    assert not np.array_equal(out["predicted_rollout"][:, 1::7], gt[:, 1::7])
+
+
+def test_input_validation():
+    from sgnn_b200.single_scale import evaluate as EV
+    f = Fixture("single_h64")
+    sim, S, _, _ = make_sim(f, "tf32")
+    pos, st, ty = f.t("positions").cuda(), f.t("strains").cuda(), f.t("particle_types").cuda()
+    with pytest.raises(ValueError):
+        EV.rollout(sim, pos[:, 0], ty, torch.tensor(240), st, 0, 2, "cuda", S)
+    with pytest.raises(ValueError):
+        EV.rollout(sim, pos, ty, torch.tensor(240), st[:, :10], 0, 2, "cuda", S)
+    with pytest.raises(ValueError):
+        EV.rollout(sim, pos[:, :5], ty, torch.tensor(240), st, 0, 2, "cuda", S)
