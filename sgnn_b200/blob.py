@@ -8,6 +8,9 @@ import torch
 from . import _lib as L
 
 
+VEC_REGION_BYTES = 8192     # SGNN_VEC_REGION_BYTES in csrc/params.h
+
+
 def pad32(k: int) -> int:
     return (k + 31) // 32 * 32
 
@@ -21,7 +24,8 @@ class BlobBuilder:
         self.round_tf32 = round_tf32
         self._images = []   # (byte_off, weight, row0, n, col0, k, kpad, scale)
         self._vectors = []  # (float_off, tensor)
-        self._bytes = 0
+        self._bytes = VEC_REGION_BYTES     # images start after the vector region
+        self._vec_bytes = 0
 
     def add_image(self, weight: torch.Tensor, row0: int, n: int, col0: int, k: int,
                   kpad: Optional[int] = None, scale: float = 1.0) -> int:
@@ -35,9 +39,11 @@ class BlobBuilder:
         return off
 
     def add_vector(self, t: torch.Tensor) -> int:
-        off = (self._bytes + 15) // 16 * 16
+        off = (self._vec_bytes + 15) // 16 * 16
+        if off + t.numel() * 4 > VEC_REGION_BYTES:
+            raise L.SgnnError(f"fp32 vectors of this kernel exceed the {VEC_REGION_BYTES}-byte blob region")
         self._vectors.append((off // 4, t))
-        self._bytes = off + t.numel() * 4
+        self._vec_bytes = off + t.numel() * 4
         return off // 4
 
     def finish(self) -> Tuple[torch.Tensor, int]:

@@ -12,32 +12,39 @@
 namespace sgnn {
 
 struct EncMisc {
-  uint64_t bar_w, bar_mma;
+  uint64_t bar_w, bar_mma, bar_stream;
   uint32_t tmem_slot;
   int pad;
 };
 
 struct EdgeEncSmem {
-  int hid, misc, simt, total;
+  int wbuf, hid, misc, simt, total;
 };
-__host__ __device__ inline EdgeEncSmem edge_enc_smem(int blob_bytes, int hidden, int out, bool tc) {
+__host__ __device__ inline EdgeEncSmem edge_enc_smem(int blob_bytes, int hidden, int out, bool tc,
+                                                     bool streamed) {
   EdgeEncSmem s;
   const int w = hidden > out ? hidden : out;
-  s.hid = align_up(blob_bytes, 1024);
+  s.wbuf = align_up(blob_smem_bytes(blob_bytes, streamed), 1024);
+  s.hid = s.wbuf + (streamed ? wbuf_bytes(tc) : 0);
   s.misc = s.hid + kTileRows * w * 4;
   s.simt = align_up(s.misc + (int)sizeof(EncMisc), 1024);
-  s.total = s.simt + (tc ? 0 : kTileRows * pow2_cols(2 * w) * 4) + 1024;
+  s.total = s.simt + (tc ? 0 : kTileRows * pow2_cols(w) * 4) + 1024;
   return s;
+}
+
+__host__ inline bool edge_enc_streamed(int blob_bytes, int hidden, int out, bool tc) {
+  return edge_enc_smem(blob_bytes, hidden, out, tc, false).total > 227 * 1024;
 }
 
 constexpr int kMaxEdgeFeat = 8;
 
 template <bool TC>
-__global__ void __launch_bounds__(kThreads) edge_encoder_kernel(const SgnnEdgeEncoderParams p) {
+__global__ void __launch_bounds__(kThreads) edge_encoder_kernel(const SgnnEdgeEncoderParams p,
+                                                                const int streamed) {
   char* smem = smem_base_1024();
   const int hidden = p.mlp.hidden, out = p.mlp.out;
   const int w = hidden > out ? hidden : out;
-  const EdgeEncSmem L = edge_enc_smem(p.blob_bytes, hidden, out, TC);
+  const EdgeEncSmem L = edge_enc_smem(p.blob_bytes, hidden, out, TC, streamed != 0);
   const float* blob_f = reinterpret_cast<const float*>(smem);
   char* hid = smem + L.hid;
   EncMisc* misc = reinterpret_cast<EncMisc*>(smem + L.misc);
@@ -47,13 +54,10 @@ __global__ void __launch_bounds__(kThreads) edge_encoder_kernel(const SgnnEdgeEn
   const int n_tiles = (n_edges + kTileRows - 1) / kTileRows;
   if ((int)blockIdx.x >= n_tiles) return;
 
-  if (tid == 0) {
-    mbar_init(&misc->bar_w, 1);
-    mbar_fence_init();
-    tma_load_span(smem, reinterpret_cast<const char*>(p.blob), p.blob_bytes, &misc->bar_w);
-  }
+  WeightStage ws;
+  weights_setup(ws, p.blob, p.blob_bytes, smem, smem + L.wbuf, &misc->bar_w, &misc->bar_stream, streamed);
   TileAcc<TC> acc;
-  acc_setup<TC>(acc, pow2_cols(2 * w), &misc->bar_mma, &misc->tmem_slot,
+  acc_setup<TC>(acc, TC ? pow2_cols(2 * w) : pow2_cols(w), &misc->bar_mma, &misc->tmem_slot,
                 reinterpret_cast<float*>(smem + L.simt));
   mbar_wait(&misc->bar_w, 0);
   const int tile_bytes = kTileRows * out * 4;
@@ -96,7 +100,7 @@ __global__ void __launch_bounds__(kThreads) edge_encoder_kernel(const SgnnEdgeEn
         a_tile_store32<TC>(hid, c, v);
       }
     }
-    const int acc_col = mlp_run_rest<TC>(acc, hid, smem, p.mlp, w, 1);
+    const int acc_col = mlp_run_rest<TC>(acc, ws, hid, p.mlp, w, 1);
     // ---- LayerNorm -> tile (A-operand layout) staged in `hid`, then one TMA bulk store ----
     float mean = 0.f, rstd = 1.f;
     if (p.mlp.has_ln) row_ln_stats<TC>(acc, acc_col, out, blob_f + p.mlp.b_off[p.mlp.n_hidden], mean, rstd);
@@ -127,7 +131,8 @@ __global__ void __launch_bounds__(kThreads) edge_encoder_kernel(const SgnnEdgeEn
 using namespace sgnn;
 
 extern "C" size_t sgnn_edge_encoder_smem_bytes(int blob_bytes, int hidden, int out, int tc) {
-  return (size_t)edge_enc_smem(blob_bytes, hidden, out, tc != 0).total;
+  const bool st = edge_enc_streamed(blob_bytes, hidden, out, tc != 0);
+  return (size_t)edge_enc_smem(blob_bytes, hidden, out, tc != 0, st).total;
 }
 
 extern "C" int sgnn_edge_encoder_fwd(const SgnnEdgeEncoderParams* p, int use_tensor_cores, int grid,
@@ -141,16 +146,18 @@ extern "C" int sgnn_edge_encoder_fwd(const SgnnEdgeEncoderParams* p, int use_ten
   SGNN_CHECK_ARG(p->feat != nullptr || p->k_in == p->dim + 1, "edge_encoder: k_in must be dim+1");
   SGNN_CHECK_ARG(p->blob_bytes % 16 == 0, "edge_encoder: blob size must be a multiple of 16");
   if (p->max_tiles <= 0) return SGNN_OK;
-  const int smem = edge_enc_smem(p->blob_bytes, p->mlp.hidden, p->mlp.out, use_tensor_cores).total;
+  const int streamed = edge_enc_streamed(p->blob_bytes, p->mlp.hidden, p->mlp.out, use_tensor_cores);
+  const int smem = edge_enc_smem(p->blob_bytes, p->mlp.hidden, p->mlp.out, use_tensor_cores, streamed).total;
+  SGNN_CHECK_ARG(p->blob_bytes >= SGNN_VEC_REGION_BYTES, "edge_encoder: blob lacks the vector region");
   SGNN_CHECK_ARG(smem <= 227 * 1024, "edge_encoder: needs %d bytes of shared memory (> 227 KB)", smem);
   if (grid > p->max_tiles) grid = p->max_tiles;
   if (grid < 1) grid = 1;
   if (use_tensor_cores) {
     SGNN_ENSURE_SMEM(edge_encoder_kernel<true>, smem);
-    edge_encoder_kernel<true><<<grid, kThreads, smem, (cudaStream_t)stream>>>(*p);
+    edge_encoder_kernel<true><<<grid, kThreads, smem, (cudaStream_t)stream>>>(*p, streamed);
   } else {
     SGNN_ENSURE_SMEM(edge_encoder_kernel<false>, smem);
-    edge_encoder_kernel<false><<<grid, kThreads, smem, (cudaStream_t)stream>>>(*p);
+    edge_encoder_kernel<false><<<grid, kThreads, smem, (cudaStream_t)stream>>>(*p, streamed);
   }
   SGNN_LAUNCH_CHECK();
   return SGNN_OK;

@@ -20,7 +20,7 @@
 namespace sgnn {
 
 struct EdgeMisc {
-  uint64_t bar_w, bar_e, bar_mma;
+  uint64_t bar_w, bar_e, bar_mma, bar_stream;
   uint32_t tmem_slot;
   int n_edges;
   int tgt_s[kTileRows + 4];     // [0] = receiver of the edge before the tile, [1+r] = row r
@@ -30,19 +30,24 @@ struct EdgeMisc {
 };
 
 struct EdgeLayerSmem {
-  int blob, e_tile, hid, misc, simt, total;
+  int blob, wbuf, e_tile, hid, misc, simt, total;
 };
 __host__ __device__ inline EdgeLayerSmem edge_layer_smem(int blob_bytes, int he, int hidden, int out,
-                                                         bool tc) {
+                                                         bool tc, bool streamed) {
   EdgeLayerSmem s;
   const int w = hidden > out ? hidden : out;
   s.blob = 0;
-  s.e_tile = align_up(blob_bytes, 1024);
+  s.wbuf = align_up(blob_smem_bytes(blob_bytes, streamed), 1024);
+  s.e_tile = s.wbuf + (streamed ? wbuf_bytes(tc) : 0);
   s.hid = s.e_tile + kTileRows * he * 4;
   s.misc = s.hid + kTileRows * w * 4;
   s.simt = align_up(s.misc + (int)sizeof(EdgeMisc), 1024);
-  s.total = s.simt + (tc ? 0 : kTileRows * pow2_cols(2 * w) * 4) + 1024;  // +1024: base alignment
+  s.total = s.simt + (tc ? 0 : kTileRows * pow2_cols(w) * 4) + 1024;  // +1024: base alignment
   return s;
+}
+// resident weights when everything fits in 227 KB, else streamed
+__host__ inline bool edge_layer_streamed(int blob_bytes, int he, int hidden, int out, bool tc) {
+  return edge_layer_smem(blob_bytes, he, hidden, out, tc, false).total > 227 * 1024;
 }
 
 __device__ __forceinline__ float m_tile_read(const float* m, int row, int col, int width) {
@@ -50,11 +55,12 @@ __device__ __forceinline__ float m_tile_read(const float* m, int row, int col, i
 }
 
 template <bool TC>
-__global__ void __launch_bounds__(kThreads) edge_layer_kernel(const SgnnEdgeLayerParams p) {
+__global__ void __launch_bounds__(kThreads) edge_layer_kernel(const SgnnEdgeLayerParams p,
+                                                              const int streamed) {
   char* smem = smem_base_1024();
   const int hidden = p.mlp.hidden, out = p.mlp.out, he = p.he, nh = p.mlp.n_hidden;
   const int w = hidden > out ? hidden : out;
-  const EdgeLayerSmem L = edge_layer_smem(p.blob_bytes, he, hidden, out, TC);
+  const EdgeLayerSmem L = edge_layer_smem(p.blob_bytes, he, hidden, out, TC, streamed != 0);
   const float* blob_f = reinterpret_cast<const float*>(smem + L.blob);
   char* e_tile = smem + L.e_tile;
   char* hid = smem + L.hid;
@@ -66,16 +72,15 @@ __global__ void __launch_bounds__(kThreads) edge_layer_kernel(const SgnnEdgeLaye
   const int n_tiles = (n_edges + kTileRows - 1) / kTileRows;
   if ((int)blockIdx.x >= n_tiles) return;   // uniform per CTA, before any barrier/TMEM use
 
-  if (tid == 0) {
-    mbar_init(&misc->bar_w, 1);
-    mbar_init(&misc->bar_e, 1);
-    mbar_fence_init();
-    tma_load_span(smem + L.blob, reinterpret_cast<const char*>(p.blob), p.blob_bytes, &misc->bar_w);
+  WeightStage ws;
+  if (tid == 0) mbar_init(&misc->bar_e, 1);
+  weights_setup(ws, p.blob, p.blob_bytes, smem + L.blob, smem + L.wbuf, &misc->bar_w,
+                &misc->bar_stream, streamed);
+  if (tid == 0)
     tma_load_span(e_tile, reinterpret_cast<const char*>(p.e_tiles) + (long)blockIdx.x * tile_bytes,
                   tile_bytes, &misc->bar_e);
-  }
   TileAcc<TC> acc;
-  acc_setup<TC>(acc, pow2_cols(2 * w), &misc->bar_mma, &misc->tmem_slot,
+  acc_setup<TC>(acc, TC ? pow2_cols(2 * w) : pow2_cols(w), &misc->bar_mma, &misc->tmem_slot,
                 reinterpret_cast<float*>(smem + L.simt));
   mbar_wait(&misc->bar_w, 0);
   uint32_t phase_e = 0;
@@ -96,8 +101,8 @@ __global__ void __launch_bounds__(kThreads) edge_layer_kernel(const SgnnEdgeLaye
     // ---- stage 0: e0 (2^l W1c)^T, then + P[tgt] + Q[src], ReLU ----
     mbar_wait(&misc->bar_e, phase_e);
     phase_e ^= 1u;
-    gemm_step<TC>(acc, e_tile, smem + p.mlp.w_off[0], he, hidden, 0, false);
-    gemm_wait<TC>(acc);
+    gemm_weights<TC>(acc, ws, e_tile, p.mlp.w_off[0], he, hidden, 0, false);
+    gemm_weights_wait<TC>(acc, ws);
     if constexpr (!TC) __syncthreads();      // every thread has finished reading the e0 tile
     if (tid == 0 && tile + (int)gridDim.x < n_tiles)
       tma_load_span(e_tile, reinterpret_cast<const char*>(p.e_tiles) +
@@ -127,8 +132,8 @@ __global__ void __launch_bounds__(kThreads) edge_layer_kernel(const SgnnEdgeLaye
     for (int l = 1; l < nh; ++l) {
       a_tile_publish<TC>();
       region ^= 1;
-      gemm_step<TC>(acc, hid, smem + p.mlp.w_off[l], hidden, hidden, region * w, false);
-      gemm_wait<TC>(acc);
+      gemm_weights<TC>(acc, ws, hid, p.mlp.w_off[l], hidden, hidden, region * w, false);
+      gemm_weights_wait<TC>(acc, ws);
       const float* b = blob_f + p.mlp.b_off[l];
       for (int c = 0; c < hidden; c += 32) {
         float v[32];
@@ -141,8 +146,8 @@ __global__ void __launch_bounds__(kThreads) edge_layer_kernel(const SgnnEdgeLaye
     // ---- output stage + LayerNorm -> message tile M (aliases hid) ----
     a_tile_publish<TC>();
     region ^= 1;
-    gemm_step<TC>(acc, hid, smem + p.mlp.w_off[nh], hidden, out, region * w, false);
-    gemm_wait<TC>(acc);
+    gemm_weights<TC>(acc, ws, hid, p.mlp.w_off[nh], hidden, out, region * w, false);
+    gemm_weights_wait<TC>(acc, ws);
     float* m_tile = reinterpret_cast<float*>(hid);
     {
       const float* b = blob_f + p.mlp.b_off[nh];
@@ -249,7 +254,8 @@ static int check_mlp(const SgnnMlp& m, const char* who) {
 }
 
 extern "C" size_t sgnn_edge_layer_smem_bytes(int blob_bytes, int he, int hidden, int out, int tc) {
-  return (size_t)edge_layer_smem(blob_bytes, he, hidden, out, tc != 0).total;
+  const bool st = edge_layer_streamed(blob_bytes, he, hidden, out, tc != 0);
+  return (size_t)edge_layer_smem(blob_bytes, he, hidden, out, tc != 0, st).total;
 }
 
 extern "C" int sgnn_edge_layer_fwd(const SgnnEdgeLayerParams* p, int use_tensor_cores, int grid,
@@ -262,17 +268,19 @@ extern "C" int sgnn_edge_layer_fwd(const SgnnEdgeLayerParams* p, int use_tensor_
   SGNN_CHECK_ARG(p->blob_bytes % 16 == 0, "edge_layer: blob size must be a multiple of 16");
   SGNN_CHECK_ARG(p->mlp.has_ln, "edge_layer: the edge MLP ends in a LayerNorm in the reference");
   if (p->max_tiles <= 0 || p->n_nodes <= 0) return SGNN_OK;
-  const int smem = edge_layer_smem(p->blob_bytes, p->he, p->mlp.hidden, p->mlp.out, use_tensor_cores).total;
-  SGNN_CHECK_ARG(smem <= 227 * 1024, "edge_layer: needs %d bytes of shared memory (> 227 KB); "
-                 "this layer shape is not supported by the resident-weight kernel", smem);
+  const int streamed = edge_layer_streamed(p->blob_bytes, p->he, p->mlp.hidden, p->mlp.out, use_tensor_cores);
+  const int smem = edge_layer_smem(p->blob_bytes, p->he, p->mlp.hidden, p->mlp.out, use_tensor_cores, streamed).total;
+  SGNN_CHECK_ARG(smem <= 227 * 1024, "edge_layer: needs %d bytes of shared memory (> 227 KB) even with "
+                 "streamed weights; this layer shape is not supported", smem);
+  SGNN_CHECK_ARG(p->blob_bytes >= SGNN_VEC_REGION_BYTES, "edge_layer: blob lacks the vector region");
   if (grid > p->max_tiles) grid = p->max_tiles;
   if (grid < 1) grid = 1;
   if (use_tensor_cores) {
     SGNN_ENSURE_SMEM(edge_layer_kernel<true>, smem);
-    edge_layer_kernel<true><<<grid, kThreads, smem, (cudaStream_t)stream>>>(*p);
+    edge_layer_kernel<true><<<grid, kThreads, smem, (cudaStream_t)stream>>>(*p, streamed);
   } else {
     SGNN_ENSURE_SMEM(edge_layer_kernel<false>, smem);
-    edge_layer_kernel<false><<<grid, kThreads, smem, (cudaStream_t)stream>>>(*p);
+    edge_layer_kernel<false><<<grid, kThreads, smem, (cudaStream_t)stream>>>(*p, streamed);
   }
   SGNN_LAUNCH_CHECK();
   return SGNN_OK;

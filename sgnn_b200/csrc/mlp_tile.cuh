@@ -27,7 +27,10 @@ struct TileAcc {
 };
 
 // ---- fp32 SIMT accumulator addressing (thread == row; conflict-free 16-byte accesses) ----
+// Columns wrap modulo acc_cols (a power of two): the FFMA mode keeps ONE live accumulator region
+// at a time, so the ping-pong regions of the tensor-core mode may alias.
 __device__ __forceinline__ float4* simt_acc_chunk(float* base, int row, int chunk, int acc_cols) {
+  chunk &= (acc_cols >> 2) - 1;
   return reinterpret_cast<float4*>(base + (size_t)row * acc_cols) + (chunk ^ (row & 7));
 }
 
@@ -82,6 +85,65 @@ __device__ __forceinline__ void gemm_wait(TileAcc<TC>& acc) {
     mbar_wait(acc.bar, acc.phase);
     acc.phase ^= 1u;
     tc_fence_after_sync();
+  }
+}
+
+// ---- weight images: resident in shared memory, or streamed per GEMM ----------------------
+// Blob layout (params.h): [0, kVecRegionBytes) fp32 vectors, then the GEMM images.  When the
+// whole blob fits next to the kernel's tiles it is staged once and stays resident.  Otherwise
+// (H = 128 with two hidden layers: 192-384 KB of images) only the vector region is resident and
+// every GEMM pulls its image from global memory (L2-resident) into one 64 KB stage buffer by TMA,
+// in chunks of whole K-blocks.
+constexpr int kVecRegionBytes = SGNN_VEC_REGION_BYTES;
+constexpr int kWbufBytesTc = 65536;     // tensor-core mode: up to 4 K-blocks of a 128-row image
+constexpr int kWbufBytesSimt = 16384;   // FFMA parity mode: shared memory also holds the accumulators
+__host__ __device__ inline int wbuf_bytes(bool tc) { return tc ? kWbufBytesTc : kWbufBytesSimt; }
+
+struct WeightStage {
+  const char* gblob;   // the blob in global memory
+  char* smem_blob;     // shared copy: whole blob (resident) or the vector region (streamed)
+  char* wbuf;          // streamed: stage buffer
+  uint64_t* bar;       // streamed: TMA completion barrier
+  uint32_t phase;
+  int streamed;
+  int busy;            // streamed: MMAs reading wbuf issued and not yet waited for
+};
+
+// gemm_wait for GEMMs issued through gemm_weights
+template <bool TC>
+__device__ __forceinline__ void gemm_weights_wait(TileAcc<TC>& acc, WeightStage& ws) {
+  gemm_wait<TC>(acc);
+  ws.busy = 0;
+}
+
+// D[128 x n] (+)= A[128 x k] * W^T with W the image at byte offset w_off of the blob.
+// All threads call (uniform control flow).  Completion is observed with gemm_wait().
+template <bool TC>
+__device__ __forceinline__ void gemm_weights(TileAcc<TC>& acc, WeightStage& ws, const void* a_tile,
+                                             int w_off, int k, int n, int acc_col, bool accumulate) {
+  if (!ws.streamed) {
+    gemm_step<TC>(acc, a_tile, ws.smem_blob + w_off, k, n, acc_col, accumulate);
+    return;
+  }
+  const int kb_total = k / kKBlock;
+  int kb_chunk = wbuf_bytes(TC) / (n * kKBlockBytes);
+  if (kb_chunk > kb_total) kb_chunk = kb_total;
+  for (int kb0 = 0; kb0 < kb_total; kb0 += kb_chunk) {
+    const int nkb = kb_total - kb0 < kb_chunk ? kb_total - kb0 : kb_chunk;
+    if (ws.busy) gemm_weights_wait<TC>(acc, ws);   // earlier MMAs have finished reading wbuf
+    __syncthreads();                      // FFMA mode: every thread is done with wbuf
+    if (threadIdx.x == 0) {
+      const int bytes = nkb * n * kKBlockBytes;
+      mbar_arrive_expect_tx(ws.bar, (uint32_t)bytes);
+      const char* src = ws.gblob + w_off + (long)kb0 * n * kKBlockBytes;
+      for (int off = 0; off < bytes; off += 32768)
+        tma_bulk_g2s(ws.wbuf + off, src + off, (uint32_t)(bytes - off < 32768 ? bytes - off : 32768), ws.bar);
+    }
+    mbar_wait(ws.bar, ws.phase);
+    ws.phase ^= 1u;
+    gemm_step<TC>(acc, reinterpret_cast<const char*>(a_tile) + kb0 * kTileRows * kKBlockBytes, ws.wbuf,
+                  nkb * kKBlock, n, acc_col, accumulate || kb0 > 0);
+    ws.busy = 1;
   }
 }
 
@@ -182,14 +244,14 @@ __device__ __forceinline__ void row_ln_stats(const TileAcc<TC>& acc, int col, in
 // Returns the accumulator column where the last Linear's output (bias not yet added) starts.
 // `w` = accumulator region width, `region` = region used by layer 0.  All threads call.
 template <bool TC>
-__device__ __forceinline__ int mlp_run_rest(TileAcc<TC>& acc, char* hid, const char* smem_blob,
+__device__ __forceinline__ int mlp_run_rest(TileAcc<TC>& acc, WeightStage& ws, char* hid,
                                             const SgnnMlp& m, int w, int region) {
-  const float* blob_f = reinterpret_cast<const float*>(smem_blob);
+  const float* blob_f = reinterpret_cast<const float*>(ws.smem_blob);
   for (int l = 1; l < m.n_hidden; ++l) {
     a_tile_publish<TC>();
     region ^= 1;
-    gemm_step<TC>(acc, hid, smem_blob + m.w_off[l], m.hidden, m.hidden, region * w, false);
-    gemm_wait<TC>(acc);
+    gemm_weights<TC>(acc, ws, hid, m.w_off[l], m.hidden, m.hidden, region * w, false);
+    gemm_weights_wait<TC>(acc, ws);
     const float* b = blob_f + m.b_off[l];
     for (int c = 0; c < m.hidden; c += 32) {
       float v[32];
@@ -202,8 +264,8 @@ __device__ __forceinline__ int mlp_run_rest(TileAcc<TC>& acc, char* hid, const c
   a_tile_publish<TC>();
   region ^= 1;
   const int n_out = (m.out + 15) & ~15;      // UMMA N granularity at M = 128
-  gemm_step<TC>(acc, hid, smem_blob + m.w_off[m.n_hidden], m.hidden, n_out, region * w, false);
-  gemm_wait<TC>(acc);
+  gemm_weights<TC>(acc, ws, hid, m.w_off[m.n_hidden], m.hidden, n_out, region * w, false);
+  gemm_weights_wait<TC>(acc, ws);
   return region * w;
 }
 
@@ -285,6 +347,32 @@ __device__ __forceinline__ void acc_teardown(TileAcc<TC>& acc) {
     __syncthreads();
     if (threadIdx.x < 32) tmem_dealloc(acc.tmem_base, (uint32_t)acc.acc_cols);
   }
+}
+
+// Stage the blob (resident: all of it; streamed: the vector region) and describe it in `ws`.
+// Called by all threads before acc_setup's barrier; wait with mbar_wait(bar_w, 0) afterwards.
+__device__ __forceinline__ void weights_setup(WeightStage& ws, const void* gblob, int blob_bytes,
+                                              char* smem_blob, char* wbuf, uint64_t* bar_w,
+                                              uint64_t* bar_stream, int streamed) {
+  ws.gblob = reinterpret_cast<const char*>(gblob);
+  ws.smem_blob = smem_blob;
+  ws.wbuf = wbuf;
+  ws.bar = bar_stream;
+  ws.phase = 0;
+  ws.streamed = streamed;
+  ws.busy = 0;
+  if (threadIdx.x == 0) {
+    mbar_init(bar_w, 1);
+    mbar_init(bar_stream, 1);
+    mbar_fence_init();
+    int bytes = blob_bytes;
+    if (streamed && bytes > kVecRegionBytes) bytes = kVecRegionBytes;
+    tma_load_span(smem_blob, ws.gblob, bytes, bar_w);
+  }
+}
+// shared-memory bytes taken by the blob / the stage buffer
+__host__ __device__ inline int blob_smem_bytes(int blob_bytes, bool streamed) {
+  return streamed ? kVecRegionBytes : blob_bytes;
 }
 
 // dynamic shared memory base, aligned to 1024 bytes (SWIZZLE_128B atoms)

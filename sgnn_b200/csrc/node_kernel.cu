@@ -19,17 +19,17 @@
 namespace sgnn {
 
 struct NodeMisc {
-  uint64_t bar_w, bar_mma;
+  uint64_t bar_w, bar_mma, bar_stream;
   uint32_t tmem_slot;
   int pad;
 };
 
 struct NodeSmem {
-  int a, misc, simt, acc_cols, total;
+  int wbuf, a, misc, simt, acc_cols, total;
 };
 __host__ __device__ inline int imax(int a, int b) { return a > b ? a : b; }
 
-__host__ __device__ inline NodeSmem node_smem(const SgnnNodeParams& p, bool tc) {
+__host__ __device__ inline NodeSmem node_smem(const SgnnNodeParams& p, bool tc, bool streamed) {
   NodeSmem s;
   int ka = p.k_pad, wacc = 32;
   if (p.has_mlp) {
@@ -42,12 +42,18 @@ __host__ __device__ inline NodeSmem node_smem(const SgnnNodeParams& p, bool tc) 
     ka = imax(ka, p.dec.hidden);
     cols = imax(cols, 2 * p.dec.hidden);
   }
+  if (!tc) cols = (cols + 1) / 2;      // FFMA mode: one live region (columns wrap), P and Q in turn
   s.acc_cols = pow2_cols(cols);
-  s.a = align_up(p.blob_bytes, 1024);
+  s.wbuf = align_up(blob_smem_bytes(p.blob_bytes, streamed), 1024);
+  s.a = s.wbuf + (streamed ? wbuf_bytes(tc) : 0);
   s.misc = s.a + kTileRows * ka * 4;
   s.simt = align_up(s.misc + (int)sizeof(NodeMisc), 1024);
   s.total = s.simt + (tc ? 0 : kTileRows * s.acc_cols * 4) + 1024;
   return s;
+}
+
+__host__ inline bool node_streamed(const SgnnNodeParams& p, bool tc) {
+  return node_smem(p, tc, false).total > 227 * 1024;
 }
 
 template <bool TC>
@@ -123,9 +129,9 @@ __device__ __forceinline__ void prologue_rows(const SgnnNodeParams& p, char* a_t
 }
 
 template <bool TC>
-__global__ void __launch_bounds__(kThreads) node_kernel(const SgnnNodeParams p) {
+__global__ void __launch_bounds__(kThreads) node_kernel(const SgnnNodeParams p, const int streamed) {
   char* smem = smem_base_1024();
-  const NodeSmem L = node_smem(p, TC);
+  const NodeSmem L = node_smem(p, TC, streamed != 0);
   const float* blob_f = reinterpret_cast<const float*>(smem);
   char* a_tile = smem + L.a;
   NodeMisc* misc = reinterpret_cast<NodeMisc*>(smem + L.misc);
@@ -133,11 +139,8 @@ __global__ void __launch_bounds__(kThreads) node_kernel(const SgnnNodeParams p) 
   const int n_tiles = (p.n_rows + kTileRows - 1) / kTileRows;
   if ((int)blockIdx.x >= n_tiles) return;
 
-  if (tid == 0) {
-    mbar_init(&misc->bar_w, 1);
-    mbar_fence_init();
-    tma_load_span(smem, reinterpret_cast<const char*>(p.blob), p.blob_bytes, &misc->bar_w);
-  }
+  WeightStage ws;
+  weights_setup(ws, p.blob, p.blob_bytes, smem, smem + L.wbuf, &misc->bar_w, &misc->bar_stream, streamed);
   TileAcc<TC> acc;
   acc_setup<TC>(acc, L.acc_cols, &misc->bar_mma, &misc->tmem_slot, reinterpret_cast<float*>(smem + L.simt));
   mbar_wait(&misc->bar_w, 0);
@@ -157,8 +160,8 @@ __global__ void __launch_bounds__(kThreads) node_kernel(const SgnnNodeParams p) 
     if (p.has_mlp) {
       const int hidden = p.mlp.hidden, out = p.mlp.out;
       a_tile_publish<TC>();
-      gemm_step<TC>(acc, a_tile, smem + p.mlp.w_off[0], p.k_pad, hidden, 0, false);
-      gemm_wait<TC>(acc);
+      gemm_weights<TC>(acc, ws, a_tile, p.mlp.w_off[0], p.k_pad, hidden, 0, false);
+      gemm_weights_wait<TC>(acc, ws);
       {
         const float* b = blob_f + p.mlp.b_off[0];
         for (int c = 0; c < hidden; c += 32) {
@@ -169,7 +172,7 @@ __global__ void __launch_bounds__(kThreads) node_kernel(const SgnnNodeParams p) 
           a_tile_store32<TC>(a_tile, c, v);
         }
       }
-      const int acc_col = mlp_run_rest<TC>(acc, a_tile, smem, p.mlp, w, 0);
+      const int acc_col = mlp_run_rest<TC>(acc, ws, a_tile, p.mlp, w, 0);
       float mean = 0.f, rstd = 1.f;
       if (p.mlp.has_ln) row_ln_stats<TC>(acc, acc_col, out, blob_f + p.mlp.b_off[p.mlp.n_hidden], mean, rstd);
       for (int c = 0; c < out; c += 32) {
@@ -198,21 +201,30 @@ __global__ void __launch_bounds__(kThreads) node_kernel(const SgnnNodeParams p) 
     if (p.tail == SGNN_TAIL_PQ) {
       const int hq = p.pq_hidden;
       a_tile_publish<TC>();
-      gemm_step<TC>(acc, a_tile, smem + p.wp_off, x_width, hq, 0, false);
-      gemm_step<TC>(acc, a_tile, smem + p.wq_off, x_width, hq, hq, false);
-      gemm_wait<TC>(acc);
+      if constexpr (TC) {
+        gemm_weights<TC>(acc, ws, a_tile, p.wp_off, x_width, hq, 0, false);
+        gemm_weights<TC>(acc, ws, a_tile, p.wq_off, x_width, hq, hq, false);
+        gemm_weights_wait<TC>(acc, ws);
+      }
       const float* b1 = blob_f + p.pq_bias_off;
-      for (int c = 0; c < 2 * hq; c += 32) {
-        float v[32];
-        acc_load32<TC>(acc, c, v);
-        if (c < hq) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] += b1[c + j];
+      for (int half = 0; half < 2; ++half) {
+        if constexpr (!TC) {      // one accumulator region: P, then Q
+          gemm_weights<TC>(acc, ws, a_tile, half ? p.wq_off : p.wp_off, x_width, hq, 0, false);
+          gemm_weights_wait<TC>(acc, ws);
         }
-        if (valid) {
-          float4* dst = reinterpret_cast<float4*>(p.pq_out + i * 2 * hq + c);
+        const int base = TC ? half * hq : 0;
+        for (int c = 0; c < hq; c += 32) {
+          float v[32];
+          acc_load32<TC>(acc, base + c, v);
+          if (half == 0) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) dst[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            for (int j = 0; j < 32; ++j) v[j] += b1[c + j];
+          }
+          if (valid) {
+            float4* dst = reinterpret_cast<float4*>(p.pq_out + i * 2 * hq + half * hq + c);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) dst[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          }
         }
       }
     } else if (p.tail == SGNN_TAIL_DECODE) {
@@ -221,8 +233,8 @@ __global__ void __launch_bounds__(kThreads) node_kernel(const SgnnNodeParams p) 
       for (int l = 0; l < p.dec.n_hidden; ++l) {
         a_tile_publish<TC>();
         region ^= 1;
-        gemm_step<TC>(acc, a_tile, smem + p.dec.w_off[l], kin, hd, region * hd, false);
-        gemm_wait<TC>(acc);
+        gemm_weights<TC>(acc, ws, a_tile, p.dec.w_off[l], kin, hd, region * hd, false);
+        gemm_weights_wait<TC>(acc, ws);
         kin = hd;
         if (l + 1 < p.dec.n_hidden) {
           const float* b = blob_f + p.dec.b_off[l];
@@ -281,7 +293,7 @@ __global__ void __launch_bounds__(kThreads) node_kernel(const SgnnNodeParams p) 
 using namespace sgnn;
 
 extern "C" size_t sgnn_node_smem_bytes(const SgnnNodeParams* p, int tc) {
-  return (size_t)node_smem(*p, tc != 0).total;
+  return (size_t)node_smem(*p, tc != 0, node_streamed(*p, tc != 0)).total;
 }
 
 extern "C" int sgnn_node_fwd(const SgnnNodeParams* p, int use_tensor_cores, int grid, void* stream) {
@@ -304,7 +316,9 @@ extern "C" int sgnn_node_fwd(const SgnnNodeParams* p, int use_tensor_cores, int 
   }
   SGNN_CHECK_ARG(p->blob_bytes % 16 == 0, "node: blob size must be a multiple of 16");
   if (p->n_rows <= 0) return SGNN_OK;
-  const NodeSmem L = node_smem(*p, use_tensor_cores);
+  const int streamed = node_streamed(*p, use_tensor_cores);
+  const NodeSmem L = node_smem(*p, use_tensor_cores, streamed);
+  SGNN_CHECK_ARG(p->blob_bytes >= SGNN_VEC_REGION_BYTES, "node: blob lacks the vector region");
   SGNN_CHECK_ARG(L.acc_cols <= 512, "node: needs %d TMEM columns (> 512)", L.acc_cols);
   SGNN_CHECK_ARG(L.total <= 227 * 1024, "node: needs %d bytes of shared memory (> 227 KB); layer shape unsupported", L.total);
   const int n_tiles = sgnn_ceil_div(p->n_rows, kTileRows);
@@ -312,10 +326,10 @@ extern "C" int sgnn_node_fwd(const SgnnNodeParams* p, int use_tensor_cores, int 
   if (grid < 1) grid = 1;
   if (use_tensor_cores) {
     SGNN_ENSURE_SMEM(node_kernel<true>, L.total);
-    node_kernel<true><<<grid, kThreads, L.total, (cudaStream_t)stream>>>(*p);
+    node_kernel<true><<<grid, kThreads, L.total, (cudaStream_t)stream>>>(*p, streamed);
   } else {
     SGNN_ENSURE_SMEM(node_kernel<false>, L.total);
-    node_kernel<false><<<grid, kThreads, L.total, (cudaStream_t)stream>>>(*p);
+    node_kernel<false><<<grid, kThreads, L.total, (cudaStream_t)stream>>>(*p, streamed);
   }
   SGNN_LAUNCH_CHECK();
   return SGNN_OK;

@@ -9,6 +9,10 @@
 #include <stdint.h>
 
 #define SGNN_MAX_HIDDEN 3   /* hidden layers per MLP (reference uses 1 and 2) */
+/* Blob layout: bytes [0, SGNN_VEC_REGION_BYTES) hold the fp32 vectors, the GEMM images follow at
+ * 1024-byte aligned offsets.  Kernels whose images do not fit in shared memory keep only the
+ * vector region resident and stream the images per GEMM. */
+#define SGNN_VEC_REGION_BYTES 8192
 
 #ifdef __cplusplus
 extern "C" {

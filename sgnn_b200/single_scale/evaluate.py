@@ -66,7 +66,7 @@ class RolloutPlan:
             return
         ver = params_version(self.sim.parameters())
         if self.graph is None or self.version != ver:
-            self.sim._engine(self.n, self.traj.device)             # (re)pack weights outside capture
+            self.sim._prepare(self.n, self.traj.device)            # (re)pack weights outside capture
             saved = self.traj[:, self.s].clone()
             self.launch_steps(0, 1)                                # warm-up: func attributes, lazy init
             torch.cuda.synchronize()
@@ -84,7 +84,7 @@ class RolloutPlan:
 
 def get_plan(sim, n, t, s, dim, mode, device, use_graph=True) -> RolloutPlan:
     cache = sim.__dict__.setdefault("_rollout_plans", {})
-    key = (n, t, s, dim, mode, str(device), use_graph)
+    key = (n, t, s, dim, mode, str(device), use_graph, getattr(sim, "_graph_token", 0))
     if key not in cache:
         cache[key] = RolloutPlan(sim, n, t, s, dim, mode, device, use_graph)
     return cache[key]

@@ -92,6 +92,10 @@ class LearnedSimulator(nn.Module):
             self._engines[key] = hit
         return hit[1], hit[2]
 
+    def _prepare(self, n: int, device):
+        """Build / refresh kernel plans outside a CUDA-graph capture."""
+        self._engine(n, device)
+
     def _check_positions(self, position_sequence):
         if len(position_sequence.shape) != 3:
             raise ValueError(f"Expected position_sequence to have 3 dimensions, got {len(position_sequence.shape)}")

@@ -1,0 +1,188 @@
+"""GPU parity of the multi-scale path (MultiScaleGraph / MultiScaleGNN / MultiScaleSimulator /
+rollout driver) against golden fixtures generated from the unmodified reference, and against the
+reference's own golden vectors (sgnn/multi_scale/test/test_multi_scale_graph.py:119-140,325-348).
+
+Tolerances as in tests/test_single_scale_gpu.py: fp32 mode 2e-4 on the network output, tf32 mode
+3e-2; positions scale with acc_std.  Edge sets, hierarchy indices, node features: bit-exact.
+"""
+import numpy as np
+import pytest
+import torch
+
+from tests.util import Fixture
+
+pytestmark = pytest.mark.gpu
+
+TOL = {"fp32": 2e-4, "tf32": 3e-2}
+FIXTURES = ["multi_ref_fixture", "multi_h128"]
+
+
+def graph_of(f, device="cuda"):
+    hier = {}
+    s = 0
+    while f"hier/{s}/sampling_indices" in f.z.files:
+        idx = f.t(f"hier/{s}/sampling_indices")
+        hier[s] = {"sampling_indices": idx, "spacing": float(f[f"hier/{s}/spacing"][0]),
+                   "num_particles": idx.numel()}
+        s += 1
+    return {"graph_hierarchy": hier, "grid2mesh_edges": f.t("g2m").to(device),
+            "mesh2mesh_edges": f.t("m2m").to(device), "mesh2grid_edges": f.t("m2g").to(device)}
+
+
+def make_sim(f, precision):
+    from sgnn_b200.multi_scale import MultiScaleSimulator
+    S, H, nedge_out, L, nmlp, num_scales, window, ntypes, emb, nsteps = f["meta"].tolist()
+    mult = float(f["mult"][0])
+    nnode_in = (S - 1) * 2 + 1 + (emb if ntypes > 1 else 0)
+    sim = MultiScaleSimulator(2, nnode_in, 3, nedge_out, H, L, nmlp, f.stats(), ntypes, emb,
+                              num_scales=num_scales, window_size=window, radius_multiplier=mult,
+                              device="cuda", precision=precision)
+    sim.load_state_dict(f.state_dict())
+    return sim.cuda().eval(), S, nsteps, (num_scales, window, mult)
+
+
+@pytest.mark.parametrize("name", FIXTURES)
+def test_graph_matches_reference(name):
+    from sgnn_b200.multi_scale import MultiScaleConfig, MultiScaleGraph
+    f = Fixture(name)
+    _, _, _, (num_scales, window, mult) = make_sim(f, "fp32")
+    pos0 = f.t("positions")[:, 0].cuda()
+    out = MultiScaleGraph(MultiScaleConfig(num_scales, window, mult)).create_all_edges(pos0)
+    for s, h in out["graph_hierarchy"].items():
+        assert torch.equal(h["sampling_indices"].cpu(), f.t(f"hier/{s}/sampling_indices"))
+        assert h["spacing"] == float(f[f"hier/{s}/spacing"][0])
+    for key, short in (("grid2mesh_edges", "g2m"), ("mesh2mesh_edges", "m2m"), ("mesh2grid_edges", "m2g")):
+        assert out[key].dtype == torch.int64 and out[key].is_cuda
+        assert torch.equal(out[key].cpu(), f.t(short)), key
+    # CPU input: computed on the GPU, returned on the caller's device
+    out_cpu = MultiScaleGraph(MultiScaleConfig(num_scales, window, mult)).create_all_edges(pos0.cpu())
+    assert not out_cpu["mesh2mesh_edges"].is_cuda
+    assert torch.equal(out_cpu["mesh2mesh_edges"], f.t("m2m"))
+
+
+def test_reference_golden_hierarchy_vectors():
+    """4x4 unit lattice, window 2 -> [0,2,8,10], [0]; 16x16, 5 scales -> 256/64/16/4/1."""
+    from sgnn_b200.multi_scale import MultiScaleConfig, MultiScaleGraph
+    x = torch.arange(4, dtype=torch.float32)
+    xx, yy = torch.meshgrid(x, x, indexing="ij")
+    pos = torch.stack([xx.flatten(), yy.flatten()], 1).cuda()
+    g = MultiScaleGraph(MultiScaleConfig(num_scales=3, window_size=2))
+    h = g.build_hierarchy(pos)
+    assert h[0]["sampling_indices"].tolist() == list(range(16))
+    assert h[1]["sampling_indices"].tolist() == [0, 2, 8, 10]
+    assert h[2]["sampling_indices"].tolist() == [0]
+    assert [h[s]["spacing"] for s in range(3)] == [0.5, 1.0, 2.0]
+    x = torch.arange(16, dtype=torch.float32) * 0.5
+    xx, yy = torch.meshgrid(x, x, indexing="ij")
+    pos = torch.stack([xx.flatten(), yy.flatten()], 1).cuda()
+    g = MultiScaleGraph(MultiScaleConfig(num_scales=5, window_size=2))
+    out = g.create_all_edges(pos)
+    assert [out["graph_hierarchy"][s]["num_particles"] for s in range(5)] == [256, 64, 16, 4, 1]
+    g2m, m2g = out["grid2mesh_edges"], out["mesh2grid_edges"]
+    assert g2m.shape == m2g.shape                                   # symmetry (:183-208)
+    n = 256
+    for key in ("grid2mesh_edges", "mesh2mesh_edges", "mesh2grid_edges"):
+        assert int(out[key].min()) >= 0 and int(out[key].max()) < n
+    with pytest.raises(ValueError):
+        MultiScaleConfig(num_scales=1)
+
+
+@pytest.mark.parametrize("name", FIXTURES)
+@pytest.mark.parametrize("precision", ["fp32", "tf32"])
+def test_features(name, precision):
+    f = Fixture(name)
+    sim, S, _, _ = make_sim(f, precision)
+    with pytest.raises(ValueError):
+        sim.predict_positions(f.t("positions")[:, :S].cuda(), None, f.t("particle_types").cuda())
+    sim.set_static_graph(graph_of(f))
+    pos, types = f.t("positions").cuda(), f.t("particle_types").cuda()
+    nf, ei, ef = sim._encoder_preprocessor(pos[:, :S], torch.tensor([pos.shape[0]]), types)
+    assert torch.equal(nf.cpu(), f.t("node_features_f32"))
+    for k in ("g2m", "m2m", "m2g"):
+        assert torch.equal(ei[k].cpu(), f.t(k))
+        assert torch.allclose(ef[k].cpu(), f.t(f"edge_features_f32/{k}"), atol=1e-6, rtol=1e-6), k
+
+
+@pytest.mark.parametrize("name", FIXTURES)
+@pytest.mark.parametrize("precision", ["fp32", "tf32"])
+def test_rollout_matches_reference(name, precision):
+    f = Fixture(name)
+    sim, S, nsteps, _ = make_sim(f, precision)
+    sim.set_static_graph(graph_of(f, "cpu"))            # CPU edge tensors are accepted, as in the loaders
+    pos, types = f.t("positions").cuda(), f.t("particle_types").cuda()
+    n = pos.shape[0]
+    acc_std = f.stats()["acceleration"]["std"].max().item()
+    ref32, ref64 = f.t("rollout_f32"), f.t("rollout_f64")
+    gap = (ref32.double() - ref64).abs().max().item()
+    cur = pos[:, :S].contiguous()
+    worst = 0.0
+    for step in range(nsteps):
+        nxt, strain = sim.predict_positions(cur, torch.tensor([n]), types)
+        assert nxt.shape == (n, 2) and strain.shape == (n,)
+        err = (nxt.cpu().double() - ref64[step]).abs().max().item()
+        worst = max(worst, err)
+        tol = TOL[precision] * acc_std * (step + 1) * 3 + 4 * gap
+        assert err <= tol, (step, err, tol)
+        serr = (strain.cpu() - f.t("rollout_strain_f32")[step]).abs().max().item()
+        assert serr <= TOL[precision] * (step + 1) * 3, (step, serr)
+        cur = torch.cat([cur[:, 1:], nxt[:, None, :]], dim=1)
+    print(f"{name} {precision}: max |pos - ref64| = {worst:.3e} (gap {gap:.3e}, acc_std {acc_std:.3e})")
+
+
+@pytest.mark.parametrize("precision", ["fp32", "tf32"])
+def test_gnn_module_forward_unsorted_edges(precision):
+    """MultiScaleGNN.forward on explicit features; shuffled / duplicated edge lists
+    (test_multi_scale_gnn.py:16-71) give the oracle's answer."""
+    from oracle import sgnn_oracle_ms as OM
+    from sgnn_b200.single_scale import graph_network as G
+    f = Fixture("multi_ref_fixture")
+    sim, S, _, _ = make_sim(f, precision)
+    G.set_default_precision(precision)
+    try:
+        gnn = sim._multi_scale_gnn
+        g = torch.Generator().manual_seed(3)
+        n = 25
+        x = torch.randn(n, 27, generator=g)
+        def rnd(e):
+            ei = torch.randint(0, n, (2, e), generator=g)
+            return ei, torch.randn(e, 3, generator=g)
+        (a, fa), (b, fb), (c, fc) = rnd(40), rnd(60), rnd(1)
+        b = torch.cat([b, b[:, :7]], 1); fb = torch.cat([fb, fb[:7]], 0)      # duplicates
+        out = gnn(x.cuda(), a.cuda(), fa.cuda(), b.cuda(), fb.cuda(), c.cuda(), fc.cuda(), None)
+        want = OM.multi_scale_gnn(f.state_dict(), "_multi_scale_gnn.", x, a, fa, b, fb, c, fc)
+        assert out.shape == (n, 3) and torch.isfinite(out).all()
+        err = (out.cpu() - want).abs().max().item()
+        print(f"MultiScaleGNN module forward {precision}: max abs err {err:.3e}")
+        assert err <= TOL[precision]
+        # empty edge set
+        e0 = torch.empty(2, 0, dtype=torch.long)
+        out0 = gnn(x.cuda(), a.cuda(), fa.cuda(), e0.cuda(), torch.empty(0, 3).cuda(), c.cuda(), fc.cuda(), None)
+        want0 = OM.multi_scale_gnn(f.state_dict(), "_multi_scale_gnn.", x, a, fa, e0, torch.empty(0, 3), c, fc)
+        assert (out0.cpu() - want0).abs().max().item() <= TOL[precision]
+    finally:
+        G.set_default_precision("tf32")
+
+
+@pytest.mark.parametrize("precision", ["fp32", "tf32"])
+def test_rollout_driver(precision):
+    from sgnn_b200.multi_scale.multi_scale_evaluate import evaluate_multi_scale_rollout
+    f = Fixture("multi_h128")
+    sim, S, nsteps, _ = make_sim(f, precision)
+    sim.set_static_graph(graph_of(f))
+    pos, types = f.t("positions").cuda(), f.t("particle_types").cuda()
+    n = pos.shape[0]
+    strains = torch.zeros(pos.shape[1], n).cuda()
+    a = evaluate_multi_scale_rollout(sim, pos, types, torch.tensor([n]), strains, nsteps, 2, "cuda", S)
+    b = evaluate_multi_scale_rollout(sim, pos, types, torch.tensor([n]), strains, nsteps, 2, "cuda", S,
+                                     use_cuda_graph=False)
+    assert np.array_equal(a["predicted_rollout"], b["predicted_rollout"])
+    acc_std = f.stats()["acceleration"]["std"].max().item()
+    ref64 = f["rollout_f64"]
+    for step in range(nsteps):
+        err = np.abs(a["predicted_rollout"][step] - ref64[step]).max()
+        assert err <= TOL[precision] * acc_std * (step + 1) * 3 + 2e-4, (step, err)
+    assert a["rmse_position"].shape == (nsteps,) and a["predicted_strain"].shape == (nsteps, n)
+    # save / load round trip keeps the reference's key names
+    import io
+    keys = set(sim.state_dict().keys())
+    assert keys == set(f.state_dict().keys())
