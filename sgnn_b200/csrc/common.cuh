@@ -69,9 +69,10 @@ constexpr int kKBlockBytes = 128;
 // round-to-nearest (ties away) to TF32, kept in an fp32 container. The tensor core ignores
 // the 13 low mantissa bits; rounding first halves the representation error and unbiases it.
 __device__ __forceinline__ float to_tf32(float x) {
-  uint32_t u;
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
-  return __uint_as_float(u);
+  // cvt.rna.tf32.f32 expands to ~5 instructions on sm_100; for every non-NaN input it equals
+  // "add half an ulp of the 10-bit mantissa to the magnitude, clear the 13 low bits" (carries
+  // into the exponent round up to the next binade, the largest finite values round to inf).
+  return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
 }
 
 // ---- swizzled K-major tile addressing -------------------------------------------------
@@ -202,6 +203,53 @@ __device__ __forceinline__ void umma_gemm_tf32(uint32_t tmem_d, uint32_t a_base,
       acc = 1u;
     }
   }
+}
+
+// D[tmem] (+)= A[tmem] * B[smem]^T, K = 8 (tf32).  A: 128 lanes x 8 consecutive 32-bit columns.
+__device__ __forceinline__ void umma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b,
+                                             uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// D[128 x n] = A[128 x k] * W[n x k]^T with A in TMEM (columns tmem_a .. tmem_a + k)
+__device__ __forceinline__ void umma_gemm_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint32_t w_base,
+                                                  int k, int n) {
+  const uint32_t idesc = umma_idesc_tf32(kTileRows, n);
+  uint32_t acc = 0u;
+  for (int kb = 0; kb < k / kKBlock; ++kb) {
+    const uint32_t w_kb = w_base + kb * n * kKBlockBytes;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      umma_tf32_ts(tmem_d, tmem_a + kb * kKBlock + j * 8, umma_desc_sw128(w_kb + j * 32), idesc, acc);
+      acc = 1u;
+    }
+  }
+}
+// registers -> TMEM: this warp's 32 lanes x 32 consecutive 32-bit columns starting at `taddr`
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const float* v) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+      "r"(__float_as_uint(v[0])), "r"(__float_as_uint(v[1])), "r"(__float_as_uint(v[2])),
+      "r"(__float_as_uint(v[3])), "r"(__float_as_uint(v[4])), "r"(__float_as_uint(v[5])),
+      "r"(__float_as_uint(v[6])), "r"(__float_as_uint(v[7])), "r"(__float_as_uint(v[8])),
+      "r"(__float_as_uint(v[9])), "r"(__float_as_uint(v[10])), "r"(__float_as_uint(v[11])),
+      "r"(__float_as_uint(v[12])), "r"(__float_as_uint(v[13])), "r"(__float_as_uint(v[14])),
+      "r"(__float_as_uint(v[15])), "r"(__float_as_uint(v[16])), "r"(__float_as_uint(v[17])),
+      "r"(__float_as_uint(v[18])), "r"(__float_as_uint(v[19])), "r"(__float_as_uint(v[20])),
+      "r"(__float_as_uint(v[21])), "r"(__float_as_uint(v[22])), "r"(__float_as_uint(v[23])),
+      "r"(__float_as_uint(v[24])), "r"(__float_as_uint(v[25])), "r"(__float_as_uint(v[26])),
+      "r"(__float_as_uint(v[27])), "r"(__float_as_uint(v[28])), "r"(__float_as_uint(v[29])),
+      "r"(__float_as_uint(v[30])), "r"(__float_as_uint(v[31]))
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() {
+  asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
 }
 
 // TMEM -> registers: this warp's 32 lanes x 32 consecutive fp32 columns starting at `taddr`

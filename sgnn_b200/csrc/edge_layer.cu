@@ -14,6 +14,8 @@
 //
 // Algorithmic HBM bytes per edge: 4*he (e0) + 8 (src,tgt) ; per node 4*out (agg) ; P/Q rows
 // are gathers that mostly hit L2 (counted once per node: 8*hidden).
+#include <stdlib.h>
+
 #include "mlp_tile.cuh"
 #include "params.h"
 
@@ -258,6 +260,8 @@ extern "C" size_t sgnn_edge_layer_smem_bytes(int blob_bytes, int he, int hidden,
   return (size_t)edge_layer_smem(blob_bytes, he, hidden, out, tc != 0, st).total;
 }
 
+int sgnn_edge_layer_fast_try(const SgnnEdgeLayerParams* p, void* stream);   // edge_layer_fast.cu
+
 extern "C" int sgnn_edge_layer_fwd(const SgnnEdgeLayerParams* p, int use_tensor_cores, int grid,
                                    void* stream) {
   int rc = check_mlp(p->mlp, "edge_layer");
@@ -268,6 +272,10 @@ extern "C" int sgnn_edge_layer_fwd(const SgnnEdgeLayerParams* p, int use_tensor_
   SGNN_CHECK_ARG(p->blob_bytes % 16 == 0, "edge_layer: blob size must be a multiple of 16");
   SGNN_CHECK_ARG(p->mlp.has_ln, "edge_layer: the edge MLP ends in a LayerNorm in the reference");
   if (p->max_tiles <= 0 || p->n_nodes <= 0) return SGNN_OK;
+  if (use_tensor_cores && !getenv("SGNN_EDGE_GENERIC")) {     // throughput kernel where instantiated
+    const int r = sgnn_edge_layer_fast_try(p, stream);
+    if (r != 0) return r < 0 ? r : SGNN_OK;
+  }
   const int streamed = edge_layer_streamed(p->blob_bytes, p->he, p->mlp.hidden, p->mlp.out, use_tensor_cores);
   const int smem = edge_layer_smem(p->blob_bytes, p->he, p->mlp.hidden, p->mlp.out, use_tensor_cores, streamed).total;
   SGNN_CHECK_ARG(smem <= 227 * 1024, "edge_layer: needs %d bytes of shared memory (> 227 KB) even with "

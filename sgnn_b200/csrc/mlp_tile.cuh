@@ -218,24 +218,26 @@ __device__ __forceinline__ void a_tile_load_rows(void* a_tile, int col0, const f
 template <bool TC>
 __device__ __forceinline__ void row_ln_stats(const TileAcc<TC>& acc, int col, int n,
                                              const float* __restrict__ bias, float& mean, float& rstd) {
-  float s = 0.f;
+  // 4 interleaved partial sums (column j goes to accumulator j & 3), as in edge_layer_fast.cu
+  float s4[4] = {0.f, 0.f, 0.f, 0.f};
   for (int c = 0; c < n; c += 32) {
     float v[32];
     acc_load32<TC>(acc, col + c, v);
 #pragma unroll
-    for (int j = 0; j < 32; ++j) s += v[j] + bias[c + j];
+    for (int j = 0; j < 32; ++j) s4[j & 3] += v[j] + bias[c + j];
   }
-  mean = s / (float)n;
-  float q = 0.f;
+  mean = ((s4[0] + s4[1]) + (s4[2] + s4[3])) / (float)n;
+  float q4[4] = {0.f, 0.f, 0.f, 0.f};
   for (int c = 0; c < n; c += 32) {
     float v[32];
     acc_load32<TC>(acc, col + c, v);
 #pragma unroll
     for (int j = 0; j < 32; ++j) {
       const float d = v[j] + bias[c + j] - mean;
-      q = fmaf(d, d, q);
+      q4[j & 3] = fmaf(d, d, q4[j & 3]);
     }
   }
+  const float q = (q4[0] + q4[1]) + (q4[2] + q4[3]);
   rstd = 1.0f / sqrtf(q / (float)n + 1e-5f);   // IEEE sqrt and divide, as torch
 }
 
@@ -375,11 +377,12 @@ __host__ __device__ inline int blob_smem_bytes(int blob_bytes, bool streamed) {
   return streamed ? kVecRegionBytes : blob_bytes;
 }
 
-// dynamic shared memory base, aligned to 1024 bytes (SWIZZLE_128B atoms)
+// dynamic shared memory base, aligned to 1024 bytes (SWIZZLE_128B atoms).  Declared with the
+// alignment instead of rounding a generic pointer up, so the compiler keeps the shared address
+// space (LDS/STS instead of generic LD/ST).  None of the tile kernels has static shared memory.
 __device__ __forceinline__ char* smem_base_1024() {
-  extern __shared__ char sgnn_dyn_smem[];
-  uintptr_t p = reinterpret_cast<uintptr_t>(sgnn_dyn_smem);
-  return reinterpret_cast<char*>((p + 1023) & ~(uintptr_t)1023);
+  extern __shared__ __align__(1024) char sgnn_dyn_smem[];
+  return sgnn_dyn_smem;
 }
 
 }  // namespace sgnn

@@ -39,3 +39,13 @@ def test_gemm_tile_tf32(k, n):
         return ((x.view(torch.int32) + 0x1000) & ~0x1FFF).view(torch.float32)
     ref_t = (rt(a).double() @ rt(w).double().T).float()
     assert torch.allclose(d, ref_t, atol=3e-5 * k ** 0.5, rtol=1e-5)
+
+
+@pytest.mark.parametrize("k,n", [(32, 32), (64, 64), (128, 64), (64, 128), (128, 128)])
+def test_gemm_tile_tf32_a_in_tmem(k, n):
+    """A operand staged in tensor memory (tcgen05.st + tcgen05.mma with A from TMEM)."""
+    a, w, d = _run(k, n, 2)
+    def rt(x):
+        return ((x.view(torch.int32) + 0x1000) & ~0x1FFF).view(torch.float32)
+    ref_t = (rt(a).double() @ rt(w).double().T).float()
+    assert torch.allclose(d, ref_t, atol=3e-5 * k ** 0.5, rtol=1e-5)
