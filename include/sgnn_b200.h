@@ -63,6 +63,25 @@ int sgnn_edge_layer_fwd(const SgnnEdgeLayerParams* p, int use_tensor_cores, int 
 size_t sgnn_node_smem_bytes(const SgnnNodeParams* p, int tc);
 int sgnn_node_fwd(const SgnnNodeParams* p, int use_tensor_cores, int grid, void* stream);
 
+/* Training-path graph primitives (deterministic, no atomics) and stand-alone feature builders.
+ *   gather_add_rows : out[e] = P[tgt[e]] + Q[src[e]]   -- PyG propagate's index_select x2 feeding
+ *                     the x_i | x_j columns of edge_fn's first Linear (graph_network.py:173,197)
+ *   segment_sum_rows: out[i] = sum over CSR row i of m[perm ? perm[k] : k] -- propagate's
+ *                     scatter_add aggregate (graph_network.py:173); also the backward of the gathers
+ *   gather_rows     : out[e] = rows[idx[e]]             -- backward of segment_sum
+ *   node_features / edge_features: learned_simulator.py:257-312, multi_scale_simulator.py:173-238 */
+int sgnn_gather_add_rows(const float* P, long ldp, const float* Q, long ldq, const int* tgt,
+                         const int* src, int n_edges, int width, float* out, void* stream);
+int sgnn_segment_sum_rows(const float* m, const int* rowptr, const int* perm, int n_rows, int width,
+                          float* out, void* stream);
+int sgnn_gather_rows(const float* rows, long ld, const int* idx, int n_out, int width, float* out,
+                     void* stream);
+int sgnn_node_features(const float* pos_seq, long stride, int n, int seq_len, int dim,
+                       const float* vel_mean, const float* vel_std, float wall_offset, float wall_max,
+                       float wall_div, float* out, long ld_out, void* stream);
+int sgnn_edge_features(const float* pos, long stride, int dim, float radius, const int* src,
+                       const int* tgt, int n_edges, float* out, void* stream);
+
 /* self-test of the GEMM tile primitive (tests/test_gemm_tile_gpu.py)                        */
 int sgnn_debug_gemm(const float* a, const float* wimg, int k, int n, float* d, int tc, void* stream);
 

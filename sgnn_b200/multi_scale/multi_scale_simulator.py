@@ -189,6 +189,36 @@ class MultiScaleSimulator(nn.Module):
         self._step(seq, nparticles_per_example, particle_types, next_pos=next_pos, strain=strain)
         return next_pos, strain
 
+    def predict_accelerations(self, next_positions, position_sequence_noise, position_sequence,
+                              nparticles_per_example, particle_types):
+        """Training forward with autograd (reference :312-345); see sgnn_b200/train_ops.py."""
+        from .. import train_ops as T
+        self._validate_static_graph()
+        L.require_cuda(position_sequence, "position_sequence")
+        noisy = self._window((position_sequence + position_sequence_noise).detach())
+        n, s, dim = noisy.shape
+        dev = noisy.device
+        st = self._stats(dev)
+        rg, rc = self._radii()
+        csrs, _ = self._graph(n, dev)
+        tg = self.__dict__.get("_train_graphs")
+        if tg is None or tg[0] is not csrs:
+            tg = self.__dict__["_train_graphs"] = (csrs, [T.TrainGraph.from_csr(c) for c in csrs])
+        graphs = tg[1]
+        extra = self._particle_type_embedding(particle_types) if self._nparticle_types > 1 else None
+        nf = T.node_features(noisy, st["velocity"]["mean"], st["velocity"]["std"], rg, rg, extra)
+        last = noisy[0, s - 1]
+        efs = [T.edge_features(last, noisy.stride(0), dim, r, g) for r, g in zip((rg, rc, rg), graphs)]
+        g = self._multi_scale_gnn
+        blocks = [(g.g2m_block.edge_fn, g.g2m_block.node_fn, 0)]
+        blocks += [(b.edge_fn, b.node_fn, 1) for b in g.m2m_blocks]
+        blocks += [(g.m2g_block.edge_fn, g.m2g_block.node_fn, 2)]
+        pred = T.epd_forward(g.grid_node_encoder, [g.g2m_edge_encoder, g.m2m_edge_encoder, g.m2g_edge_encoder],
+                             blocks, g.prediction_head, nf, efs, graphs)
+        next_adj = next_positions + position_sequence_noise[:, -1]
+        target = self._inverse_decoder_postprocessor(next_adj, noisy)
+        return pred[:, :dim], target, pred[:, -1]
+
     def _decoder_postprocessor(self, normalized_acceleration, position_sequence):
         st = self._stats(normalized_acceleration.device)["acceleration"]
         acceleration = normalized_acceleration * st["std"] + st["mean"]

@@ -175,6 +175,35 @@ class LearnedSimulator(nn.Module):
         self._step(seq, nparticles_per_example, particle_types, next_pos=next_pos, strain=strain)
         return next_pos, strain
 
+    def predict_accelerations(self, next_positions, position_sequence_noise, position_sequence,
+                              nparticles_per_example, particle_types):
+        """Training forward (reference :440-491): noisy inputs -> graph on the noisy last frame
+        -> network with autograd -> (predicted normalised acceleration, target, predicted strain).
+        Graph and features come from the sm_100a kernels, the message-passing glue and its
+        backward from csrc/graph_ops.cu, GEMM/LayerNorm from cuBLAS/ATen (sgnn_b200/train_ops.py)."""
+        from .. import train_ops as T
+        self._check_positions(position_sequence)
+        noisy = self._window((position_sequence + position_sequence_noise).detach())
+        n, s, dim = noisy.shape
+        dev = noisy.device
+        st = self._stats(dev)
+        radius = float(self._connectivity_radius)
+        rg = self.__dict__.get("_train_rg")
+        if rg is None or rg.n != n or rg.csr.rowptr.device != dev:
+            rg = self.__dict__["_train_rg"] = RadiusGraph(n, MAX_NUM_NEIGHBORS, True, dev)
+        csr = rg.build(noisy[0, s - 1], noisy.stride(0), dim, example_ptr_of(nparticles_per_example, dev), radius)
+        graph = T.TrainGraph.from_csr(csr)
+        extra = self._particle_type_embedding(particle_types) if self._nparticle_types > 1 else None
+        nf = T.node_features(noisy, st["velocity"]["mean"], st["velocity"]["std"], radius, 1.0, extra)
+        ef = T.edge_features(noisy[0, s - 1], noisy.stride(0), dim, radius, graph)
+        epd = self._encode_process_decode
+        blocks = [(g.edge_fn, g.node_fn, 0) for g in epd._processor.gnn_stacks]
+        pred = T.epd_forward(epd._encoder.node_fn, [epd._encoder.edge_fn], blocks, epd._decoder.node_fn,
+                             nf, [ef], [graph])
+        next_adj = next_positions + position_sequence_noise[:, -1]
+        target = self._inverse_decoder_postprocessor(next_adj, noisy)
+        return pred[:, :dim], target, pred[:, -1]
+
     def _decoder_postprocessor(self, normalized_acceleration, position_sequence):
         """Euler integrator on explicit tensors (reference :381-411); the fused step applies the
         same arithmetic inside the decoder kernel."""

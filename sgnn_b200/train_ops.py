@@ -1,0 +1,183 @@
+"""Training path of the Encode-Process-Decode networks (forward WITH autograd + backward).
+
+Inference runs the fused tile kernels (engine.py).  Training needs the intermediate activations
+and their gradients, so it is laid out differently:
+
+  * the message-passing glue -- the x_i / x_j gathers, the sum-aggregation and their backward
+    passes (the reference's index_select x2 + scatter_add atomics inside PyG's propagate,
+    sgnn/single_scale/graph_network.py:173) -- runs on the deterministic CUDA kernels of
+    csrc/graph_ops.cu through torch.autograd.Function wrappers (no atomics anywhere: the backward of
+    the source gather is a segmented sum over a source-sorted permutation);
+  * the [E,3H] and [N,2H] concat buffers of the reference never exist: the first Linear of each
+    MLP is applied per column block (P = x W_a^T + b, Q = x W_b^T per NODE, e W_c^T per edge);
+  * neighbour search and the node/edge features come from the sm_100a kernels (no gradient flows
+    into positions, as in the reference);
+  * the dense GEMMs and LayerNorm use cuBLAS / ATen through torch on the very same nn.Linear /
+    nn.LayerNorm parameter objects, so autograd produces the parameter gradients and the
+    reference's optimizer code (Adam, train.py:199,271-273) runs unchanged.
+
+There is no CPU path: every entry raises on non-CUDA tensors.
+"""
+import ctypes as C
+from typing import List, Optional
+
+import torch
+import torch.nn.functional as F
+
+from . import _lib as L
+from .blob import linears_of
+
+
+class TrainGraph:
+    """Receiver-sorted edge list (int32) with E known on the host, plus -- built on first use --
+    the source-sorted permutation needed by the backward of the source gather."""
+
+    def __init__(self, rowptr: torch.Tensor, src: torch.Tensor, tgt: torch.Tensor, n_nodes: int,
+                 n_edges: int):
+        self.rowptr, self.n, self.e = rowptr, n_nodes, n_edges
+        self.src, self.tgt = src[:n_edges], tgt[:n_edges]
+        self._by_src = None
+
+    @staticmethod
+    def from_csr(csr) -> "TrainGraph":
+        e = int(csr.rowptr[-1].item())          # the one host sync of a training step
+        return TrainGraph(csr.rowptr, csr.src, csr.tgt, csr.n_nodes, e)
+
+    def by_source(self):
+        """(perm, rowptr_src): edges stably sorted by source; segment j = edges leaving node j."""
+        if self._by_src is None:
+            src = self.src.long()
+            perm = torch.sort(src, stable=True).indices.int()
+            counts = torch.bincount(src, minlength=self.n)
+            rp = torch.zeros(self.n + 1, dtype=torch.int32, device=src.device)
+            rp[1:] = torch.cumsum(counts, 0).int()
+            self._by_src = (perm, rp)
+        return self._by_src
+
+
+def _f32(t):
+    L.require_cuda(t, "tensor")
+    return t.contiguous().float()
+
+
+def segment_sum_rows(m: torch.Tensor, rowptr: torch.Tensor, n_rows: int, perm=None) -> torch.Tensor:
+    m = _f32(m)
+    out = torch.empty(n_rows, m.shape[1], dtype=torch.float32, device=m.device)
+    L.check(L.lib().sgnn_segment_sum_rows(L.ptr(m), L.ptr(rowptr), L.ptr(perm), n_rows, m.shape[1],
+                                          L.ptr(out), L.stream_ptr()))
+    return out
+
+
+def gather_rows(rows: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+    rows = _f32(rows)
+    out = torch.empty(idx.numel(), rows.shape[1], dtype=torch.float32, device=rows.device)
+    L.check(L.lib().sgnn_gather_rows(L.ptr(rows), C.c_long(rows.shape[1]), L.ptr(idx), idx.numel(),
+                                     rows.shape[1], L.ptr(out), L.stream_ptr()))
+    return out
+
+
+class _GatherAdd(torch.autograd.Function):
+    """out[e] = P[tgt[e]] + Q[src[e]]."""
+
+    @staticmethod
+    def forward(ctx, p, q, graph: TrainGraph):
+        p, q = _f32(p), _f32(q)
+        ctx.graph = graph
+        out = torch.empty(graph.e, p.shape[1], dtype=torch.float32, device=p.device)
+        L.check(L.lib().sgnn_gather_add_rows(L.ptr(p), C.c_long(p.shape[1]), L.ptr(q), C.c_long(q.shape[1]),
+                                             L.ptr(graph.tgt), L.ptr(graph.src), graph.e, p.shape[1],
+                                             L.ptr(out), L.stream_ptr()))
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        g = ctx.graph
+        dout = _f32(dout)
+        dp = segment_sum_rows(dout, g.rowptr, g.n)                     # edges are receiver-sorted
+        perm, rp = g.by_source()
+        dq = segment_sum_rows(dout, rp, g.n, perm)
+        return dp, dq, None
+
+
+class _SegmentSum(torch.autograd.Function):
+    """agg[i] = sum of m over the CSR row of receiver i (rows summed in edge order)."""
+
+    @staticmethod
+    def forward(ctx, m, graph: TrainGraph):
+        ctx.graph = graph
+        return segment_sum_rows(m, graph.rowptr, graph.n)
+
+    @staticmethod
+    def backward(ctx, dagg):
+        return gather_rows(dagg, ctx.graph.tgt), None
+
+
+def gather_add(p, q, graph):
+    return _GatherAdd.apply(p, q, graph)
+
+
+def segment_sum(m, graph):
+    return _SegmentSum.apply(m, graph)
+
+
+# ---------------------------------------------------------------------------------------------
+def node_features(seq: torch.Tensor, vel_mean, vel_std, wall_max: float, wall_div: float,
+                  extra: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """[N, (S-1)*dim + 1 (+ extra columns)] node features from the position window."""
+    n, s, dim = seq.shape
+    k = (s - 1) * dim + 1
+    width = k + (0 if extra is None else extra.shape[1])
+    out = torch.empty(n, width, dtype=torch.float32, device=seq.device)
+    L.check(L.lib().sgnn_node_features(L.ptr(seq), C.c_long(seq.stride(0)), n, s, dim, L.ptr(vel_mean),
+                                       L.ptr(vel_std), C.c_float(2.0), C.c_float(wall_max),
+                                       C.c_float(wall_div), L.ptr(out), C.c_long(width), L.stream_ptr()))
+    if extra is not None:
+        out = torch.cat([out[:, :k], extra], dim=1)     # keeps the embedding's autograd edge
+    return out
+
+
+def edge_features(last_pos: torch.Tensor, pos_stride: int, dim: int, radius: float,
+                  graph: TrainGraph) -> torch.Tensor:
+    out = torch.empty(graph.e, dim + 1, dtype=torch.float32, device=graph.src.device)
+    L.check(L.lib().sgnn_edge_features(C.c_void_p(last_pos.data_ptr()), C.c_long(pos_stride), dim,
+                                       C.c_float(radius), L.ptr(graph.src), L.ptr(graph.tgt), graph.e,
+                                       L.ptr(out), L.stream_ptr()))
+    return out
+
+
+def _rest_of_mlp(seq_mlp, h):
+    """Apply everything after the first Linear of a build_mlp Sequential (Act-0, NN-1, ...)."""
+    first = True
+    for m in seq_mlp.children():
+        if first and isinstance(m, torch.nn.Linear):
+            first = False
+            continue
+        h = m(h)
+    return h
+
+
+def interaction_block(edge_fn, node_fn, x, e, graph: TrainGraph):
+    """One InteractionNetwork / G2M / M2M / M2G block with autograd (graph_network.py:150-222).
+    Returns (x + node update, e + e): the reference's update() hands back its input edge latent."""
+    nn_in = x.shape[1]
+    w1 = linears_of(edge_fn[0])[0]
+    p = F.linear(x, w1.weight[:, :nn_in], w1.bias)                # x_target block (+ bias)
+    q = F.linear(x, w1.weight[:, nn_in:2 * nn_in])                # x_source block
+    pre = F.linear(e, w1.weight[:, 2 * nn_in:]) + gather_add(p, q, graph)
+    msg = edge_fn[1](_rest_of_mlp(edge_fn[0], pre))               # ... -> LayerNorm
+    agg = segment_sum(msg, graph)
+    v1 = linears_of(node_fn[0])[0]
+    na = agg.shape[1]
+    pre_n = F.linear(agg, v1.weight[:, :na]) + F.linear(x, v1.weight[:, na:], v1.bias)
+    upd = node_fn[1](_rest_of_mlp(node_fn[0], pre_n))
+    return x + upd, e + e
+
+
+def epd_forward(node_encoder, edge_encoders: List, blocks: List, decoder, nf, efs: List,
+                graphs: List[TrainGraph]):
+    """blocks: list of (edge_fn, node_fn, edge_set_index).  Returns the decoder output [N, dim+1]."""
+    x = node_encoder(nf)
+    es = [enc(ef) for enc, ef in zip(edge_encoders, efs)]
+    for edge_fn, node_fn, k in blocks:
+        x, es[k] = interaction_block(edge_fn, node_fn, x, es[k], graphs[k])
+    return decoder(x)

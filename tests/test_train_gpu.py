@@ -1,0 +1,109 @@
+"""GPU parity of the training path: predict_accelerations (noisy inputs, targets), the loss and
+EVERY parameter gradient against the unmodified reference's fp64 run (golden fixtures), for the
+single-scale and the multi-scale simulators.  The training path computes in fp32 (cuBLAS GEMMs with
+TF32 off + the deterministic graph kernels), so the bar is the reference's own fp32-vs-fp64 gap
+times a small factor: |g - g64| <= 20 * gap32 + 1e-6 * max|g64|."""
+import pytest
+import torch
+
+from tests.util import Fixture
+
+pytestmark = pytest.mark.gpu
+
+
+def _check_grads(sim, f, loss_scale=1.0):
+    g64 = f.grads()
+    seen = 0
+    for k, p in sim.named_parameters():
+        if k not in g64:
+            assert p.grad is None or float(p.grad.abs().max()) == 0.0, k
+            continue
+        gap, gmax = f[f"grad_gap/{k}"].tolist()
+        err = (p.grad.cpu() * loss_scale - g64[k]).abs().max().item()
+        assert err <= 20 * gap + 1e-6 * gmax + 1e-9, (k, err, gap, gmax)
+        seen += 1
+    assert seen == len(g64)
+
+
+@pytest.mark.parametrize("name", ["single_h64", "single_h32_batch"])
+def test_single_scale_train_step_matches_reference(name):
+    from tests.test_single_scale_gpu import make_sim
+    f = Fixture(name)
+    sim, S, radius, _ = make_sim(f, "tf32")
+    sim.train()
+    pos, noise = f.t("train/positions").cuda(), f.t("train/noise").cuda()
+    nxt, nstrain = f.t("train/next_position").cuda(), f.t("train/next_strain").cuda()
+    counts, types = f.t("train/counts").cuda(), f.t("train/particle_types").cuda()
+    pa, ta, ps = sim.predict_accelerations(nxt, noise, pos, counts, types)
+    assert torch.allclose(ta.cpu(), f.t("train/target_acc_f32"), atol=1e-4, rtol=1e-4)
+    assert (pa.cpu().double() - f.t("train/pred_acc_f64")).abs().max() <= 5e-5
+    assert (ps.cpu().double() - f.t("train/pred_strain_f64")).abs().max() <= 5e-5
+    loss = (((pa - ta) ** 2).sum(-1) + (ps - nstrain) ** 2).mean()
+    assert abs(loss.item() - float(f["train/loss_f64"])) <= 1e-4 * max(1.0, float(f["train/loss_f64"]))
+    sim.zero_grad()
+    loss.backward()
+    _check_grads(sim, f)
+    # deterministic backward (no atomics)
+    g1 = [p.grad.clone() for p in sim.parameters() if p.grad is not None]
+    sim.zero_grad()
+    pa, ta, ps = sim.predict_accelerations(nxt, noise, pos, counts, types)
+    (((pa - ta) ** 2).sum(-1) + (ps - nstrain) ** 2).mean().backward()
+    g2 = [p.grad for p in sim.parameters() if p.grad is not None]
+    assert all(torch.equal(a, b) for a, b in zip(g1, g2))
+
+
+@pytest.mark.parametrize("name", ["multi_ref_fixture", "multi_h128"])
+def test_multi_scale_train_step_matches_reference(name):
+    from tests.test_multi_scale_gpu import graph_of, make_sim
+    f = Fixture(name)
+    sim, S, _, _ = make_sim(f, "tf32")
+    sim.set_static_graph(graph_of(f))
+    sim.train()
+    pos, types = f.t("positions").cuda(), f.t("particle_types").cuda()
+    n = pos.shape[0]
+    noise = f.t("train/noise").cuda()
+    pa, ta, ps = sim.predict_accelerations(pos[:, S], noise, pos[:, :S], torch.tensor([n]), types)
+    assert torch.allclose(ta.cpu(), f.t("train/target_acc_f32"), atol=1e-4, rtol=1e-4)
+    assert (pa.cpu().double() - f.t("train/pred_acc_f64")).abs().max() <= 5e-5
+    loss = (((pa - ta) ** 2).sum(-1) + ps ** 2).mean()
+    assert abs(loss.item() - float(f["train/loss_f64"])) <= 1e-4 * max(1.0, float(f["train/loss_f64"]))
+    sim.zero_grad()
+    loss.backward()
+    _check_grads(sim, f)
+
+
+def test_train_step_api_decreases_loss_and_graph_ops_gradcheck():
+    """training.train_step end to end (noise on device, Adam), plus a finite-difference check of
+    the two autograd Functions in fp32 against a dense torch restatement."""
+    from sgnn_b200 import train_ops as T, training
+    from tests.test_single_scale_gpu import make_sim
+    f = Fixture("single_h64")
+    sim, S, radius, _ = make_sim(f, "tf32")
+    sim.train()
+    batch = {"positions": f.t("train/positions").cuda(), "particle_type": f.t("train/particle_types").cuda(),
+             "n_particles_per_example": f.t("train/counts").cuda(),
+             "next_position": f.t("train/next_position").cuda(), "next_strain": f.t("train/next_strain").cuda()}
+    opt = torch.optim.Adam(sim.parameters(), lr=1e-3)
+    noise = f.t("train/noise").cuda()
+    losses = [training.train_step(sim, opt, batch, 0.02, noise=noise).item() for _ in range(8)]
+    assert losses[-1] < losses[0]
+    assert abs(losses[0] - float(f["train/loss_f64"])) <= 1e-4 * max(1.0, float(f["train/loss_f64"]))
+    # graph ops vs dense torch
+    g = torch.Generator().manual_seed(0)
+    n, e, w = 50, 400, 32
+    tgt = torch.sort(torch.randint(0, n, (e,), generator=g)).values
+    src = torch.randint(0, n, (e,), generator=g)
+    rowptr = torch.zeros(n + 1, dtype=torch.int32)
+    rowptr[1:] = torch.cumsum(torch.bincount(tgt, minlength=n), 0).int()
+    graph = T.TrainGraph(rowptr.cuda(), src.int().cuda(), tgt.int().cuda(), n, e)
+    p = torch.randn(n, w, generator=g).cuda().requires_grad_()
+    q = torch.randn(n, w, generator=g).cuda().requires_grad_()
+    wgt = torch.randn(e, w, generator=g).cuda()
+    out = T.segment_sum(T.gather_add(p, q, graph) * wgt, graph)
+    out.square().sum().backward()
+    p2, q2 = p.detach().clone().requires_grad_(), q.detach().clone().requires_grad_()
+    ref = torch.zeros(n, w, device="cuda").index_add_(0, tgt.cuda(), (p2[tgt.cuda()] + q2[src.cuda()]) * wgt)
+    ref.square().sum().backward()
+    assert torch.allclose(out, ref, atol=1e-4, rtol=1e-5)
+    assert torch.allclose(p.grad, p2.grad, atol=1e-3, rtol=1e-4)
+    assert torch.allclose(q.grad, q2.grad, atol=1e-3, rtol=1e-4)
