@@ -208,6 +208,120 @@ def large_config(pk, dev, nx=2048, ny=512):
     return out
 
 
+def make_train_batch(dev, samples, seed0=100):
+    """`samples` independent synthetic samples concatenated as the reference's collate_fn does
+    (taylor_impact_data_loader.py:243-284): positions [sum N, S, 2], next_position, next_strain."""
+    pos, nxt, strain = [], [], []
+    for k in range(samples):
+        traj, stats, radius = make_case(seed=seed0 + k, nsteps=1)
+        pos.append(traj["positions"][:, :S])
+        nxt.append(traj["positions"][:, S])
+        strain.append(traj["strains"][S])
+    n = pos[0].shape[0]
+    return {"positions": torch.cat(pos).to(dev), "next_position": torch.cat(nxt).to(dev),
+            "next_strain": torch.cat(strain).to(dev),
+            "particle_type": torch.zeros(n * samples, dtype=torch.int64, device=dev),
+            "n_particles_per_example": torch.full((samples,), n, dtype=torch.int64, device=dev)}, stats, radius
+
+
+def train_config(dev, rank, world, steps=10, warmup=3, samples=8):
+    """BASELINE configs[2]: single-scale training, 8 samples per GPU, flat-gradient allreduce."""
+    import torch.distributed as dist
+    from sgnn_b200 import training
+    batch, stats, radius = make_train_batch(dev, samples, seed0=100 + 1000 * rank)
+    sim = make_sim(stats, radius, dev).train()
+    opt = torch.optim.Adam(sim.parameters(), lr=1e-4)
+    reducer = training.FlatGradAllReduce(sim.parameters()) if world > 1 else None
+    n_glob = batch["positions"].shape[0] * world
+    gen = torch.Generator(device=dev).manual_seed(2 + rank)
+    losses = []
+    for _ in range(warmup):
+        training.train_step(sim, opt, batch, 0.02 * 25.0, reducer=reducer, n_global=n_glob, generator=gen)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(steps):
+        losses.append(training.train_step(sim, opt, batch, 0.02 * 25.0, reducer=reducer, n_global=n_glob,
+                                          generator=gen))
+    b.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([a.elapsed_time(b)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = ms.item() / steps
+    return {"train_steps_per_s": 1e3 / ms, "ms_per_train_step": ms, "samples_per_gpu": samples,
+            "particles_per_step_global": n_glob, "samples_per_s": samples * world * 1e3 / ms,
+            "loss_first": losses[0].item() * world, "loss_last": losses[-1].item() * world,
+            "collective": "one flat fp32 gradient allreduce (NCCL)" if world > 1 else "none (1 GPU)",
+            "gemm": "cuBLAS fp32", "graph_ops": "sgnn_b200 CUDA (deterministic)"}
+
+
+def multiscale_config(dev, rank, steps=5):
+    """BASELINE configs[3]: multi-scale variant, 2D, layers=5, hidden=128 (nmlp=2, scales=2,
+    window=2, 120x40 lattice at the hard-coded 0.5 spacing), 100-step rollout as one CUDA graph."""
+    from sgnn_b200.multi_scale import MultiScaleConfig, MultiScaleGraph, MultiScaleSimulator
+    from sgnn_b200.single_scale import evaluate as EV
+    traj = synthetic.taylor_trajectory(NX, NY, 0.5, nframes=S + ROLLOUT_STEPS, seed=rank)
+    stats = synthetic.normalization_stats(synthetic.metadata_from(traj["positions"]), 0.02)
+    torch.manual_seed(1)
+    sim = MultiScaleSimulator(2, (S - 1) * 2 + 1, 3, 128, 128, LAYERS, 2, stats, 1, 9, num_scales=2,
+                              window_size=2, radius_multiplier=2.0, device=dev).to(dev).eval()
+    pos = traj["positions"].to(dev)
+    graph = MultiScaleGraph(MultiScaleConfig(2, 2, 2.0)).create_all_edges(pos[:, 0].contiguous())
+    sim.set_static_graph(graph)
+    n, t, dim = pos.shape
+    plan = EV.get_plan(sim, n, t, S, dim, "autoregressive", dev, True)
+    for _ in range(3):
+        plan.traj[:, :S].copy_(pos[:, :S])
+        plan.run()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    tot = 0.0
+    for _ in range(steps):
+        plan.traj[:, :S].copy_(pos[:, :S])
+        a.record()
+        plan.run()
+        b.record()
+        torch.cuda.synchronize()
+        tot += a.elapsed_time(b)
+    ms = tot / steps
+    return {"particles": n, "edges": {k: int(graph[k].shape[1]) for k in ("grid2mesh_edges", "mesh2mesh_edges", "mesh2grid_edges")},
+            "ms_per_100_step_rollout": ms, "particle_steps_per_s": n * (t - S) / (ms * 1e-3),
+            "finite": bool(torch.isfinite(plan.traj).all().item())}
+
+
+def sharded_config(dev, rank, world, nx=2048, ny=512, nsteps=6):
+    """BASELINE configs[4]: >= 1M particles, rollout sharded by spatial slab, one ghost-frame
+    exchange per step over NCCL P2P (sgnn_b200/sharding.py).  Timed on the device, max over ranks."""
+    import torch.distributed as dist
+    from sgnn_b200 import sharding as SH
+    traj, stats, radius = make_case(seed=7, nx=nx, ny=ny, nsteps=1)
+    sim = make_sim(stats, radius, dev)
+    n = nx * ny
+    lo, hi = SH.slab_bounds(n, world)[rank]
+    init = traj["positions"][lo:hi, :S].to(dev).contiguous()
+    del traj
+    comm = SH.DistComm()
+    SH.sharded_rollout(sim, init, 2, comm, n_layers=LAYERS, refresh_every=nsteps)          # warm-up
+    dist.barrier()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    pred, _ = SH.sharded_rollout(sim, init, nsteps, comm, n_layers=LAYERS, refresh_every=nsteps)
+    b.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([a.elapsed_time(b)], device=dev, dtype=torch.float64)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ok = torch.tensor([float(torch.isfinite(pred).all().item())], device=dev)
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    return {"particles": n, "ranks": world, "steps": nsteps, "ms_per_step": ms.item() / nsteps,
+            "particle_steps_per_s": n * nsteps / (ms.item() * 1e-3), "finite": bool(ok.item()),
+            "exchange": "ghost region of L*r + skin, one new-frame P2P exchange per step (NCCL)",
+            "includes": "ghost selection + full-window exchange at the start (host syncs), neighbour search"}
+
+
 def run_gpu(args):
     import torch.distributed as dist
     from sgnn_b200 import _lib as L
@@ -312,6 +426,24 @@ def run_gpu(args):
                 line["large"] = large_config(pk, dev)
             except Exception as ex:           # report, never hide
                 line["large"] = {"error": repr(ex)}
+    if not args.no_extra:
+        # every rank takes part (the train step has a collective); rank 0 reports
+        try:
+            tr = train_config(dev, rank, world)
+        except Exception as ex:
+            tr = {"error": repr(ex)}
+        try:
+            ms = multiscale_config(dev, rank) if rank == 0 else None
+        except Exception as ex:
+            ms = {"error": repr(ex)}
+        sh = None
+        if world > 1:
+            try:
+                sh = sharded_config(dev, rank, world)
+            except Exception as ex:
+                sh = {"error": repr(ex)}
+        if line is not None:
+            line["train"], line["multi_scale"], line["sharded_1m"] = tr, ms, sh
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -326,6 +458,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="sgnn_b200", choices=["sgnn_b200", "reference"])
     ap.add_argument("--no-large", action="store_true", help="skip the 1M-particle single-step section")
+    ap.add_argument("--no-extra", action="store_true", help="skip the training and multi-scale sections")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

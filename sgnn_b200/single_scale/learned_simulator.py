@@ -89,6 +89,9 @@ class LearnedSimulator(nn.Module):
                             latent=self._latent_dim, n_nodes=n, edge_caps=[rg.csr.max_edges],
                             precision=self.precision, device=device)
             hit = (ver, eng, rg)
+            self._engines.pop(key, None)
+            while len(self._engines) >= 2:                 # bounded cache: shapes change at halo refreshes
+                self._engines.pop(next(iter(self._engines)))
             self._engines[key] = hit
         return hit[1], hit[2]
 
