@@ -103,7 +103,9 @@ __global__ void __launch_bounds__(kFastThreads, 1) edge_layer_fast_kernel(const 
   const uint32_t tmem_w = misc->tmem_slot + (uint32_t)(w * 2 * REG);     // this worker's columns
   const uint32_t lane_base = (uint32_t)(wq * 32) << 16;
 
-  const int tile0 = blockIdx.x * kWorkers + w, stride = gridDim.x * kWorkers;
+  // tiles go round-robin over CTAs first, then over a CTA's workers: small problems spread over
+  // all SMs (one tile per SM) instead of packing four tiles onto a quarter of them
+  const int tile0 = blockIdx.x + w * gridDim.x, stride = gridDim.x * kWorkers;
   if (wt == 0 && tile0 < n_tiles)
     tma_load_span(e_buf, reinterpret_cast<const char*>(p.e_tiles) + (long)tile0 * tile_bytes, tile_bytes,
                   &wk->bar_e);
@@ -352,7 +354,7 @@ int sgnn_edge_layer_fast_try(const SgnnEdgeLayerParams* p, void* stream) {
     SGNN_CUDA(cudaGetDevice(&dev));
     SGNN_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   }
-  int grid = sgnn_ceil_div(p->max_tiles, kWorkers);
+  int grid = p->max_tiles;
   if (grid > sms) grid = sms;
   if (grid < 1) grid = 1;
   SGNN_ENSURE_SMEM((edge_layer_fast_kernel<64, 64, 64>), smem);

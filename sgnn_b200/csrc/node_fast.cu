@@ -1,0 +1,357 @@
+// Node side of the Encode-Process-Decode network, throughput version for 64-wide latents (same
+// maths as node_kernel.cu; reference: Encoder.node_fn graph_network.py:86-90, InteractionNetwork
+// .update + residual :176,201-222, Decoder :321-333, Euler integrator learned_simulator.py:381-411).
+//
+// ONE persistent CTA per SM, 4 tile workers of 128 threads sharing one resident weight image.
+// Thread t of a worker owns node row t of the worker's 128-row tile from the first load to the
+// last store: it reads its own agg / x rows (full 128-byte lines), rounds them to TF32 and parks
+// them in TENSOR MEMORY as the A operand (tcgen05.st); every GEMM of the chain takes A from TMEM
+// and B (weights) from shared memory, so there is NO activation tile in shared memory at all and
+// no swizzle arithmetic.  TMEM per worker: region A (64 columns) + region D (64 columns);
+//   [agg] -> A, MMA (K=64) -> D ; [x] -> A, MMA accumulate -> D ; bias+ReLU in place (D becomes A)
+//   hidden..out GEMMs ping-pong between the two regions ; LayerNorm + residual in registers
+//   x' (TF32) -> A ; P = x' W1a^T -> D, then Q = x' W1b^T -> D   (or the decoder MLP + integrator)
+#include "mlp_tile.cuh"
+#include "params.h"
+
+namespace sgnn {
+
+constexpr int kNodeWorkers = 4;
+constexpr int kNodeFastThreads = kNodeWorkers * kThreads;
+constexpr int NW = 64;                               // every width handled by this kernel
+
+struct NodeFastMisc {
+  uint64_t bar_w;
+  uint64_t bar_m[kNodeWorkers];
+  uint32_t tmem_slot;
+  int pad;
+};
+
+__host__ __device__ inline int node_fast_smem(int blob_bytes) {
+  return align_up(blob_bytes, 16) + (int)sizeof(NodeFastMisc) + 1024;
+}
+
+__device__ __forceinline__ float tf32r(float x) { return __uint_as_float(__float_as_uint(x) + 0x1000u); }
+
+__device__ __forceinline__ void nworker_bar(int w) {
+  asm volatile("bar.sync %0, %1;" ::"r"(w + 1), "r"(kThreads) : "memory");
+}
+
+// The worker's threads have written an A operand into TMEM: publish it, let thread 0 issue the
+// MMAs described by `issue`, wait for them, and make the accumulator readable by everyone.
+template <class Issue>
+__device__ __forceinline__ void run_mma(int w, int wt, uint64_t* bar, uint32_t& phase, Issue issue) {
+  tmem_st_wait();
+  tc_fence_before_sync();
+  nworker_bar(w);
+  if (wt == 0) {
+    tc_fence_after_sync();
+    issue();
+    tc_commit(bar);
+    mbar_wait(bar, phase);
+  }
+  phase ^= 1u;
+  nworker_bar(w);
+  tc_fence_after_sync();
+}
+
+// 64 fp32 of a row -> TF32 -> TMEM columns [col, col + 64)
+__device__ __forceinline__ void row_to_tmem(uint32_t taddr, float* v) {
+#pragma unroll
+  for (int j = 0; j < NW; ++j) v[j] = tf32r(v[j]);
+  tmem_st32(taddr, v);
+  tmem_st32(taddr + 32, v + 32);
+}
+
+__device__ __forceinline__ void load_row64(const float* __restrict__ src, float* v) {
+  const float4* s4 = reinterpret_cast<const float4*>(src);
+#pragma unroll
+  for (int j = 0; j < NW / 4; ++j) {
+    const float4 t = __ldg(s4 + j);
+    v[4 * j] = t.x; v[4 * j + 1] = t.y; v[4 * j + 2] = t.z; v[4 * j + 3] = t.w;
+  }
+}
+
+__global__ void __launch_bounds__(kNodeFastThreads, 1) node_fast_kernel(const SgnnNodeParams p) {
+  constexpr int TMEM_COLS = 512;
+  char* smem = smem_base_1024();
+  const float* blob_f = reinterpret_cast<const float*>(smem);
+  NodeFastMisc* misc = reinterpret_cast<NodeFastMisc*>(smem + align_up(p.blob_bytes, 16));
+  const int tid = threadIdx.x, w = tid >> 7, wt = tid & 127, wq = wt >> 5;
+  const int n_tiles = (p.n_rows + kTileRows - 1) / kTileRows;
+
+  if (tid == 0) {
+    mbar_init(&misc->bar_w, 1);
+    for (int i = 0; i < kNodeWorkers; ++i) mbar_init(&misc->bar_m[i], 1);
+    mbar_fence_init();
+    tma_load_span(smem, reinterpret_cast<const char*>(p.blob), p.blob_bytes, &misc->bar_w);
+  }
+  if (tid < 32) tmem_alloc(&misc->tmem_slot, TMEM_COLS);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t lane_base = (uint32_t)(wq * 32) << 16;
+  const uint32_t RA = misc->tmem_slot + (uint32_t)(w * 2 * NW);       // column addresses (MMA operands)
+  const uint32_t RD = RA + NW;
+  const uint32_t tA = RA + lane_base, tD = RD + lane_base;            // this thread's lanes
+  uint64_t* bar = &misc->bar_m[w];
+  uint32_t phase = 0;
+  mbar_wait(&misc->bar_w, 0);
+  const uint32_t sW = smem_u32(smem);
+  const int nh = p.mlp.n_hidden;
+
+  for (int tile = blockIdx.x + w * gridDim.x; tile < n_tiles; tile += gridDim.x * kNodeWorkers) {
+    const long i = (long)tile * kTileRows + wt;
+    const bool valid = i < p.n_rows;
+    float v[NW];
+
+    // ---- first Linear: A from the prologue, D = region D ----
+    if (p.prologue == SGNN_PRO_AGG_X) {
+#pragma unroll
+      for (int j = 0; j < NW; ++j) v[j] = 0.f;
+      if (valid) {
+        const int beg = p.rowptr[i], end = p.rowptr[i + 1];
+        if (end > beg) {
+          load_row64(p.agg + i * NW, v);
+          const int t0 = beg >> 7, t1 = (end - 1) >> 7;
+          for (int t = t0 + 1; t <= t1; ++t) {           // CSR row straddling edge tiles (rare)
+            const float4* h4 = reinterpret_cast<const float4*>(p.head + (long)t * NW);
+#pragma unroll
+            for (int j = 0; j < NW / 4; ++j) {
+              const float4 h = __ldg(h4 + j);
+              v[4 * j] += h.x; v[4 * j + 1] += h.y; v[4 * j + 2] += h.z; v[4 * j + 3] += h.w;
+            }
+          }
+        }
+      }
+      row_to_tmem(tA, v);
+      run_mma(w, wt, bar, phase, [&] { umma_gemm_tf32_ts(RD, RA, sW + p.mlp.w_off[0], NW, NW); });
+#pragma unroll
+      for (int j = 0; j < NW; ++j) v[j] = 0.f;
+      if (valid) load_row64(p.x_in + i * NW, v);
+      row_to_tmem(tA, v);
+      run_mma(w, wt, bar, phase, [&] {           // x columns of W0: K-blocks 2,3 ; accumulate
+        const uint32_t idesc = umma_idesc_tf32(kTileRows, NW);
+        const uint32_t wb = sW + p.mlp.w_off[0] + 2 * NW * kKBlockBytes;
+        for (int kb = 0; kb < 2; ++kb)
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            umma_tf32_ts(RD, RA + kb * kKBlock + j * 8, umma_desc_sw128(wb + kb * NW * kKBlockBytes + j * 32),
+                         idesc, 1u);
+      });
+    } else {   // SGNN_PRO_FEATURES: (S-1)*dim velocities + wall distance (+ embedding), K padded to 32
+      float f[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) f[j] = 0.f;
+      if (valid) {
+        const float* ps = p.pos_seq + i * p.pos_seq_stride;
+        int k = 0;
+        for (int t = 0; t + 1 < p.seq_len; ++t)
+          for (int d = 0; d < p.dim; ++d) {
+            const float vel = __fsub_rn(ps[(t + 1) * p.dim + d], ps[t * p.dim + d]);
+            const float val = __fdiv_rn(__fsub_rn(vel, p.vel_mean[d]), p.vel_std[d]);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) if (j == k) f[j] = val;      // registers: static indices only
+            ++k;
+          }
+        float wd = __fadd_rn(ps[(p.seq_len - 1) * p.dim], p.wall_offset);
+        wd = __fdiv_rn(fminf(fmaxf(wd, 0.f), p.wall_max), p.wall_div);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) if (j == k) f[j] = wd;
+        if (p.feat_out)
+          for (int j = 0; j < p.k_in; ++j) {
+            float val = 0.f;
+#pragma unroll
+            for (int q = 0; q < 32; ++q) if (q == j) val = f[q];
+            p.feat_out[i * p.k_in + j] = val;
+          }
+      }
+#pragma unroll
+      for (int j = 0; j < 32; ++j) f[j] = tf32r(f[j]);
+      tmem_st32(tA, f);
+      run_mma(w, wt, bar, phase, [&] { umma_gemm_tf32_ts(RD, RA, sW + p.mlp.w_off[0], 32, NW); });
+    }
+
+    // ---- bias + ReLU in place, hidden layers ping-pong A <-> D, then the output Linear ----
+    uint32_t cur = RD, oth = RA;                         // cur: region holding the fresh accumulator
+    for (int l = 0; l < nh; ++l) {
+      const float* b = blob_f + p.mlp.b_off[l];
+      const uint32_t tc = cur + lane_base;
+#pragma unroll
+      for (int c = 0; c < NW; c += 32) {
+        float h[32];
+        tmem_ld32(tc + c, h);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) h[j] = tf32r(fmaxf(h[j] + b[c + j], 0.f));
+        tmem_st32(tc + c, h);
+      }
+      const uint32_t a = cur, d = oth;
+      const int woff = p.mlp.w_off[l + 1];
+      run_mma(w, wt, bar, phase, [&] { umma_gemm_tf32_ts(d, a, sW + woff, NW, NW); });
+      cur = d; oth = a;
+    }
+
+    // ---- LayerNorm, residual, x' ----
+    {
+      const uint32_t tc = cur + lane_base;
+      tmem_ld32(tc, v);
+      tmem_ld32(tc + 32, v + 32);
+      const float* b = blob_f + p.mlp.b_off[nh];
+#pragma unroll
+      for (int j = 0; j < NW; ++j) v[j] += b[j];
+      if (p.mlp.has_ln) {
+        const float* gam = blob_f + p.mlp.gamma_off;
+        const float* bet = blob_f + p.mlp.beta_off;
+        float s4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int j = 0; j < NW; ++j) s4[j & 3] += v[j];
+        const float mean = ((s4[0] + s4[1]) + (s4[2] + s4[3])) / (float)NW;
+        float q4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int j = 0; j < NW; ++j) {
+          v[j] -= mean;
+          q4[j & 3] = fmaf(v[j], v[j], q4[j & 3]);
+        }
+        const float rstd = 1.0f / sqrtf(((q4[0] + q4[1]) + (q4[2] + q4[3])) / (float)NW + 1e-5f);
+#pragma unroll
+        for (int j = 0; j < NW; ++j) v[j] = v[j] * rstd * gam[j] + bet[j];
+      }
+      if (valid) {
+        if (p.residual) {
+          const float4* xr = reinterpret_cast<const float4*>(p.x_in + i * NW);
+#pragma unroll
+          for (int j = 0; j < NW / 4; ++j) {
+            const float4 x = __ldg(xr + j);
+            v[4 * j] += x.x; v[4 * j + 1] += x.y; v[4 * j + 2] += x.z; v[4 * j + 3] += x.w;
+          }
+        }
+        if (p.x_out) {
+          float4* xo = reinterpret_cast<float4*>(p.x_out + i * NW);
+#pragma unroll
+          for (int j = 0; j < NW / 4; ++j) xo[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        }
+      }
+    }
+
+    // ---- tail: x' (TF32) becomes the A operand in the region that is NOT `cur` ... both are free
+    //      now (the accumulator has been read), use region A for x' and region D for the products ----
+    if (p.tail == SGNN_TAIL_PQ) {
+      row_to_tmem(tA, v);
+      const float* b1 = blob_f + p.pq_bias_off;
+      for (int half = 0; half < 2; ++half) {
+        const int woff = half ? p.wq_off : p.wp_off;
+        run_mma(w, wt, bar, phase, [&] { umma_gemm_tf32_ts(RD, RA, sW + woff, NW, NW); });
+        float o[NW];
+        tmem_ld32(tD, o);
+        tmem_ld32(tD + 32, o + 32);
+        if (half == 0) {
+#pragma unroll
+          for (int j = 0; j < NW; ++j) o[j] += b1[j];
+        }
+        if (valid) {
+          float4* dst = reinterpret_cast<float4*>(p.pq_out + i * 2 * NW + half * NW);
+#pragma unroll
+          for (int j = 0; j < NW / 4; ++j) dst[j] = make_float4(o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
+        }
+        tc_fence_before_sync();        // region D is read before the next product overwrites it
+      }
+    } else if (p.tail == SGNN_TAIL_DECODE) {
+      row_to_tmem(tA, v);
+      uint32_t a = RA, d = RD;
+      for (int l = 0; l < p.dec.n_hidden; ++l) {
+        const int woff = p.dec.w_off[l];
+        const uint32_t aa = a, dd = d;
+        run_mma(w, wt, bar, phase, [&] { umma_gemm_tf32_ts(dd, aa, sW + woff, NW, NW); });
+        if (l + 1 < p.dec.n_hidden) {
+          const float* b = blob_f + p.dec.b_off[l];
+          const uint32_t td = d + lane_base;
+#pragma unroll
+          for (int c = 0; c < NW; c += 32) {
+            float h[32];
+            tmem_ld32(td + c, h);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) h[j] = tf32r(fmaxf(h[j] + b[c + j], 0.f));
+            tmem_st32(td + c, h);
+          }
+        }
+        const uint32_t t = a; a = d; d = t;
+      }
+      // `a` now names the region with the last hidden pre-activation; final Linear in FFMA
+      float o[8];
+      const int nout = p.dec.out;
+      const float* bl = blob_f + p.dec.b_off[p.dec.n_hidden];
+      const float* wl = blob_f + p.dec_wlast_off;
+      const float* bh = blob_f + p.dec.b_off[p.dec.n_hidden - 1];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) o[k] = 0.f;
+      const uint32_t ta = a + lane_base;
+#pragma unroll
+      for (int c = 0; c < NW; c += 32) {
+        float h[32];
+        tmem_ld32(ta + c, h);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) h[j] = fmaxf(h[j] + bh[c + j], 0.f);
+        for (int k = 0; k < nout; ++k) {
+          float acc = o[k];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) acc = fmaf(h[j], wl[k * NW + c + j], acc);
+          o[k] = acc;
+        }
+      }
+      if (valid) {
+        for (int k = 0; k < nout; ++k) o[k] += bl[k];
+        if (p.dec_out)
+          for (int k = 0; k < nout; ++k) p.dec_out[i * nout + k] = o[k];
+        if (p.strain_out) p.strain_out[i] = o[nout - 1];
+        if (p.next_pos) {
+          const float* ps = p.pos_seq + i * p.pos_seq_stride;
+          for (int d2 = 0; d2 < p.dim; ++d2) {
+            const float acc = __fadd_rn(__fmul_rn(o[d2], p.acc_std[d2]), p.acc_mean[d2]);
+            const float last = ps[(p.seq_len - 1) * p.dim + d2];
+            const float vel = __fsub_rn(last, ps[(p.seq_len - 2) * p.dim + d2]);
+            p.next_pos[i * p.next_pos_stride + d2] = __fadd_rn(last, __fadd_rn(vel, acc));
+          }
+        }
+      }
+    }
+    tc_fence_before_sync();
+    nworker_bar(w);                  // all TMEM reads of this tile retired before the next tile's stores
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  if (tid < 32) tmem_dealloc(misc->tmem_slot, TMEM_COLS);
+}
+
+}  // namespace sgnn
+
+using namespace sgnn;
+
+// 1 = launched, 0 = shape not covered (caller uses the generic kernel), < 0 = error
+int sgnn_node_fast_try(const SgnnNodeParams* p, void* stream) {
+  if (!p->has_mlp || p->mlp.hidden != NW || p->mlp.out != NW) return 0;
+  if (p->prologue == SGNN_PRO_AGG_X) {
+    if (p->agg_w != NW || p->x_w != NW) return 0;
+  } else if (p->prologue == SGNN_PRO_FEATURES) {
+    if (p->k_pad != 32 || p->emb != nullptr || p->dim > 3) return 0;
+  } else {
+    return 0;
+  }
+  if (p->residual && p->x_w != NW) return 0;
+  if (p->tail == SGNN_TAIL_PQ && p->pq_hidden != NW) return 0;
+  if (p->tail == SGNN_TAIL_DECODE && (p->dec.hidden != NW || p->dec.out > 8)) return 0;
+  const int smem = node_fast_smem(p->blob_bytes);
+  if (smem > 227 * 1024) return 0;
+  static int sms = 0;
+  if (sms == 0) {
+    int dev = 0;
+    SGNN_CUDA(cudaGetDevice(&dev));
+    SGNN_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  }
+  const int n_tiles = sgnn_ceil_div(p->n_rows, kTileRows);
+  int grid = n_tiles < sms ? n_tiles : sms;
+  if (grid < 1) grid = 1;
+  SGNN_ENSURE_SMEM(node_fast_kernel, smem);
+  node_fast_kernel<<<grid, kNodeFastThreads, smem, (cudaStream_t)stream>>>(*p);
+  SGNN_LAUNCH_CHECK();
+  return 1;
+}

@@ -14,6 +14,8 @@
 //                       FFMA, then the Euler integrator (_decoder_postprocessor, :381-411)
 // A persistent CTA of 128 threads walks 128-node tiles; thread t owns row t in all epilogues.
 // Algorithmic HBM bytes per node and layer: 4*(agg_w + x_w) read + 4*out + 8*pq_hidden written.
+#include <stdlib.h>
+
 #include "mlp_tile.cuh"
 
 namespace sgnn {
@@ -296,6 +298,8 @@ extern "C" size_t sgnn_node_smem_bytes(const SgnnNodeParams* p, int tc) {
   return (size_t)node_smem(*p, tc != 0, node_streamed(*p, tc != 0)).total;
 }
 
+int sgnn_node_fast_try(const SgnnNodeParams* p, void* stream);     // node_fast.cu
+
 extern "C" int sgnn_node_fwd(const SgnnNodeParams* p, int use_tensor_cores, int grid, void* stream) {
   SGNN_CHECK_ARG(p->k_pad % 32 == 0 && p->k_pad >= 32 && p->k_pad <= 256, "node: k_pad=%d must be a multiple of 32 in [32,256]", p->k_pad);
   SGNN_CHECK_ARG(p->k_in <= p->k_pad, "node: k_in > k_pad");
@@ -316,6 +320,10 @@ extern "C" int sgnn_node_fwd(const SgnnNodeParams* p, int use_tensor_cores, int 
   }
   SGNN_CHECK_ARG(p->blob_bytes % 16 == 0, "node: blob size must be a multiple of 16");
   if (p->n_rows <= 0) return SGNN_OK;
+  if (use_tensor_cores && !getenv("SGNN_NODE_GENERIC")) {      // throughput kernel for 64-wide latents
+    const int r = sgnn_node_fast_try(p, stream);
+    if (r != 0) return r < 0 ? r : SGNN_OK;
+  }
   const int streamed = node_streamed(*p, use_tensor_cores);
   const NodeSmem L = node_smem(*p, use_tensor_cores, streamed);
   SGNN_CHECK_ARG(p->blob_bytes >= SGNN_VEC_REGION_BYTES, "node: blob lacks the vector region");

@@ -1,4 +1,4 @@
-"""GPU: the throughput edge-layer kernel (4 tile workers per SM, hidden activations through TMEM)
+"""GPU: the throughput edge-layer and node kernels (4 tile workers per SM, hidden activations through TMEM)
 must reproduce the one-tile-per-CTA kernel it replaces, on graphs with many tiles, ragged tails,
 CSR rows straddling warps/tiles (degree 20) and nmlp_layers in {1, 2}."""
 import os
@@ -27,14 +27,17 @@ def test_fast_equals_generic(regime, nx, ny, nmlp):
     n = pos.shape[0]
     types = traj["particle_types"].cuda()
     os.environ.pop("SGNN_EDGE_GENERIC", None)
+    os.environ.pop("SGNN_NODE_GENERIC", None)
     a, sa = sim.predict_positions(pos[:, :11], [n], types)
     b, sb = sim.predict_positions(pos[:, :11], [n], types)
     assert torch.equal(a, b)                                   # deterministic
     os.environ["SGNN_EDGE_GENERIC"] = "1"
+    os.environ["SGNN_NODE_GENERIC"] = "1"
     try:
         c, sc = sim.predict_positions(pos[:, :11], [n], types)
     finally:
         os.environ.pop("SGNN_EDGE_GENERIC", None)
+        os.environ.pop("SGNN_NODE_GENERIC", None)
     torch.cuda.synchronize()
     assert torch.isfinite(a).all()
     err = (a - c).abs().max().item()
