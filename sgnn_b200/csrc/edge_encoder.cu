@@ -7,6 +7,8 @@
 // The first Linear has k_in = dim + 1 = 3 inputs: it is evaluated with FFMA by the row's
 // thread (a K = 3 GEMM would waste a whole 32-wide K-block); the remaining layers are tcgen05 GEMMs.
 // Algorithmic HBM bytes per edge: 8 (src, tgt) + 4 * out written; positions are L2-resident gathers.
+#include <stdlib.h>
+
 #include "mlp_tile.cuh"
 
 namespace sgnn {
@@ -135,6 +137,8 @@ extern "C" size_t sgnn_edge_encoder_smem_bytes(int blob_bytes, int hidden, int o
   return (size_t)edge_enc_smem(blob_bytes, hidden, out, tc != 0, st).total;
 }
 
+int sgnn_edge_encoder_fast_try(const SgnnEdgeEncoderParams* p, void* stream);   // edge_encoder_fast.cu
+
 extern "C" int sgnn_edge_encoder_fwd(const SgnnEdgeEncoderParams* p, int use_tensor_cores, int grid,
                                      void* stream) {
   SGNN_CHECK_ARG(p->mlp.n_hidden >= 1 && p->mlp.n_hidden <= SGNN_MAX_HIDDEN, "edge_encoder: n_hidden=%d", p->mlp.n_hidden);
@@ -146,6 +150,10 @@ extern "C" int sgnn_edge_encoder_fwd(const SgnnEdgeEncoderParams* p, int use_ten
   SGNN_CHECK_ARG(p->feat != nullptr || p->k_in == p->dim + 1, "edge_encoder: k_in must be dim+1");
   SGNN_CHECK_ARG(p->blob_bytes % 16 == 0, "edge_encoder: blob size must be a multiple of 16");
   if (p->max_tiles <= 0) return SGNN_OK;
+  if (use_tensor_cores && !getenv("SGNN_ENC_GENERIC")) {
+    const int r = sgnn_edge_encoder_fast_try(p, stream);
+    if (r != 0) return r < 0 ? r : SGNN_OK;
+  }
   const int streamed = edge_enc_streamed(p->blob_bytes, p->mlp.hidden, p->mlp.out, use_tensor_cores);
   const int smem = edge_enc_smem(p->blob_bytes, p->mlp.hidden, p->mlp.out, use_tensor_cores, streamed).total;
   SGNN_CHECK_ARG(p->blob_bytes >= SGNN_VEC_REGION_BYTES, "edge_encoder: blob lacks the vector region");

@@ -111,13 +111,28 @@ __global__ void __launch_bounds__(kFastThreads, 1) edge_layer_fast_kernel(const 
                   &wk->bar_e);
   mbar_wait(&misc->bar_w, 0);
   uint32_t phase_e = 0, phase_m = 0;
+  // sender / receiver of this thread's row, loaded one tile ahead so that the P/Q rows of the NEXT
+  // tile can be pulled into L2 while this tile computes (PQ is 512 B per node: at 1M particles it
+  // does not fit in L2 and a cold gather costs a full HBM round trip with the whole worker stalled)
+  int s_nx = 0, t_nx = -3;
+  if (tile0 < n_tiles && tile0 * kTileRows + wt < n_edges) {
+    s_nx = __ldg(p.src + tile0 * kTileRows + wt);
+    t_nx = __ldg(p.tgt + tile0 * kTileRows + wt);
+  }
 
   for (int tile = tile0; tile < n_tiles; tile += stride) {
     const int e0 = tile * kTileRows;
     const int nvalid = n_edges - e0 < kTileRows ? n_edges - e0 : kTileRows;
     const bool valid = wt < nvalid;
-    const int s = valid ? __ldg(p.src + e0 + wt) : 0;
-    const int t = valid ? __ldg(p.tgt + e0 + wt) : -3;
+    const int s = s_nx, t = t_nx;
+    {
+      const long en = (long)(tile + stride) * kTileRows + wt;
+      s_nx = 0; t_nx = -3;
+      if (en < n_edges) {
+        s_nx = __ldg(p.src + en);
+        t_nx = __ldg(p.tgt + en);
+      }
+    }
     if (wt < 8) wk->piece_flag[wt] = 0;
     wk->tgt_s[wt] = t;             // read back by this row's own warp only (after __syncwarp)
 
@@ -148,6 +163,16 @@ __global__ void __launch_bounds__(kFastThreads, 1) edge_layer_fast_kernel(const 
         const float4 a = __ldg(prow + j), b = __ldg(qrow + j);
         pq[4 * j] = a.x + b.x; pq[4 * j + 1] = a.y + b.y;
         pq[4 * j + 2] = a.z + b.z; pq[4 * j + 3] = a.w + b.w;
+      }
+    }
+
+    if (t_nx >= 0) {
+      const char* pn = reinterpret_cast<const char*>(p.pq + (long)t_nx * 2 * HID);
+      const char* qn = reinterpret_cast<const char*>(p.pq + (long)s_nx * 2 * HID + HID);
+#pragma unroll
+      for (int b = 0; b < HID * 4; b += 128) {
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(pn + b));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(qn + b));
       }
     }
 

@@ -33,11 +33,13 @@ def test_fast_equals_generic(regime, nx, ny, nmlp):
     assert torch.equal(a, b)                                   # deterministic
     os.environ["SGNN_EDGE_GENERIC"] = "1"
     os.environ["SGNN_NODE_GENERIC"] = "1"
+    os.environ["SGNN_ENC_GENERIC"] = "1"
     try:
         c, sc = sim.predict_positions(pos[:, :11], [n], types)
     finally:
         os.environ.pop("SGNN_EDGE_GENERIC", None)
         os.environ.pop("SGNN_NODE_GENERIC", None)
+        os.environ.pop("SGNN_ENC_GENERIC", None)
     torch.cuda.synchronize()
     assert torch.isfinite(a).all()
     err = (a - c).abs().max().item()
