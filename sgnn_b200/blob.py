@@ -61,6 +61,9 @@ class BlobBuilder:
                                          C.c_void_p(blob.data_ptr() + off), L.stream_ptr()))
         for foff, t in self._vectors:
             blob[foff:foff + t.numel()].copy_(t.detach().reshape(-1).float())
+        # kernels stage the blob BEFORE their programmatic-dependent-launch wait (it is constant
+        # for them): make sure the packing above has finished before anything can be launched
+        torch.cuda.current_stream().synchronize()
         return blob, total
 
 

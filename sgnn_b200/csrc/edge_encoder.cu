@@ -43,6 +43,8 @@ constexpr int kMaxEdgeFeat = 8;
 template <bool TC>
 __global__ void __launch_bounds__(kThreads) edge_encoder_kernel(const SgnnEdgeEncoderParams p,
                                                                 const int streamed) {
+  pdl_launch_dependents();
+  pdl_wait();
   char* smem = smem_base_1024();
   const int hidden = p.mlp.hidden, out = p.mlp.out;
   const int w = hidden > out ? hidden : out;
@@ -162,10 +164,10 @@ extern "C" int sgnn_edge_encoder_fwd(const SgnnEdgeEncoderParams* p, int use_ten
   if (grid < 1) grid = 1;
   if (use_tensor_cores) {
     SGNN_ENSURE_SMEM(edge_encoder_kernel<true>, smem);
-    edge_encoder_kernel<true><<<grid, kThreads, smem, (cudaStream_t)stream>>>(*p, streamed);
+    SGNN_CUDA(sgnn_launch((edge_encoder_kernel<true>), dim3(grid), dim3(kThreads), smem, (cudaStream_t)stream, *p, streamed));
   } else {
     SGNN_ENSURE_SMEM(edge_encoder_kernel<false>, smem);
-    edge_encoder_kernel<false><<<grid, kThreads, smem, (cudaStream_t)stream>>>(*p, streamed);
+    SGNN_CUDA(sgnn_launch((edge_encoder_kernel<false>), dim3(grid), dim3(kThreads), smem, (cudaStream_t)stream, *p, streamed));
   }
   SGNN_LAUNCH_CHECK();
   return SGNN_OK;

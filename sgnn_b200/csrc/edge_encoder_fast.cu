@@ -35,9 +35,7 @@ __global__ void __launch_bounds__(kEncFastThreads, 1) edge_encoder_fast_kernel(c
   EncFastMisc* misc = reinterpret_cast<EncFastMisc*>(smem + stage_off + kEncWorkers * kTileRows * EW * 4);
   const int tid = threadIdx.x, w = tid >> 7, wt = tid & 127, wq = wt >> 5;
   char* stage = smem + stage_off + w * (kTileRows * EW * 4);     // this worker's output tile image
-  const int n_edges = p.rowptr ? p.rowptr[p.n_nodes] : p.n_nodes;
-  const int n_tiles = (n_edges + kTileRows - 1) / kTileRows;
-
+  pdl_launch_dependents();
   if (tid == 0) {
     mbar_init(&misc->bar_w, 1);
     for (int i = 0; i < kEncWorkers; ++i) mbar_init(&misc->bar_m[i], 1);
@@ -53,6 +51,9 @@ __global__ void __launch_bounds__(kEncFastThreads, 1) edge_encoder_fast_kernel(c
   uint64_t* bar = &misc->bar_m[w];
   uint32_t phase = 0;
   mbar_wait(&misc->bar_w, 0);
+  pdl_wait();          // everything above touched only shared/tensor memory and the constant weights
+  const int n_edges = p.rowptr ? p.rowptr[p.n_nodes] : p.n_nodes;
+  const int n_tiles = (n_edges + kTileRows - 1) / kTileRows;
   const uint32_t sW = smem_u32(smem);
   const int nh = p.mlp.n_hidden;
   const int tile_floats = kTileRows * EW;
@@ -197,11 +198,10 @@ int sgnn_edge_encoder_fast_try(const SgnnEdgeEncoderParams* p, void* stream) {
   if (grid < 1) grid = 1;
   if (p->k_in == 3) {
     SGNN_ENSURE_SMEM(edge_encoder_fast_kernel<3>, smem);
-    edge_encoder_fast_kernel<3><<<grid, kEncFastThreads, smem, (cudaStream_t)stream>>>(*p);
+    SGNN_CUDA(sgnn_launch((edge_encoder_fast_kernel<3>), dim3(grid), dim3(kEncFastThreads), smem, (cudaStream_t)stream, *p));
   } else {
     SGNN_ENSURE_SMEM(edge_encoder_fast_kernel<4>, smem);
-    edge_encoder_fast_kernel<4><<<grid, kEncFastThreads, smem, (cudaStream_t)stream>>>(*p);
+    SGNN_CUDA(sgnn_launch((edge_encoder_fast_kernel<4>), dim3(grid), dim3(kEncFastThreads), smem, (cudaStream_t)stream, *p));
   }
-  SGNN_LAUNCH_CHECK();
   return 1;
 }

@@ -59,6 +59,8 @@ __device__ __forceinline__ float m_tile_read(const float* m, int row, int col, i
 template <bool TC>
 __global__ void __launch_bounds__(kThreads) edge_layer_kernel(const SgnnEdgeLayerParams p,
                                                               const int streamed) {
+  pdl_launch_dependents();
+  pdl_wait();
   char* smem = smem_base_1024();
   const int hidden = p.mlp.hidden, out = p.mlp.out, he = p.he, nh = p.mlp.n_hidden;
   const int w = hidden > out ? hidden : out;
@@ -285,10 +287,10 @@ extern "C" int sgnn_edge_layer_fwd(const SgnnEdgeLayerParams* p, int use_tensor_
   if (grid < 1) grid = 1;
   if (use_tensor_cores) {
     SGNN_ENSURE_SMEM(edge_layer_kernel<true>, smem);
-    edge_layer_kernel<true><<<grid, kThreads, smem, (cudaStream_t)stream>>>(*p, streamed);
+    SGNN_CUDA(sgnn_launch((edge_layer_kernel<true>), dim3(grid), dim3(kThreads), smem, (cudaStream_t)stream, *p, streamed));
   } else {
     SGNN_ENSURE_SMEM(edge_layer_kernel<false>, smem);
-    edge_layer_kernel<false><<<grid, kThreads, smem, (cudaStream_t)stream>>>(*p, streamed);
+    SGNN_CUDA(sgnn_launch((edge_layer_kernel<false>), dim3(grid), dim3(kThreads), smem, (cudaStream_t)stream, *p, streamed));
   }
   SGNN_LAUNCH_CHECK();
   return SGNN_OK;

@@ -84,9 +84,7 @@ __global__ void __launch_bounds__(kFastThreads, 1) edge_layer_fast_kernel(const 
   constexpr int tile_bytes = kTileRows * HE * 4;
   const int nh = p.mlp.n_hidden;
 
-  const int n_edges = p.rowptr[p.n_nodes];
-  const int n_tiles = (n_edges + kTileRows - 1) / kTileRows;
-
+  pdl_launch_dependents();
   if (tid == 0) {
     mbar_init(&misc->bar_w, 1);
     for (int i = 0; i < kWorkers; ++i) {
@@ -100,6 +98,9 @@ __global__ void __launch_bounds__(kFastThreads, 1) edge_layer_fast_kernel(const 
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
+  pdl_wait();          // everything above touched only shared/tensor memory and the constant weights
+  const int n_edges = p.rowptr[p.n_nodes];
+  const int n_tiles = (n_edges + kTileRows - 1) / kTileRows;
   const uint32_t tmem_w = misc->tmem_slot + (uint32_t)(w * 2 * REG);     // this worker's columns
   const uint32_t lane_base = (uint32_t)(wq * 32) << 16;
 
@@ -383,7 +384,6 @@ int sgnn_edge_layer_fast_try(const SgnnEdgeLayerParams* p, void* stream) {
   if (grid > sms) grid = sms;
   if (grid < 1) grid = 1;
   SGNN_ENSURE_SMEM((edge_layer_fast_kernel<64, 64, 64>), smem);
-  edge_layer_fast_kernel<64, 64, 64><<<grid, kFastThreads, smem, (cudaStream_t)stream>>>(*p);
-  SGNN_LAUNCH_CHECK();
+  SGNN_CUDA(sgnn_launch((edge_layer_fast_kernel<64, 64, 64>), dim3(grid), dim3(kFastThreads), smem, (cudaStream_t)stream, *p));
   return 1;
 }

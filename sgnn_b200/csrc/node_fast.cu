@@ -80,6 +80,7 @@ __global__ void __launch_bounds__(kNodeFastThreads, 1) node_fast_kernel(const Sg
   const int tid = threadIdx.x, w = tid >> 7, wt = tid & 127, wq = wt >> 5;
   const int n_tiles = (p.n_rows + kTileRows - 1) / kTileRows;
 
+  pdl_launch_dependents();
   if (tid == 0) {
     mbar_init(&misc->bar_w, 1);
     for (int i = 0; i < kNodeWorkers; ++i) mbar_init(&misc->bar_m[i], 1);
@@ -97,6 +98,7 @@ __global__ void __launch_bounds__(kNodeFastThreads, 1) node_fast_kernel(const Sg
   uint64_t* bar = &misc->bar_m[w];
   uint32_t phase = 0;
   mbar_wait(&misc->bar_w, 0);
+  pdl_wait();          // everything above touched only shared/tensor memory and the constant weights
   const uint32_t sW = smem_u32(smem);
   const int nh = p.mlp.n_hidden;
 
@@ -351,7 +353,6 @@ int sgnn_node_fast_try(const SgnnNodeParams* p, void* stream) {
   int grid = n_tiles < sms ? n_tiles : sms;
   if (grid < 1) grid = 1;
   SGNN_ENSURE_SMEM(node_fast_kernel, smem);
-  node_fast_kernel<<<grid, kNodeFastThreads, smem, (cudaStream_t)stream>>>(*p);
-  SGNN_LAUNCH_CHECK();
+  SGNN_CUDA(sgnn_launch(node_fast_kernel, dim3(grid), dim3(kNodeFastThreads), smem, (cudaStream_t)stream, *p));
   return 1;
 }

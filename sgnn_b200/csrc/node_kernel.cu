@@ -132,6 +132,8 @@ __device__ __forceinline__ void prologue_rows(const SgnnNodeParams& p, char* a_t
 
 template <bool TC>
 __global__ void __launch_bounds__(kThreads) node_kernel(const SgnnNodeParams p, const int streamed) {
+  pdl_launch_dependents();
+  pdl_wait();
   char* smem = smem_base_1024();
   const NodeSmem L = node_smem(p, TC, streamed != 0);
   const float* blob_f = reinterpret_cast<const float*>(smem);
@@ -334,10 +336,10 @@ extern "C" int sgnn_node_fwd(const SgnnNodeParams* p, int use_tensor_cores, int 
   if (grid < 1) grid = 1;
   if (use_tensor_cores) {
     SGNN_ENSURE_SMEM(node_kernel<true>, L.total);
-    node_kernel<true><<<grid, kThreads, L.total, (cudaStream_t)stream>>>(*p, streamed);
+    SGNN_CUDA(sgnn_launch((node_kernel<true>), dim3(grid), dim3(kThreads), L.total, (cudaStream_t)stream, *p, streamed));
   } else {
     SGNN_ENSURE_SMEM(node_kernel<false>, L.total);
-    node_kernel<false><<<grid, kThreads, L.total, (cudaStream_t)stream>>>(*p, streamed);
+    SGNN_CUDA(sgnn_launch((node_kernel<false>), dim3(grid), dim3(kThreads), L.total, (cudaStream_t)stream, *p, streamed));
   }
   SGNN_LAUNCH_CHECK();
   return SGNN_OK;

@@ -58,8 +58,12 @@ __device__ __forceinline__ int cell_coord(float x, float lo, double inv_h, int n
   return min(max(c, 0), nc - 1);
 }
 
-__global__ void bbox_init_kernel(int* bbox) {
-  if (threadIdx.x < 4) {
+// also zeroes the cell counters (replaces a memset node between two kernels)
+__global__ void bbox_init_kernel(int* bbox, int* cell_count, int n_cells) {
+  pdl_launch_dependents();
+  pdl_wait();
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_cells; i += gridDim.x * blockDim.x) cell_count[i] = 0;
+  if (blockIdx.x == 0 && threadIdx.x < 4) {
     bbox[threadIdx.x] = 0x7fffffff;
     bbox[4 + threadIdx.x] = (int)0x80000000;
   }
@@ -67,6 +71,8 @@ __global__ void bbox_init_kernel(int* bbox) {
 
 __global__ void __launch_bounds__(256) bbox_kernel(const float* __restrict__ pos, long stride, int n,
                                                    int dim, int* __restrict__ bbox) {
+  pdl_launch_dependents();
+  pdl_wait();
   float mn[3] = {INFINITY, INFINITY, INFINITY}, mx[3] = {-INFINITY, -INFINITY, -INFINITY};
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     for (int d = 0; d < dim; ++d) {
@@ -96,14 +102,10 @@ __device__ __forceinline__ int example_of(const int* __restrict__ ptr, int n_exa
   return lo;
 }
 
-__global__ void __launch_bounds__(256)
-cell_count_kernel(const float* __restrict__ pos, long stride, int n, int dim,
-                  const int* __restrict__ ex_ptr, int n_examples, const int* __restrict__ bbox,
-                  float h0, int cell_cap, int* __restrict__ cell_of, int* __restrict__ rank,
-                  int* __restrict__ cell_count) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const CellGrid g = make_grid(bbox, dim, h0, n_examples, cell_cap);
+__device__ __forceinline__ void cell_count_one(int i, const float* __restrict__ pos, long stride, int dim,
+                                               const int* __restrict__ ex_ptr, int n_examples,
+                                               const CellGrid& g, int* __restrict__ cell_of,
+                                               int* __restrict__ rank, int* __restrict__ cell_count) {
   int c = example_of(ex_ptr, n_examples, i);
   for (int d = dim - 1; d >= 0; --d)
     c = c * g.nc[d] + cell_coord(pos[(long)i * stride + d], g.lo[d], g.inv_h, g.nc[d]);
@@ -112,11 +114,21 @@ cell_count_kernel(const float* __restrict__ pos, long stride, int n, int dim,
 }
 
 __global__ void __launch_bounds__(256)
-cell_fill_kernel(const float* __restrict__ pos, long stride, int n, int dim,
-                 const int* __restrict__ cell_of, const int* __restrict__ rank,
-                 const int* __restrict__ cell_start, float4* __restrict__ sorted) {
+cell_count_kernel(const float* __restrict__ pos, long stride, int n, int dim,
+                  const int* __restrict__ ex_ptr, int n_examples, const int* __restrict__ bbox,
+                  float h0, int cell_cap, int* __restrict__ cell_of, int* __restrict__ rank,
+                  int* __restrict__ cell_count) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
+  const CellGrid g = make_grid(bbox, dim, h0, n_examples, cell_cap);
+  cell_count_one(i, pos, stride, dim, ex_ptr, n_examples, g, cell_of, rank, cell_count);
+}
+
+__device__ __forceinline__ void cell_fill_one(int i, const float* __restrict__ pos, long stride, int dim,
+                                              const int* __restrict__ cell_of, const int* __restrict__ rank,
+                                              const int* __restrict__ cell_start, float4* __restrict__ sorted) {
   float4 e;
   e.x = pos[(long)i * stride];
   e.y = dim > 1 ? pos[(long)i * stride + 1] : 0.f;
@@ -125,15 +137,23 @@ cell_fill_kernel(const float* __restrict__ pos, long stride, int n, int dim,
   sorted[cell_start[cell_of[i]] + rank[i]] = e;
 }
 
-// One thread per query, taken in cell-sorted order (neighbouring threads share candidates).
-__global__ void __launch_bounds__(128)
-neighbor_kernel(int n, int dim, const int* __restrict__ ex_ptr, int n_examples,
-                const int* __restrict__ bbox, float h0, int cell_cap, float r2, int kq, int loop,
-                int slab, const int* __restrict__ cell_of, const int* __restrict__ cell_start,
-                const float4* __restrict__ sorted, int* __restrict__ cnt, int* __restrict__ nbr) {
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= n) return;
-  const CellGrid g = make_grid(bbox, dim, h0, n_examples, cell_cap);
+__global__ void __launch_bounds__(256)
+cell_fill_kernel(const float* __restrict__ pos, long stride, int n, int dim,
+                 const int* __restrict__ cell_of, const int* __restrict__ rank,
+                 const int* __restrict__ cell_start, float4* __restrict__ sorted) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  cell_fill_one(i, pos, stride, dim, cell_of, rank, cell_start, sorted);
+}
+
+// Neighbours of the t-th particle in cell-sorted order (neighbouring threads share candidates).
+__device__ __forceinline__ void neighbor_one(int t, int dim, const CellGrid& g, float r2, int kq, int loop,
+                                             int slab, const int* __restrict__ cell_of,
+                                             const int* __restrict__ cell_start,
+                                             const float4* __restrict__ sorted, int* __restrict__ cnt,
+                                             int* __restrict__ nbr) {
   const float4 q = sorted[t];
   const int i = __float_as_int(q.w);
   int c = cell_of[i];
@@ -171,9 +191,24 @@ neighbor_kernel(int n, int dim, const int* __restrict__ ex_ptr, int n_examples,
   cnt[i] = kept;
 }
 
+__global__ void __launch_bounds__(128)
+neighbor_kernel(int n, int dim, const int* __restrict__ ex_ptr, int n_examples,
+                const int* __restrict__ bbox, float h0, int cell_cap, float r2, int kq, int loop,
+                int slab, const int* __restrict__ cell_of, const int* __restrict__ cell_start,
+                const float4* __restrict__ sorted, int* __restrict__ cnt, int* __restrict__ nbr) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  const CellGrid g = make_grid(bbox, dim, h0, n_examples, cell_cap);
+  neighbor_one(t, dim, g, r2, kq, loop, slab, cell_of, cell_start, sorted, cnt, nbr);
+}
+
 __global__ void __launch_bounds__(256)
 compact_kernel(int n, int slab, const int* __restrict__ rowptr, const int* __restrict__ nbr,
                int* __restrict__ src, int* __restrict__ tgt) {
+  pdl_launch_dependents();
+  pdl_wait();
   const long gid = (long)blockIdx.x * blockDim.x + threadIdx.x;
   const int i = (int)(gid / slab), k = (int)(gid % slab);
   if (i >= n) return;
@@ -226,6 +261,13 @@ extern "C" size_t sgnn_radius_graph_workspace_bytes(int n, int max_neighbors) {
   return carve(nullptr, n, max_neighbors + 1).bytes + 256;
 }
 
+// number of kernels one sgnn_radius_graph_csr call launches (host-side launch accounting)
+extern "C" int sgnn_radius_graph_launches(int n, int max_neighbors) {
+  if (n <= 0) return 0;
+  const int cell_items = 2 * n + 1024 + 1;
+  return 6 + (cell_items <= kScanChunk ? 1 : 3) + (n <= kScanChunk ? 1 : 3);
+}
+
 extern "C" int sgnn_radius_graph_csr(const float* pos, long pos_stride, int n, int dim,
                                      const int* example_ptr, int n_examples, double r,
                                      int max_neighbors, int loop, void* workspace,
@@ -250,24 +292,24 @@ extern "C" int sgnn_radius_graph_csr(const float* pos, long pos_stride, int n, i
   const float h0 = (float)(r * (1.0 + 1e-5)) ;     // cell edge just above r
   const int kq = loop ? max_neighbors : max_neighbors + 1;
 
-  bbox_init_kernel<<<1, 32, 0, st>>>(w.bbox);
-  SGNN_CUDA(cudaMemsetAsync(w.cell_count, 0, sizeof(int) * ((size_t)w.cell_cap + 2), st));
+  SGNN_CUDA(sgnn_launch(bbox_init_kernel, dim3(sgnn_ceil_div(w.cell_cap + 2, 1024)), dim3(256), 0, st, w.bbox,
+                        w.cell_count, w.cell_cap + 2));
   const int nb256 = sgnn_ceil_div(n, 256);
-  bbox_kernel<<<nb256 < 592 ? nb256 : 592, 256, 0, st>>>(pos, pos_stride, n, dim, w.bbox);
-  cell_count_kernel<<<nb256, 256, 0, st>>>(pos, pos_stride, n, dim, example_ptr, n_examples, w.bbox,
-                                           h0, w.cell_cap, w.cell_of, w.rank, w.cell_count);
+  SGNN_CUDA(sgnn_launch(bbox_kernel, dim3(nb256 < 592 ? nb256 : 592), dim3(256), 0, st, pos, pos_stride, n, dim, w.bbox));
+  SGNN_CUDA(sgnn_launch(cell_count_kernel, dim3(nb256), dim3(256), 0, st, pos, pos_stride, n, dim, example_ptr, n_examples, w.bbox,
+                                           h0, w.cell_cap, w.cell_of, w.rank, w.cell_count));
   SGNN_LAUNCH_CHECK();
   int rc = exclusive_scan_i32(w.cell_count, w.cell_count, w.cell_cap + 1, w.scan_tmp, st);
   if (rc) return rc;
-  cell_fill_kernel<<<nb256, 256, 0, st>>>(pos, pos_stride, n, dim, w.cell_of, w.rank, w.cell_count,
-                                          w.sorted);
-  neighbor_kernel<<<sgnn_ceil_div(n, 128), 128, 0, st>>>(n, dim, example_ptr, n_examples, w.bbox, h0,
+  SGNN_CUDA(sgnn_launch(cell_fill_kernel, dim3(nb256), dim3(256), 0, st, pos, pos_stride, n, dim, w.cell_of, w.rank, w.cell_count,
+                                          w.sorted));
+  SGNN_CUDA(sgnn_launch(neighbor_kernel, dim3(sgnn_ceil_div(n, 128)), dim3(128), 0, st, n, dim, example_ptr, n_examples, w.bbox, h0,
                                                          w.cell_cap, r2, kq, loop, slab, w.cell_of,
-                                                         w.cell_count, w.sorted, w.cnt, w.nbr);
+                                                         w.cell_count, w.sorted, w.cnt, w.nbr));
   SGNN_LAUNCH_CHECK();
   rc = exclusive_scan_i32(w.cnt, rowptr, n, w.scan_tmp, st);
   if (rc) return rc;
-  compact_kernel<<<sgnn_ceil_div((long)n * slab, 256), 256, 0, st>>>(n, slab, rowptr, w.nbr, src, tgt);
+  SGNN_CUDA(sgnn_launch(compact_kernel, dim3(sgnn_ceil_div((long)n * slab, 256)), dim3(256), 0, st, n, slab, rowptr, w.nbr, src, tgt));
   SGNN_LAUNCH_CHECK();
   return SGNN_OK;
 }

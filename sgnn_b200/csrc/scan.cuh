@@ -8,8 +8,8 @@
 namespace sgnn {
 
 constexpr int kScanThreads = 1024;
-constexpr int kScanItems = 8;
-constexpr int kScanChunk = kScanThreads * kScanItems;  // 8192
+constexpr int kScanItems = 16;
+constexpr int kScanChunk = kScanThreads * kScanItems;  // 16384
 
 // block-wide exclusive scan of one value per thread; returns the exclusive prefix, total via ref
 __device__ __forceinline__ int block_exclusive_scan(int v, int& total) {
@@ -49,6 +49,8 @@ template <int MODE>
 __global__ void __launch_bounds__(kScanThreads) scan_chunk_kernel(const int* __restrict__ in,
                                                                   int* __restrict__ out, int n,
                                                                   int* __restrict__ sums) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int base = blockIdx.x * kScanChunk + threadIdx.x * kScanItems;
   int v[kScanItems];
   int s = 0;
@@ -72,6 +74,8 @@ __global__ void __launch_bounds__(kScanThreads) scan_chunk_kernel(const int* __r
 
 __global__ void scan_add_kernel(int* __restrict__ out, int n, const int* __restrict__ sums,
                                 int nblocks) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int b = blockIdx.x;
   const int off = sums[b];
   for (int i = threadIdx.x; i < kScanChunk; i += blockDim.x) {
@@ -86,17 +90,17 @@ inline size_t scan_tmp_ints(int n) { return (size_t)sgnn_ceil_div(n, kScanChunk)
 // tmp: scan_tmp_ints(n) ints.  Launches 1 kernel (n <= 8192) or 3.
 inline int exclusive_scan_i32(const int* in, int* out, int n, int* tmp, cudaStream_t st) {
   if (n <= kScanChunk) {
-    scan_chunk_kernel<0><<<1, kScanThreads, 0, st>>>(in, out, n, nullptr);
+    SGNN_CUDA(sgnn_launch((scan_chunk_kernel<0>), dim3(1), dim3(kScanThreads), 0, st, in, out, n, nullptr));
     SGNN_LAUNCH_CHECK();
     return SGNN_OK;
   }
   const int nb = sgnn_ceil_div(n, kScanChunk);
   SGNN_CHECK_ARG(nb <= kScanChunk, "exclusive_scan_i32: n=%d too large", n);
-  scan_chunk_kernel<1><<<nb, kScanThreads, 0, st>>>(in, out, n, tmp);
+  SGNN_CUDA(sgnn_launch((scan_chunk_kernel<1>), dim3(nb), dim3(kScanThreads), 0, st, in, out, n, tmp));
   SGNN_LAUNCH_CHECK();
-  scan_chunk_kernel<0><<<1, kScanThreads, 0, st>>>(tmp, tmp, nb, nullptr);
+  SGNN_CUDA(sgnn_launch((scan_chunk_kernel<0>), dim3(1), dim3(kScanThreads), 0, st, tmp, tmp, nb, nullptr));
   SGNN_LAUNCH_CHECK();
-  scan_add_kernel<<<nb, 256, 0, st>>>(out, n, tmp, nb);
+  SGNN_CUDA(sgnn_launch(scan_add_kernel, dim3(nb), dim3(1024), 0, st, out, n, tmp, nb));
   SGNN_LAUNCH_CHECK();
   return SGNN_OK;
 }

@@ -74,7 +74,7 @@ class RadiusGraph:
             C.c_void_p(pos.data_ptr()), C.c_long(pos_stride), self.n, dim, L.ptr(example_ptr),
             example_ptr.numel() - 1, C.c_double(radius), self.k, int(self.loop), L.ptr(self.ws),
             C.c_size_t(self.ws_bytes), L.ptr(self.csr.rowptr), L.ptr(self.csr.src),
-            L.ptr(self.csr.tgt), L.stream_ptr()), launches=9)
+            L.ptr(self.csr.tgt), L.stream_ptr()), launches=L.lib().sgnn_radius_graph_launches(self.n, self.k))
         return self.csr
 
 
