@@ -83,6 +83,9 @@ int sgnn_node_features(const float* pos_seq, long stride, int n, int seq_len, in
 int sgnn_edge_features(const float* pos, long stride, int dim, float radius, const int* src,
                        const int* tgt, int n_edges, float* out, void* stream);
 
+/* debug: %globaltimer stamps of the throughput node kernel's phases (CTA 0); NULL switches it off */
+int sgnn_debug_node_timeline(unsigned long long* buf);
+
 /* self-test of the GEMM tile primitive (tests/test_gemm_tile_gpu.py)                        */
 int sgnn_debug_gemm(const float* a, const float* wimg, int k, int n, float* d, int tc, void* stream);
 

@@ -16,6 +16,21 @@
 
 namespace sgnn {
 
+// optional in-kernel timeline (compile with -DSGNN_TIMELINE; profiles/node_timeline.py):
+// %globaltimer stamps of CTA 0 / thread 0 into a user buffer.  Compiled out of the product build.
+__device__ unsigned long long* g_node_timeline = nullptr;
+__device__ __forceinline__ void stamp(int slot) {
+#ifdef SGNN_TIMELINE
+  if (g_node_timeline != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    g_node_timeline[slot] = t;
+  }
+#else
+  (void)slot;
+#endif
+}
+
 constexpr int kNodeWorkers = 4;
 constexpr int kNodeFastThreads = kNodeWorkers * kThreads;
 constexpr int NW = 64;                               // every width handled by this kernel
@@ -81,6 +96,7 @@ __global__ void __launch_bounds__(kNodeFastThreads, 1) node_fast_kernel(const Sg
   const int n_tiles = (p.n_rows + kTileRows - 1) / kTileRows;
 
   pdl_launch_dependents();
+  stamp(0);
   if (tid == 0) {
     mbar_init(&misc->bar_w, 1);
     for (int i = 0; i < kNodeWorkers; ++i) mbar_init(&misc->bar_m[i], 1);
@@ -97,8 +113,11 @@ __global__ void __launch_bounds__(kNodeFastThreads, 1) node_fast_kernel(const Sg
   const uint32_t tA = RA + lane_base, tD = RD + lane_base;            // this thread's lanes
   uint64_t* bar = &misc->bar_m[w];
   uint32_t phase = 0;
+  stamp(1);
   mbar_wait(&misc->bar_w, 0);
-  pdl_wait();          // everything above touched only shared/tensor memory and the constant weights
+  stamp(2);
+  pdl_wait();
+  stamp(3);          // everything above touched only shared/tensor memory and the constant weights
   const uint32_t sW = smem_u32(smem);
   const int nh = p.mlp.n_hidden;
 
@@ -126,12 +145,15 @@ __global__ void __launch_bounds__(kNodeFastThreads, 1) node_fast_kernel(const Sg
           }
         }
       }
+      stamp(4);
       row_to_tmem(tA, v);
       run_mma(w, wt, bar, phase, [&] { umma_gemm_tf32_ts(RD, RA, sW + p.mlp.w_off[0], NW, NW); });
+      stamp(5);
 #pragma unroll
       for (int j = 0; j < NW; ++j) v[j] = 0.f;
       if (valid) load_row64(p.x_in + i * NW, v);
       row_to_tmem(tA, v);
+      stamp(6);
       run_mma(w, wt, bar, phase, [&] {           // x columns of W0: K-blocks 2,3 ; accumulate
         const uint32_t idesc = umma_idesc_tf32(kTileRows, NW);
         const uint32_t wb = sW + p.mlp.w_off[0] + 2 * NW * kKBlockBytes;
@@ -174,6 +196,7 @@ __global__ void __launch_bounds__(kNodeFastThreads, 1) node_fast_kernel(const Sg
       run_mma(w, wt, bar, phase, [&] { umma_gemm_tf32_ts(RD, RA, sW + p.mlp.w_off[0], 32, NW); });
     }
 
+    stamp(7);
     // ---- bias + ReLU in place, hidden layers ping-pong A <-> D, then the output Linear ----
     uint32_t cur = RD, oth = RA;                         // cur: region holding the fresh accumulator
     for (int l = 0; l < nh; ++l) {
@@ -193,6 +216,7 @@ __global__ void __launch_bounds__(kNodeFastThreads, 1) node_fast_kernel(const Sg
       cur = d; oth = a;
     }
 
+    stamp(8);
     // ---- LayerNorm, residual, x' ----
     {
       const uint32_t tc = cur + lane_base;
@@ -235,6 +259,7 @@ __global__ void __launch_bounds__(kNodeFastThreads, 1) node_fast_kernel(const Sg
       }
     }
 
+    stamp(9);
     // ---- tail: x' (TF32) becomes the A operand in the region that is NOT `cur` ... both are free
     //      now (the accumulator has been read), use region A for x' and region D for the products ----
     if (p.tail == SGNN_TAIL_PQ) {
@@ -316,17 +341,25 @@ __global__ void __launch_bounds__(kNodeFastThreads, 1) node_fast_kernel(const Sg
         }
       }
     }
+    stamp(10);
     tc_fence_before_sync();
     nworker_bar(w);                  // all TMEM reads of this tile retired before the next tile's stores
   }
   tc_fence_before_sync();
   __syncthreads();
   if (tid < 32) tmem_dealloc(misc->tmem_slot, TMEM_COLS);
+  stamp(11);
 }
 
 }  // namespace sgnn
 
 using namespace sgnn;
+
+// debug: device buffer of >= 16 uint64 receiving %globaltimer stamps of the node kernel (NULL = off)
+extern "C" int sgnn_debug_node_timeline(unsigned long long* buf) {
+  SGNN_CUDA(cudaMemcpyToSymbol(g_node_timeline, &buf, sizeof(buf)));
+  return SGNN_OK;
+}
 
 // 1 = launched, 0 = shape not covered (caller uses the generic kernel), < 0 = error
 int sgnn_node_fast_try(const SgnnNodeParams* p, void* stream) {
