@@ -57,6 +57,10 @@ int sgnn_edge_encoder_fwd(const SgnnEdgeEncoderParams* p, int use_tensor_cores, 
  * scatter_add): graph_network.py:173,178-199; multi_scale_gnn.py:84-110,132-157,179-205.   */
 size_t sgnn_edge_layer_smem_bytes(int blob_bytes, int he, int hidden, int out, int tc);
 int sgnn_edge_layer_fwd(const SgnnEdgeLayerParams* p, int use_tensor_cores, int grid, void* stream);
+/* 1 if a layer of this shape can run in GATHER mode (SgnnEdgeLayerParams.wxs_off > 0: the sender
+ * rows are gathered by TMA and multiplied by W1b inside the first GEMM; the producing node kernels
+ * must then use tail SGNN_TAIL_PX).  Same reference lines as sgnn_edge_layer_fwd.               */
+int sgnn_edge_layer_gather_supported(int he, int hidden, int out, int n_hidden, int blob_bytes);
 
 /* Node features + Encoder.node_fn (learned_simulator.py:257-290, graph_network.py:86-90);
  * InteractionNetwork.update + residual (graph_network.py:176,201-222); Decoder + Euler

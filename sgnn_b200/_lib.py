@@ -13,7 +13,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "libsgnn_b200.so")
 MAX_HIDDEN = 3
 
 PRO_FEATURES, PRO_AGG_X, PRO_ROWS = 0, 1, 2
-TAIL_NONE, TAIL_PQ, TAIL_DECODE = 0, 1, 2
+TAIL_NONE, TAIL_PQ, TAIL_DECODE, TAIL_PX = 0, 1, 2, 3
 
 
 class SgnnError(RuntimeError):
@@ -30,7 +30,7 @@ class EdgeLayerParams(C.Structure):
     _fields_ = [("e_tiles", C.c_void_p), ("pq", C.c_void_p), ("src", C.c_void_p),
                 ("tgt", C.c_void_p), ("rowptr", C.c_void_p), ("n_nodes", C.c_int), ("he", C.c_int),
                 ("blob", C.c_void_p), ("blob_bytes", C.c_int), ("mlp", Mlp), ("agg", C.c_void_p),
-                ("head", C.c_void_p), ("max_tiles", C.c_int)]
+                ("head", C.c_void_p), ("max_tiles", C.c_int), ("wxs_off", C.c_int)]
 
 
 class EdgeEncoderParams(C.Structure):

@@ -263,6 +263,7 @@ extern "C" size_t sgnn_edge_layer_smem_bytes(int blob_bytes, int he, int hidden,
 }
 
 int sgnn_edge_layer_fast_try(const SgnnEdgeLayerParams* p, void* stream);   // edge_layer_fast.cu
+int sgnn_edge_layer_gather_launch(const SgnnEdgeLayerParams* p, void* stream);   // edge_layer_ws.cu
 
 extern "C" int sgnn_edge_layer_fwd(const SgnnEdgeLayerParams* p, int use_tensor_cores, int grid,
                                    void* stream) {
@@ -274,6 +275,10 @@ extern "C" int sgnn_edge_layer_fwd(const SgnnEdgeLayerParams* p, int use_tensor_
   SGNN_CHECK_ARG(p->blob_bytes % 16 == 0, "edge_layer: blob size must be a multiple of 16");
   SGNN_CHECK_ARG(p->mlp.has_ln, "edge_layer: the edge MLP ends in a LayerNorm in the reference");
   if (p->max_tiles <= 0 || p->n_nodes <= 0) return SGNN_OK;
+  if (p->wxs_off > 0) {      // gather mode: the Q half of pq holds TF32-rounded node latents, not x W1b^T
+    SGNN_CHECK_ARG(use_tensor_cores, "edge_layer: gather mode needs the tensor-core path");
+    return sgnn_edge_layer_gather_launch(p, stream);
+  }
   if (use_tensor_cores && !getenv("SGNN_EDGE_GENERIC")) {     // throughput kernel where instantiated
     const int r = sgnn_edge_layer_fast_try(p, stream);
     if (r != 0) return r < 0 ? r : SGNN_OK;

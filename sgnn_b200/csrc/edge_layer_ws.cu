@@ -1,0 +1,496 @@
+// Edge side of one message-passing layer, warp-specialised version for 64-wide latents with one
+// hidden layer (reference: InteractionNetwork.message + PyG sum-aggregation,
+// sgnn/single_scale/graph_network.py:173,178-199).
+//
+//   m_e = LN(W2 relu(W1 [x_tgt | x_src | e] + b1) + b2),   agg_i = sum_{e: tgt = i} m_e
+//
+// Split of the first Linear: the receiver term is per NODE (P = x W1a^T + b1, written by the node
+// kernel, read here with near-broadcast loads because edges are receiver-sorted); the sender term
+// and the edge term go through the tensor core as ONE K = 128 product [e0 | x_src] [W1c | W1b]^T.
+// The x_src rows are gathered by the TMA unit (tile::gather4 on a tensor map over the TF32-rounded
+// node latents) straight into the swizzled operand layout: no thread issues a gather load, the L1
+// pipe -- the busiest unit of the previous kernel (profiles/README.md r01f: 64 %) -- carries only
+// the P loads and the segmented-sum scratch.
+//
+// Roles (640 threads, one persistent CTA per SM; registers re-split with setmaxnreg):
+//   warps 0-15  four epilogue groups of 128 threads; group g owns TMEM columns [128g, 128g + 128)
+//               (accumulator 0 / hidden activations in place, accumulator 1) and every 4th tile
+//   warp 16     producer: e0 K-blocks by TMA bulk copy, x_src K-blocks by TMA gather4, into a ring
+//               of 16 KB slots shared by all tiles of the CTA
+//   warp 17     one thread issues every tcgen05.mma, polling the barriers of both GEMMs so that
+//               the second GEMM of tile t never waits behind the loads of tile t + 1
+// Hand-offs are mbarriers only (full/empty per slot; acc0_ready, hid_ready, acc1_ready,
+// region_free per group); the only CTA-wide barriers are at start-up and tear-down.
+#include "mlp_tile.cuh"
+#include "params.h"
+#include "tensormap.cuh"
+
+namespace sgnn {
+
+constexpr int kWsGroups = 4;
+constexpr int kWsEpiThreads = kWsGroups * kThreads;        // 512
+constexpr int kWsThreads = kWsEpiThreads + 128;            // + one warpgroup: producer warp, MMA warp, 2 idle
+constexpr int kWsEpiRegs = 112, kWsAuxRegs = 32;           // setmaxnreg moves registers INSIDE the CTA only: launch at 96, (96-32)*128 released = (112-96)*512 taken
+constexpr int kWsW = 64;                                   // he = hidden = out
+constexpr int kWsSlotBytes = kTileRows * kKBlockBytes;     // 16 KB: 128 rows x one K-block
+constexpr int kWsMaxSlots = 8;
+constexpr int kWsScrRows = 16;
+constexpr int kWsScrStride = 36;
+constexpr int kWsScrFloats = kWsScrRows * kWsScrStride;
+
+struct WsGroup {
+  uint64_t acc0_ready, hid_ready, acc1_ready, region_free;
+  int tgt_s[kTileRows];
+  int piece_tgt[8];
+  int piece_flag[8];
+  float pieces[8 * kWsW];
+};
+struct WsMisc {
+  uint64_t bar_w;
+  uint64_t full[kWsMaxSlots], empty[kWsMaxSlots];
+  uint32_t tmem_slot;
+  int pad;
+  WsGroup g[kWsGroups];
+};
+struct WsSmem {
+  int ring, scratch, misc, total, slots;
+};
+__host__ __device__ inline WsSmem edge_ws_smem(int blob_bytes) {
+  WsSmem s;
+  s.ring = align_up(blob_bytes, 1024);
+  const int fixed = 16 * kWsScrFloats * 4 + (int)sizeof(WsMisc) + 16 + 1024;
+  int slots = (227 * 1024 - s.ring - fixed) / kWsSlotBytes;
+  s.slots = slots > kWsMaxSlots ? kWsMaxSlots : slots;
+  s.scratch = s.ring + s.slots * kWsSlotBytes;
+  s.misc = align_up(s.scratch + 16 * kWsScrFloats * 4, 16);
+  s.total = s.misc + (int)sizeof(WsMisc) + 1024;
+  return s;
+}
+
+__device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// wait with a long hardware suspend hint: 16 epilogue warps that SPIN on try_wait compete with the
+// working warps for instruction fetch (ncu r01h: "no instruction" was 46 % of all stall samples)
+__device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WS_WAIT:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
+      "@p bra WS_DONE;\n\t"
+      "bra WS_WAIT;\n\t"
+      "WS_DONE:\n\t}" ::"r"(smem_u32(bar)),
+      "r"(parity), "r"(0x989680u)
+      : "memory");
+}
+__device__ __forceinline__ float ws_tf32r(float x) { return __uint_as_float(__float_as_uint(x) + 0x1000u); }
+__device__ __forceinline__ void ws_group_bar(int g) {
+  asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "r"(kThreads) : "memory");
+}
+
+// ---------------------------------------------------------------------------------- producer
+__device__ __forceinline__ void ws_producer(const SgnnEdgeLayerParams& p, const CUtensorMap* xmap, char* ring,
+                                            WsMisc* misc, int slots, int n_my, int n_edges, int lane) {
+  uint32_t it = 0;
+  for (int i = 0; i < n_my; ++i) {
+    const long tile = blockIdx.x + (long)i * gridDim.x;
+    const long e = tile * kTileRows + 4 * lane;
+    int4 idx = make_int4(0, 0, 0, 0);
+    if (e + 3 < n_edges) {
+      idx = __ldg(reinterpret_cast<const int4*>(p.src + e));
+    } else {
+      if (e < n_edges) idx.x = __ldg(p.src + e);
+      if (e + 1 < n_edges) idx.y = __ldg(p.src + e + 1);
+      if (e + 2 < n_edges) idx.z = __ldg(p.src + e + 2);
+    }
+#pragma unroll 1
+    for (int kb = 0; kb < 4; ++kb, ++it) {
+      const uint32_t s = it % (uint32_t)slots, use = it / (uint32_t)slots;
+      if (use > 0) mbar_wait_sleep(&misc->empty[s], (use - 1) & 1u);
+      char* dst = ring + s * kWsSlotBytes;
+      if (lane == 0) mbar_arrive_expect_tx(&misc->full[s], kWsSlotBytes);
+      if (kb < 2) {
+        if (lane == 0)
+          tma_bulk_g2s(dst, reinterpret_cast<const char*>(p.e_tiles) + tile * (2 * kWsSlotBytes) + kb * kWsSlotBytes,
+                       kWsSlotBytes, &misc->full[s]);
+      } else {
+        tma_gather4(dst + lane * 512, xmap, (kb - 2) * kKBlock, idx.x, idx.y, idx.z, idx.w, &misc->full[s]);
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------- MMA issuer
+__device__ __forceinline__ void ws_mma(const SgnnEdgeLayerParams& p, uint32_t ring_u32, uint32_t smem_base_u32,
+                                       WsMisc* misc, int slots, int n_my, uint32_t tmem, int wxs_off) {
+  const uint32_t idesc = umma_idesc_tf32(kTileRows, kWsW);
+  const uint32_t w_e = smem_base_u32 + p.mlp.w_off[0], w_x = smem_base_u32 + wxs_off;
+  const uint32_t w_2 = smem_base_u32 + p.mlp.w_off[1];
+  int a = 0, akb = 0, b = 0;
+  uint32_t it = 0;
+  while (b < n_my) {
+    __nanosleep(40);      // polling back-off: this thread must not hog its scheduler's fetch slots
+    if (b < a && mbar_test(&misc->g[b & 3].hid_ready, (uint32_t)(b >> 2) & 1u)) {
+      tc_fence_after_sync();
+      const uint32_t base = tmem + (uint32_t)((b & 3) * 2 * kWsW);
+      umma_gemm_tf32_ts(base + kWsW, base, w_2, kWsW, kWsW);
+      tc_commit(&misc->g[b & 3].acc1_ready);
+      ++b;
+    }
+    if (a < n_my) {
+      if (akb == 0 && a >= kWsGroups &&
+          !mbar_test(&misc->g[a & 3].region_free, (uint32_t)((a >> 2) - 1) & 1u))
+        continue;
+      const uint32_t s = it % (uint32_t)slots, use = it / (uint32_t)slots;
+      if (!mbar_test(&misc->full[s], use & 1u)) continue;
+      tc_fence_after_sync();
+      const uint32_t a_kb = ring_u32 + s * kWsSlotBytes;
+      const uint32_t w_kb = (akb < 2 ? w_e : w_x) + (uint32_t)((akb & 1) * kWsW * kKBlockBytes);
+      const uint32_t d = tmem + (uint32_t)((a & 3) * 2 * kWsW);
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        umma_tf32(d, umma_desc_sw128(a_kb + j * 32), umma_desc_sw128(w_kb + j * 32), idesc,
+                  (akb > 0 || j > 0) ? 1u : 0u);
+      tc_commit(&misc->empty[s]);
+      ++it;
+      if (++akb == 4) {
+        tc_commit(&misc->g[a & 3].acc0_ready);
+        akb = 0;
+        ++a;
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------- epilogue
+// Thread wt of group g owns row wt of the group's tiles (TMEM lane wt).
+//
+// Code size matters here: the whole per-tile path must stay inside the 32 KB SM instruction cache.
+// The first version of this epilogue was 54 KB of unrolled code (36 KB of it the segmented sums);
+// with 16 warps in different places the instruction-cache hit rate was 52 % and the GPC-level
+// instruction cache ran at 94 % of its request peak -- "no instruction" was 46 % of all stall
+// samples (profiles/README.md r01h).  Hence: branch-free predicated segment scan, packed fp32x2
+// arithmetic for the LayerNorm, no duplicated special cases.
+__device__ __forceinline__ float2 f2(float a, float b) { return make_float2(a, b); }
+
+__device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const float* blob_f, WsMisc* misc,
+                                            float* scr, int g, int wt, int n_my, int n_edges, uint32_t tmem) {
+  constexpr int W = kWsW;
+  constexpr unsigned FULL = 0xffffffffu;
+  const int lane = wt & 31, wq = wt >> 5;
+  WsGroup* wk = &misc->g[g];
+  const uint32_t lane_base = (uint32_t)(wq * 32) << 16;
+  const uint32_t t0 = tmem + (uint32_t)(g * 2 * W) + lane_base, t1 = t0 + W;
+  const int stride_tiles = gridDim.x * kWsGroups;
+  const float4* b4 = reinterpret_cast<const float4*>(blob_f + p.mlp.b_off[1]);
+  const float4* gam4 = reinterpret_cast<const float4*>(blob_f + p.mlp.gamma_off);
+  const float4* bet4 = reinterpret_cast<const float4*>(blob_f + p.mlp.beta_off);
+
+#pragma unroll 1
+  for (int i = g; i < n_my; i += kWsGroups) {
+    const uint32_t par = (uint32_t)(i >> 2) & 1u;
+    const int tile = blockIdx.x + i * gridDim.x;
+    const int e0 = tile * kTileRows;
+    const int nvalid = n_edges - e0 < kTileRows ? n_edges - e0 : kTileRows;
+    const bool valid = wt < nvalid;
+    const int t = valid ? __ldg(p.tgt + e0 + wt) : -3;
+
+    // ---- segment structure of this warp's 32 rows (warp-uniform) ----
+    const int nrows = nvalid - wq * 32 < 0 ? 0 : (nvalid - wq * 32 > 32 ? 32 : nvalid - wq * 32);
+    int t_prev = __shfl_up_sync(FULL, t, 1);
+    if (lane == 0) {
+      const int idx = e0 + wq * 32 - 1;
+      t_prev = (idx >= 0 && idx < n_edges) ? __ldg(p.tgt + idx) : -2;
+    }
+    // bit r: row r starts a new receiver; rows past the end of the edge list never do
+    const unsigned starts = __ballot_sync(FULL, t != t_prev) & (nrows == 32 ? FULL : ((1u << nrows) - 1u));
+    int t_after = -3;
+    {
+      const int idx = e0 + wq * 32 + nrows;
+      if (nrows > 0 && idx < n_edges) t_after = __ldg(p.tgt + idx);
+    }
+    const int t_first = __shfl_sync(FULL, t, 0);
+    const int t_last = __shfl_sync(FULL, t, nrows > 0 ? nrows - 1 : 0);
+    const bool first_cont = nrows > 0 && !(starts & 1u);      // row 0 continues the previous warp's receiver
+    const bool cont_next = nrows > 0 && t_after == t_last;    // the last receiver continues in the next warp
+    const bool one_piece = first_cont && starts == 0u;        // the whole warp is the middle of one receiver
+
+    // ---- P[tgt]: W fp32 per row; consecutive rows share receivers, so a warp touches few lines ----
+    float pr[W];
+    {
+      const float4* prow = reinterpret_cast<const float4*>(p.pq + (long)(valid ? t : 0) * 2 * W);
+#pragma unroll
+      for (int j = 0; j < W / 4; ++j) {
+        const float4 a = __ldg(prow + j);
+        pr[4 * j] = a.x; pr[4 * j + 1] = a.y; pr[4 * j + 2] = a.z; pr[4 * j + 3] = a.w;
+      }
+    }
+    {   // pull the P rows of this group's next tile into L2 (one lane per receiver: a prefetch issues per lane)
+      const long en = (long)(tile + stride_tiles) * kTileRows + wt;
+      const int tn = en < n_edges ? __ldg(p.tgt + en) : -1;
+      const int tp = __shfl_up_sync(FULL, tn, 1);
+      if (tn >= 0 && (lane == 0 || tn != tp)) {
+        const char* pn = reinterpret_cast<const char*>(p.pq + (long)tn * 2 * W);
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(pn));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(pn + 128));
+      }
+    }
+
+    // ---- hidden = relu(acc0 + P), rounded to TF32, back into the same TMEM columns ----
+    mbar_wait_sleep(&wk->acc0_ready, par);
+    tc_fence_after_sync();
+#pragma unroll
+    for (int c = 0; c < W; c += 32) {
+      float v[32];
+      tmem_ld32(t0 + c, v);
+#pragma unroll
+      for (int j = 0; j < 32; j += 2) {
+        const float2 s = __fadd2_rn(f2(v[j], v[j + 1]), f2(pr[c + j], pr[c + j + 1]));
+        v[j] = ws_tf32r(fmaxf(s.x, 0.f));
+        v[j + 1] = ws_tf32r(fmaxf(s.y, 0.f));
+      }
+      tmem_st32(t0 + c, v);
+    }
+    tmem_st_wait();
+    tc_fence_before_sync();
+    mbar_arrive(&wk->hid_ready);
+
+    // ---- output Linear's accumulator -> registers; the TMEM region is free again at once ----
+    mbar_wait_sleep(&wk->acc1_ready, par);
+    tc_fence_after_sync();
+    float y[W];
+    tmem_ld32(t1, y);
+    tmem_ld32(t1 + 32, y + 32);
+    tc_fence_before_sync();
+    mbar_arrive(&wk->region_free);
+    {   // bias + LayerNorm in packed fp32x2 (same operations and order as the scalar code: identical bits)
+      float2 s01 = f2(0.f, 0.f), s23 = f2(0.f, 0.f);
+#pragma unroll
+      for (int j = 0; j < W / 4; ++j) {
+        const float4 b = b4[j];
+        const float2 a = __fadd2_rn(f2(y[4 * j], y[4 * j + 1]), f2(b.x, b.y));
+        const float2 c = __fadd2_rn(f2(y[4 * j + 2], y[4 * j + 3]), f2(b.z, b.w));
+        y[4 * j] = a.x; y[4 * j + 1] = a.y; y[4 * j + 2] = c.x; y[4 * j + 3] = c.y;
+        s01 = __fadd2_rn(s01, a);
+        s23 = __fadd2_rn(s23, c);
+      }
+      const float nmean = -(((s01.x + s01.y) + (s23.x + s23.y)) / (float)W);
+      const float2 nm = f2(nmean, nmean);
+      float2 q01 = f2(0.f, 0.f), q23 = f2(0.f, 0.f);
+#pragma unroll
+      for (int j = 0; j < W / 4; ++j) {
+        const float2 a = __fadd2_rn(f2(y[4 * j], y[4 * j + 1]), nm);
+        const float2 c = __fadd2_rn(f2(y[4 * j + 2], y[4 * j + 3]), nm);
+        y[4 * j] = a.x; y[4 * j + 1] = a.y; y[4 * j + 2] = c.x; y[4 * j + 3] = c.y;
+        q01 = __ffma2_rn(a, a, q01);
+        q23 = __ffma2_rn(c, c, q23);
+      }
+      // rows past the end of the edge list contribute zeros to the sums below
+      const float rstd = valid ? 1.0f / sqrtf(((q01.x + q01.y) + (q23.x + q23.y)) / (float)W + 1e-5f) : 0.f;
+      const float2 r2 = f2(rstd, rstd);
+#pragma unroll
+      for (int j = 0; j < W / 4; ++j) {
+        const float4 ga = gam4[j], be = valid ? bet4[j] : make_float4(0.f, 0.f, 0.f, 0.f);
+        const float2 a = __ffma2_rn(__fmul2_rn(f2(y[4 * j], y[4 * j + 1]), r2), f2(ga.x, ga.y), f2(be.x, be.y));
+        const float2 c = __ffma2_rn(__fmul2_rn(f2(y[4 * j + 2], y[4 * j + 3]), r2), f2(ga.z, ga.w), f2(be.z, be.w));
+        y[4 * j] = a.x; y[4 * j + 1] = a.y; y[4 * j + 2] = c.x; y[4 * j + 3] = c.y;
+      }
+    }
+
+    // ---- segmented sums over this warp's rows: lane = column, rows in order.  Rolled loops (4 rows
+    //      per trip): the code stays small, the rare "receiver complete" path is out of line. ----
+    // (the shared piece slots and flags are written only here, after acc1_ready: warp 0 arrived on
+    //  hid_ready after it finished stitching the previous tile, so nothing it still reads is touched)
+    if (lane == 0) {      // pieces of receivers that straddle warps / tiles, stitched by warp 0 below
+      wk->piece_tgt[2 * wq] = t_first;
+      wk->piece_flag[2 * wq] = first_cont ? ((one_piece && cont_next) ? 3 : 1) : 0;
+      wk->piece_tgt[2 * wq + 1] = t_last;
+      wk->piece_flag[2 * wq + 1] = (cont_next && !one_piece) ? 1 : 0;
+    }
+    if (nrows > 0) {
+      wk->tgt_s[wt] = t;                           // read back by this row's own warp only
+      float* const piece_head = &wk->pieces[(2 * wq) * W + lane];
+      float* const piece_tail = &wk->pieces[(2 * wq + 1) * W + lane];
+      const int* tg = wk->tgt_s + wq * 32;
+#pragma unroll
+      for (int c0 = 0; c0 < W; c0 += 32) {
+        float* const aggc = p.agg + c0 + lane;
+        unsigned m = starts & ~1u;                 // a receiver starting at row 0 has nothing before it to flush
+        bool is_head = first_cont;
+        int off = t_first * W;                     // agg offset of the receiver being summed
+        float sum = 0.f;
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          __syncwarp();
+          if ((lane >> 4) == half) {
+            float4* d4 = reinterpret_cast<float4*>(scr + (lane & 15) * kWsScrStride);
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              d4[j] = make_float4(y[c0 + 4 * j], y[c0 + 4 * j + 1], y[c0 + 4 * j + 2], y[c0 + 4 * j + 3]);
+          }
+          __syncwarp();
+          const float* col = scr + lane;
+#pragma unroll 1
+          for (int k = 0; k < 16; k += 4) {
+            float v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) v[u] = col[(k + u) * kWsScrStride];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              if (m & 1u) {                        // warp-uniform: the receiver ending at the previous row is complete
+                if (is_head) piece_head[c0] = sum; else aggc[off] = sum;
+                is_head = false;
+                off = tg[half * 16 + k + u] * W;
+                sum = 0.f;
+              }
+              sum += v[u];
+              m >>= 1;
+            }
+          }
+        }
+        if (cont_next && !one_piece) piece_tail[c0] = sum;
+        else if (is_head) piece_head[c0] = sum;
+        else aggc[off] = sum;
+      }
+    }
+    ws_group_bar(g);
+
+    // ---- stitch the pieces of CSR rows that straddle warps / tiles (warp 0 of the group).  The
+    //      next tile's pieces are written only after all 128 threads arrived on hid_ready, i.e.
+    //      after this warp left the stitch. ----
+    if (wq == 0) {
+      float carry[W / 32];
+      bool has = false, from_prev = false;
+      int ctgt = -1;
+#pragma unroll 1
+      for (int q = 0; q < 4; ++q) {
+        const int f0 = wk->piece_flag[2 * q];
+        if (f0) {
+          if (!has) {
+            has = true; from_prev = true; ctgt = wk->piece_tgt[2 * q];
+#pragma unroll
+            for (int j = 0; j < W / 32; ++j) carry[j] = 0.f;
+          }
+#pragma unroll
+          for (int j = 0; j < W / 32; ++j) carry[j] += wk->pieces[(2 * q) * W + 32 * j + lane];
+          if (!(f0 & 2)) {
+            float* dst = from_prev ? p.head + (long)tile * W : p.agg + (long)ctgt * W;
+#pragma unroll
+            for (int j = 0; j < W / 32; ++j) dst[32 * j + lane] = carry[j];
+            has = false;
+          }
+        }
+        if (wk->piece_flag[2 * q + 1]) {
+          has = true; from_prev = false; ctgt = wk->piece_tgt[2 * q + 1];
+#pragma unroll
+          for (int j = 0; j < W / 32; ++j) carry[j] = wk->pieces[(2 * q + 1) * W + 32 * j + lane];
+        }
+      }
+      if (has) {   // the row continues into the next tile: its remainder arrives as that tile's head
+        float* dst = from_prev ? p.head + (long)tile * W : p.agg + (long)ctgt * W;
+#pragma unroll
+        for (int j = 0; j < W / 32; ++j) dst[32 * j + lane] = carry[j];
+      }
+      __syncwarp();
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------- kernel
+__global__ void __launch_bounds__(kWsThreads, 1)
+edge_layer_ws_kernel(const SgnnEdgeLayerParams p, const __grid_constant__ CUtensorMap xmap) {
+  constexpr int TMEM_COLS = 512;
+  char* smem = smem_base_1024();
+  const WsSmem L = edge_ws_smem(p.blob_bytes);
+  WsMisc* misc = reinterpret_cast<WsMisc*>(smem + L.misc);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+  pdl_launch_dependents();
+  if (tid == 0) {
+    mbar_init(&misc->bar_w, 1);
+    for (int s = 0; s < kWsMaxSlots; ++s) {
+      mbar_init(&misc->full[s], 1);
+      mbar_init(&misc->empty[s], 1);
+    }
+    for (int g = 0; g < kWsGroups; ++g) {
+      mbar_init(&misc->g[g].acc0_ready, 1);
+      mbar_init(&misc->g[g].hid_ready, kThreads);
+      mbar_init(&misc->g[g].acc1_ready, 1);
+      mbar_init(&misc->g[g].region_free, kThreads);
+    }
+    mbar_fence_init();
+    tma_load_span(smem, reinterpret_cast<const char*>(p.blob), p.blob_bytes, &misc->bar_w);
+    tensormap_prefetch(&xmap);
+  }
+  if (tid < 32) tmem_alloc(&misc->tmem_slot, TMEM_COLS);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  pdl_wait();          // everything above touched only shared/tensor memory and the constant weights
+  const int n_edges = p.rowptr[p.n_nodes];
+  const int n_tiles = (n_edges + kTileRows - 1) / kTileRows;
+  const int n_my = (int)blockIdx.x < n_tiles ? (n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+  const uint32_t tmem = misc->tmem_slot;
+
+  if (warp < 16) {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kWsEpiRegs));
+    mbar_wait(&misc->bar_w, 0);
+    float* scr = reinterpret_cast<float*>(smem + L.scratch) + warp * kWsScrFloats;
+    ws_epilogue(p, reinterpret_cast<const float*>(smem), misc, scr, warp >> 2, tid & 127, n_my, n_edges, tmem);
+  } else {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kWsAuxRegs));
+  }
+  if (warp == 16) {
+    ws_producer(p, &xmap, smem + L.ring, misc, L.slots, n_my, n_edges, lane);
+  } else if (warp == 17) {
+    if (lane == 0) {
+      mbar_wait(&misc->bar_w, 0);
+      ws_mma(p, smem_u32(smem + L.ring), smem_u32(smem), misc, L.slots, n_my, tmem, p.wxs_off);
+    }
+    __syncwarp();
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  if (tid < 32) tmem_dealloc(tmem, TMEM_COLS);
+}
+
+}  // namespace sgnn
+
+using namespace sgnn;
+
+// 1 if the layer can run in gather mode (the node kernels must then put the TF32-rounded node
+// latents in the Q half of the pq buffer: tail SGNN_TAIL_PX)
+extern "C" int sgnn_edge_layer_gather_supported(int he, int hidden, int out, int n_hidden, int blob_bytes) {
+  if (!(he == kWsW && hidden == kWsW && out == kWsW && n_hidden == 1)) return 0;
+  const WsSmem s = edge_ws_smem(blob_bytes);
+  return s.slots >= 5 && s.total <= 227 * 1024 && tensormap_encoder() != nullptr;
+}
+
+int sgnn_edge_layer_gather_launch(const SgnnEdgeLayerParams* p, void* stream) {
+  SGNN_CHECK_ARG(p->he == kWsW && p->mlp.hidden == kWsW && p->mlp.out == kWsW && p->mlp.n_hidden == 1,
+                 "edge_layer (gather mode): widths must be 64 with one hidden layer");
+  const WsSmem s = edge_ws_smem(p->blob_bytes);
+  SGNN_CHECK_ARG(s.slots >= 5 && s.total <= 227 * 1024, "edge_layer (gather mode): needs %d bytes of shared memory", s.total);
+  CUtensorMap map;
+  const int rc = make_row_gather_map(&map, p->pq + kWsW, p->n_nodes, kWsW, 2 * kWsW * 4);
+  if (rc != SGNN_OK) return rc;
+  static int sms = 0;
+  if (sms == 0) {
+    int dev = 0;
+    SGNN_CUDA(cudaGetDevice(&dev));
+    SGNN_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  }
+  int grid = p->max_tiles < sms ? p->max_tiles : sms;
+  if (grid < 1) grid = 1;
+  SGNN_ENSURE_SMEM(edge_layer_ws_kernel, s.total);
+  SGNN_CUDA(sgnn_launch(edge_layer_ws_kernel, dim3(grid), dim3(kWsThreads), s.total, (cudaStream_t)stream, *p, map));
+  return SGNN_OK;
+}

@@ -262,10 +262,16 @@ __global__ void __launch_bounds__(kNodeFastThreads, 1) node_fast_kernel(const Sg
     stamp(9);
     // ---- tail: x' (TF32) becomes the A operand in the region that is NOT `cur` ... both are free
     //      now (the accumulator has been read), use region A for x' and region D for the products ----
-    if (p.tail == SGNN_TAIL_PQ) {
-      row_to_tmem(tA, v);
+    if (p.tail == SGNN_TAIL_PQ || p.tail == SGNN_TAIL_PX) {
+      row_to_tmem(tA, v);              // v is now rounded to TF32 (low mantissa bits are ignored by the MMA)
+      if (p.tail == SGNN_TAIL_PX && valid) {     // gather mode: the edge kernel multiplies x_src by W1b itself
+        float4* dst = reinterpret_cast<float4*>(p.pq_out + i * 2 * NW + NW);
+#pragma unroll
+        for (int j = 0; j < NW / 4; ++j) dst[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+      }
       const float* b1 = blob_f + p.pq_bias_off;
-      for (int half = 0; half < 2; ++half) {
+      const int n_half = p.tail == SGNN_TAIL_PQ ? 2 : 1;
+      for (int half = 0; half < n_half; ++half) {
         const int woff = half ? p.wq_off : p.wp_off;
         run_mma(w, wt, bar, phase, [&] { umma_gemm_tf32_ts(RD, RA, sW + woff, NW, NW); });
         float o[NW];
@@ -372,7 +378,7 @@ int sgnn_node_fast_try(const SgnnNodeParams* p, void* stream) {
     return 0;
   }
   if (p->residual && p->x_w != NW) return 0;
-  if (p->tail == SGNN_TAIL_PQ && p->pq_hidden != NW) return 0;
+  if ((p->tail == SGNN_TAIL_PQ || p->tail == SGNN_TAIL_PX) && p->pq_hidden != NW) return 0;
   if (p->tail == SGNN_TAIL_DECODE && (p->dec.hidden != NW || p->dec.out > 8)) return 0;
   const int smem = node_fast_smem(p->blob_bytes);
   if (smem > 227 * 1024) return 0;

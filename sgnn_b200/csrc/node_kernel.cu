@@ -326,6 +326,8 @@ extern "C" int sgnn_node_fwd(const SgnnNodeParams* p, int use_tensor_cores, int 
     const int r = sgnn_node_fast_try(p, stream);
     if (r != 0) return r < 0 ? r : SGNN_OK;
   }
+  SGNN_CHECK_ARG(p->tail != SGNN_TAIL_PX, "node: tail PX (gather-mode edge kernel) exists only in the 64-wide "
+                 "tensor-core kernel; this layer shape / precision must use tail PQ");
   const int streamed = node_streamed(*p, use_tensor_cores);
   const NodeSmem L = node_smem(*p, use_tensor_cores, streamed);
   SGNN_CHECK_ARG(p->blob_bytes >= SGNN_VEC_REGION_BYTES, "node: blob lacks the vector region");

@@ -47,6 +47,9 @@ typedef struct {
   float* head;            /* [n_tiles, out]: partial sum of a CSR row continuing from the      */
                           /* previous tile (added back by the node kernel)                     */
   int max_tiles;
+  int wxs_off;            /* 0: PQ mode.  > 0: GATHER mode -- byte offset of the W1b image; the Q half */
+                          /* of `pq` then holds the TF32-rounded node latents x (node tail            */
+                          /* SGNN_TAIL_PX) and the sender term x_src W1b^T is part of the first GEMM  */
 } SgnnEdgeLayerParams;
 
 /* Edge encoder: features from positions -> MLP -> LN -> e0 tiles.  Reference:
@@ -74,10 +77,11 @@ typedef struct {
 } SgnnEdgeEncoderParams;
 
 enum { SGNN_PRO_FEATURES = 0, SGNN_PRO_AGG_X = 1, SGNN_PRO_ROWS = 2 };
-enum { SGNN_TAIL_NONE = 0, SGNN_TAIL_PQ = 1, SGNN_TAIL_DECODE = 2 };
+enum { SGNN_TAIL_NONE = 0, SGNN_TAIL_PQ = 1, SGNN_TAIL_DECODE = 2, SGNN_TAIL_PX = 3 };
 
 /* Node-side kernel: prologue -> MLP (-> LN) (-> + residual) -> x_out, then an optional tail
- * GEMM on x_out: PQ for the next layer's edge kernel, or the decoder + Euler integrator. */
+ * GEMM on x_out: PQ for the next layer's edge kernel (PX: P and the TF32-rounded x_out in Q's
+ * place, for an edge kernel in gather mode), or the decoder + Euler integrator. */
 typedef struct {
   int n_rows;
   int prologue;

@@ -9,6 +9,7 @@ with device pointers only -- no allocation, no host sync, capturable in a CUDA g
                with the reference's edge-latent doubling folded into the weights (scale 2^l)
 """
 import ctypes as C
+import os
 from typing import Dict, List, Optional
 
 import torch
@@ -147,13 +148,16 @@ class EdgeLayerPlan:
     the first Linear's columns are [x_target | x_source | e] (graph_network.py:197)."""
 
     def __init__(self, edge_fn: torch.nn.Sequential, nnode: int, nedge: int, scale: float, tc: bool,
-                 device):
+                 device, gather: bool = False):
         lins, ln = linears_of(edge_fn[0]), edge_fn[1]
         assert lins[0].in_features == 2 * nnode + nedge
         b = BlobBuilder(device, tc)
         self.p = L.EdgeLayerParams()
         fill_mlp(b, self.p.mlp, lins, ln, first_cols=(2 * nnode, nedge), first_scale=scale,
                  first_bias=False)
+        self.gather = gather
+        if gather:      # sender columns of W1: multiplied inside the edge kernel (TMA-gathered x_src rows)
+            self.p.wxs_off = b.add_image(lins[0].weight, 0, lins[0].out_features, nnode, nnode, pad32(nnode))
         self.blob, nbytes = b.finish()
         self.p.blob, self.p.blob_bytes, self.p.he = self.blob.data_ptr(), nbytes, nedge
         self.tc, self.hidden, self.out = tc, self.p.mlp.hidden, self.p.mlp.out
@@ -180,7 +184,7 @@ class NodePlan:
     def __init__(self, prologue: int, k_in: int, body: Optional[torch.nn.Sequential], tc: bool,
                  device, nnode_next: int = 0, pq_from: Optional[torch.nn.Sequential] = None,
                  decoder: Optional[torch.nn.Sequential] = None, residual: bool = False,
-                 body_has_ln: bool = True):
+                 body_has_ln: bool = True, px: bool = False):
         b = BlobBuilder(device, tc)
         p = self.p = L.NodeParams()
         p.prologue, p.k_in, p.k_pad = prologue, k_in, pad32(k_in)
@@ -197,9 +201,10 @@ class NodePlan:
         p.tail = L.TAIL_NONE
         if pq_from is not None:
             w1 = linears_of(pq_from[0])[0]
-            p.tail, p.pq_hidden = L.TAIL_PQ, w1.out_features
+            p.tail, p.pq_hidden = (L.TAIL_PX if px else L.TAIL_PQ), w1.out_features
             p.wp_off = b.add_image(w1.weight, 0, w1.out_features, 0, nnode_next, pad32(width))
-            p.wq_off = b.add_image(w1.weight, 0, w1.out_features, nnode_next, nnode_next, pad32(width))
+            if not px:      # PX: the Q half of pq carries the TF32-rounded x itself (edge kernel in gather mode)
+                p.wq_off = b.add_image(w1.weight, 0, w1.out_features, nnode_next, nnode_next, pad32(width))
             p.pq_bias_off = b.add_vector(w1.bias)
         elif decoder is not None:
             lins = linears_of(decoder)
@@ -240,16 +245,18 @@ class EpdEngine:
         tc = precision == "tf32"
         self.tc, self.n, self.dim, self.latent, self.device = tc, n_nodes, dim, latent, device
         self.edge_enc = [EdgeEncoderPlan(seq, dim + 1, tc, device) for seq in edge_encoders]
+        self.gather = self._gather_mode(node_encoder, blocks, k_node_in, latent, tc)
         self.blocks = []
         for bi, (edge_fn, node_fn, es, layer) in enumerate(blocks):
             nedge = self.edge_enc[es].out
-            ep = EdgeLayerPlan(edge_fn, latent, nedge, float(2 ** layer), tc, device)
+            ep = EdgeLayerPlan(edge_fn, latent, nedge, float(2 ** layer), tc, device, gather=self.gather)
             nxt = blocks[bi + 1][0] if bi + 1 < len(blocks) else None
             npn = NodePlan(L.PRO_AGG_X, ep.out + latent, node_fn, tc, device, nnode_next=latent,
-                           pq_from=nxt, decoder=None if nxt is not None else decoder, residual=True)
+                           pq_from=nxt, decoder=None if nxt is not None else decoder, residual=True,
+                           px=self.gather)
             self.blocks.append((ep, npn, es))
         self.node_enc = NodePlan(L.PRO_FEATURES, k_node_in, node_encoder, tc, device,
-                                 nnode_next=latent, pq_from=blocks[0][0])
+                                 nnode_next=latent, pq_from=blocks[0][0], px=self.gather)
         f32 = dict(dtype=torch.float32, device=device)
         max_hidden = max(ep.hidden for ep, _, _ in self.blocks)
         max_out = max(ep.out for ep, _, _ in self.blocks)
@@ -260,6 +267,27 @@ class EpdEngine:
         self.e_tiles = [torch.empty(((c + TILE - 1) // TILE) * TILE * enc.out + 32, **f32)
                         for c, enc in zip(edge_caps, self.edge_enc)]
         self.dec_out = torch.empty(n_nodes, linears_of(decoder)[-1].out_features, **f32)
+
+    def _gather_mode(self, node_encoder, blocks, k_node_in: int, latent: int, tc: bool) -> bool:
+        """True when every edge layer can take its sender rows by TMA gather (edge_layer_ws.cu): all
+        widths 64, one hidden layer in the edge MLPs, and every node kernel that feeds an edge layer
+        is the 64-wide tensor-core kernel (the only one with tail PX).  SGNN_EDGE_PQ=1 forces the
+        P/Q formulation (A/B measurements)."""
+        if not tc or latent != 64 or os.environ.get("SGNN_EDGE_PQ") or os.environ.get("SGNN_EDGE_GENERIC") \
+                or os.environ.get("SGNN_NODE_GENERIC"):
+            return False
+        if pad32(k_node_in) != 32 or any(enc.out != 64 for enc in self.edge_enc):
+            return False
+        for seq in [node_encoder] + [nf for _, nf, _, _ in blocks]:
+            lins = linears_of(seq[0])
+            if any(l.out_features != 64 for l in lins):
+                return False
+        for edge_fn, _, _, _ in blocks:
+            lins = linears_of(edge_fn[0])
+            if len(lins) != 2 or any(l.out_features != 64 for l in lins):
+                return False
+        vec = L.VEC_REGION_BYTES if hasattr(L, "VEC_REGION_BYTES") else 8192
+        return bool(L.lib().sgnn_edge_layer_gather_supported(64, 64, 64, 1, vec + 3 * 64 * 64 * 4))
 
     def forward(self, *, pos_seq, pos_seq_stride: int, seq_len: int, csrs: List[Csr],
                 radii: List[float], vel_mean, vel_std, wall_max: float, wall_div: float,

@@ -23,8 +23,13 @@ def test_fast_equals_generic(regime, nx, ny, nmlp):
     traj = synthetic.taylor_trajectory(nx, ny, spacing, nframes=12, seed=3)
     pos = traj["positions"].cuda()
     stats = synthetic.normalization_stats(synthetic.metadata_from(traj["positions"]), 0.02 * spacing / 0.5)
-    sim = _sim(nmlp, radius, stats)
-    n = pos.shape[0]
+    os.environ["SGNN_EDGE_PQ"] = "1"       # this test is about the P/Q kernels; gather mode: test_edge_gather_gpu.py
+    try:
+        sim = _sim(nmlp, radius, stats)
+        n = pos.shape[0]
+        sim._engine(n, pos.device)         # the engine (and its mode) is built here
+    finally:
+        os.environ.pop("SGNN_EDGE_PQ", None)
     types = traj["particle_types"].cuda()
     os.environ.pop("SGNN_EDGE_GENERIC", None)
     os.environ.pop("SGNN_NODE_GENERIC", None)
