@@ -28,6 +28,8 @@ def build(force=False, verbose=False):
     objdir = os.path.join(os.path.dirname(HERE), "build")
     os.makedirs(objdir, exist_ok=True)
     flags = [f for f in NVCC_FLAGS if not f.startswith("--use_fast_math")]
+    if os.environ.get("SGNN_TIMELINE"):          # in-kernel globaltimer stamps (profiles/*_timeline.py only)
+        flags.append("-DSGNN_TIMELINE")
     procs = []
     objs = []
     for src in sorted(glob.glob(os.path.join(CSRC, "*.cu"))):

@@ -15,11 +15,11 @@
 // Roles (640 threads, one persistent CTA per SM; registers re-split with setmaxnreg):
 //   warps 0-15  four epilogue groups of 128 threads; group g owns TMEM columns [128g, 128g + 128)
 //               (accumulator 0 / hidden activations in place, accumulator 1) and every 4th tile
-//   warp 16     producer: e0 K-blocks by TMA bulk copy, x_src K-blocks by TMA gather4, into a ring
-//               of 16 KB slots shared by all tiles of the CTA
-//   warp 17     one thread issues every tcgen05.mma, polling the barriers of both GEMMs so that
-//               the second GEMM of tile t never waits behind the loads of tile t + 1
-// Hand-offs are mbarriers only (full/empty per slot; acc0_ready, hid_ready, acc1_ready,
+//   warps 16,19 producers: a tile's e0 image by TMA bulk copy and its x_src K-blocks by TMA gather4
+//               into one of two 64 KB tile stages
+//   warps 17,18 one thread each issues the tcgen05.mma of the first / the second GEMM, so that the
+//               second GEMM of tile t never waits behind the loads of tile t + 1
+// Hand-offs are mbarriers only (full/empty per stage; acc0_ready, hid_ready, acc1_ready,
 // region_free per group); the only CTA-wide barriers are at start-up and tear-down.
 #include "mlp_tile.cuh"
 #include "params.h"
@@ -30,10 +30,12 @@ namespace sgnn {
 constexpr int kWsGroups = 4;
 constexpr int kWsEpiThreads = kWsGroups * kThreads;        // 512
 constexpr int kWsThreads = kWsEpiThreads + 128;            // + one warpgroup: producer warp, MMA warp, 2 idle
-constexpr int kWsEpiRegs = 112, kWsAuxRegs = 32;           // setmaxnreg moves registers INSIDE the CTA only: launch at 96, (96-32)*128 released = (112-96)*512 taken
+constexpr int kWsEpiRegs = 104, kWsAuxRegs = 48;           // setmaxnreg moves registers INSIDE the CTA only: launch at 96; (96-48)*128 released >= (104-96)*512 taken
 constexpr int kWsW = 64;                                   // he = hidden = out
 constexpr int kWsSlotBytes = kTileRows * kKBlockBytes;     // 16 KB: 128 rows x one K-block
-constexpr int kWsMaxSlots = 8;
+constexpr int kWsStageBytes = 4 * kWsSlotBytes;            // one tile: e0 K-blocks 0,1 then x_src K-blocks 0,1
+constexpr int kWsStages = 2;
+constexpr int kWsVecBytes = 1024;                          // resident part of the blob's vector region
 constexpr int kWsScrRows = 16;
 constexpr int kWsScrStride = 36;
 constexpr int kWsScrFloats = kWsScrRows * kWsScrStride;
@@ -47,21 +49,22 @@ struct WsGroup {
 };
 struct WsMisc {
   uint64_t bar_w;
-  uint64_t full[kWsMaxSlots], empty[kWsMaxSlots];
+  uint64_t full[kWsStages], empty[kWsStages][4];     // full per tile stage, empty per K-block slot of a stage
   uint32_t tmem_slot;
   int pad;
   WsGroup g[kWsGroups];
 };
+// Shared memory: [vectors 1 KB | weight images | 2 tile stages | scan scratch | barriers + pieces].
+// Only the first kWsVecBytes of the blob's 8 KB vector region are used by this layer (b2, gamma,
+// beta) and only they are staged; the images follow at their blob offset minus kWsImgShift.
+constexpr int kWsImgShift = SGNN_VEC_REGION_BYTES - kWsVecBytes;
 struct WsSmem {
-  int ring, scratch, misc, total, slots;
+  int ring, scratch, misc, total;
 };
 __host__ __device__ inline WsSmem edge_ws_smem(int blob_bytes) {
   WsSmem s;
-  s.ring = align_up(blob_bytes, 1024);
-  const int fixed = 16 * kWsScrFloats * 4 + (int)sizeof(WsMisc) + 16 + 1024;
-  int slots = (227 * 1024 - s.ring - fixed) / kWsSlotBytes;
-  s.slots = slots > kWsMaxSlots ? kWsMaxSlots : slots;
-  s.scratch = s.ring + s.slots * kWsSlotBytes;
+  s.ring = align_up(blob_bytes - kWsImgShift, 1024);
+  s.scratch = s.ring + kWsStages * kWsStageBytes;
   s.misc = align_up(s.scratch + 16 * kWsScrFloats * 4, 16);
   s.total = s.misc + (int)sizeof(WsMisc) + 1024;
   return s;
@@ -91,82 +94,195 @@ __device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity) 
       "r"(parity), "r"(0x989680u)
       : "memory");
 }
+// The single-thread issuers and the producers poll instead: waking from the hardware suspend costs
+// ~0.4 us (in-kernel timeline), which the serial issue chains cannot afford five times per tile.
+__device__ __forceinline__ void mbar_wait_spin(uint64_t* bar, uint32_t parity) {
+  while (!mbar_test(bar, parity)) {
+  }
+}
+// One elected lane of a CONVERGED warp (elect.sync).  The whole warp runs the issuer loops and only
+// the tcgen05 instructions sit under this predicate: inside `if (lane == 0)` the warp is divergent,
+// the compiler may not use uniform registers there and wraps every tcgen05.mma in a 20-instruction
+// ELECT / R2UR.BROADCAST x5 / BRA.U.ANY loop (~110 cycles per MMA, measured: 0.25 us per K-block).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred = 0;
+  asm volatile(
+      "{\n\t.reg .b32 rx;\n\t.reg .pred px;\n\t"
+      "elect.sync rx|px, %1;\n\t"
+      "@px mov.s32 %0, 1;\n\t}"
+      : "+r"(pred)
+      : "r"(0xffffffffu));
+  return pred != 0;
+}
 __device__ __forceinline__ float ws_tf32r(float x) { return __uint_as_float(__float_as_uint(x) + 0x1000u); }
 __device__ __forceinline__ void ws_group_bar(int g) {
   asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "r"(kThreads) : "memory");
 }
 
-// ---------------------------------------------------------------------------------- producer
+// measurement switches (sgnn_debug_ws_flags; results are WRONG when set): bit 0 = sender K-blocks by
+// plain bulk copy instead of gather4 (same bytes), bit 2 = epilogue stops after reading acc1
+__device__ int g_ws_flags = 0;
+// timeline of the MMA issuer of CTA 0 (SGNN_TIMELINE builds only): per tile 16 SM-clock stamps
+// [region free, slot0 full, slot1 full, slot2 full, slot3 full / MMA0 committed, hid_ready seen, -, -]
+__device__ unsigned long long* g_ws_timeline = nullptr;
+__device__ __forceinline__ void ws_stamp(int tile_i, int k) {
+#ifdef SGNN_TIMELINE
+  if (g_ws_timeline && blockIdx.x == 0 && tile_i < 256 && (threadIdx.x & 31) == 0) {
+    g_ws_timeline[tile_i * 16 + k] = (unsigned long long)clock64();     // (globaltimer reads cost ~0.25 us each)
+  }
+#endif
+}
+
+// ---------------------------------------------------------------------------------- producers
+// Two warps fill a stage: `part` 0 = sender K-block 0, `part` 1 = the tile's e0 image (one 32 KB TMA
+// bulk copy) + sender K-block 1.  Sender rows are gathered with cp.async (16 bytes per lane, 8 lanes
+// per 128-byte row segment, 4 rows per instruction, L2 -> shared memory without registers), written
+// straight into the SWIZZLE_128B operand layout; every lane's copies arrive on the stage's mbarrier.
+// TMA tile::gather4 does the same job in one instruction per 4 rows but takes its operands from
+// UNIFORM registers: issued per lane it compiles to a 70-cycle ELECT / R2UR loop, issued by one lane
+// from shuffled indices to ~25 dependent instructions -- 2.0 us per tile either way, the bottleneck
+// of the kernel (profiles/README.md r01h); the LSU takes per-lane addresses natively.  The gather4
+// path is kept behind measurement switch bit 1.
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_arrive_noinc(uint64_t* bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
 __device__ __forceinline__ void ws_producer(const SgnnEdgeLayerParams& p, const CUtensorMap* xmap, char* ring,
-                                            WsMisc* misc, int slots, int n_my, int n_edges, int lane) {
-  uint32_t it = 0;
+                                            WsMisc* misc, int n_my, int n_edges, int lane, int part) {
+  constexpr unsigned FULL = 0xffffffffu;
+  const int flags = g_ws_flags;
+  const int rg = lane >> 3, ch = lane & 7;            // row within a group of 4, 16-byte chunk of the K-block
+  const char* xbase = reinterpret_cast<const char*>(p.pq) + (kWsW + part * kKBlock) * 4 + ch * 16;
+  // destination of (row 4j + rg, chunk ch) inside the K-block image: row * 128 + ((ch ^ (row & 7)) << 4)
+  const uint32_t d_even = (uint32_t)(rg * 128 + ((ch ^ rg) << 4)), d_odd = (uint32_t)(rg * 128 + ((ch ^ (4 + rg)) << 4));
+  int rows_nx[4];                                      // sender ids of rows lane, lane + 32, lane + 64, lane + 96,
+  {                                                    // loaded one tile ahead (a cold read is ~1 us on this serial chain)
+    const long e0 = (long)blockIdx.x * kTileRows;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) rows_nx[c] = (n_my > 0 && e0 + c * 32 + lane < n_edges) ? __ldg(p.src + e0 + c * 32 + lane) : 0;
+  }
   for (int i = 0; i < n_my; ++i) {
     const long tile = blockIdx.x + (long)i * gridDim.x;
-    const long e = tile * kTileRows + 4 * lane;
-    int4 idx = make_int4(0, 0, 0, 0);
-    if (e + 3 < n_edges) {
-      idx = __ldg(reinterpret_cast<const int4*>(p.src + e));
-    } else {
-      if (e < n_edges) idx.x = __ldg(p.src + e);
-      if (e + 1 < n_edges) idx.y = __ldg(p.src + e + 1);
-      if (e + 2 < n_edges) idx.z = __ldg(p.src + e + 2);
+    int rows[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) rows[c] = rows_nx[c];
+    {
+      const long e0 = (tile + gridDim.x) * kTileRows;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) rows_nx[c] = (i + 1 < n_my && e0 + c * 32 + lane < n_edges) ? __ldg(p.src + e0 + c * 32 + lane) : 0;
     }
-#pragma unroll 1
-    for (int kb = 0; kb < 4; ++kb, ++it) {
-      const uint32_t s = it % (uint32_t)slots, use = it / (uint32_t)slots;
-      if (use > 0) mbar_wait_sleep(&misc->empty[s], (use - 1) & 1u);
-      char* dst = ring + s * kWsSlotBytes;
-      if (lane == 0) mbar_arrive_expect_tx(&misc->full[s], kWsSlotBytes);
-      if (kb < 2) {
-        if (lane == 0)
-          tma_bulk_g2s(dst, reinterpret_cast<const char*>(p.e_tiles) + tile * (2 * kWsSlotBytes) + kb * kWsSlotBytes,
-                       kWsSlotBytes, &misc->full[s]);
-      } else {
-        tma_gather4(dst + lane * 512, xmap, (kb - 2) * kKBlock, idx.x, idx.y, idx.z, idx.w, &misc->full[s]);
+    const int st = i & 1, use = i >> 1;
+    if (use > 0) {      // a K-block slot is free as soon as ITS four MMAs are done: refills start mid-tile
+      if (part == 1) {
+        mbar_wait_spin(&misc->empty[st][0], (uint32_t)(use - 1) & 1u);
+        mbar_wait_spin(&misc->empty[st][1], (uint32_t)(use - 1) & 1u);
       }
+    }
+    ws_stamp(i, 8 + 4 * part);
+    char* stage = ring + st * kWsStageBytes;
+    uint64_t* full = &misc->full[st];
+    char* dst = stage + (2 + part) * kWsSlotBytes;
+    if (use > 0 && (flags & 3)) mbar_wait_spin(&misc->empty[st][2 + part], (uint32_t)(use - 1) & 1u);
+    if (part == 1 || (flags & 3)) {
+      if (elect_one()) {
+        uint32_t tx = part == 1 ? 2 * kWsSlotBytes : 0;
+        if (flags & 3) tx += kWsSlotBytes;
+        mbar_arrive_expect_tx(full, tx);
+        if (part == 1)
+          tma_bulk_g2s(stage, reinterpret_cast<const char*>(p.e_tiles) + tile * (2 * kWsSlotBytes), 2 * kWsSlotBytes, full);
+        if (flags & 1)
+          tma_bulk_g2s(dst, reinterpret_cast<const char*>(p.e_tiles) + tile * (2 * kWsSlotBytes) + part * kWsSlotBytes,
+                       kWsSlotBytes, full);
+      }
+      __syncwarp();
+    }
+    if (use > 0) mbar_wait_spin(&misc->empty[st][2 + part], (uint32_t)(use - 1) & 1u);
+    ws_stamp(i, 9 + 4 * part);
+    if (flags & 1) {
+      // sender K-block replaced by a bulk copy of the same size (measurement only)
+    } else if (flags & 2) {
+#pragma unroll 4
+      for (int j = 0; j < 32; ++j) {
+        const int c = j >> 3, l0 = (4 * j) & 31;
+        const int r0 = __shfl_sync(FULL, rows[c], l0), r1 = __shfl_sync(FULL, rows[c], l0 + 1);
+        const int r2 = __shfl_sync(FULL, rows[c], l0 + 2), r3 = __shfl_sync(FULL, rows[c], l0 + 3);
+        if (elect_one()) tma_gather4(dst + j * 512, xmap, part * kKBlock, r0, r1, r2, r3, full);
+      }
+      __syncwarp();
+    } else {
+      const uint32_t d0 = smem_u32(dst);
+#pragma unroll
+      for (int jb = 0; jb < 32; jb += 4) {           // shuffles first, then the copies: the volatile copies pin the order
+        int row[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) row[u] = __shfl_sync(FULL, rows[(jb + u) >> 3], (4 * (jb + u) + rg) & 31);
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          cp_async16(d0 + (jb + u) * 512 + (((jb + u) & 1) ? d_odd : d_even), xbase + (long)row[u] * (2 * kWsW * 4));
+      }
+    }
+    ws_stamp(i, 10 + 4 * part);
+    if (!(flags & 3)) {
+      cp_async_arrive_noinc(full);       // counts once this lane's copies have landed
+    } else if (part == 1 || lane != 0) {
+      mbar_arrive(full);                 // same arrival count as the cp.async path (part 0: lane 0 arrived with expect_tx)
     }
   }
 }
 
-// ---------------------------------------------------------------------------------- MMA issuer
-__device__ __forceinline__ void ws_mma(const SgnnEdgeLayerParams& p, uint32_t ring_u32, uint32_t smem_base_u32,
-                                       WsMisc* misc, int slots, int n_my, uint32_t tmem, int wxs_off) {
+// ---------------------------------------------------------------------------------- MMA issuers
+// Two warps, each BLOCKING on its own mbarriers; the tcgen05 instructions sit under elect.sync in
+// converged code so that their operands stay in uniform registers.  One wait and one commit per
+// tile: every wait / fence / commit on this serial chain costs 100-200 cycles.
+// First GEMM: acc0 = [e0 | x_src] [W1c | W1b]^T, K = 128 = the four K-blocks of a stage.
+__device__ __forceinline__ void ws_mma0(const SgnnEdgeLayerParams& p, uint32_t ring_u32, uint32_t smem_base_u32,
+                                        WsMisc* misc, int n_my, uint32_t tmem, int wxs_off) {
   const uint32_t idesc = umma_idesc_tf32(kTileRows, kWsW);
-  const uint32_t w_e = smem_base_u32 + p.mlp.w_off[0], w_x = smem_base_u32 + wxs_off;
-  const uint32_t w_2 = smem_base_u32 + p.mlp.w_off[1];
-  int a = 0, akb = 0, b = 0;
-  uint32_t it = 0;
-  while (b < n_my) {
-    __nanosleep(40);      // polling back-off: this thread must not hog its scheduler's fetch slots
-    if (b < a && mbar_test(&misc->g[b & 3].hid_ready, (uint32_t)(b >> 2) & 1u)) {
-      tc_fence_after_sync();
-      const uint32_t base = tmem + (uint32_t)((b & 3) * 2 * kWsW);
+  const uint32_t w_e = smem_base_u32 + p.mlp.w_off[0] - kWsImgShift, w_x = smem_base_u32 + wxs_off - kWsImgShift;
+  for (int a = 0; a < n_my; ++a) {
+    if (a >= kWsGroups) mbar_wait_spin(&misc->g[a & 3].region_free, (uint32_t)((a >> 2) - 1) & 1u);
+    ws_stamp(a, 0);
+    const uint32_t d = tmem + (uint32_t)((a & 3) * 2 * kWsW);
+    const int st = a & 1;
+    mbar_wait_spin(&misc->full[st], (uint32_t)(a >> 1) & 1u);
+    fence_proxy_async_smem();          // cp.async wrote through the generic proxy, tcgen05.mma reads through the async one
+    tc_fence_after_sync();
+    ws_stamp(a, 1);
+    const uint32_t a_st = ring_u32 + st * kWsStageBytes;
+    if (elect_one()) {
+#pragma unroll
+      for (int kb = 0; kb < 4; ++kb) {
+        const uint32_t a_kb = a_st + kb * kWsSlotBytes;
+        const uint32_t w_kb = (kb < 2 ? w_e : w_x) + (uint32_t)((kb & 1) * kWsW * kKBlockBytes);
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          umma_tf32(d, umma_desc_sw128(a_kb + j * 32), umma_desc_sw128(w_kb + j * 32), idesc,
+                    (kb > 0 || j > 0) ? 1u : 0u);
+        tc_commit(&misc->empty[st][kb]);
+      }
+      tc_commit(&misc->g[a & 3].acc0_ready);
+    }
+    __syncwarp();
+    ws_stamp(a, 2);
+  }
+}
+// Second GEMM: acc1 = hidden W2^T with the hidden activations read from TMEM.
+__device__ __forceinline__ void ws_mma1(const SgnnEdgeLayerParams& p, uint32_t smem_base_u32, WsMisc* misc, int n_my,
+                                        uint32_t tmem) {
+  const uint32_t w_2 = smem_base_u32 + p.mlp.w_off[1] - kWsImgShift;
+  for (int b = 0; b < n_my; ++b) {
+    mbar_wait_spin(&misc->g[b & 3].hid_ready, (uint32_t)(b >> 2) & 1u);
+    tc_fence_after_sync();
+    ws_stamp(b, 5);
+    const uint32_t base = tmem + (uint32_t)((b & 3) * 2 * kWsW);
+    if (elect_one()) {
       umma_gemm_tf32_ts(base + kWsW, base, w_2, kWsW, kWsW);
       tc_commit(&misc->g[b & 3].acc1_ready);
-      ++b;
     }
-    if (a < n_my) {
-      if (akb == 0 && a >= kWsGroups &&
-          !mbar_test(&misc->g[a & 3].region_free, (uint32_t)((a >> 2) - 1) & 1u))
-        continue;
-      const uint32_t s = it % (uint32_t)slots, use = it / (uint32_t)slots;
-      if (!mbar_test(&misc->full[s], use & 1u)) continue;
-      tc_fence_after_sync();
-      const uint32_t a_kb = ring_u32 + s * kWsSlotBytes;
-      const uint32_t w_kb = (akb < 2 ? w_e : w_x) + (uint32_t)((akb & 1) * kWsW * kKBlockBytes);
-      const uint32_t d = tmem + (uint32_t)((a & 3) * 2 * kWsW);
-#pragma unroll
-      for (int j = 0; j < 4; ++j)
-        umma_tf32(d, umma_desc_sw128(a_kb + j * 32), umma_desc_sw128(w_kb + j * 32), idesc,
-                  (akb > 0 || j > 0) ? 1u : 0u);
-      tc_commit(&misc->empty[s]);
-      ++it;
-      if (++akb == 4) {
-        tc_commit(&misc->g[a & 3].acc0_ready);
-        akb = 0;
-        ++a;
-      }
-    }
+    __syncwarp();
   }
 }
 
@@ -247,6 +363,7 @@ __device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const 
     // ---- hidden = relu(acc0 + P), rounded to TF32, back into the same TMEM columns ----
     mbar_wait_sleep(&wk->acc0_ready, par);
     tc_fence_after_sync();
+    if (wt == 0) ws_stamp(i, 6);
 #pragma unroll
     for (int c = 0; c < W; c += 32) {
       float v[32];
@@ -271,6 +388,10 @@ __device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const 
     tmem_ld32(t1 + 32, y + 32);
     tc_fence_before_sync();
     mbar_arrive(&wk->region_free);
+    if (g_ws_flags & 4) {      // measurement switch: skip LayerNorm, sums and stitch (wrong results)
+      if (y[0] == 123.456f) p.agg[wt] = y[1];
+      continue;
+    }
     {   // bias + LayerNorm in packed fp32x2 (same operations and order as the scalar code: identical bits)
       float2 s01 = f2(0.f, 0.f), s23 = f2(0.f, 0.f);
 #pragma unroll
@@ -362,6 +483,7 @@ __device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const 
       }
     }
     ws_group_bar(g);
+    if (wt == 0) ws_stamp(i, 7);
 
     // ---- stitch the pieces of CSR rows that straddle warps / tiles (warp 0 of the group).  The
     //      next tile's pieces are written only after all 128 threads arrived on hid_ready, i.e.
@@ -416,9 +538,9 @@ edge_layer_ws_kernel(const SgnnEdgeLayerParams p, const __grid_constant__ CUtens
   pdl_launch_dependents();
   if (tid == 0) {
     mbar_init(&misc->bar_w, 1);
-    for (int s = 0; s < kWsMaxSlots; ++s) {
-      mbar_init(&misc->full[s], 1);
-      mbar_init(&misc->empty[s], 1);
+    for (int s = 0; s < kWsStages; ++s) {
+      mbar_init(&misc->full[s], 65);           // 2 x 32 producer lanes + the expect_tx arrival of the e0 copy
+      for (int k = 0; k < 4; ++k) mbar_init(&misc->empty[s][k], 1);
     }
     for (int g = 0; g < kWsGroups; ++g) {
       mbar_init(&misc->g[g].acc0_ready, 1);
@@ -427,7 +549,11 @@ edge_layer_ws_kernel(const SgnnEdgeLayerParams p, const __grid_constant__ CUtens
       mbar_init(&misc->g[g].region_free, kThreads);
     }
     mbar_fence_init();
-    tma_load_span(smem, reinterpret_cast<const char*>(p.blob), p.blob_bytes, &misc->bar_w);
+    mbar_arrive_expect_tx(&misc->bar_w, (uint32_t)(p.blob_bytes - kWsImgShift));
+    tma_bulk_g2s(smem, p.blob, kWsVecBytes, &misc->bar_w);
+    for (int off = SGNN_VEC_REGION_BYTES; off < p.blob_bytes; off += 16384)
+      tma_bulk_g2s(smem + off - kWsImgShift, reinterpret_cast<const char*>(p.blob) + off,
+                   (uint32_t)(p.blob_bytes - off < 16384 ? p.blob_bytes - off : 16384), &misc->bar_w);
     tensormap_prefetch(&xmap);
   }
   if (tid < 32) tmem_alloc(&misc->tmem_slot, TMEM_COLS);
@@ -449,13 +575,15 @@ edge_layer_ws_kernel(const SgnnEdgeLayerParams p, const __grid_constant__ CUtens
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kWsAuxRegs));
   }
   if (warp == 16) {
-    ws_producer(p, &xmap, smem + L.ring, misc, L.slots, n_my, n_edges, lane);
+    ws_producer(p, &xmap, smem + L.ring, misc, n_my, n_edges, lane, 0);
+  } else if (warp == 19) {
+    ws_producer(p, &xmap, smem + L.ring, misc, n_my, n_edges, lane, 1);
   } else if (warp == 17) {
-    if (lane == 0) {
-      mbar_wait(&misc->bar_w, 0);
-      ws_mma(p, smem_u32(smem + L.ring), smem_u32(smem), misc, L.slots, n_my, tmem, p.wxs_off);
-    }
-    __syncwarp();
+    mbar_wait(&misc->bar_w, 0);
+    ws_mma0(p, smem_u32(smem + L.ring), smem_u32(smem), misc, n_my, tmem, p.wxs_off);
+  } else if (warp == 18) {
+    mbar_wait(&misc->bar_w, 0);
+    ws_mma1(p, smem_u32(smem), misc, n_my, tmem);
   }
   tc_fence_before_sync();
   __syncthreads();
@@ -471,14 +599,28 @@ using namespace sgnn;
 extern "C" int sgnn_edge_layer_gather_supported(int he, int hidden, int out, int n_hidden, int blob_bytes) {
   if (!(he == kWsW && hidden == kWsW && out == kWsW && n_hidden == 1)) return 0;
   const WsSmem s = edge_ws_smem(blob_bytes);
-  return s.slots >= 5 && s.total <= 227 * 1024 && tensormap_encoder() != nullptr;
+  return s.total <= 227 * 1024 && tensormap_encoder() != nullptr;
+}
+
+extern "C" int sgnn_debug_ws_timeline(void* buf) {
+  SGNN_CUDA(cudaMemcpyToSymbol(g_ws_timeline, &buf, sizeof(buf)));
+  return SGNN_OK;
+}
+extern "C" int sgnn_debug_ws_flags(int flags) {
+  SGNN_CUDA(cudaMemcpyToSymbol(g_ws_flags, &flags, sizeof(flags)));
+  return SGNN_OK;
 }
 
 int sgnn_edge_layer_gather_launch(const SgnnEdgeLayerParams* p, void* stream) {
   SGNN_CHECK_ARG(p->he == kWsW && p->mlp.hidden == kWsW && p->mlp.out == kWsW && p->mlp.n_hidden == 1,
                  "edge_layer (gather mode): widths must be 64 with one hidden layer");
   const WsSmem s = edge_ws_smem(p->blob_bytes);
-  SGNN_CHECK_ARG(s.slots >= 5 && s.total <= 227 * 1024, "edge_layer (gather mode): needs %d bytes of shared memory", s.total);
+  SGNN_CHECK_ARG(s.total <= 227 * 1024, "edge_layer (gather mode): needs %d bytes of shared memory", s.total);
+  SGNN_CHECK_ARG((p->mlp.b_off[1] + kWsW) * 4 <= kWsVecBytes && (p->mlp.gamma_off + kWsW) * 4 <= kWsVecBytes &&
+                     (p->mlp.beta_off + kWsW) * 4 <= kWsVecBytes,
+                 "edge_layer (gather mode): the layer's vectors must lie in the first %d bytes of the blob", kWsVecBytes);
+  SGNN_CHECK_ARG(p->mlp.w_off[0] >= SGNN_VEC_REGION_BYTES && p->mlp.w_off[1] >= SGNN_VEC_REGION_BYTES &&
+                     p->wxs_off >= SGNN_VEC_REGION_BYTES, "edge_layer (gather mode): image offsets inside the vector region");
   CUtensorMap map;
   const int rc = make_row_gather_map(&map, p->pq + kWsW, p->n_nodes, kWsW, 2 * kWsW * 4);
   if (rc != SGNN_OK) return rc;

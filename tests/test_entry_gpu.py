@@ -35,10 +35,10 @@ def test_train_resume_predict(tmp_path):
     dev = torch.device("cuda")
     torch.manual_seed(0)
     sim = T._get_simulator(md, cfg["noise_std"], cfg["noise_std"], dev, cfg)
-    before = {k: v.clone() for k, v in sim.state_dict().items()}
+    before = {k: v.detach().cpu().clone() for k, v in sim.state_dict().items()}
     step, lowest = T.train(sim, md, dev, cfg, log_every=3)
     assert step == 6 and np.isfinite(lowest)
-    assert any(not torch.equal(before[k], v) for k, v in sim.state_dict().items())
+    assert any(not torch.equal(before[k], v.detach().cpu()) for k, v in sim.state_dict().items())
     saved = sorted((tmp_path / "models" / "t").glob("model-best-*.pt"))
     assert saved and saved[0].name == "model-best-000003.pt"
     st = torch.load(str(saved[-1]).replace("model-best", "train_state-best"))
