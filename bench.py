@@ -148,16 +148,36 @@ def edge_layer_alg(n, e, he=H, hidden=H, out=H):
     return by, fl
 
 
-def roofline_entry(ms, n, e, pk, traffic=None):
+def ncu_traffic(kernel, n):
+    """DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) of `kernel` at `n`
+    particles from the committed `ncu --set full` capture (profiles/traffic.json), else None."""
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "traffic.json")) as f:
+            t = json.load(f)
+        return t.get(kernel, {}).get(str(n))
+    except (OSError, ValueError):
+        return None
+
+
+def roofline_entry(ms, n, e, pk, traffic=None, kernel="edge_layer_ws_kernel"):
     by, fl = edge_layer_alg(n, e)
+    if traffic is None:
+        traffic = ncu_traffic(kernel, n)
     tf32_peak = pk["bf16_tflops"] / 2.0            # TF32 dense = 1/2 BF16 (nominal ratio)
     t_hbm, t_tc = by / (pk["hbm_gbs"] * 1e9), fl / (tf32_peak * 1e12)
     achieved = by / (ms * 1e-3) / 1e9
-    return {"kernel": "edge_layer_kernel<tf32>", "bound": "hbm" if t_hbm >= t_tc else "tensor",
+    return {"kernel": kernel, "bound": "hbm" if t_hbm >= t_tc else "tensor",
             "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"],
             "traffic": traffic, "peak_source": pk["source"], "ms_per_launch": ms,
             "alg_bytes_per_launch": by, "alg_flops_per_launch": fl,
             "tensor_frac": fl / (ms * 1e-3) / 1e12 / tf32_peak, "edges": e, "nodes": n}
+
+
+def edge_kernel_name(eng):
+    """The kernel behind EdgeLayerPlan.launch for this engine (sgnn_edge_layer_fwd dispatch)."""
+    if getattr(eng, "gather", False):
+        return "edge_layer_ws_kernel"
+    return "edge_layer_fast_kernel<64,64,64>" if eng.tc and eng.latent == 64 else "edge_layer_kernel"
 
 
 def measure_edge_layer(sim, n, dev, reps=50):
@@ -202,7 +222,7 @@ def large_config(pk, dev, nx=2048, ny=512):
     step_ms = a.elapsed_time(b)
     out = {"particles": n, "edges": e, "ms_per_step": step_ms, "particle_steps_per_s": n / (step_ms * 1e-3),
            "kernels_ms": {k: {"launches": v[0], "mean_ms": v[1]} for k, v in prof.items()},
-           "roofline": roofline_entry(prof["edge_layer"][1], n, e, pk)}
+           "roofline": roofline_entry(prof["edge_layer"][1], n, e, pk, kernel=edge_kernel_name(eng))}
     del plan, sim
     torch.cuda.empty_cache()
     return out
@@ -403,7 +423,7 @@ def run_gpu(args):
     line = None
     if rank == 0:
         ms_edge, e_edges = measure_edge_layer(sim, n, dev)
-        roof = roofline_entry(ms_edge, n, e_edges, pk)
+        roof = roofline_entry(ms_edge, n, e_edges, pk, kernel=edge_kernel_name(sim._engine(n, dev)[0]))
         roof["timing"] = "50 back-to-back launches between CUDA events; working set L2-resident at this size"
         cores = os.cpu_count() or 1
         cpu_steps = 5

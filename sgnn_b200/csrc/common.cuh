@@ -192,6 +192,23 @@ __device__ __forceinline__ void tc_commit(uint64_t* bar) {
                : "memory");
 }
 
+// One elected lane of a CONVERGED warp (elect.sync).  tcgen05.mma / commit / TMA take their operands
+// from uniform registers; under `if (threadIdx.x == 0)` the warp is divergent, the compiler may not
+// use the uniform datapath there and wraps EVERY such instruction in a ~20-instruction ELECT /
+// R2UR.BROADCAST / BRA.U.ANY loop (~110 cycles per MMA, measured with the in-kernel timeline of
+// edge_layer_ws.cu).  Issue sites therefore run in whole, converged warps and put only the
+// tcgen05 / TMA instructions under this predicate.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred = 0;
+  asm volatile(
+      "{\n\t.reg .b32 rx;\n\t.reg .pred px;\n\t"
+      "elect.sync rx|px, %1;\n\t"
+      "@px mov.s32 %0, 1;\n\t}"
+      : "+r"(pred)
+      : "r"(0xffffffffu));
+  return pred != 0;
+}
+
 // shared-memory matrix descriptor: K-major, SWIZZLE_128B, 8-row groups 1024 B apart
 __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
   uint64_t d = 0;

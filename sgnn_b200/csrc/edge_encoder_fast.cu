@@ -107,10 +107,13 @@ __global__ void __launch_bounds__(kEncFastThreads, 1) edge_encoder_fast_kernel(c
       tmem_st_wait();
       tc_fence_before_sync();
       enc_worker_bar(w);
-      if (wt == 0) {
+      if (wt < 32) {           // the worker's first warp, converged (see elect_one in common.cuh)
         tc_fence_after_sync();
-        umma_gemm_tf32_ts(d, a, sW + p.mlp.w_off[l], EW, EW);
-        tc_commit(bar);
+        if (elect_one()) {
+          umma_gemm_tf32_ts(d, a, sW + p.mlp.w_off[l], EW, EW);
+          tc_commit(bar);
+        }
+        __syncwarp();
         mbar_wait(bar, phase);
       }
       phase ^= 1u;

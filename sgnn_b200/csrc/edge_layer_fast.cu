@@ -179,17 +179,21 @@ __global__ void __launch_bounds__(kFastThreads, 1) edge_layer_fast_kernel(const 
 
     // ---- stage 0: e0 (2^l W1c)^T on the tensor core, accumulator in region 0.  One thread waits
     //      on the mbarriers; the other 127 sleep in the worker's hardware barrier. ----
-    if (wt == 0) {
+    if (wt < 32) {             // the worker's first warp, converged (see elect_one in common.cuh)
       mbar_wait(&wk->bar_e, phase_e);
       phase_e ^= 1u;
       tc_fence_after_sync();
-      umma_gemm_tf32(tmem_w, smem_u32(e_buf), smem_u32(smem + p.mlp.w_off[0]), HE, HID);
-      tc_commit(&wk->bar_m);
+      if (elect_one()) {
+        umma_gemm_tf32(tmem_w, smem_u32(e_buf), smem_u32(smem + p.mlp.w_off[0]), HE, HID);
+        tc_commit(&wk->bar_m);
+      }
+      __syncwarp();
       mbar_wait(&wk->bar_m, phase_m);
       phase_m ^= 1u;
-      if (tile + stride < n_tiles)                 // the e0 buffer is free: prefetch the next tile
+      if (tile + stride < n_tiles && elect_one())  // the e0 buffer is free: prefetch the next tile
         tma_load_span(e_buf, reinterpret_cast<const char*>(p.e_tiles) + (long)(tile + stride) * tile_bytes,
                       tile_bytes, &wk->bar_e);
+      __syncwarp();
     }
     worker_bar(w);
     tc_fence_after_sync();
@@ -208,10 +212,13 @@ __global__ void __launch_bounds__(kFastThreads, 1) edge_layer_fast_kernel(const 
     // ---- hidden -> hidden stages (nmlp_layers > 1): A in region ra, D in region 1 - ra ----
     int ra = 0;
     for (int l = 1; l < nh; ++l) {
-      if (wt == 0) {
+      if (wt < 32) {
         tc_fence_after_sync();
-        umma_gemm_tf32_ts(tmem_w + (1 - ra) * REG, tmem_w + ra * REG, smem_u32(smem + p.mlp.w_off[l]), HID, HID);
-        tc_commit(&wk->bar_m);
+        if (elect_one()) {
+          umma_gemm_tf32_ts(tmem_w + (1 - ra) * REG, tmem_w + ra * REG, smem_u32(smem + p.mlp.w_off[l]), HID, HID);
+          tc_commit(&wk->bar_m);
+        }
+        __syncwarp();
         mbar_wait(&wk->bar_m, phase_m);
         phase_m ^= 1u;
       }
@@ -233,10 +240,13 @@ __global__ void __launch_bounds__(kFastThreads, 1) edge_layer_fast_kernel(const 
     }
 
     // ---- output stage + LayerNorm: the row's OUT values stay in registers ----
-    if (wt == 0) {
+    if (wt < 32) {
       tc_fence_after_sync();
-      umma_gemm_tf32_ts(tmem_w + (1 - ra) * REG, tmem_w + ra * REG, smem_u32(smem + p.mlp.w_off[nh]), HID, OUT);
-      tc_commit(&wk->bar_m);
+      if (elect_one()) {
+        umma_gemm_tf32_ts(tmem_w + (1 - ra) * REG, tmem_w + ra * REG, smem_u32(smem + p.mlp.w_off[nh]), HID, OUT);
+        tc_commit(&wk->bar_m);
+      }
+      __syncwarp();
       mbar_wait(&wk->bar_m, phase_m);
       phase_m ^= 1u;
     }

@@ -100,20 +100,6 @@ __device__ __forceinline__ void mbar_wait_spin(uint64_t* bar, uint32_t parity) {
   while (!mbar_test(bar, parity)) {
   }
 }
-// One elected lane of a CONVERGED warp (elect.sync).  The whole warp runs the issuer loops and only
-// the tcgen05 instructions sit under this predicate: inside `if (lane == 0)` the warp is divergent,
-// the compiler may not use uniform registers there and wraps every tcgen05.mma in a 20-instruction
-// ELECT / R2UR.BROADCAST x5 / BRA.U.ANY loop (~110 cycles per MMA, measured: 0.25 us per K-block).
-__device__ __forceinline__ bool elect_one() {
-  uint32_t pred = 0;
-  asm volatile(
-      "{\n\t.reg .b32 rx;\n\t.reg .pred px;\n\t"
-      "elect.sync rx|px, %1;\n\t"
-      "@px mov.s32 %0, 1;\n\t}"
-      : "+r"(pred)
-      : "r"(0xffffffffu));
-  return pred != 0;
-}
 __device__ __forceinline__ float ws_tf32r(float x) { return __uint_as_float(__float_as_uint(x) + 0x1000u); }
 __device__ __forceinline__ void ws_group_bar(int g) {
   asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "r"(kThreads) : "memory");

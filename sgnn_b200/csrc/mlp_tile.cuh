@@ -42,9 +42,10 @@ template <bool TC>
 __device__ __forceinline__ void gemm_step(TileAcc<TC>& acc, const void* a_tile, const void* w_img,
                                           int k, int n, int acc_col, bool accumulate) {
   if constexpr (TC) {
-    if (threadIdx.x == 0) {
+    if (threadIdx.x < 32) {            // warp 0, converged: the elected lane issues from uniform registers
       tc_fence_after_sync();
-      umma_gemm_tf32(acc.tmem_base + acc_col, smem_u32(a_tile), smem_u32(w_img), k, n, accumulate);
+      if (elect_one()) umma_gemm_tf32(acc.tmem_base + acc_col, smem_u32(a_tile), smem_u32(w_img), k, n, accumulate);
+      __syncwarp();
     }
   } else {
     const int row = threadIdx.x;
@@ -81,7 +82,10 @@ __device__ __forceinline__ void gemm_step(TileAcc<TC>& acc, const void* a_tile, 
 template <bool TC>
 __device__ __forceinline__ void gemm_wait(TileAcc<TC>& acc) {
   if constexpr (TC) {
-    if (threadIdx.x == 0) tc_commit(acc.bar);
+    if (threadIdx.x < 32) {            // same warp (and, elect.sync picking the lowest lane, same thread) as the MMAs
+      if (elect_one()) tc_commit(acc.bar);
+      __syncwarp();
+    }
     mbar_wait(acc.bar, acc.phase);
     acc.phase ^= 1u;
     tc_fence_after_sync();

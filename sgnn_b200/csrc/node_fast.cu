@@ -52,17 +52,20 @@ __device__ __forceinline__ void nworker_bar(int w) {
   asm volatile("bar.sync %0, %1;" ::"r"(w + 1), "r"(kThreads) : "memory");
 }
 
-// The worker's threads have written an A operand into TMEM: publish it, let thread 0 issue the
+// The worker's threads have written an A operand into TMEM: publish it, let one lane of warp 0 issue the
 // MMAs described by `issue`, wait for them, and make the accumulator readable by everyone.
 template <class Issue>
 __device__ __forceinline__ void run_mma(int w, int wt, uint64_t* bar, uint32_t& phase, Issue issue) {
   tmem_st_wait();
   tc_fence_before_sync();
   nworker_bar(w);
-  if (wt == 0) {
+  if (wt < 32) {             // the worker's first warp, converged (see elect_one in common.cuh)
     tc_fence_after_sync();
-    issue();
-    tc_commit(bar);
+    if (elect_one()) {
+      issue();
+      tc_commit(bar);
+    }
+    __syncwarp();
     mbar_wait(bar, phase);
   }
   phase ^= 1u;

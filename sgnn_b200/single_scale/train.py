@@ -120,7 +120,8 @@ def load_model(simulator, device, config: dict):
     if not (mp.exists() and sp.exists()):
         raise FileNotFoundError(f"Specified model_file {mp} and train_state_file {sp} not found.")
     simulator.load(str(mp))
-    state = torch.load(str(sp), map_location=device)
+    simulator.to(device)                       # before the optimizer: load_state_dict casts its state to the parameters' device
+    state = torch.load(str(sp), map_location="cpu")
     optimizer = torch.optim.Adam(simulator.parameters())
     optimizer.load_state_dict(state["optimizer_state"])
     gts = state["global_train_state"]
