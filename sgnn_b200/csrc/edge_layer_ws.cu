@@ -39,6 +39,7 @@ constexpr int kWsVecBytes = 1024;                          // resident part of t
 constexpr int kWsScrRows = 16;
 constexpr int kWsScrStride = 36;
 constexpr int kWsScrFloats = kWsScrRows * kWsScrStride;
+constexpr int kWsScrStride2 = 68;                          // 8-row passes over all 64 columns: 64 + 4 pad (8 x 68 <= 16 x 36)
 
 struct WsGroup {
   uint64_t acc0_ready, hid_ready, acc1_ready, region_free;
@@ -293,8 +294,22 @@ __device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const 
   const uint32_t t0 = tmem + (uint32_t)(g * 2 * W) + lane_base, t1 = t0 + W;
   const int stride_tiles = gridDim.x * kWsGroups;
   const float4* b4 = reinterpret_cast<const float4*>(blob_f + p.mlp.b_off[1]);
-  const float4* gam4 = reinterpret_cast<const float4*>(blob_f + p.mlp.gamma_off);
-  const float4* bet4 = reinterpret_cast<const float4*>(blob_f + p.mlp.beta_off);
+  // The LayerNorm affine is applied AFTER the sums: sum_e (z_e * gamma + beta) = gamma * sum_e z_e +
+  // count * beta, per receiver (and per piece of a receiver, the pieces add up).  In the scan a lane
+  // owns columns 2*lane, 2*lane + 1.
+  const float2 gam2 = reinterpret_cast<const float2*>(blob_f + p.mlp.gamma_off)[lane];
+  const float2 bet2 = reinterpret_cast<const float2*>(blob_f + p.mlp.beta_off)[lane];
+  float2* const piece_head = reinterpret_cast<float2*>(&wk->pieces[(2 * wq) * W]) + lane;
+  float2* const piece_tail = reinterpret_cast<float2*>(&wk->pieces[(2 * wq + 1) * W]) + lane;
+  float2* const agg2 = reinterpret_cast<float2*>(p.agg) + lane;
+  const int* tg = wk->tgt_s + wq * 32;
+
+  // receiver of this thread's row, loaded one tile ahead (a cold read costs ~1 us on the group's serial chain)
+  int t_nx = -3;
+  if (g < n_my) {
+    const long e = (long)(blockIdx.x + g * gridDim.x) * kTileRows + wt;
+    if (e < n_edges) t_nx = __ldg(p.tgt + e);
+  }
 
 #pragma unroll 1
   for (int i = g; i < n_my; i += kWsGroups) {
@@ -303,7 +318,11 @@ __device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const 
     const int e0 = tile * kTileRows;
     const int nvalid = n_edges - e0 < kTileRows ? n_edges - e0 : kTileRows;
     const bool valid = wt < nvalid;
-    const int t = valid ? __ldg(p.tgt + e0 + wt) : -3;
+    const int t = t_nx;
+    {
+      const long en = (long)(tile + stride_tiles) * kTileRows + wt;
+      t_nx = (i + kWsGroups < n_my && en < n_edges) ? __ldg(p.tgt + en) : -3;
+    }
 
     // ---- segment structure of this warp's 32 rows (warp-uniform) ----
     const int nrows = nvalid - wq * 32 < 0 ? 0 : (nvalid - wq * 32 > 32 ? 32 : nvalid - wq * 32);
@@ -335,16 +354,6 @@ __device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const 
         pr[4 * j] = a.x; pr[4 * j + 1] = a.y; pr[4 * j + 2] = a.z; pr[4 * j + 3] = a.w;
       }
     }
-    {   // pull the P rows of this group's next tile into L2 (one lane per receiver: a prefetch issues per lane)
-      const long en = (long)(tile + stride_tiles) * kTileRows + wt;
-      const int tn = en < n_edges ? __ldg(p.tgt + en) : -1;
-      const int tp = __shfl_up_sync(FULL, tn, 1);
-      if (tn >= 0 && (lane == 0 || tn != tp)) {
-        const char* pn = reinterpret_cast<const char*>(p.pq + (long)tn * 2 * W);
-        asm volatile("prefetch.global.L2 [%0];" ::"l"(pn));
-        asm volatile("prefetch.global.L2 [%0];" ::"l"(pn + 128));
-      }
-    }
 
     // ---- hidden = relu(acc0 + P), rounded to TF32, back into the same TMEM columns ----
     mbar_wait_sleep(&wk->acc0_ready, par);
@@ -366,6 +375,16 @@ __device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const 
     tc_fence_before_sync();
     mbar_arrive(&wk->hid_ready);
 
+    {   // while the second GEMM runs: pull the P rows of this group's next tile into L2 (one lane per
+        // receiver: a prefetch instruction issues once per active lane)
+      const int tp = __shfl_up_sync(FULL, t_nx, 1);
+      if (t_nx >= 0 && (lane == 0 || t_nx != tp)) {
+        const char* pn = reinterpret_cast<const char*>(p.pq + (long)t_nx * 2 * W);
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(pn));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(pn + 128));
+      }
+    }
+
     // ---- output Linear's accumulator -> registers; the TMEM region is free again at once ----
     mbar_wait_sleep(&wk->acc1_ready, par);
     tc_fence_after_sync();
@@ -378,7 +397,7 @@ __device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const 
       if (y[0] == 123.456f) p.agg[wt] = y[1];
       continue;
     }
-    {   // bias + LayerNorm in packed fp32x2 (same operations and order as the scalar code: identical bits)
+    {   // bias + LayerNorm without its affine, in packed fp32x2
       float2 s01 = f2(0.f, 0.f), s23 = f2(0.f, 0.f);
 #pragma unroll
       for (int j = 0; j < W / 4; ++j) {
@@ -404,19 +423,18 @@ __device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const 
       const float rstd = valid ? 1.0f / sqrtf(((q01.x + q01.y) + (q23.x + q23.y)) / (float)W + 1e-5f) : 0.f;
       const float2 r2 = f2(rstd, rstd);
 #pragma unroll
-      for (int j = 0; j < W / 4; ++j) {
-        const float4 ga = gam4[j], be = valid ? bet4[j] : make_float4(0.f, 0.f, 0.f, 0.f);
-        const float2 a = __ffma2_rn(__fmul2_rn(f2(y[4 * j], y[4 * j + 1]), r2), f2(ga.x, ga.y), f2(be.x, be.y));
-        const float2 c = __ffma2_rn(__fmul2_rn(f2(y[4 * j + 2], y[4 * j + 3]), r2), f2(ga.z, ga.w), f2(be.z, be.w));
-        y[4 * j] = a.x; y[4 * j + 1] = a.y; y[4 * j + 2] = c.x; y[4 * j + 3] = c.y;
+      for (int j = 0; j < W / 2; ++j) {
+        const float2 a = __fmul2_rn(f2(y[2 * j], y[2 * j + 1]), r2);
+        y[2 * j] = a.x; y[2 * j + 1] = a.y;
       }
     }
 
-    // ---- segmented sums over this warp's rows: lane = column, rows in order.  Rolled loops (4 rows
-    //      per trip): the code stays small, the rare "receiver complete" path is out of line. ----
-    // (the shared piece slots and flags are written only here, after acc1_ready: warp 0 arrived on
-    //  hid_ready after it finished stitching the previous tile, so nothing it still reads is touched)
-    if (lane == 0) {      // pieces of receivers that straddle warps / tiles, stitched by warp 0 below
+    // ---- segmented sums over this warp's rows in four passes of 8 rows: the 8 rows go through a
+    //      padded scratch, then lane = column pair walks them in order.  Rolled loops keep the code
+    //      small; the rare "receiver complete" path applies the LayerNorm affine and stores.
+    //      (The shared piece slots and flags are written only here, after acc1_ready: warp 0 arrived
+    //      on hid_ready after it finished stitching the previous tile, so nothing it reads is touched.)
+    if (lane == 0) {
       wk->piece_tgt[2 * wq] = t_first;
       wk->piece_flag[2 * wq] = first_cont ? ((one_piece && cont_next) ? 3 : 1) : 0;
       wk->piece_tgt[2 * wq + 1] = t_last;
@@ -424,49 +442,44 @@ __device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const 
     }
     if (nrows > 0) {
       wk->tgt_s[wt] = t;                           // read back by this row's own warp only
-      float* const piece_head = &wk->pieces[(2 * wq) * W + lane];
-      float* const piece_tail = &wk->pieces[(2 * wq + 1) * W + lane];
-      const int* tg = wk->tgt_s + wq * 32;
-#pragma unroll
-      for (int c0 = 0; c0 < W; c0 += 32) {
-        float* const aggc = p.agg + c0 + lane;
-        unsigned m = starts & ~1u;                 // a receiver starting at row 0 has nothing before it to flush
-        bool is_head = first_cont;
-        int off = t_first * W;                     // agg offset of the receiver being summed
-        float sum = 0.f;
-#pragma unroll
-        for (int half = 0; half < 2; ++half) {
-          __syncwarp();
-          if ((lane >> 4) == half) {
-            float4* d4 = reinterpret_cast<float4*>(scr + (lane & 15) * kWsScrStride);
-#pragma unroll
-            for (int j = 0; j < 8; ++j)
-              d4[j] = make_float4(y[c0 + 4 * j], y[c0 + 4 * j + 1], y[c0 + 4 * j + 2], y[c0 + 4 * j + 3]);
-          }
-          __syncwarp();
-          const float* col = scr + lane;
+      unsigned m = starts & ~1u;                   // a receiver starting at row 0 has nothing before it to flush
+      bool is_head = first_cont;
+      int off = t_first * (W / 2);                 // float2 offset of the receiver being summed
+      int r_start = 0;
+      float2 sum = f2(0.f, 0.f);
 #pragma unroll 1
-          for (int k = 0; k < 16; k += 4) {
-            float v[4];
+      for (int q = 0; q < 4; ++q) {
+        __syncwarp();
+        if ((lane >> 3) == q) {
+          float4* d4 = reinterpret_cast<float4*>(scr + (lane & 7) * kWsScrStride2);
 #pragma unroll
-            for (int u = 0; u < 4; ++u) v[u] = col[(k + u) * kWsScrStride];
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-              if (m & 1u) {                        // warp-uniform: the receiver ending at the previous row is complete
-                if (is_head) piece_head[c0] = sum; else aggc[off] = sum;
-                is_head = false;
-                off = tg[half * 16 + k + u] * W;
-                sum = 0.f;
-              }
-              sum += v[u];
-              m >>= 1;
-            }
-          }
+          for (int j = 0; j < W / 4; ++j) d4[j] = make_float4(y[4 * j], y[4 * j + 1], y[4 * j + 2], y[4 * j + 3]);
         }
-        if (cont_next && !one_piece) piece_tail[c0] = sum;
-        else if (is_head) piece_head[c0] = sum;
-        else aggc[off] = sum;
+        __syncwarp();
+        const float2* col = reinterpret_cast<const float2*>(scr) + lane;
+        float2 v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = col[k * (kWsScrStride2 / 2)];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          if (m & 1u) {                            // warp-uniform: the receiver ending at the previous row is complete
+            const float cnt = (float)(q * 8 + k - r_start);
+            const float2 o = __ffma2_rn(sum, gam2, f2(cnt * bet2.x, cnt * bet2.y));
+            if (is_head) *piece_head = o; else agg2[off] = o;
+            is_head = false;
+            r_start = q * 8 + k;
+            off = tg[r_start] * (W / 2);
+            sum = f2(0.f, 0.f);
+          }
+          sum = __fadd2_rn(sum, v[k]);
+          m >>= 1;
+        }
       }
+      const float cnt = (float)(nrows - r_start);
+      const float2 o = __ffma2_rn(sum, gam2, f2(cnt * bet2.x, cnt * bet2.y));
+      if (cont_next && !one_piece) *piece_tail = o;
+      else if (is_head) *piece_head = o;
+      else agg2[off] = o;
     }
     ws_group_bar(g);
     if (wt == 0) ws_stamp(i, 7);
