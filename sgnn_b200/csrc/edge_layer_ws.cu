@@ -305,10 +305,13 @@ __device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const 
   const int* tg = wk->tgt_s + wq * 32;
 
   // receiver of this thread's row, loaded one tile ahead (a cold read costs ~1 us on the group's serial chain)
-  int t_nx = -3;
+  // (with the receivers of the rows before and after it: the segment structure then needs no load)
+  int t_nx = -3, tb_nx = -2, ta_nx = -3;
   if (g < n_my) {
     const long e = (long)(blockIdx.x + g * gridDim.x) * kTileRows + wt;
     if (e < n_edges) t_nx = __ldg(p.tgt + e);
+    if (e - 1 >= 0 && e - 1 < n_edges) tb_nx = __ldg(p.tgt + e - 1);
+    if (e + 1 < n_edges) ta_nx = __ldg(p.tgt + e + 1);
   }
 
 #pragma unroll 1
@@ -318,28 +321,22 @@ __device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const 
     const int e0 = tile * kTileRows;
     const int nvalid = n_edges - e0 < kTileRows ? n_edges - e0 : kTileRows;
     const bool valid = wt < nvalid;
-    const int t = t_nx;
+    const int t = t_nx, t_prev = tb_nx, t_next = ta_nx;
     {
       const long en = (long)(tile + stride_tiles) * kTileRows + wt;
-      t_nx = (i + kWsGroups < n_my && en < n_edges) ? __ldg(p.tgt + en) : -3;
+      const bool more = i + kWsGroups < n_my;
+      t_nx = (more && en < n_edges) ? __ldg(p.tgt + en) : -3;
+      tb_nx = (more && en - 1 < n_edges) ? __ldg(p.tgt + en - 1) : -2;
+      ta_nx = (more && en + 1 < n_edges) ? __ldg(p.tgt + en + 1) : -3;
     }
 
     // ---- segment structure of this warp's 32 rows (warp-uniform) ----
     const int nrows = nvalid - wq * 32 < 0 ? 0 : (nvalid - wq * 32 > 32 ? 32 : nvalid - wq * 32);
-    int t_prev = __shfl_up_sync(FULL, t, 1);
-    if (lane == 0) {
-      const int idx = e0 + wq * 32 - 1;
-      t_prev = (idx >= 0 && idx < n_edges) ? __ldg(p.tgt + idx) : -2;
-    }
     // bit r: row r starts a new receiver; rows past the end of the edge list never do
     const unsigned starts = __ballot_sync(FULL, t != t_prev) & (nrows == 32 ? FULL : ((1u << nrows) - 1u));
-    int t_after = -3;
-    {
-      const int idx = e0 + wq * 32 + nrows;
-      if (nrows > 0 && idx < n_edges) t_after = __ldg(p.tgt + idx);
-    }
     const int t_first = __shfl_sync(FULL, t, 0);
     const int t_last = __shfl_sync(FULL, t, nrows > 0 ? nrows - 1 : 0);
+    const int t_after = __shfl_sync(FULL, t_next, nrows > 0 ? nrows - 1 : 0);
     const bool first_cont = nrows > 0 && !(starts & 1u);      // row 0 continues the previous warp's receiver
     const bool cont_next = nrows > 0 && t_after == t_last;    // the last receiver continues in the next warp
     const bool one_piece = first_cont && starts == 0u;        // the whole warp is the middle of one receiver
@@ -389,8 +386,7 @@ __device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const 
     mbar_wait_sleep(&wk->acc1_ready, par);
     tc_fence_after_sync();
     float y[W];
-    tmem_ld32(t1, y);
-    tmem_ld32(t1 + 32, y + 32);
+    tmem_ld64(t1, y);
     tc_fence_before_sync();
     mbar_arrive(&wk->region_free);
     if (g_ws_flags & 4) {      // measurement switch: skip LayerNorm, sums and stitch (wrong results)
