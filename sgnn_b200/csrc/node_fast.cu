@@ -225,25 +225,50 @@ __global__ void __launch_bounds__(kNodeFastThreads, 1) node_fast_kernel(const Sg
       const uint32_t tc = cur + lane_base;
       tmem_ld32(tc, v);
       tmem_ld32(tc + 32, v + 32);
-      const float* b = blob_f + p.mlp.b_off[nh];
-#pragma unroll
-      for (int j = 0; j < NW; ++j) v[j] += b[j];
+      // bias + LayerNorm in packed fp32x2 (the same operations in the same order as the scalar form:
+      // identical bits, half the issue slots -- one warp per scheduler runs this chain at small N)
+      const float4* b4 = reinterpret_cast<const float4*>(blob_f + p.mlp.b_off[nh]);
       if (p.mlp.has_ln) {
-        const float* gam = blob_f + p.mlp.gamma_off;
-        const float* bet = blob_f + p.mlp.beta_off;
-        float s4[4] = {0.f, 0.f, 0.f, 0.f};
+        const float4* gam4 = reinterpret_cast<const float4*>(blob_f + p.mlp.gamma_off);
+        const float4* bet4 = reinterpret_cast<const float4*>(blob_f + p.mlp.beta_off);
+        float2 s01 = make_float2(0.f, 0.f), s23 = make_float2(0.f, 0.f);
 #pragma unroll
-        for (int j = 0; j < NW; ++j) s4[j & 3] += v[j];
-        const float mean = ((s4[0] + s4[1]) + (s4[2] + s4[3])) / (float)NW;
-        float q4[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-        for (int j = 0; j < NW; ++j) {
-          v[j] -= mean;
-          q4[j & 3] = fmaf(v[j], v[j], q4[j & 3]);
+        for (int j = 0; j < NW / 4; ++j) {
+          const float4 b = b4[j];
+          const float2 a = __fadd2_rn(make_float2(v[4 * j], v[4 * j + 1]), make_float2(b.x, b.y));
+          const float2 c = __fadd2_rn(make_float2(v[4 * j + 2], v[4 * j + 3]), make_float2(b.z, b.w));
+          v[4 * j] = a.x; v[4 * j + 1] = a.y; v[4 * j + 2] = c.x; v[4 * j + 3] = c.y;
+          s01 = __fadd2_rn(s01, a);
+          s23 = __fadd2_rn(s23, c);
         }
-        const float rstd = 1.0f / sqrtf(((q4[0] + q4[1]) + (q4[2] + q4[3])) / (float)NW + 1e-5f);
+        const float nmean = -(((s01.x + s01.y) + (s23.x + s23.y)) / (float)NW);
+        const float2 nm = make_float2(nmean, nmean);
+        float2 q01 = make_float2(0.f, 0.f), q23 = make_float2(0.f, 0.f);
 #pragma unroll
-        for (int j = 0; j < NW; ++j) v[j] = v[j] * rstd * gam[j] + bet[j];
+        for (int j = 0; j < NW / 4; ++j) {
+          const float2 a = __fadd2_rn(make_float2(v[4 * j], v[4 * j + 1]), nm);
+          const float2 c = __fadd2_rn(make_float2(v[4 * j + 2], v[4 * j + 3]), nm);
+          v[4 * j] = a.x; v[4 * j + 1] = a.y; v[4 * j + 2] = c.x; v[4 * j + 3] = c.y;
+          q01 = __ffma2_rn(a, a, q01);
+          q23 = __ffma2_rn(c, c, q23);
+        }
+        const float rstd = 1.0f / sqrtf(((q01.x + q01.y) + (q23.x + q23.y)) / (float)NW + 1e-5f);
+        const float2 r2 = make_float2(rstd, rstd);
+#pragma unroll
+        for (int j = 0; j < NW / 4; ++j) {
+          const float4 ga = gam4[j], be = bet4[j];
+          const float2 a = __ffma2_rn(__fmul2_rn(make_float2(v[4 * j], v[4 * j + 1]), r2), make_float2(ga.x, ga.y),
+                                      make_float2(be.x, be.y));
+          const float2 c = __ffma2_rn(__fmul2_rn(make_float2(v[4 * j + 2], v[4 * j + 3]), r2), make_float2(ga.z, ga.w),
+                                      make_float2(be.z, be.w));
+          v[4 * j] = a.x; v[4 * j + 1] = a.y; v[4 * j + 2] = c.x; v[4 * j + 3] = c.y;
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < NW / 4; ++j) {
+          const float4 b = b4[j];
+          v[4 * j] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
+        }
       }
       if (valid) {
         if (p.residual) {

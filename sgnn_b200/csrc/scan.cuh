@@ -54,17 +54,38 @@ __global__ void __launch_bounds__(kScanThreads) scan_chunk_kernel(const int* __r
   const int base = blockIdx.x * kScanChunk + threadIdx.x * kScanItems;
   int v[kScanItems];
   int s = 0;
+  // a thread's 16 items are one 64-byte line: four 16-byte loads / stores when it is whole and aligned
+  const bool vec = base + kScanItems <= n && ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
+  if (vec) {
 #pragma unroll
-  for (int i = 0; i < kScanItems; ++i) {
-    v[i] = (base + i < n) ? in[base + i] : 0;
-    s += v[i];
+    for (int i = 0; i < kScanItems / 4; ++i) {
+      const int4 q = reinterpret_cast<const int4*>(in + base)[i];
+      v[4 * i] = q.x; v[4 * i + 1] = q.y; v[4 * i + 2] = q.z; v[4 * i + 3] = q.w;
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i) v[i] = (base + i < n) ? in[base + i] : 0;
   }
+#pragma unroll
+  for (int i = 0; i < kScanItems; ++i) s += v[i];
   int total;
   int prefix = block_exclusive_scan(s, total);
+  if (vec) {
 #pragma unroll
-  for (int i = 0; i < kScanItems; ++i) {
-    if (base + i < n) out[base + i] = prefix;
-    prefix += v[i];
+    for (int i = 0; i < kScanItems / 4; ++i) {
+      int4 q;
+      q.x = prefix; prefix += v[4 * i];
+      q.y = prefix; prefix += v[4 * i + 1];
+      q.z = prefix; prefix += v[4 * i + 2];
+      q.w = prefix; prefix += v[4 * i + 3];
+      reinterpret_cast<int4*>(out + base)[i] = q;
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i) {
+      if (base + i < n) out[base + i] = prefix;
+      prefix += v[i];
+    }
   }
   if (threadIdx.x == 0) {
     if (MODE == 0) out[n] = total;
