@@ -71,36 +71,6 @@ __host__ __device__ inline WsSmem edge_ws_smem(int blob_bytes) {
   return s;
 }
 
-__device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-      "selp.u32 %0, 1, 0, p;\n\t}"
-      : "=r"(ok)
-      : "r"(smem_u32(bar)), "r"(parity)
-      : "memory");
-  return ok != 0;
-}
-// wait with a long hardware suspend hint: 16 epilogue warps that SPIN on try_wait compete with the
-// working warps for instruction fetch (ncu r01h: "no instruction" was 46 % of all stall samples)
-__device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "WS_WAIT:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
-      "@p bra WS_DONE;\n\t"
-      "bra WS_WAIT;\n\t"
-      "WS_DONE:\n\t}" ::"r"(smem_u32(bar)),
-      "r"(parity), "r"(0x989680u)
-      : "memory");
-}
-// The single-thread issuers and the producers poll instead: waking from the hardware suspend costs
-// ~0.4 us (in-kernel timeline), which the serial issue chains cannot afford five times per tile.
-__device__ __forceinline__ void mbar_wait_spin(uint64_t* bar, uint32_t parity) {
-  while (!mbar_test(bar, parity)) {
-  }
-}
 __device__ __forceinline__ float ws_tf32r(float x) { return __uint_as_float(__float_as_uint(x) + 0x1000u); }
 __device__ __forceinline__ void ws_group_bar(int g) {
   asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "r"(kThreads) : "memory");

@@ -301,6 +301,7 @@ extern "C" size_t sgnn_node_smem_bytes(const SgnnNodeParams* p, int tc) {
 }
 
 int sgnn_node_fast_try(const SgnnNodeParams* p, void* stream);     // node_fast.cu
+int sgnn_node_ws_try(const SgnnNodeParams* p, void* stream);       // node_ws.cu
 
 extern "C" int sgnn_node_fwd(const SgnnNodeParams* p, int use_tensor_cores, int grid, void* stream) {
   SGNN_CHECK_ARG(p->k_pad % 32 == 0 && p->k_pad >= 32 && p->k_pad <= 256, "node: k_pad=%d must be a multiple of 32 in [32,256]", p->k_pad);
@@ -323,7 +324,9 @@ extern "C" int sgnn_node_fwd(const SgnnNodeParams* p, int use_tensor_cores, int 
   SGNN_CHECK_ARG(p->blob_bytes % 16 == 0, "node: blob size must be a multiple of 16");
   if (p->n_rows <= 0) return SGNN_OK;
   if (use_tensor_cores && !getenv("SGNN_NODE_GENERIC")) {      // throughput kernel for 64-wide latents
-    const int r = sgnn_node_fast_try(p, stream);
+    int r = sgnn_node_ws_try(p, stream);
+    if (r != 0) return r < 0 ? r : SGNN_OK;
+    r = sgnn_node_fast_try(p, stream);
     if (r != 0) return r < 0 ? r : SGNN_OK;
   }
   SGNN_CHECK_ARG(p->tail != SGNN_TAIL_PX, "node: tail PX (gather-mode edge kernel) exists only in the 64-wide "

@@ -131,6 +131,8 @@ typedef struct {
   float* next_pos;        /* [n, dim] */
   long next_pos_stride;
   float* strain_out;      /* [n] */
+  const float* xr_in;     /* AGG_X, optional: x_in rounded to TF32 (row i at xr_in + i * xr_ld), as written */
+  long xr_ld;             /* by a node kernel with tail PX into the Q half of pq; enables node_ws_kernel    */
 } SgnnNodeParams;
 
 #ifdef __cplusplus

@@ -51,7 +51,38 @@ static inline int make_row_gather_map(CUtensorMap* map, const void* base, long r
   return SGNN_OK;
 }
 
+// same matrix, box = `box_rows` rows x one 128-byte K-block: one TMA tile load lands a whole K-block of
+// a row-major [rows, cols] matrix as a K-major SWIZZLE_128B operand tile (rows past the end read as 0)
+static inline int make_row_tile_map(CUtensorMap* map, const void* base, long rows, int cols, long pitch_bytes,
+                                    int box_rows) {
+  EncodeTiledFn enc = tensormap_encoder();
+  if (!enc) {
+    sgnn_set_error("cuTensorMapEncodeTiled is not available from this driver");
+    return SGNN_ERR_CUDA;
+  }
+  const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  const cuuint64_t strides[1] = {(cuuint64_t)pitch_bytes};
+  const cuuint32_t box[2] = {(cuuint32_t)kKBlock, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1u, 1u};
+  const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    sgnn_set_error("cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    return SGNN_ERR_CUDA;
+  }
+  return SGNN_OK;
+}
+
 #ifdef __CUDACC__
+// one box of a 2D tensor map (inner coordinate `col`, outer coordinate `row`) -> shared memory
+__device__ __forceinline__ void tma_tile_2d(void* smem_dst, const CUtensorMap* map, int col, int row, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];" ::"r"(smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(col), "r"(row)
+      : "memory");
+}
 // four rows (row indices r0..r3) x one 128-byte K-block starting at column `col` -> 512 bytes at dst
 __device__ __forceinline__ void tma_gather4(void* smem_dst, const CUtensorMap* map, int col, int r0, int r1, int r2,
                                             int r3, uint64_t* bar) {

@@ -315,6 +315,8 @@ class EpdEngine:
             last = bi == len(self.blocks) - 1
             kw = dict(agg=self.agg, head=self.head, rowptr=csr.rowptr, agg_w=ep.out,
                       x_in=self.x[x_cur], x_w=self.latent, x_out=self.x[1 - x_cur])
+            if self.gather:     # Q half of pq = this layer's input latents rounded to TF32 (node tail PX)
+                kw.update(xr_in=self.pq.data_ptr() + 4 * self.latent, xr_ld=2 * self.latent)
             if not last:
                 kw.update(pq_out=self.pq)
             else:
