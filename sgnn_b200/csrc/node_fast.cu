@@ -154,7 +154,16 @@ __global__ void __launch_bounds__(kNodeFastThreads, 1) node_fast_kernel(const Sg
       stamp(5);
 #pragma unroll
       for (int j = 0; j < NW; ++j) v[j] = 0.f;
-      if (valid) load_row64(p.x_in + i * NW, v);
+      if (valid) {
+        // xr_in: the rounded copy bits(x) + 0x1000 a PX tail left in the Q half of pq -- exactly invertible
+        if (p.xr_in) {
+          load_row64(p.xr_in + i * p.xr_ld, v);
+#pragma unroll
+          for (int j = 0; j < NW; ++j) v[j] = __uint_as_float(__float_as_uint(v[j]) - 0x1000u);
+        } else {
+          load_row64(p.x_in + i * NW, v);
+        }
+      }
       row_to_tmem(tA, v);
       stamp(6);
       run_mma(w, wt, bar, phase, [&] {           // x columns of W0: K-blocks 2,3 ; accumulate
@@ -272,11 +281,16 @@ __global__ void __launch_bounds__(kNodeFastThreads, 1) node_fast_kernel(const Sg
       }
       if (valid) {
         if (p.residual) {
-          const float4* xr = reinterpret_cast<const float4*>(p.x_in + i * NW);
+          const bool rounded = p.prologue == SGNN_PRO_AGG_X && p.xr_in != nullptr;
+          const float4* xr = reinterpret_cast<const float4*>(rounded ? p.xr_in + i * p.xr_ld : p.x_in + i * NW);
+          const uint32_t unr = rounded ? 0x1000u : 0u;
 #pragma unroll
           for (int j = 0; j < NW / 4; ++j) {
             const float4 x = __ldg(xr + j);
-            v[4 * j] += x.x; v[4 * j + 1] += x.y; v[4 * j + 2] += x.z; v[4 * j + 3] += x.w;
+            v[4 * j] += __uint_as_float(__float_as_uint(x.x) - unr);
+            v[4 * j + 1] += __uint_as_float(__float_as_uint(x.y) - unr);
+            v[4 * j + 2] += __uint_as_float(__float_as_uint(x.z) - unr);
+            v[4 * j + 3] += __uint_as_float(__float_as_uint(x.w) - unr);
           }
         }
         if (p.x_out) {

@@ -5,99 +5,124 @@
 //   x'_i = x_i + LN(V2 relu(V1 [agg_i | x_i] + c1) + c2);  tail: P = x' W1a^T + b1 and the TF32-rounded
 //   x' for the next edge layer (SGNN_TAIL_PX), or decoder MLP + Euler integrator (SGNN_TAIL_DECODE).
 //
-// node_fast.cu runs this as four independent serial chains per SM (row loads -> TMEM -> MMA -> ... ,
-// five MMA round trips per tile): bound by global-load and round-trip latency at 41 % of the HBM
-// roofline.  Here, as in edge_layer_ws.cu:
-//   warp 16      producer: the tile's [agg | x] operand (K = 128) by FOUR TMA tile loads (2D tensor maps
-//                over the row-major agg and rounded-x matrices, box 128 rows x one K-block, SWIZZLE_128B:
-//                the copy engine does the row-major -> K-major swizzled transposition) into one of two
-//                64 KB stages; coordinates are warp-uniform, so no per-lane issue loops
-//   warps 17-19  one issuer warp per GEMM (first Linear from shared memory, second Linear and the
-//                tail GEMM with A in TMEM), tcgen05 under elect.sync in converged code
-//   warps 0-15   four epilogue groups of 128 threads (thread = row = TMEM lane); a group owns TMEM
-//                columns [128g, 128g + 128) and every 4th tile
+// node_fast.cu runs this as four independent serial chains per SM with every row read and written by
+// its own thread (16-byte accesses 256 or 512 bytes apart): ncu shows the L1 data pipe at 67 % with the
+// issue slots 13 % busy -- the kernel is bound by uncoalesced LSU wavefronts, not by HBM.  Here NO tile
+// data goes through the LSU to global memory at all:
+//   * the latents travel between layers only as the "rounded" copy in the Q half of pq: bits(x) + 0x1000,
+//     low mantissa bits kept (the tensor core ignores them).  That is exactly invertible, so the same
+//     copy serves as the TF32 operand of both GEMMs that consume x AND as the fp32 residual
+//     (x = bits - 0x1000): 1024 algorithmic bytes per node and layer instead of 1792
+//   * warp 16 (producer) brings the tile's [agg | x] operand (K = 128) in by four TMA tile loads (2D
+//     tensor maps, box 128 rows x one 128-byte K-block, SWIZZLE_128B: the copy engine does the row-major
+//     -> K-major transposition); agg into one of two short-lived slots (free again after the first GEMM),
+//     x into the slot of the epilogue group that owns the tile, where it stays for the whole chain
+//   * warps 17-19: one issuer warp per GEMM (first Linear from shared memory, second Linear and the tail
+//     GEMM with A in TMEM), tcgen05 under elect.sync in converged code
+//   * warps 0-11: three epilogue groups of 128 threads (thread = row = TMEM lane), each owning TMEM
+//     columns [128g, 128g + 128) and every 3rd tile.  The residual is read from the group's x slot, x'
+//     is written back over it and leaves by a TMA tensor store; P follows through the same slot
 // The agg rows arrive unpatched: a receiver whose CSR row straddles edge tiles still lacks the `head`
-// partials and a receiver without edges has no agg row at all.  The owning thread patches its row in
-// the stage (rare) before the group releases the tile to the first issuer.
+// partials and a receiver without edges has no agg row at all.  The owning thread completes and rounds
+// its row in the slot before the group releases the tile to the first issuer.
 #include "mlp_tile.cuh"
 #include "params.h"
 #include "tensormap.cuh"
 
 namespace sgnn {
 
-constexpr int kNwGroups = 4;
+constexpr int kNwGroups = 3;
 constexpr int kNwThreads = kNwGroups * kThreads + 128;     // + one warpgroup: producer and three issuer warps
-constexpr int kNwEpiRegs = 104, kNwAuxRegs = 48;           // setmaxnreg split (see edge_layer_ws.cu)
+// setmaxnreg: 512 threads launch at 128; (128 - 56) * 128 released = (152 - 128) * 384 acquired
+constexpr int kNwEpiRegs = 152, kNwAuxRegs = 56;
 constexpr int kNwW = 64;
-constexpr int kNwSlotBytes = kTileRows * kKBlockBytes;     // 16 KB
-constexpr int kNwStageBytes = 4 * kNwSlotBytes;            // agg K-blocks 0,1 then x K-blocks 0,1
-constexpr int kNwStages = 2;
+constexpr int kNwKbBytes = kTileRows * kKBlockBytes;       // 16 KB: one K-block of a 128-row operand tile
+constexpr int kNwSlotBytes = 2 * kNwKbBytes;               // 32 KB: 64 columns
+constexpr int kNwAggSlots = 2;
+constexpr int kNwVecBytes = 2048;                          // resident part of the blob's vector region
+constexpr int kNwImgBytes = 4 * kNwW * kNwW * 4;           // W0 (K = 128) + W1 + tail image
 
 struct NwGroup {
-  // `full` is per GROUP, not per stage: a group sees only every 4th tile, and a parity wait is only
-  // unambiguous on a barrier whose every phase the waiter consumes
-  uint64_t full, patched, acc0_ready, hid_ready, acc1_ready, xo_ready, acc2_ready, region_free;
+  // `full` is per GROUP, not per slot: a parity wait is only unambiguous on a barrier whose every phase
+  // the waiter consumes, and a group sees only every 3rd tile
+  uint64_t full, patched, acc0_ready, hid_ready, acc1_ready, xo_ready, acc2_ready, region_free, slot_free;
 };
 struct NwMisc {
   uint64_t bar_w;
-  uint64_t empty[kNwStages];
+  uint64_t agg_empty[kNwAggSlots];
   uint32_t tmem_slot;
   int pad;
   NwGroup g[kNwGroups];
 };
-struct NwSmem {
-  int ring, misc, total;
-};
-__host__ __device__ inline NwSmem node_ws_smem(int blob_bytes) {
-  NwSmem s;
-  s.ring = align_up(blob_bytes, 1024);
-  s.misc = s.ring + kNwStages * kNwStageBytes;
-  s.total = s.misc + (int)sizeof(NwMisc) + 1024;
-  return s;
-}
+constexpr int kNwImgOff = kNwVecBytes;
+constexpr int kNwAggOff = kNwImgOff + kNwImgBytes;
+constexpr int kNwXOff = kNwAggOff + kNwAggSlots * kNwSlotBytes;
+constexpr int kNwMiscOff = kNwXOff + kNwGroups * kNwSlotBytes;
+constexpr int kNwSmemBytes = kNwMiscOff + 1024;
+static_assert(sizeof(NwMisc) <= 1024, "misc block");
+static_assert(kNwSmemBytes <= 227 * 1024, "shared memory budget");
 
 __device__ __forceinline__ float nw_tf32r(float x) { return __uint_as_float(__float_as_uint(x) + 0x1000u); }
+__device__ __forceinline__ float nw_unround(float x) { return __uint_as_float(__float_as_uint(x) - 0x1000u); }
 __device__ __forceinline__ float2 nf2(float a, float b) { return make_float2(a, b); }
+__device__ __forceinline__ void nw_group_bar(int g) {
+  asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "r"(kThreads) : "memory");
+}
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, int col, int row, const void* smem_src) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(map)),
+               "r"(smem_u32(smem_src)), "r"(col), "r"(row)
+               : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 
 // ---------------------------------------------------------------------------------- producer
-__device__ __forceinline__ void nw_producer(const CUtensorMap* agg_map, const CUtensorMap* x_map, char* ring,
+__device__ __forceinline__ void nw_producer(const CUtensorMap* agg_map, const CUtensorMap* x_map, char* smem,
                                             NwMisc* misc, int n_my) {
   for (int i = 0; i < n_my; ++i) {
     const int tile = blockIdx.x + i * gridDim.x;
-    const int st = i & 1, use = i >> 1;
-    if (use > 0) mbar_wait_spin(&misc->empty[st], (uint32_t)(use - 1) & 1u);
-    char* stage = ring + st * kNwStageBytes;
-    uint64_t* full = &misc->g[i & 3].full;
+    const int g = i % kNwGroups, use_g = i / kNwGroups, sa = i & 1;
+    uint64_t* full = &misc->g[g].full;
+    char* agg_slot = smem + kNwAggOff + sa * kNwSlotBytes;
+    char* x_slot = smem + kNwXOff + g * kNwSlotBytes;
+    if (i >= kNwAggSlots) mbar_wait_spin(&misc->agg_empty[sa], (uint32_t)((i >> 1) - 1) & 1u);
     if (elect_one()) {
-      mbar_arrive_expect_tx(full, kNwStageBytes);
-      tma_tile_2d(stage, agg_map, 0, tile * kTileRows, full);
-      tma_tile_2d(stage + kNwSlotBytes, agg_map, kKBlock, tile * kTileRows, full);
-      tma_tile_2d(stage + 2 * kNwSlotBytes, x_map, 0, tile * kTileRows, full);
-      tma_tile_2d(stage + 3 * kNwSlotBytes, x_map, kKBlock, tile * kTileRows, full);
+      mbar_arrive_expect_tx(full, 2 * kNwSlotBytes);
+      tma_tile_2d(agg_slot, agg_map, 0, tile * kTileRows, full);
+      tma_tile_2d(agg_slot + kNwKbBytes, agg_map, kKBlock, tile * kTileRows, full);
+    }
+    __syncwarp();
+    if (use_g > 0) mbar_wait_spin(&misc->g[g].slot_free, (uint32_t)(use_g - 1) & 1u);
+    if (elect_one()) {
+      tma_tile_2d(x_slot, x_map, 0, tile * kTileRows, full);
+      tma_tile_2d(x_slot + kNwKbBytes, x_map, kKBlock, tile * kTileRows, full);
     }
     __syncwarp();
   }
 }
 
 // ---------------------------------------------------------------------------------- MMA issuers
-// acc0 = [agg | x] W0^T, K = 128 from the stage (W0 image: K-blocks 0,1 = agg columns, 2,3 = x columns)
-__device__ __forceinline__ void nw_mma0(uint32_t ring_u32, uint32_t w0, NwMisc* misc, int n_my, uint32_t tmem) {
+// acc0 = [agg | x] W0^T, K = 128 (W0 image: K-blocks 0,1 = agg columns, 2,3 = x columns)
+__device__ __forceinline__ void nw_mma0(uint32_t smem_u, uint32_t w0, NwMisc* misc, int n_my, uint32_t tmem) {
   const uint32_t idesc = umma_idesc_tf32(kTileRows, kNwW);
   for (int a = 0; a < n_my; ++a) {
-    const int g = a & 3, st = a & 1;
-    if (a >= kNwGroups) mbar_wait_spin(&misc->g[g].region_free, (uint32_t)((a >> 2) - 1) & 1u);
-    mbar_wait_spin(&misc->g[g].patched, (uint32_t)(a >> 2) & 1u);     // implies the group's `full`
+    const int g = a % kNwGroups, use_g = a / kNwGroups, sa = a & 1;
+    if (use_g > 0) mbar_wait_spin(&misc->g[g].region_free, (uint32_t)(use_g - 1) & 1u);
+    mbar_wait_spin(&misc->g[g].patched, (uint32_t)use_g & 1u);     // implies the group's `full`
     tc_fence_after_sync();
     const uint32_t d = tmem + (uint32_t)(g * 2 * kNwW);
-    const uint32_t a_st = ring_u32 + st * kNwStageBytes;
+    const uint32_t a_agg = smem_u + kNwAggOff + sa * kNwSlotBytes;
+    const uint32_t a_x = smem_u + kNwXOff + g * kNwSlotBytes;
     if (elect_one()) {
 #pragma unroll
-      for (int kb = 0; kb < 4; ++kb)
+      for (int kb = 0; kb < 4; ++kb) {
+        const uint32_t a_kb = (kb < 2 ? a_agg : a_x) + (kb & 1) * kNwKbBytes;
 #pragma unroll
         for (int j = 0; j < 4; ++j)
-          umma_tf32(d, umma_desc_sw128(a_st + kb * kNwSlotBytes + j * 32),
-                    umma_desc_sw128(w0 + kb * kNwW * kKBlockBytes + j * 32), idesc, (kb > 0 || j > 0) ? 1u : 0u);
-      tc_commit(&misc->empty[st]);
+          umma_tf32(d, umma_desc_sw128(a_kb + j * 32), umma_desc_sw128(w0 + kb * kNwW * kKBlockBytes + j * 32), idesc,
+                    (kb > 0 || j > 0) ? 1u : 0u);
+        if (kb == 1) tc_commit(&misc->agg_empty[sa]);
+      }
       tc_commit(&misc->g[g].acc0_ready);
     }
     __syncwarp();
@@ -106,10 +131,11 @@ __device__ __forceinline__ void nw_mma0(uint32_t ring_u32, uint32_t w0, NwMisc* 
 // D (region 1) = A (region 0, TMEM) W^T for the second Linear (which == 0) and the tail GEMM (which == 1)
 __device__ __forceinline__ void nw_mma_ts(uint32_t w_img, NwMisc* misc, int n_my, uint32_t tmem, int which) {
   for (int b = 0; b < n_my; ++b) {
-    NwGroup* gr = &misc->g[b & 3];
-    mbar_wait_spin(which == 0 ? &gr->hid_ready : &gr->xo_ready, (uint32_t)(b >> 2) & 1u);
+    const int g = b % kNwGroups;
+    NwGroup* gr = &misc->g[g];
+    mbar_wait_spin(which == 0 ? &gr->hid_ready : &gr->xo_ready, (uint32_t)(b / kNwGroups) & 1u);
     tc_fence_after_sync();
-    const uint32_t base = tmem + (uint32_t)((b & 3) * 2 * kNwW);
+    const uint32_t base = tmem + (uint32_t)(g * 2 * kNwW);
     if (elect_one()) {
       umma_gemm_tf32_ts(base + kNwW, base, w_img, kNwW, kNwW);
       tc_commit(which == 0 ? &gr->acc1_ready : &gr->acc2_ready);
@@ -119,17 +145,20 @@ __device__ __forceinline__ void nw_mma_ts(uint32_t w_img, NwMisc* misc, int n_my
 }
 
 // ---------------------------------------------------------------------------------- epilogue
-__device__ __forceinline__ void nw_epilogue(const SgnnNodeParams& p, const float* blob_f, char* ring, NwMisc* misc,
-                                            int g, int wt, int n_my, uint32_t tmem) {
+__device__ __forceinline__ void nw_epilogue(const SgnnNodeParams& p, const CUtensorMap* pq_map, char* smem,
+                                            NwMisc* misc, int g, int wt, int n_my, uint32_t tmem) {
   constexpr int W = kNwW;
   const int wq = wt >> 5;
   NwGroup* gr = &misc->g[g];
   const uint32_t lane_base = (uint32_t)(wq * 32) << 16;
   const uint32_t t0 = tmem + (uint32_t)(g * 2 * W) + lane_base, t1 = t0 + W;
-  const float4* b0 = reinterpret_cast<const float4*>(blob_f + p.mlp.b_off[0]);
-  const float4* b1 = reinterpret_cast<const float4*>(blob_f + p.mlp.b_off[1]);
-  const float4* gam4 = reinterpret_cast<const float4*>(blob_f + p.mlp.gamma_off);
-  const float4* bet4 = reinterpret_cast<const float4*>(blob_f + p.mlp.beta_off);
+  const float* vec = reinterpret_cast<const float*>(smem);
+  const float4* b0 = reinterpret_cast<const float4*>(vec + p.mlp.b_off[0]);
+  const float4* b1 = reinterpret_cast<const float4*>(vec + p.mlp.b_off[1]);
+  const float4* gam4 = reinterpret_cast<const float4*>(vec + p.mlp.gamma_off);
+  const float4* bet4 = reinterpret_cast<const float4*>(vec + p.mlp.beta_off);
+  char* x_slot = smem + kNwXOff + g * kNwSlotBytes;
+  const bool px = p.tail == SGNN_TAIL_PX;
 
   // CSR bounds of this thread's row, loaded one tile ahead
   int beg_nx = 0, end_nx = 0;
@@ -140,7 +169,7 @@ __device__ __forceinline__ void nw_epilogue(const SgnnNodeParams& p, const float
 
 #pragma unroll 1
   for (int i = g; i < n_my; i += kNwGroups) {
-    const uint32_t par = (uint32_t)(i >> 2) & 1u;
+    const uint32_t par = (uint32_t)(i / kNwGroups) & 1u;
     const int tile = blockIdx.x + i * gridDim.x;
     const long r = (long)tile * kTileRows + wt;
     const bool valid = r < p.n_rows;
@@ -151,11 +180,11 @@ __device__ __forceinline__ void nw_epilogue(const SgnnNodeParams& p, const float
       if (i + kNwGroups < n_my && rn < p.n_rows) { beg_nx = __ldg(p.rowptr + rn); end_nx = __ldg(p.rowptr + rn + 1); }
     }
 
-    // ---- this thread's agg row in the stage: complete it (rare) and round it to TF32 (the copy engine
+    // ---- this thread's agg row in its slot: complete it (rare) and round it to TF32 (the copy engine
     //      delivered raw fp32; the x half was rounded by its producer), then release the tile ----
     mbar_wait_sleep(&gr->full, par);
     {
-      char* agg_rows = ring + (i & 1) * kNwStageBytes;
+      char* agg_rows = smem + kNwAggOff + (i & 1) * kNwSlotBytes;
       const bool has = valid && end > beg;           // no edges: the edge kernel never wrote this agg row
       const int t_lo = (beg >> 7) + 1, t_hi = has ? ((end - 1) >> 7) : 0;   // later edge tiles of a straddling CSR row
 #pragma unroll 4
@@ -169,7 +198,7 @@ __device__ __forceinline__ void nw_epilogue(const SgnnNodeParams& p, const float
         *q = make_float4(nw_tf32r(a.x), nw_tf32r(a.y), nw_tf32r(a.z), nw_tf32r(a.w));
       }
     }
-    fence_proxy_async_smem();                    // generic-proxy patch -> visible to tcgen05.mma
+    fence_proxy_async_smem();                    // generic-proxy writes -> visible to tcgen05.mma
     mbar_arrive(&gr->patched);
 
     // ---- hidden = relu(acc0 + c1), rounded to TF32, back into the same TMEM columns ----
@@ -230,57 +259,80 @@ __device__ __forceinline__ void nw_epilogue(const SgnnNodeParams& p, const float
         y[4 * j] = a.x; y[4 * j + 1] = a.y; y[4 * j + 2] = c.x; y[4 * j + 3] = c.y;
       }
     }
-    if (valid) {
-      const float4* xr = reinterpret_cast<const float4*>(p.x_in + r * W);
+    // residual from the group's x slot (rounded copy -> exact fp32), x' (rounded) back in its place:
+    // A operand of the tail GEMM through TMEM, sender/next-layer copy through the slot and a TMA store
+    {
+      float4* xo = (p.x_out != nullptr && valid) ? reinterpret_cast<float4*>(p.x_out + r * W) : nullptr;
 #pragma unroll
-      for (int j = 0; j < W / 4; ++j) {
-        const float4 x = __ldg(xr + j);
-        y[4 * j] += x.x; y[4 * j + 1] += x.y; y[4 * j + 2] += x.z; y[4 * j + 3] += x.w;
-      }
-      if (p.x_out) {
-        float4* xo = reinterpret_cast<float4*>(p.x_out + r * W);
-#pragma unroll
-        for (int j = 0; j < W / 4; ++j) xo[j] = make_float4(y[4 * j], y[4 * j + 1], y[4 * j + 2], y[4 * j + 3]);
+      for (int c = 0; c < W / 4; ++c) {
+        float4* q = reinterpret_cast<float4*>(x_slot + sw128_chunk_offset(wt, c, kTileRows));
+        const float4 xr = *q;
+        const float a0 = y[4 * c] + nw_unround(xr.x), a1 = y[4 * c + 1] + nw_unround(xr.y);
+        const float a2 = y[4 * c + 2] + nw_unround(xr.z), a3 = y[4 * c + 3] + nw_unround(xr.w);
+        if (xo) xo[c] = make_float4(a0, a1, a2, a3);          // only on request (tests, last layer)
+        y[4 * c] = nw_tf32r(a0); y[4 * c + 1] = nw_tf32r(a1); y[4 * c + 2] = nw_tf32r(a2); y[4 * c + 3] = nw_tf32r(a3);
+        if (px) *q = make_float4(y[4 * c], y[4 * c + 1], y[4 * c + 2], y[4 * c + 3]);
       }
     }
-    // x' rounded to TF32: A operand of the tail GEMM (TMEM region 0) and, for the next edge layer's
-    // sender gather, the Q half of the pq row
-#pragma unroll
-    for (int j = 0; j < W; ++j) y[j] = nw_tf32r(y[j]);
     tmem_st32(t0, y);
     tmem_st32(t0 + 32, y + 32);
-    if (p.tail == SGNN_TAIL_PX && valid) {
-      float4* dst = reinterpret_cast<float4*>(p.pq_out + r * 2 * W + W);
-#pragma unroll
-      for (int j = 0; j < W / 4; ++j) dst[j] = make_float4(y[4 * j], y[4 * j + 1], y[4 * j + 2], y[4 * j + 3]);
-    }
     tmem_st_wait();
     tc_fence_before_sync();
     mbar_arrive(&gr->xo_ready);
+    fence_proxy_async_smem();
+    nw_group_bar(g);                             // every row of x' is in the slot / has been read from it
 
-    // ---- tail ----
-    mbar_wait_sleep(&gr->acc2_ready, par);
-    tc_fence_after_sync();
-    if (p.tail == SGNN_TAIL_PX) {
+    if (px) {
+      if (wq == 0) {
+        if (elect_one()) {
+          tma_store_2d(pq_map, W, tile * kTileRows, x_slot);
+          tma_store_2d(pq_map, W + kKBlock, tile * kTileRows, x_slot + kNwKbBytes);
+          tma_store_commit();
+        }
+        __syncwarp();
+      }
+      mbar_wait_sleep(&gr->acc2_ready, par);
+      tc_fence_after_sync();
       float o[W];
       tmem_ld64(t1, o);
       tc_fence_before_sync();
       mbar_arrive(&gr->region_free);
-      if (valid) {
-        const float4* pb = reinterpret_cast<const float4*>(blob_f + p.pq_bias_off);
-        float4* dst = reinterpret_cast<float4*>(p.pq_out + r * 2 * W);
+      if (wq == 0) {
+        if (elect_one()) tma_store_wait_read();  // the copy engine has read x' out of the slot
+        __syncwarp();
+      }
+      nw_group_bar(g);
+      const float4* pb = reinterpret_cast<const float4*>(vec + p.pq_bias_off);
 #pragma unroll
-        for (int j = 0; j < W / 4; ++j) {
-          const float4 b = pb[j];
-          dst[j] = make_float4(o[4 * j] + b.x, o[4 * j + 1] + b.y, o[4 * j + 2] + b.z, o[4 * j + 3] + b.w);
+      for (int c = 0; c < W / 4; ++c) {
+        const float4 b = pb[c];
+        *reinterpret_cast<float4*>(x_slot + sw128_chunk_offset(wt, c, kTileRows)) =
+            make_float4(o[4 * c] + b.x, o[4 * c + 1] + b.y, o[4 * c + 2] + b.z, o[4 * c + 3] + b.w);
+      }
+      fence_proxy_async_smem();
+      nw_group_bar(g);
+      if (wq == 0) {
+        if (elect_one()) {
+          tma_store_2d(pq_map, 0, tile * kTileRows, x_slot);
+          tma_store_2d(pq_map, kKBlock, tile * kTileRows, x_slot + kNwKbBytes);
+          tma_store_commit();
+          tma_store_wait_read();
+          mbar_arrive(&gr->slot_free);
         }
+        __syncwarp();
       }
     } else {      // SGNN_TAIL_DECODE with one hidden layer: relu(acc2 + d1) -> Linear(64 -> out <= 8) in FFMA -> integrator
+      if (wq == 0) {
+        if (elect_one()) mbar_arrive(&gr->slot_free);
+        __syncwarp();
+      }
+      mbar_wait_sleep(&gr->acc2_ready, par);
+      tc_fence_after_sync();
       float o[8];
       const int nout = p.dec.out;
-      const float* bl = blob_f + p.dec.b_off[1];
-      const float* wl = blob_f + p.dec_wlast_off;
-      const float* bh = blob_f + p.dec.b_off[0];
+      const float* bl = p.blob + p.dec.b_off[1];        // decoder vectors: read-only, L1-resident
+      const float* wl = p.blob + p.dec_wlast_off;
+      const float4* bh = reinterpret_cast<const float4*>(p.blob + p.dec.b_off[0]);
 #pragma unroll
       for (int k = 0; k < 8; ++k) o[k] = 0.f;
 #pragma unroll
@@ -288,49 +340,69 @@ __device__ __forceinline__ void nw_epilogue(const SgnnNodeParams& p, const float
         float h[32];
         tmem_ld32(t1 + c, h);
 #pragma unroll
-        for (int j = 0; j < 32; ++j) h[j] = fmaxf(h[j] + bh[c + j], 0.f);
-        for (int k = 0; k < nout; ++k) {
-          float acc = o[k];
+        for (int j = 0; j < 32; j += 4) {
+          const float4 b = __ldg(bh + ((c + j) >> 2));
+          h[j] = fmaxf(h[j] + b.x, 0.f); h[j + 1] = fmaxf(h[j + 1] + b.y, 0.f);
+          h[j + 2] = fmaxf(h[j + 2] + b.z, 0.f); h[j + 3] = fmaxf(h[j + 3] + b.w, 0.f);
+        }
 #pragma unroll
-          for (int j = 0; j < 32; ++j) acc = fmaf(h[j], wl[k * W + c + j], acc);
-          o[k] = acc;
+        for (int k = 0; k < 8; ++k) {
+          if (k < nout) {
+            const float4* w4 = reinterpret_cast<const float4*>(wl + k * W + c);
+            float acc = o[k];
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              const float4 w = __ldg(w4 + (j >> 2));
+              acc = fmaf(h[j], w.x, acc); acc = fmaf(h[j + 1], w.y, acc);
+              acc = fmaf(h[j + 2], w.z, acc); acc = fmaf(h[j + 3], w.w, acc);
+            }
+            o[k] = acc;
+          }
         }
       }
       tc_fence_before_sync();
       mbar_arrive(&gr->region_free);
       if (valid) {
-        for (int k = 0; k < nout; ++k) o[k] += bl[k];
-        if (p.dec_out)
-          for (int k = 0; k < nout; ++k) p.dec_out[r * nout + k] = o[k];
-        if (p.strain_out) p.strain_out[r] = o[nout - 1];
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          if (k < nout) {
+            o[k] += __ldg(bl + k);
+            if (p.dec_out) p.dec_out[r * nout + k] = o[k];
+            if (p.strain_out && k == nout - 1) p.strain_out[r] = o[k];
+          }
         if (p.next_pos) {
           const float* ps = p.pos_seq + r * p.pos_seq_stride;
-          for (int d = 0; d < p.dim; ++d) {
-            const float a = __fadd_rn(__fmul_rn(o[d], p.acc_std[d]), p.acc_mean[d]);
-            const float last = ps[(p.seq_len - 1) * p.dim + d];
-            const float vel = __fsub_rn(last, ps[(p.seq_len - 2) * p.dim + d]);
-            p.next_pos[r * p.next_pos_stride + d] = __fadd_rn(last, __fadd_rn(vel, a));
-          }
+#pragma unroll
+          for (int d = 0; d < 3; ++d)
+            if (d < p.dim) {
+              const float a = __fadd_rn(__fmul_rn(o[d], p.acc_std[d]), p.acc_mean[d]);
+              const float last = ps[(p.seq_len - 1) * p.dim + d];
+              const float vel = __fsub_rn(last, ps[(p.seq_len - 2) * p.dim + d]);
+              p.next_pos[r * p.next_pos_stride + d] = __fadd_rn(last, __fadd_rn(vel, a));
+            }
         }
       }
     }
+  }
+  if (px && wq == 0) {
+    if (elect_one()) tma_store_wait_all();
+    __syncwarp();
   }
 }
 
 // ---------------------------------------------------------------------------------- kernel
 __global__ void __launch_bounds__(kNwThreads, 1)
 node_ws_kernel(const SgnnNodeParams p, const __grid_constant__ CUtensorMap agg_map,
-               const __grid_constant__ CUtensorMap x_map) {
+               const __grid_constant__ CUtensorMap x_map, const __grid_constant__ CUtensorMap pq_map) {
   constexpr int TMEM_COLS = 512;
   char* smem = smem_base_1024();
-  const NwSmem L = node_ws_smem(p.blob_bytes);
-  NwMisc* misc = reinterpret_cast<NwMisc*>(smem + L.misc);
+  NwMisc* misc = reinterpret_cast<NwMisc*>(smem + kNwMiscOff);
   const int tid = threadIdx.x, warp = tid >> 5;
 
   pdl_launch_dependents();
   if (tid == 0) {
     mbar_init(&misc->bar_w, 1);
-    for (int s = 0; s < kNwStages; ++s) mbar_init(&misc->empty[s], 1);
+    for (int s = 0; s < kNwAggSlots; ++s) mbar_init(&misc->agg_empty[s], 1);
     for (int g = 0; g < kNwGroups; ++g) {
       mbar_init(&misc->g[g].full, 1);
       mbar_init(&misc->g[g].patched, kThreads);
@@ -340,11 +412,18 @@ node_ws_kernel(const SgnnNodeParams p, const __grid_constant__ CUtensorMap agg_m
       mbar_init(&misc->g[g].xo_ready, kThreads);
       mbar_init(&misc->g[g].acc2_ready, 1);
       mbar_init(&misc->g[g].region_free, kThreads);
+      mbar_init(&misc->g[g].slot_free, 1);
     }
     mbar_fence_init();
-    tma_load_span(smem, reinterpret_cast<const char*>(p.blob), p.blob_bytes, &misc->bar_w);
+    // resident weights: the head of the vector region and the three GEMM images that follow it
+    const char* blob = reinterpret_cast<const char*>(p.blob);
+    mbar_arrive_expect_tx(&misc->bar_w, kNwVecBytes + kNwImgBytes);
+    tma_bulk_g2s(smem, blob, kNwVecBytes, &misc->bar_w);
+    tma_bulk_g2s(smem + kNwImgOff, blob + SGNN_VEC_REGION_BYTES, 32768, &misc->bar_w);
+    tma_bulk_g2s(smem + kNwImgOff + 32768, blob + SGNN_VEC_REGION_BYTES + 32768, 32768, &misc->bar_w);
     tensormap_prefetch(&agg_map);
     tensormap_prefetch(&x_map);
+    tensormap_prefetch(&pq_map);
   }
   if (tid < 32) tmem_alloc(&misc->tmem_slot, TMEM_COLS);
   tc_fence_before_sync();
@@ -354,21 +433,23 @@ node_ws_kernel(const SgnnNodeParams p, const __grid_constant__ CUtensorMap agg_m
   const int n_tiles = (p.n_rows + kTileRows - 1) / kTileRows;
   const int n_my = (int)blockIdx.x < n_tiles ? (n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
   const uint32_t tmem = misc->tmem_slot;
-  const uint32_t sW = smem_u32(smem);
+  const uint32_t sU = smem_u32(smem);
+  const uint32_t img = sU + kNwImgOff - SGNN_VEC_REGION_BYTES;      // image at blob byte offset `o` lives at img + o
 
-  if (warp < 16) {
+  if (warp < 4 * kNwGroups) {
     asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kNwEpiRegs));
     mbar_wait(&misc->bar_w, 0);
-    nw_epilogue(p, reinterpret_cast<const float*>(smem), smem + L.ring, misc, warp >> 2, tid & 127, n_my, tmem);
+    nw_epilogue(p, &pq_map, smem, misc, warp >> 2, tid & 127, n_my, tmem);
   } else {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kNwAuxRegs));
-    if (warp == 16) {
-      nw_producer(&agg_map, &x_map, smem + L.ring, misc, n_my);
+    const int role = warp - 4 * kNwGroups;
+    if (role == 0) {
+      nw_producer(&agg_map, &x_map, smem, misc, n_my);
     } else {
       mbar_wait(&misc->bar_w, 0);
-      if (warp == 17) nw_mma0(smem_u32(smem + L.ring), sW + p.mlp.w_off[0], misc, n_my, tmem);
-      else if (warp == 18) nw_mma_ts(sW + p.mlp.w_off[1], misc, n_my, tmem, 0);
-      else nw_mma_ts(sW + (p.tail == SGNN_TAIL_PX ? p.wp_off : p.dec.w_off[0]), misc, n_my, tmem, 1);
+      if (role == 1) nw_mma0(sU, img + p.mlp.w_off[0], misc, n_my, tmem);
+      else if (role == 2) nw_mma_ts(img + p.mlp.w_off[1], misc, n_my, tmem, 0);
+      else nw_mma_ts(img + (p.tail == SGNN_TAIL_PX ? p.wp_off : p.dec.w_off[0]), misc, n_my, tmem, 1);
     }
   }
   tc_fence_before_sync();
@@ -380,25 +461,45 @@ node_ws_kernel(const SgnnNodeParams p, const __grid_constant__ CUtensorMap agg_m
 
 using namespace sgnn;
 
+static bool nw_vec_resident(int off_floats, int n) { return off_floats >= 0 && (off_floats + n) * 4 <= kNwVecBytes; }
+static bool nw_img_resident(int off_bytes, int bytes) {
+  return off_bytes >= SGNN_VEC_REGION_BYTES && off_bytes % 1024 == 0 &&
+         off_bytes + bytes <= SGNN_VEC_REGION_BYTES + kNwImgBytes;
+}
+
 // 1 = launched, 0 = shape / mode not covered (caller falls back to node_fast_kernel), < 0 = error
 int sgnn_node_ws_try(const SgnnNodeParams* p, void* stream) {
   if (getenv("SGNN_NODE_FAST")) return 0;                       // A/B switch: keep the 4-worker kernel
   if (p->prologue != SGNN_PRO_AGG_X || !p->xr_in || !p->has_mlp || !p->residual || !p->mlp.has_ln) return 0;
   if (p->agg_w != kNwW || p->x_w != kNwW || p->mlp.hidden != kNwW || p->mlp.out != kNwW || p->mlp.n_hidden != 1) return 0;
+  const int wb = kNwW * kNwW * 4;
+  if (!nw_vec_resident(p->mlp.b_off[0], kNwW) || !nw_vec_resident(p->mlp.b_off[1], kNwW) ||
+      !nw_vec_resident(p->mlp.gamma_off, kNwW) || !nw_vec_resident(p->mlp.beta_off, kNwW))
+    return 0;
+  if (!nw_img_resident(p->mlp.w_off[0], 2 * wb) || !nw_img_resident(p->mlp.w_off[1], wb)) return 0;
+  if (p->blob_bytes < SGNN_VEC_REGION_BYTES + kNwImgBytes) return 0;
   if (p->tail == SGNN_TAIL_PX) {
-    if (p->pq_hidden != kNwW) return 0;
+    if (p->pq_hidden != kNwW || !p->pq_out || !nw_vec_resident(p->pq_bias_off, kNwW) || !nw_img_resident(p->wp_off, wb))
+      return 0;
+    // x' replaces x in place: the rounded input must BE the Q half of the output rows
+    if (p->xr_in != p->pq_out + kNwW || p->xr_ld != 2 * kNwW) return 0;
   } else if (p->tail == SGNN_TAIL_DECODE) {
-    if (p->dec.hidden != kNwW || p->dec.n_hidden != 1 || p->dec.out > 8) return 0;
+    if (p->dec.hidden != kNwW || p->dec.n_hidden != 1 || p->dec.out > 8 || p->dim > 3 || !nw_img_resident(p->dec.w_off[0], wb))
+      return 0;
   } else {
     return 0;
   }
-  const NwSmem s = node_ws_smem(p->blob_bytes);
-  if (s.total > 227 * 1024 || tensormap_encoder() == nullptr) return 0;
-  CUtensorMap agg_map, x_map;
+  if (tensormap_encoder() == nullptr) return 0;
+  CUtensorMap agg_map, x_map, pq_map;
   int rc = make_row_tile_map(&agg_map, p->agg, p->n_rows, kNwW, kNwW * 4, kTileRows);
   if (rc != SGNN_OK) return rc;
   rc = make_row_tile_map(&x_map, p->xr_in, p->n_rows, kNwW, p->xr_ld * 4, kTileRows);
   if (rc != SGNN_OK) return rc;
+  pq_map = x_map;
+  if (p->tail == SGNN_TAIL_PX) {
+    rc = make_row_tile_map(&pq_map, p->pq_out, p->n_rows, 2 * kNwW, 2 * kNwW * 4, kTileRows);
+    if (rc != SGNN_OK) return rc;
+  }
   static int sms = 0;
   if (sms == 0) {
     int dev = 0;
@@ -408,7 +509,8 @@ int sgnn_node_ws_try(const SgnnNodeParams* p, void* stream) {
   const int n_tiles = sgnn_ceil_div(p->n_rows, kTileRows);
   int grid = n_tiles < sms ? n_tiles : sms;
   if (grid < 1) grid = 1;
-  SGNN_ENSURE_SMEM(node_ws_kernel, s.total);
-  SGNN_CUDA(sgnn_launch(node_ws_kernel, dim3(grid), dim3(kNwThreads), s.total, (cudaStream_t)stream, *p, agg_map, x_map));
+  SGNN_ENSURE_SMEM(node_ws_kernel, kNwSmemBytes);
+  SGNN_CUDA(sgnn_launch(node_ws_kernel, dim3(grid), dim3(kNwThreads), kNwSmemBytes, (cudaStream_t)stream, *p, agg_map,
+                        x_map, pq_map));
   return 1;
 }

@@ -302,19 +302,23 @@ class EpdEngine:
             enc.launch(csr, self.e_tiles[k], pos=last_pos_ptr, pos_stride=pos_seq_stride, dim=dim,
                        radius=radii[k],
                        feat_out=None if edge_feat_out is None else edge_feat_out[k])
+        # Gather mode: the latents travel between layers only as the rounded copy in the Q half of pq
+        # (node_ws.cu); the fp32 buffers x[0], x[1] are written on request (tests, A/B runs) only.
+        keep_x = (not self.gather) or bool(os.environ.get("SGNN_KEEP_X") or os.environ.get("SGNN_NODE_FAST")
+                                           or os.environ.get("SGNN_NODE_GENERIC"))
         x_cur = 0
         self.node_enc.launch(
             n, pos_seq=pos_seq, pos_seq_stride=pos_seq_stride, seq_len=seq_len, dim=dim,
             vel_mean=vel_mean, vel_std=vel_std, wall_offset=2.0, wall_max=wall_max, wall_div=wall_div,
             types=types if emb is not None else None, emb=emb,
             emb_dim=0 if emb is None else emb.shape[1], feat_out=feat_out,
-            x_out=self.x[x_cur], pq_out=self.pq)
+            x_out=self.x[x_cur] if keep_x else None, pq_out=self.pq)
         for bi, (ep, npn, es) in enumerate(self.blocks):
             csr = csrs[es]
             ep.launch(csr, self.e_tiles[es], self.pq, self.agg, self.head)
             last = bi == len(self.blocks) - 1
             kw = dict(agg=self.agg, head=self.head, rowptr=csr.rowptr, agg_w=ep.out,
-                      x_in=self.x[x_cur], x_w=self.latent, x_out=self.x[1 - x_cur])
+                      x_in=self.x[x_cur], x_w=self.latent, x_out=self.x[1 - x_cur] if keep_x else None)
             if self.gather:     # Q half of pq = this layer's input latents rounded to TF32 (node tail PX)
                 kw.update(xr_in=self.pq.data_ptr() + 4 * self.latent, xr_ld=2 * self.latent)
             if not last:
@@ -325,5 +329,5 @@ class EpdEngine:
                           next_pos=next_pos, next_pos_stride=next_pos_stride, strain_out=strain_out)
             npn.launch(n, **kw)
             x_cur = 1 - x_cur
-        self.x_final = self.x[x_cur]
+        self.x_final = self.x[x_cur] if keep_x else None
         return self.dec_out

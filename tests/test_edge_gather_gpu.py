@@ -37,10 +37,12 @@ def test_gather_mode_matches_pq_mode(monkeypatch, nx, ny, regime):
     types = traj["particle_types"].cuda()
     n = pos.shape[0]
     sim_g = _sim(stats, radius)
+    monkeypatch.setenv("SGNN_KEEP_X", "1")       # gather mode keeps fp32 latents on request only
     nxt_g, strain_g = sim_g.predict_positions(pos, [torch.tensor(n)], types)
     eng, _ = sim_g._engine(n, pos.device)
     assert eng.gather, "gather mode was expected for the 64-wide single-scale network"
     x_g = eng.x_final.clone()
+    monkeypatch.delenv("SGNN_KEEP_X")
     monkeypatch.setenv("SGNN_EDGE_PQ", "1")
     sim_p = _sim(stats, radius, sim_g.state_dict())
     nxt_p, strain_p = sim_p.predict_positions(pos, [torch.tensor(n)], types)

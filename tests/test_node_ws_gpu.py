@@ -33,7 +33,8 @@ def _run(sim, pos, types):
     nxt, strain = sim.predict_positions(pos, [torch.tensor(n)], types)
     eng, _ = sim._engine(n, pos.device)
     torch.cuda.synchronize()
-    return nxt.clone(), strain.clone(), eng.x_final.clone(), eng.pq.clone(), eng
+    x = eng.x_final.clone() if eng.x_final is not None else None
+    return nxt.clone(), strain.clone(), x, eng.pq.clone(), eng
 
 
 @pytest.mark.parametrize("nx,ny,regime", [(24, 12, "A"), (60, 40, "B"), (200, 160, "A"), (400, 300, "B")])
@@ -42,8 +43,14 @@ def test_node_ws_is_bit_identical_to_node_fast(monkeypatch, nx, ny, regime):
     pos = traj["positions"][:, :S].cuda()
     types = traj["particle_types"].cuda()
     sim = _sim(stats, radius)
-    nxt_w, strain_w, x_w, pq_w, eng = _run(sim, pos, types)
+    # product configuration: the latents travel only as the rounded copy in pq, no fp32 x buffers
+    nxt_0, strain_0, x_0, pq_0, eng = _run(sim, pos, types)
     assert eng.gather, "gather mode (and with it node_ws_kernel) was expected for the 64-wide network"
+    assert x_0 is None
+    monkeypatch.setenv("SGNN_KEEP_X", "1")       # also write the fp32 latents, to compare them
+    nxt_w, strain_w, x_w, pq_w, _ = _run(sim, pos, types)
+    assert torch.equal(nxt_0, nxt_w) and torch.equal(strain_0, strain_w) and torch.equal(pq_0, pq_w)
+    monkeypatch.delenv("SGNN_KEEP_X")
     monkeypatch.setenv("SGNN_NODE_FAST", "1")
     nxt_f, strain_f, x_f, pq_f, _ = _run(sim, pos, types)
     assert torch.equal(x_w, x_f)
@@ -64,8 +71,10 @@ def test_node_ws_isolated_particles(monkeypatch):
     pos[::7] = lattice[:, None, :] + (pos[::7] - pos[::7, -1:])    # keep each window's velocities
     pos, types = pos.cuda(), traj["particle_types"].cuda()
     sim = _sim(stats, radius)
+    monkeypatch.setenv("SGNN_KEEP_X", "1")
     nxt_w, strain_w, x_w, _, eng = _run(sim, pos, types)
     assert eng.gather
+    monkeypatch.delenv("SGNN_KEEP_X")
     monkeypatch.setenv("SGNN_NODE_FAST", "1")
     nxt_f, strain_f, x_f, _, _ = _run(sim, pos, types)
     assert torch.equal(x_w, x_f) and torch.equal(nxt_w, nxt_f) and torch.equal(strain_w, strain_f)
