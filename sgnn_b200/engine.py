@@ -70,6 +70,8 @@ class RadiusGraph:
     def build(self, pos: torch.Tensor, pos_stride: int, dim: int, example_ptr: torch.Tensor,
               radius: float):
         """pos: tensor whose data_ptr is particle 0's most recent position."""
+        if "radius_graph" in SKIP:
+            return self.csr
         with _timed("radius_graph"):
           L.check(L.lib().sgnn_radius_graph_csr(
             C.c_void_p(pos.data_ptr()), C.c_long(pos_stride), self.n, dim, L.ptr(example_ptr),
@@ -80,6 +82,7 @@ class RadiusGraph:
 
 
 PROFILE = None      # set to a dict to collect (start, end) CUDA events per kernel family
+SKIP = set()        # kernel families NOT launched (profiles/chain_breakdown.py only; results are then meaningless)
 
 
 class _timed:
@@ -126,6 +129,8 @@ class EdgeEncoderPlan:
     def launch(self, csr: Csr, e_tiles, pos=None, pos_stride=0, dim=0, radius=1.0, feat=None,
                feat_out=None, n_edges: Optional[int] = None):
         p = self.p
+        if "edge_encoder" in SKIP:
+            return
         if isinstance(pos, torch.Tensor):
             pos = pos.data_ptr()
         p.pos, p.pos_stride, p.dim = pos, pos_stride, dim
@@ -165,6 +170,8 @@ class EdgeLayerPlan:
 
     def launch(self, csr: Csr, e_tiles, pq, agg, head):
         p = self.p
+        if "edge_layer" in SKIP:
+            return
         p.e_tiles, p.pq = e_tiles.data_ptr(), pq.data_ptr()
         p.src, p.tgt, p.rowptr, p.n_nodes = csr.src.data_ptr(), csr.tgt.data_ptr(), csr.rowptr.data_ptr(), csr.n_nodes
         p.agg, p.head, p.max_tiles = agg.data_ptr(), head.data_ptr(), csr.max_tiles
@@ -224,6 +231,8 @@ class NodePlan:
                 v = v.data_ptr()
             setattr(p, k, v)
         n_tiles = (n_rows + TILE - 1) // TILE
+        if "node_" + ("encoder", "layer", "rows")[p.prologue] in SKIP:
+            return
         with _timed("node_" + ("encoder", "layer", "rows")[p.prologue]):
           L.check(L.lib().sgnn_node_fwd(C.byref(p), int(self.tc), _grid(self.smem, n_tiles), L.stream_ptr()))
 
