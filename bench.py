@@ -245,7 +245,17 @@ def make_train_batch(dev, samples, seed0=100):
 
 
 def train_config(dev, rank, world, steps=10, warmup=3, samples=8):
-    """BASELINE configs[2]: single-scale training, 8 samples per GPU, flat-gradient allreduce."""
+    """BASELINE configs[2]: single-scale training, 8 samples per GPU, flat-gradient allreduce.
+    Primary numbers: fp32 GEMMs (what the reference runs, what the gradient parity tests pin);
+    `tf32` repeats the measurement with cuBLAS on the tensor cores (training.matmul_precision)."""
+    out = _train_config(dev, rank, world, steps, warmup, samples, "fp32")
+    t = _train_config(dev, rank, world, steps, warmup, samples, "tf32")
+    out["tf32"] = {k: t[k] for k in ("train_steps_per_s", "ms_per_train_step", "samples_per_s", "loss_first",
+                                     "loss_last", "gemm")}
+    return out
+
+
+def _train_config(dev, rank, world, steps, warmup, samples, matmul):
     import torch.distributed as dist
     from sgnn_b200 import training
     batch, stats, radius = make_train_batch(dev, samples, seed0=100 + 1000 * rank)
@@ -256,7 +266,8 @@ def train_config(dev, rank, world, steps=10, warmup=3, samples=8):
     gen = torch.Generator(device=dev).manual_seed(2 + rank)
     losses = []
     for _ in range(warmup):
-        training.train_step(sim, opt, batch, 0.02 * 25.0, reducer=reducer, n_global=n_glob, generator=gen)
+        training.train_step(sim, opt, batch, 0.02 * 25.0, reducer=reducer, n_global=n_glob, generator=gen,
+                            matmul=matmul)
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
@@ -264,7 +275,7 @@ def train_config(dev, rank, world, steps=10, warmup=3, samples=8):
     a.record()
     for _ in range(steps):
         losses.append(training.train_step(sim, opt, batch, 0.02 * 25.0, reducer=reducer, n_global=n_glob,
-                                          generator=gen))
+                                          generator=gen, matmul=matmul))
     b.record()
     torch.cuda.synchronize()
     ms = torch.tensor([a.elapsed_time(b)], device=dev, dtype=torch.float64)
@@ -275,7 +286,7 @@ def train_config(dev, rank, world, steps=10, warmup=3, samples=8):
             "particles_per_step_global": n_glob, "samples_per_s": samples * world * 1e3 / ms,
             "loss_first": losses[0].item() * world, "loss_last": losses[-1].item() * world,
             "collective": "one flat fp32 gradient allreduce (NCCL)" if world > 1 else "none (1 GPU)",
-            "gemm": "cuBLAS fp32", "graph_ops": "sgnn_b200 CUDA (deterministic)"}
+            "gemm": "cuBLAS " + matmul, "graph_ops": "sgnn_b200 CUDA (deterministic gather / segment-sum / LayerNorm)"}
 
 
 def multiscale_config(dev, rank, steps=5):

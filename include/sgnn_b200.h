@@ -81,6 +81,17 @@ int sgnn_segment_sum_rows(const float* m, const int* rowptr, const int* perm, in
                           float* out, void* stream);
 int sgnn_gather_rows(const float* rows, long ld, const int* idx, int n_out, int width, float* out,
                      void* stream);
+
+/* nn.LayerNorm over rows of 32 / 64 / 128 floats with autograd support (the LayerNorm closing every
+ * encoder / edge / node MLP, graph_network.py:86-96,139-147): forward keeps mean and rstd per row,
+ * backward returns dx and the deterministic column sums dgamma, dbeta.                            */
+int sgnn_layer_norm_supported(int width);
+size_t sgnn_layer_norm_bwd_workspace_bytes(int width);
+int sgnn_layer_norm_fwd(const float* x, long n_rows, int width, const float* gamma, const float* beta,
+                        float eps, float* y, float* mean, float* rstd, void* stream);
+int sgnn_layer_norm_bwd(const float* dy, const float* x, const float* mean, const float* rstd,
+                        const float* gamma, long n_rows, int width, float* dx, float* dgamma, float* dbeta,
+                        void* workspace, size_t workspace_bytes, void* stream);
 int sgnn_node_features(const float* pos_seq, long stride, int n, int seq_len, int dim,
                        const float* vel_mean, const float* vel_std, float wall_offset, float wall_max,
                        float wall_div, float* out, long ld_out, void* stream);

@@ -112,6 +112,51 @@ class _SegmentSum(torch.autograd.Function):
         return gather_rows(dagg, ctx.graph.tgt), None
 
 
+class _LayerNorm(torch.autograd.Function):
+    """nn.LayerNorm over rows of 32 / 64 / 128 floats on csrc/train_norm.cu (forward keeps mean / rstd,
+    backward is one streaming pass + a fixed-order column reduction: deterministic dgamma / dbeta)."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, eps: float):
+        x, gamma, beta = _f32(x), _f32(gamma), _f32(beta)
+        n, w = x.shape
+        y = torch.empty_like(x)
+        mean = torch.empty(n, dtype=torch.float32, device=x.device)
+        rstd = torch.empty(n, dtype=torch.float32, device=x.device)
+        L.check(L.lib().sgnn_layer_norm_fwd(L.ptr(x), C.c_long(n), w, L.ptr(gamma), L.ptr(beta), C.c_float(eps),
+                                            L.ptr(y), L.ptr(mean), L.ptr(rstd), L.stream_ptr()))
+        ctx.save_for_backward(x, gamma, mean, rstd)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, gamma, mean, rstd = ctx.saved_tensors
+        dy = _f32(dy)
+        n, w = x.shape
+        dx = torch.empty_like(x)
+        dgamma, dbeta = torch.empty_like(gamma), torch.empty_like(gamma)
+        nbytes = L.lib().sgnn_layer_norm_bwd_workspace_bytes(w)
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
+        L.check(L.lib().sgnn_layer_norm_bwd(L.ptr(dy), L.ptr(x), L.ptr(mean), L.ptr(rstd), L.ptr(gamma), C.c_long(n),
+                                            w, L.ptr(dx), L.ptr(dgamma), L.ptr(dbeta), L.ptr(ws),
+                                            C.c_size_t(nbytes), L.stream_ptr()), launches=2)
+        return dx, dgamma, dbeta, None
+
+
+def layer_norm(ln: torch.nn.LayerNorm, h: torch.Tensor) -> torch.Tensor:
+    """ln(h) for a reference nn.LayerNorm module on [rows, width] activations."""
+    w = h.shape[-1]
+    if h.dim() != 2 or not ln.elementwise_affine or ln.bias is None or tuple(ln.normalized_shape) != (w,) \
+            or not L.lib().sgnn_layer_norm_supported(w):
+        return ln(h)            # widths outside {32, 64, 128}: ATen (still CUDA; training glue only)
+    return _LayerNorm.apply(h, ln.weight, ln.bias, float(ln.eps))
+
+
+def mlp_ln(seq: torch.nn.Sequential, h: torch.Tensor) -> torch.Tensor:
+    """Sequential(build_mlp, LayerNorm) as the encoders use it."""
+    return layer_norm(seq[1], seq[0](h))
+
+
 def gather_add(p, q, graph):
     return _GatherAdd.apply(p, q, graph)
 
@@ -164,20 +209,20 @@ def interaction_block(edge_fn, node_fn, x, e, graph: TrainGraph):
     p = F.linear(x, w1.weight[:, :nn_in], w1.bias)                # x_target block (+ bias)
     q = F.linear(x, w1.weight[:, nn_in:2 * nn_in])                # x_source block
     pre = F.linear(e, w1.weight[:, 2 * nn_in:]) + gather_add(p, q, graph)
-    msg = edge_fn[1](_rest_of_mlp(edge_fn[0], pre))               # ... -> LayerNorm
+    msg = layer_norm(edge_fn[1], _rest_of_mlp(edge_fn[0], pre))   # ... -> LayerNorm
     agg = segment_sum(msg, graph)
     v1 = linears_of(node_fn[0])[0]
     na = agg.shape[1]
     pre_n = F.linear(agg, v1.weight[:, :na]) + F.linear(x, v1.weight[:, na:], v1.bias)
-    upd = node_fn[1](_rest_of_mlp(node_fn[0], pre_n))
+    upd = layer_norm(node_fn[1], _rest_of_mlp(node_fn[0], pre_n))
     return x + upd, e + e
 
 
 def epd_forward(node_encoder, edge_encoders: List, blocks: List, decoder, nf, efs: List,
                 graphs: List[TrainGraph]):
     """blocks: list of (edge_fn, node_fn, edge_set_index).  Returns the decoder output [N, dim+1]."""
-    x = node_encoder(nf)
-    es = [enc(ef) for enc, ef in zip(edge_encoders, efs)]
+    x = mlp_ln(node_encoder, nf)
+    es = [mlp_ln(enc, ef) for enc, ef in zip(edge_encoders, efs)]
     for edge_fn, node_fn, k in blocks:
         x, es[k] = interaction_block(edge_fn, node_fn, x, es[k], graphs[k])
     return decoder(x)

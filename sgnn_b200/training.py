@@ -69,10 +69,28 @@ def global_particle_count(n_local: int, device, group=None) -> int:
     return int(t.item())
 
 
+class matmul_precision:
+    """Scope for the dense GEMMs of the training path (cuBLAS through torch).  "fp32" (default) is what
+    the reference runs and what the gradient parity tests pin; "tf32" lets cuBLAS use the tensor cores
+    (TF32 operands, fp32 accumulate -- the precision the inference kernels use)."""
+
+    def __init__(self, mode: str):
+        if mode not in ("fp32", "tf32"):
+            raise ValueError("matmul precision must be 'fp32' or 'tf32'")
+        self.mode = mode
+
+    def __enter__(self):
+        self.saved = torch.backends.cuda.matmul.allow_tf32
+        torch.backends.cuda.matmul.allow_tf32 = self.mode == "tf32"
+
+    def __exit__(self, *a):
+        torch.backends.cuda.matmul.allow_tf32 = self.saved
+
+
 def train_step(simulator, optimizer, batch: Dict[str, torch.Tensor], noise_std: float,
                w_pos: float = 1.0, w_strain: float = 1.0, reducer: Optional[FlatGradAllReduce] = None,
                n_global: Optional[int] = None, noise: Optional[torch.Tensor] = None,
-               generator: Optional[torch.Generator] = None) -> torch.Tensor:
+               generator: Optional[torch.Generator] = None, matmul: str = "fp32") -> torch.Tensor:
     """One optimisation step on this rank's shard.  batch: positions [N,S,dim], particle_type [N],
     n_particles_per_example [B], next_position [N,dim], next_strain [N] (the tensors the
     reference's collate_fn emits, taylor_impact_data_loader.py:243-284), already on the device.
@@ -81,13 +99,14 @@ def train_step(simulator, optimizer, batch: Dict[str, torch.Tensor], noise_std: 
     if noise is None:
         noise = noise_utils.get_random_walk_noise_for_position_sequence(pos, noise_std, generator)
     optimizer.zero_grad(set_to_none=True)
-    pred_acc, target_acc, pred_strain = simulator.predict_accelerations(
-        next_positions=batch["next_position"], position_sequence_noise=noise, position_sequence=pos,
-        nparticles_per_example=batch["n_particles_per_example"], particle_types=batch["particle_type"])
-    per_particle = loss_terms(pred_acc, target_acc, pred_strain, batch["next_strain"], w_pos, w_strain)
-    n_glob = pos.shape[0] if n_global is None else n_global
-    loss = per_particle.sum() / n_glob
-    loss.backward()
+    with matmul_precision(matmul):
+        pred_acc, target_acc, pred_strain = simulator.predict_accelerations(
+            next_positions=batch["next_position"], position_sequence_noise=noise, position_sequence=pos,
+            nparticles_per_example=batch["n_particles_per_example"], particle_types=batch["particle_type"])
+        per_particle = loss_terms(pred_acc, target_acc, pred_strain, batch["next_strain"], w_pos, w_strain)
+        n_glob = pos.shape[0] if n_global is None else n_global
+        loss = per_particle.sum() / n_glob
+        loss.backward()
     if reducer is not None:
         reducer()
     optimizer.step()

@@ -107,3 +107,53 @@ def test_train_step_api_decreases_loss_and_graph_ops_gradcheck():
     assert torch.allclose(out, ref, atol=1e-4, rtol=1e-5)
     assert torch.allclose(p.grad, p2.grad, atol=1e-3, rtol=1e-4)
     assert torch.allclose(q.grad, q2.grad, atol=1e-3, rtol=1e-4)
+
+
+@pytest.mark.parametrize("width", [32, 64, 128])
+@pytest.mark.parametrize("rows", [1, 77, 20011])
+def test_layer_norm_kernels_match_aten(width, rows):
+    """csrc/train_norm.cu forward / backward against F.layer_norm in fp64, plus bit-reproducibility."""
+    import torch.nn.functional as F
+    from sgnn_b200 import train_ops as T
+    g = torch.Generator().manual_seed(width + rows)
+    ln = torch.nn.LayerNorm(width).cuda()
+    with torch.no_grad():
+        ln.weight.copy_(torch.randn(width, generator=g))
+        ln.bias.copy_(torch.randn(width, generator=g))
+    x = (3.0 * torch.randn(rows, width, generator=g) + 1.5).cuda().requires_grad_()
+    up = torch.randn(rows, width, generator=g).cuda()
+    y = T.layer_norm(ln, x)
+    (y * up).sum().backward()
+    got = [y.detach(), x.grad.clone(), ln.weight.grad.clone(), ln.bias.grad.clone()]
+    x64 = x.detach().double().requires_grad_()
+    w64, b64 = ln.weight.detach().double().requires_grad_(), ln.bias.detach().double().requires_grad_()
+    y64 = F.layer_norm(x64, (width,), w64, b64, ln.eps)
+    (y64 * up.double()).sum().backward()
+    want = [y64.detach(), x64.grad, w64.grad, b64.grad]
+    for a, b, name in zip(got, want, ["y", "dx", "dgamma", "dbeta"]):
+        tol = 2e-5 * max(1.0, float(b.abs().max()))
+        assert (a.double() - b).abs().max().item() <= tol, name
+    ln.zero_grad()
+    x.grad = None
+    (T.layer_norm(ln, x) * up).sum().backward()
+    assert torch.equal(x.grad, got[1]) and torch.equal(ln.weight.grad, got[2]) and torch.equal(ln.bias.grad, got[3])
+
+
+def test_tf32_matmul_mode_of_train_step_stays_close():
+    """training.train_step(matmul="tf32"): same loss to 1e-3 relative, the global flag is restored."""
+    from sgnn_b200 import training
+    from tests.test_single_scale_gpu import make_sim
+    f = Fixture("single_h64")
+    batch = {"positions": f.t("train/positions").cuda(), "particle_type": f.t("train/particle_types").cuda(),
+             "n_particles_per_example": f.t("train/counts").cuda(),
+             "next_position": f.t("train/next_position").cuda(), "next_strain": f.t("train/next_strain").cuda()}
+    noise = f.t("train/noise").cuda()
+    losses = {}
+    for mode in ("fp32", "tf32"):
+        sim, _, _, _ = make_sim(f, "tf32")
+        sim.train()
+        opt = torch.optim.SGD(sim.parameters(), lr=0.0)
+        before = torch.backends.cuda.matmul.allow_tf32
+        losses[mode] = training.train_step(sim, opt, batch, 0.02, noise=noise, matmul=mode).item()
+        assert torch.backends.cuda.matmul.allow_tf32 == before
+    assert abs(losses["tf32"] - losses["fp32"]) <= 1e-3 * max(1.0, abs(losses["fp32"]))
