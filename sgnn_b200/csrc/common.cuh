@@ -184,6 +184,15 @@ __device__ __forceinline__ void mbar_wait_spin(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// Epilogue waits: suspend in the throughput regime (many tiles per CTA in flight, the suspended warps
+// leave the issue slots and the instruction fetch to the working ones), poll in the latency regime (a
+// CTA owns one or two tiles -- 4800-particle steps -- and its kernel is ONE serial chain of five such
+// waits: in-kernel stamps put ~0.4 us of wake-up latency on every suspended wait, r01n).
+__device__ __forceinline__ void mbar_wait_mode(uint64_t* bar, uint32_t parity, bool poll) {
+  if (poll) mbar_wait_spin(bar, parity);
+  else mbar_wait_sleep(bar, parity);
+}
+
 // ---- TMA bulk copy (global -> shared, completes on an mbarrier) ------------------------
 __device__ __forceinline__ void tma_bulk_g2s(void* smem_dst, const void* gmem_src, uint32_t bytes,
                                              uint64_t* bar) {

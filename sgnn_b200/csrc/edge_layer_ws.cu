@@ -117,9 +117,20 @@ __device__ __forceinline__ void ws_producer(const SgnnEdgeLayerParams& p, const 
   const uint32_t d_even = (uint32_t)(rg * 128 + ((ch ^ rg) << 4)), d_odd = (uint32_t)(rg * 128 + ((ch ^ (4 + rg)) << 4));
   int rows_nx[4];                                      // sender ids of rows lane, lane + 32, lane + 64, lane + 96,
   {                                                    // loaded one tile ahead (a cold read is ~1 us on this serial chain)
+    // the FIRST tile's ids are fetched before the edge count is looked at (the count is itself a load issued
+    // just before: one round trip instead of two at the head of the kernel's serial chain).  Slots past the
+    // end of the edge list hold ids of earlier steps or zeros -- valid rows either way -- and are masked
+    // once the count is known; the last tile of the capacity may be partial, so it is not read ahead.
     const long e0 = (long)blockIdx.x * kTileRows;
+    const bool ahead = (long)blockIdx.x + 1 < p.max_tiles;
 #pragma unroll
-    for (int c = 0; c < 4; ++c) rows_nx[c] = (n_my > 0 && e0 + c * 32 + lane < n_edges) ? __ldg(p.src + e0 + c * 32 + lane) : 0;
+    for (int c = 0; c < 4; ++c) rows_nx[c] = ahead ? __ldg(p.src + e0 + c * 32 + lane) : 0;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const bool in = n_my > 0 && e0 + c * 32 + lane < n_edges;
+      if (!ahead && in) rows_nx[c] = __ldg(p.src + e0 + c * 32 + lane);
+      if (!in) rows_nx[c] = 0;
+    }
   }
   for (int i = 0; i < n_my; ++i) {
     const long tile = blockIdx.x + (long)i * gridDim.x;
@@ -263,25 +274,31 @@ __device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const 
   const uint32_t lane_base = (uint32_t)(wq * 32) << 16;
   const uint32_t t0 = tmem + (uint32_t)(g * 2 * W) + lane_base, t1 = t0 + W;
   const int stride_tiles = gridDim.x * kWsGroups;
+  const bool poll = false;      // polling epilogue warps measured slower even with one tile per group (r01n)
   const float4* b4 = reinterpret_cast<const float4*>(blob_f + p.mlp.b_off[1]);
   // The LayerNorm affine is applied AFTER the sums: sum_e (z_e * gamma + beta) = gamma * sum_e z_e +
   // count * beta, per receiver (and per piece of a receiver, the pieces add up).  In the scan a lane
   // owns columns 2*lane, 2*lane + 1.
-  const float2 gam2 = reinterpret_cast<const float2*>(blob_f + p.mlp.gamma_off)[lane];
-  const float2 bet2 = reinterpret_cast<const float2*>(blob_f + p.mlp.beta_off)[lane];
-  float2* const piece_head = reinterpret_cast<float2*>(&wk->pieces[(2 * wq) * W]) + lane;
-  float2* const piece_tail = reinterpret_cast<float2*>(&wk->pieces[(2 * wq + 1) * W]) + lane;
-  float2* const agg2 = reinterpret_cast<float2*>(p.agg) + lane;
-  const int* tg = wk->tgt_s + wq * 32;
 
   // receiver of this thread's row, loaded one tile ahead (a cold read costs ~1 us on the group's serial chain)
   // (with the receivers of the rows before and after it: the segment structure then needs no load)
   int t_nx = -3, tb_nx = -2, ta_nx = -3;
-  if (g < n_my) {
-    const long e = (long)(blockIdx.x + g * gridDim.x) * kTileRows + wt;
-    if (e < n_edges) t_nx = __ldg(p.tgt + e);
-    if (e - 1 >= 0 && e - 1 < n_edges) tb_nx = __ldg(p.tgt + e - 1);
-    if (e + 1 < n_edges) ta_nx = __ldg(p.tgt + e + 1);
+  {
+    // as in the producers: the first tile's receiver ids are fetched before the edge count is looked at
+    const long tile0 = (long)blockIdx.x + (long)g * gridDim.x;
+    const long e = tile0 * kTileRows + wt;
+    const bool ahead = tile0 + 1 < p.max_tiles;
+    int a = 0, b = 0, c = 0;
+    if (ahead) {
+      a = __ldg(p.tgt + e);
+      b = e >= 1 ? __ldg(p.tgt + e - 1) : 0;
+      c = __ldg(p.tgt + e + 1);
+    }
+    if (g < n_my) {
+      if (e < n_edges) t_nx = ahead ? a : __ldg(p.tgt + e);
+      if (e - 1 >= 0 && e - 1 < n_edges) tb_nx = ahead ? b : __ldg(p.tgt + e - 1);
+      if (e + 1 < n_edges) ta_nx = ahead ? c : __ldg(p.tgt + e + 1);
+    }
   }
 
 #pragma unroll 1
@@ -323,7 +340,7 @@ __device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const 
     }
 
     // ---- hidden = relu(acc0 + P), rounded to TF32, back into the same TMEM columns ----
-    mbar_wait_sleep(&wk->acc0_ready, par);
+    mbar_wait_mode(&wk->acc0_ready, par, poll);
     tc_fence_after_sync();
     if (wt == 0) ws_stamp(i, 6);
 #pragma unroll
@@ -353,7 +370,8 @@ __device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const 
     }
 
     // ---- output Linear's accumulator -> registers; the TMEM region is free again at once ----
-    mbar_wait_sleep(&wk->acc1_ready, par);
+    mbar_wait_mode(&wk->acc1_ready, par, poll);
+    if (wt == 0) ws_stamp(i, 3);
     tc_fence_after_sync();
     float y[W];
     tmem_ld64(t1, y);
@@ -395,9 +413,14 @@ __device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const 
       }
     }
 
-    // ---- segmented sums over this warp's rows in four passes of 8 rows: the 8 rows go through a
-    //      padded scratch, then lane = column pair walks them in order.  Rolled loops keep the code
-    //      small; the rare "receiver complete" path applies the LayerNorm affine and stores.
+    if (wt == 0) ws_stamp(i, 4);
+    // ---- segmented sums over this warp's 32 rows, in place: thread = row keeps its 64 columns, a
+    //      Hillis-Steele scan over the lanes (shfl.up by 1, 2, 4, ... up to the longest receiver of the
+    //      warp) leaves every receiver's sum in its LAST row, whose thread applies the LayerNorm affine
+    //      and writes the receiver's 256-byte agg row (or the warp's head / tail piece).  64 independent
+    //      chains per level instead of one 32-step serial walk per column pair behind a shared-memory
+    //      transposition: in-kernel stamps put that walk at 2.8 us per tile, 40 % of the kernel at 4800
+    //      particles and the bound of the epilogue at 1M (r01n).  Deterministic (fixed tree order).
     //      (The shared piece slots and flags are written only here, after acc1_ready: warp 0 arrived
     //      on hid_ready after it finished stitching the previous tile, so nothing it reads is touched.)
     if (lane == 0) {
@@ -407,46 +430,40 @@ __device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const 
       wk->piece_flag[2 * wq + 1] = (cont_next && !one_piece) ? 1 : 0;
     }
     if (nrows > 0) {
-      wk->tgt_s[wt] = t;                           // read back by this row's own warp only
-      unsigned m = starts & ~1u;                   // a receiver starting at row 0 has nothing before it to flush
-      bool is_head = first_cont;
-      int off = t_first * (W / 2);                 // float2 offset of the receiver being summed
-      int r_start = 0;
-      float2 sum = f2(0.f, 0.f);
+      // first row of this lane's receiver within the warp (row 0 opens a segment for the scan in any case)
+      const unsigned below = (starts | 1u) & (FULL >> (31 - lane));
+      const int seg0 = 31 - __clz((int)below);
+      const bool in_rows = lane < nrows;
+      const bool is_end = in_rows && (lane == nrows - 1 || ((starts >> (lane + 1)) & 1u));
+      const int cnt_i = lane - seg0 + 1;
+      const int maxlen = __reduce_max_sync(FULL, is_end ? cnt_i : 0);
 #pragma unroll 1
-      for (int q = 0; q < 4; ++q) {
-        __syncwarp();
-        if ((lane >> 3) == q) {
-          float4* d4 = reinterpret_cast<float4*>(scr + (lane & 7) * kWsScrStride2);
+      for (int d = 1; d < maxlen; d <<= 1) {
+        const bool take = lane - d >= seg0;
 #pragma unroll
-          for (int j = 0; j < W / 4; ++j) d4[j] = make_float4(y[4 * j], y[4 * j + 1], y[4 * j + 2], y[4 * j + 3]);
-        }
-        __syncwarp();
-        const float2* col = reinterpret_cast<const float2*>(scr) + lane;
-        float2 v[8];
-#pragma unroll
-        for (int k = 0; k < 8; ++k) v[k] = col[k * (kWsScrStride2 / 2)];
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          if (m & 1u) {                            // warp-uniform: the receiver ending at the previous row is complete
-            const float cnt = (float)(q * 8 + k - r_start);
-            const float2 o = __ffma2_rn(sum, gam2, f2(cnt * bet2.x, cnt * bet2.y));
-            if (is_head) *piece_head = o; else agg2[off] = o;
-            is_head = false;
-            r_start = q * 8 + k;
-            off = tg[r_start] * (W / 2);
-            sum = f2(0.f, 0.f);
-          }
-          sum = __fadd2_rn(sum, v[k]);
-          m >>= 1;
+        for (int j = 0; j < W; ++j) {
+          const float up = __shfl_up_sync(FULL, y[j], d);
+          if (take) y[j] += up;
         }
       }
-      const float cnt = (float)(nrows - r_start);
-      const float2 o = __ffma2_rn(sum, gam2, f2(cnt * bet2.x, cnt * bet2.y));
-      if (cont_next && !one_piece) *piece_tail = o;
-      else if (is_head) *piece_head = o;
-      else agg2[off] = o;
+      if (is_end) {
+        const bool head_piece = first_cont && seg0 == 0;                        // continues the previous warp's receiver
+        const bool tail_piece = cont_next && !one_piece && lane == nrows - 1;   // continues in the next warp
+        float* dst = tail_piece ? &wk->pieces[(2 * wq + 1) * W]
+                                : (head_piece ? &wk->pieces[(2 * wq) * W] : p.agg + (long)t * W);
+        const float cnt = (float)cnt_i;
+        const float4* g4 = reinterpret_cast<const float4*>(blob_f + p.mlp.gamma_off);
+        const float4* be4 = reinterpret_cast<const float4*>(blob_f + p.mlp.beta_off);
+#pragma unroll
+        for (int j = 0; j < W / 4; ++j) {
+          const float4 ga = g4[j], be = be4[j];
+          reinterpret_cast<float4*>(dst)[j] =
+              make_float4(fmaf(y[4 * j], ga.x, cnt * be.x), fmaf(y[4 * j + 1], ga.y, cnt * be.y),
+                          fmaf(y[4 * j + 2], ga.z, cnt * be.z), fmaf(y[4 * j + 3], ga.w, cnt * be.w));
+        }
+      }
     }
+    if (wt == 0) ws_stamp(i, 11);
     ws_group_bar(g);
     if (wt == 0) ws_stamp(i, 7);
 
@@ -501,6 +518,7 @@ edge_layer_ws_kernel(const SgnnEdgeLayerParams p, const __grid_constant__ CUtens
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
   pdl_launch_dependents();
+  if (tid == 0) ws_stamp(255, 0);              // kernel-level stamps live in row 255
   if (tid == 0) {
     mbar_init(&misc->bar_w, 1);
     for (int s = 0; s < kWsStages; ++s) {
@@ -525,11 +543,14 @@ edge_layer_ws_kernel(const SgnnEdgeLayerParams p, const __grid_constant__ CUtens
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
+  if (tid == 0) ws_stamp(255, 1);
   pdl_wait();          // everything above touched only shared/tensor memory and the constant weights
+  if (tid == 0) ws_stamp(255, 2);
   const int n_edges = p.rowptr[p.n_nodes];
   const int n_tiles = (n_edges + kTileRows - 1) / kTileRows;
   const int n_my = (int)blockIdx.x < n_tiles ? (n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
   const uint32_t tmem = misc->tmem_slot;
+  if (tid == 0 && n_edges >= 0) ws_stamp(255, 3);
 
   if (warp < 16) {
     asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kWsEpiRegs));
@@ -552,6 +573,7 @@ edge_layer_ws_kernel(const SgnnEdgeLayerParams p, const __grid_constant__ CUtens
   }
   tc_fence_before_sync();
   __syncthreads();
+  if (tid == 0) ws_stamp(255, 4);
   if (tid < 32) tmem_dealloc(tmem, TMEM_COLS);
 }
 

@@ -179,8 +179,41 @@ __global__ void __launch_bounds__(kNodeFastThreads, 1) node_fast_kernel(const Sg
       float f[32];
 #pragma unroll
       for (int j = 0; j < 32; ++j) f[j] = 0.f;
-      if (valid) {
-        const float* ps = p.pos_seq + i * p.pos_seq_stride;
+      const float* ps = p.pos_seq + (valid ? i : 0) * p.pos_seq_stride;
+      // dim == 2, windows of up to 16 frames (the reference's S = 11): the whole window in one batch of
+      // independent 8-byte loads and static register indices.  The generic loop below walks the window
+      // with dependent scalar loads and a 32-way select per feature: 6 us of the encoder kernel's 11 us
+      // at 4800 particles (in-kernel stamps, r01n).  Same arithmetic, same order: bit-identical features.
+      const bool win2 = p.dim == 2 && p.seq_len >= 2 && p.seq_len <= 16 && p.emb == nullptr &&
+                        (reinterpret_cast<uintptr_t>(p.pos_seq) & 7) == 0 && (p.pos_seq_stride & 1) == 0;
+      if (valid && win2) {
+        const float2* ps2 = reinterpret_cast<const float2*>(ps);
+        float2 wv[16];
+#pragma unroll
+        for (int t = 0; t < 16; ++t) wv[t] = t < p.seq_len ? __ldg(ps2 + t) : make_float2(0.f, 0.f);
+        const float m0 = p.vel_mean[0], m1 = p.vel_mean[1], s0 = p.vel_std[0], s1 = p.vel_std[1];
+#pragma unroll
+        for (int t = 0; t < 15; ++t)
+          if (t + 1 < p.seq_len) {
+            f[2 * t] = __fdiv_rn(__fsub_rn(__fsub_rn(wv[t + 1].x, wv[t].x), m0), s0);
+            f[2 * t + 1] = __fdiv_rn(__fsub_rn(__fsub_rn(wv[t + 1].y, wv[t].y), m1), s1);
+          }
+        float last_x = 0.f;
+#pragma unroll
+        for (int t = 0; t < 16; ++t) if (t == p.seq_len - 1) last_x = wv[t].x;
+        float wd = __fadd_rn(last_x, p.wall_offset);
+        wd = __fdiv_rn(fminf(fmaxf(wd, 0.f), p.wall_max), p.wall_div);
+        const int k = 2 * (p.seq_len - 1);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) if (j == k) f[j] = wd;
+        if (p.feat_out)
+          for (int j = 0; j < p.k_in; ++j) {
+            float val = 0.f;
+#pragma unroll
+            for (int q = 0; q < 32; ++q) if (q == j) val = f[q];
+            p.feat_out[i * p.k_in + j] = val;
+          }
+      } else if (valid) {
         int k = 0;
         for (int t = 0; t + 1 < p.seq_len; ++t)
           for (int d = 0; d < p.dim; ++d) {

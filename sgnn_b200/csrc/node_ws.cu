@@ -31,6 +31,22 @@
 
 namespace sgnn {
 
+// optional in-kernel timeline (SGNN_TIMELINE builds; profiles/node_ws_timeline.py): CTA 0 / thread 0 stamps
+// %globaltimer into slots [0,16) and clock64 into [16,32) of a user buffer, PX layers only
+__device__ unsigned long long* g_nw_timeline = nullptr;
+__device__ __forceinline__ void nw_stamp(int slot, bool on) {
+#ifdef SGNN_TIMELINE
+  if (on && g_nw_timeline != nullptr && blockIdx.x == 0 && (threadIdx.x == 0 || slot >= 11)) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    g_nw_timeline[slot] = t;
+    g_nw_timeline[16 + slot] = (unsigned long long)clock64();
+  }
+#else
+  (void)slot; (void)on;
+#endif
+}
+
 constexpr int kNwGroups = 3;
 constexpr int kNwThreads = kNwGroups * kThreads + 128;     // + one warpgroup: producer and three issuer warps
 // setmaxnreg: 512 threads launch at 128; (128 - 56) * 128 released = (152 - 128) * 384 acquired
@@ -103,12 +119,13 @@ __device__ __forceinline__ void nw_producer(const CUtensorMap* agg_map, const CU
 
 // ---------------------------------------------------------------------------------- MMA issuers
 // acc0 = [agg | x] W0^T, K = 128 (W0 image: K-blocks 0,1 = agg columns, 2,3 = x columns)
-__device__ __forceinline__ void nw_mma0(uint32_t smem_u, uint32_t w0, NwMisc* misc, int n_my, uint32_t tmem) {
+__device__ __forceinline__ void nw_mma0(uint32_t smem_u, uint32_t w0, NwMisc* misc, int n_my, uint32_t tmem, bool px) {
   const uint32_t idesc = umma_idesc_tf32(kTileRows, kNwW);
   for (int a = 0; a < n_my; ++a) {
     const int g = a % kNwGroups, use_g = a / kNwGroups, sa = a & 1;
     if (use_g > 0) mbar_wait_spin(&misc->g[g].region_free, (uint32_t)(use_g - 1) & 1u);
     mbar_wait_spin(&misc->g[g].patched, (uint32_t)use_g & 1u);     // implies the group's `full`
+    nw_stamp(11, px && (threadIdx.x & 31) == 0);
     tc_fence_after_sync();
     const uint32_t d = tmem + (uint32_t)(g * 2 * kNwW);
     const uint32_t a_agg = smem_u + kNwAggOff + sa * kNwSlotBytes;
@@ -126,6 +143,7 @@ __device__ __forceinline__ void nw_mma0(uint32_t smem_u, uint32_t w0, NwMisc* mi
       tc_commit(&misc->g[g].acc0_ready);
     }
     __syncwarp();
+    nw_stamp(12, px && (threadIdx.x & 31) == 0);
   }
 }
 // D (region 1) = A (region 0, TMEM) W^T for the second Linear (which == 0) and the tail GEMM (which == 1)
@@ -159,6 +177,7 @@ __device__ __forceinline__ void nw_epilogue(const SgnnNodeParams& p, const CUten
   const float4* bet4 = reinterpret_cast<const float4*>(vec + p.mlp.beta_off);
   char* x_slot = smem + kNwXOff + g * kNwSlotBytes;
   const bool px = p.tail == SGNN_TAIL_PX;
+  const bool poll = false;      // polling epilogue warps measured slower even with one tile per group (r01n)
 
   // CSR bounds of this thread's row, loaded one tile ahead
   int beg_nx = 0, end_nx = 0;
@@ -180,29 +199,55 @@ __device__ __forceinline__ void nw_epilogue(const SgnnNodeParams& p, const CUten
       if (i + kNwGroups < n_my && rn < p.n_rows) { beg_nx = __ldg(p.rowptr + rn); end_nx = __ldg(p.rowptr + rn + 1); }
     }
 
-    // ---- this thread's agg row in its slot: complete it (rare) and round it to TF32 (the copy engine
-    //      delivered raw fp32; the x half was rounded by its producer), then release the tile ----
-    mbar_wait_sleep(&gr->full, par);
+    // ---- this thread's agg row in its slot: complete it and round it to TF32 (the copy engine delivered
+    //      raw fp32; the x half was rounded by its producer), then release the tile.  A receiver whose CSR
+    //      row straddles two edge tiles still lacks the later tile's `head` partial: rare per ROW but nearly
+    //      certain per TILE (one tile in five ends inside a row at degree 5), and the loads sat on the
+    //      tile's serial chain, 1.8 us after the tile had landed (in-kernel stamps, r01n) -- so the partial
+    //      is fetched BEFORE the wait for the tile, next to the TMA loads it does not depend on ----
+    const bool has = valid && end > beg;             // no edges: the edge kernel never wrote this agg row
+    const int t_lo = (beg >> 7) + 1, t_hi = has ? ((end - 1) >> 7) : 0;     // later edge tiles of a straddling CSR row
+    float4 hp[W / 4];
+    if (t_hi >= t_lo) {
+      const float4* h4 = reinterpret_cast<const float4*>(p.head + (long)t_lo * W);
+#pragma unroll
+      for (int c = 0; c < W / 4; ++c) hp[c] = __ldg(h4 + c);
+    } else {
+#pragma unroll
+      for (int c = 0; c < W / 4; ++c) hp[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    mbar_wait_mode(&gr->full, par, poll);
+    nw_stamp(3, px);
     {
       char* agg_rows = smem + kNwAggOff + (i & 1) * kNwSlotBytes;
-      const bool has = valid && end > beg;           // no edges: the edge kernel never wrote this agg row
-      const int t_lo = (beg >> 7) + 1, t_hi = has ? ((end - 1) >> 7) : 0;   // later edge tiles of a straddling CSR row
-#pragma unroll 4
-      for (int c = 0; c < W / 4; ++c) {
-        float4* q = reinterpret_cast<float4*>(agg_rows + sw128_chunk_offset(wt, c, kTileRows));
-        float4 a = has ? *q : make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int t = t_lo; t <= t_hi; ++t) {
-          const float4 h = __ldg(reinterpret_cast<const float4*>(p.head + (long)t * W) + c);
-          a.x += h.x; a.y += h.y; a.z += h.z; a.w += h.w;
+      if (t_hi <= t_lo) {
+#pragma unroll
+        for (int c = 0; c < W / 4; ++c) {
+          float4* q = reinterpret_cast<float4*>(agg_rows + sw128_chunk_offset(wt, c, kTileRows));
+          float4 a = has ? *q : make_float4(0.f, 0.f, 0.f, 0.f);
+          a.x += hp[c].x; a.y += hp[c].y; a.z += hp[c].z; a.w += hp[c].w;
+          *q = make_float4(nw_tf32r(a.x), nw_tf32r(a.y), nw_tf32r(a.z), nw_tf32r(a.w));
         }
-        *q = make_float4(nw_tf32r(a.x), nw_tf32r(a.y), nw_tf32r(a.z), nw_tf32r(a.w));
+      } else {                                       // rows longer than a tile (arbitrary edge lists only)
+#pragma unroll 1
+        for (int c = 0; c < W / 4; ++c) {
+          float4* q = reinterpret_cast<float4*>(agg_rows + sw128_chunk_offset(wt, c, kTileRows));
+          float4 a = *q;
+          for (int t = t_lo; t <= t_hi; ++t) {
+            const float4 h = __ldg(reinterpret_cast<const float4*>(p.head + (long)t * W) + c);
+            a.x += h.x; a.y += h.y; a.z += h.z; a.w += h.w;
+          }
+          *q = make_float4(nw_tf32r(a.x), nw_tf32r(a.y), nw_tf32r(a.z), nw_tf32r(a.w));
+        }
       }
     }
+    nw_stamp(10, px);
     fence_proxy_async_smem();                    // generic-proxy writes -> visible to tcgen05.mma
     mbar_arrive(&gr->patched);
 
     // ---- hidden = relu(acc0 + c1), rounded to TF32, back into the same TMEM columns ----
-    mbar_wait_sleep(&gr->acc0_ready, par);
+    mbar_wait_mode(&gr->acc0_ready, par, poll);
+    nw_stamp(4, px);
     tc_fence_after_sync();
 #pragma unroll
     for (int c = 0; c < W; c += 32) {
@@ -223,7 +268,8 @@ __device__ __forceinline__ void nw_epilogue(const SgnnNodeParams& p, const CUten
     mbar_arrive(&gr->hid_ready);
 
     // ---- x' = x + LN(acc1 + c2) ----
-    mbar_wait_sleep(&gr->acc1_ready, par);
+    mbar_wait_mode(&gr->acc1_ready, par, poll);
+    nw_stamp(5, px);
     tc_fence_after_sync();
     float y[W];
     tmem_ld64(t1, y);
@@ -279,6 +325,7 @@ __device__ __forceinline__ void nw_epilogue(const SgnnNodeParams& p, const CUten
     tmem_st_wait();
     tc_fence_before_sync();
     mbar_arrive(&gr->xo_ready);
+    nw_stamp(6, px);
     fence_proxy_async_smem();
     nw_group_bar(g);                             // every row of x' is in the slot / has been read from it
 
@@ -291,7 +338,8 @@ __device__ __forceinline__ void nw_epilogue(const SgnnNodeParams& p, const CUten
         }
         __syncwarp();
       }
-      mbar_wait_sleep(&gr->acc2_ready, par);
+      mbar_wait_mode(&gr->acc2_ready, par, poll);
+      nw_stamp(7, px);
       tc_fence_after_sync();
       float o[W];
       tmem_ld64(t1, o);
@@ -326,7 +374,7 @@ __device__ __forceinline__ void nw_epilogue(const SgnnNodeParams& p, const CUten
         if (elect_one()) mbar_arrive(&gr->slot_free);
         __syncwarp();
       }
-      mbar_wait_sleep(&gr->acc2_ready, par);
+      mbar_wait_mode(&gr->acc2_ready, par, poll);
       tc_fence_after_sync();
       float o[8];
       const int nout = p.dec.out;
@@ -385,9 +433,12 @@ __device__ __forceinline__ void nw_epilogue(const SgnnNodeParams& p, const CUten
     }
   }
   if (px && wq == 0) {
-    if (elect_one()) tma_store_wait_all();
+    // shared memory must outlive the copy engine's READS only; the writes are ordered before the grid's
+    // completion (and a dependent's griddepcontrol.wait) by the hardware
+    if (elect_one()) tma_store_wait_read();
     __syncwarp();
   }
+  nw_stamp(8, px);
 }
 
 // ---------------------------------------------------------------------------------- kernel
@@ -400,6 +451,7 @@ node_ws_kernel(const SgnnNodeParams p, const __grid_constant__ CUtensorMap agg_m
   const int tid = threadIdx.x, warp = tid >> 5;
 
   pdl_launch_dependents();
+  nw_stamp(0, p.tail == SGNN_TAIL_PX);
   if (tid == 0) {
     mbar_init(&misc->bar_w, 1);
     for (int s = 0; s < kNwAggSlots; ++s) mbar_init(&misc->agg_empty[s], 1);
@@ -429,7 +481,9 @@ node_ws_kernel(const SgnnNodeParams p, const __grid_constant__ CUtensorMap agg_m
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
+  nw_stamp(1, p.tail == SGNN_TAIL_PX);
   pdl_wait();          // everything above touched only shared/tensor memory and the constant weights
+  nw_stamp(2, p.tail == SGNN_TAIL_PX);
   const int n_tiles = (p.n_rows + kTileRows - 1) / kTileRows;
   const int n_my = (int)blockIdx.x < n_tiles ? (n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
   const uint32_t tmem = misc->tmem_slot;
@@ -447,19 +501,27 @@ node_ws_kernel(const SgnnNodeParams p, const __grid_constant__ CUtensorMap agg_m
       nw_producer(&agg_map, &x_map, smem, misc, n_my);
     } else {
       mbar_wait(&misc->bar_w, 0);
-      if (role == 1) nw_mma0(sU, img + p.mlp.w_off[0], misc, n_my, tmem);
+      nw_stamp(13, p.tail == SGNN_TAIL_PX && role == 1 && (threadIdx.x & 31) == 0);
+      if (role == 1) nw_mma0(sU, img + p.mlp.w_off[0], misc, n_my, tmem, p.tail == SGNN_TAIL_PX);
       else if (role == 2) nw_mma_ts(img + p.mlp.w_off[1], misc, n_my, tmem, 0);
       else nw_mma_ts(img + (p.tail == SGNN_TAIL_PX ? p.wp_off : p.dec.w_off[0]), misc, n_my, tmem, 1);
     }
   }
   tc_fence_before_sync();
   __syncthreads();
+  nw_stamp(9, p.tail == SGNN_TAIL_PX);
   if (tid < 32) tmem_dealloc(tmem, TMEM_COLS);
 }
 
 }  // namespace sgnn
 
 using namespace sgnn;
+
+// debug: device buffer of >= 32 uint64 receiving the stamps of node_ws_kernel (NULL = off)
+extern "C" int sgnn_debug_node_ws_timeline(unsigned long long* buf) {
+  SGNN_CUDA(cudaMemcpyToSymbol(g_nw_timeline, &buf, sizeof(buf)));
+  return SGNN_OK;
+}
 
 static bool nw_vec_resident(int off_floats, int n) { return off_floats >= 0 && (off_floats + n) * 4 <= kNwVecBytes; }
 static bool nw_img_resident(int off_bytes, int bytes) {
