@@ -58,23 +58,54 @@ __global__ void __launch_bounds__(kEncFastThreads, 1) edge_encoder_fast_kernel(c
   const int nh = p.mlp.n_hidden;
   const int tile_floats = kTileRows * EW;
 
-  for (int tile = blockIdx.x + w * gridDim.x; tile < n_tiles; tile += gridDim.x * kEncWorkers) {
+  // Sender / receiver ids and their positions are fetched ONE TILE AHEAD (ids at the start of the previous
+  // tile, positions at its end): a worker is one serial chain per tile, and two dependent global round
+  // trips at its head (~1 us) are a quarter of it.
+  const int tile_step = gridDim.x * kEncWorkers;
+  const bool gather = p.feat == nullptr;
+  int s_nx = 0, t_nx = 0;
+  float ps_nx[KIN - 1], pt_nx[KIN - 1];
+#pragma unroll
+  for (int d = 0; d < KIN - 1; ++d) ps_nx[d] = pt_nx[d] = 0.f;
+  {
+    const long e = (long)(blockIdx.x + w * gridDim.x) * kTileRows + wt;
+    if (gather && e < n_edges) {
+      s_nx = __ldg(p.src + e);
+      t_nx = __ldg(p.tgt + e);
+#pragma unroll
+      for (int d = 0; d < KIN - 1; ++d) {
+        ps_nx[d] = __ldg(p.pos + (long)s_nx * p.pos_stride + d);
+        pt_nx[d] = __ldg(p.pos + (long)t_nx * p.pos_stride + d);
+      }
+    }
+  }
+  bool stage_busy = false;            // a TMA store issued from the stage buffer has not been waited for
+
+  for (int tile = blockIdx.x + w * gridDim.x; tile < n_tiles; tile += tile_step) {
     const long eidx = (long)tile * kTileRows + wt;
     const bool valid = eidx < n_edges;
     // ---- features ----
     float f[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) f[k] = 0.f;
+    float ps[KIN - 1], pt[KIN - 1];
+#pragma unroll
+    for (int d = 0; d < KIN - 1; ++d) { ps[d] = ps_nx[d]; pt[d] = pt_nx[d]; }
+    const long e_next = eidx + (long)tile_step * kTileRows;
+    const bool next_valid = gather && tile + tile_step < n_tiles && e_next < n_edges;
+    if (next_valid) {
+      s_nx = __ldg(p.src + e_next);
+      t_nx = __ldg(p.tgt + e_next);
+    }
     if (valid) {
       if (p.feat) {
 #pragma unroll
         for (int k = 0; k < KIN; ++k) f[k] = p.feat[eidx * KIN + k];
       } else {
-        const long s = p.src[eidx], t = p.tgt[eidx];
         float sq = 0.f;
 #pragma unroll
         for (int d = 0; d < KIN - 1; ++d) {
-          const float diff = __fsub_rn(p.pos[s * p.pos_stride + d], p.pos[t * p.pos_stride + d]);
+          const float diff = __fsub_rn(ps[d], pt[d]);
           f[d] = __fdiv_rn(diff, p.radius);
           sq = __fadd_rn(sq, __fmul_rn(f[d], f[d]));
         }
@@ -87,17 +118,30 @@ __global__ void __launch_bounds__(kEncFastThreads, 1) edge_encoder_fast_kernel(c
     }
     // ---- layer 0 (k_in -> 64) in fp32 FFMA, ReLU -> TMEM region A ----
     {
-      const float* w0 = blob_f + p.w0_off;
-      const float* b0 = blob_f + p.mlp.b_off[0];
+      // parameters as 16-byte broadcast loads: the scalar version issued ~450 LDS.32 per thread and tile
+      // (first-layer weights, four bias / affine vectors), an LSU load of its own at 16 warps per SM
+      const float4* w04 = reinterpret_cast<const float4*>(blob_f + p.w0_off);      // [64][KIN] row-major
+      const float4* b04 = reinterpret_cast<const float4*>(blob_f + p.mlp.b_off[0]);
 #pragma unroll
       for (int c = 0; c < EW; c += 32) {
         float v[32];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          float a = 0.f;
+        for (int j4 = 0; j4 < 8; ++j4) {         // 4 output columns: KIN 16-byte loads of weights, one of bias
+          float wv[4 * KIN];
 #pragma unroll
-          for (int k = 0; k < KIN; ++k) a = fmaf(f[k], w0[(c + j) * KIN + k], a);
-          v[j] = enc_tf32r(fmaxf(a + b0[c + j], 0.f));
+          for (int q = 0; q < KIN; ++q) {
+            const float4 t4 = w04[((c + 4 * j4) * KIN) / 4 + q];
+            wv[4 * q] = t4.x; wv[4 * q + 1] = t4.y; wv[4 * q + 2] = t4.z; wv[4 * q + 3] = t4.w;
+          }
+          const float4 bb = b04[c / 4 + j4];
+          const float bv[4] = {bb.x, bb.y, bb.z, bb.w};
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            float a = 0.f;
+#pragma unroll
+            for (int k = 0; k < KIN; ++k) a = fmaf(f[k], wv[u * KIN + k], a);
+            v[4 * j4 + u] = enc_tf32r(fmaxf(a + bv[u], 0.f));
+          }
         }
         tmem_st32(RA + lane_base + c, v);
       }
@@ -120,13 +164,17 @@ __global__ void __launch_bounds__(kEncFastThreads, 1) edge_encoder_fast_kernel(c
       enc_worker_bar(w);
       tc_fence_after_sync();
       if (l < nh) {
-        const float* b = blob_f + p.mlp.b_off[l];
+        const float4* b4 = reinterpret_cast<const float4*>(blob_f + p.mlp.b_off[l]);
 #pragma unroll
         for (int c = 0; c < EW; c += 32) {
           float h[32];
           tmem_ld32(d + lane_base + c, h);
 #pragma unroll
-          for (int j = 0; j < 32; ++j) h[j] = enc_tf32r(fmaxf(h[j] + b[c + j], 0.f));
+          for (int j = 0; j < 32; j += 4) {
+            const float4 bb = b4[(c + j) >> 2];
+            h[j] = enc_tf32r(fmaxf(h[j] + bb.x, 0.f)); h[j + 1] = enc_tf32r(fmaxf(h[j + 1] + bb.y, 0.f));
+            h[j + 2] = enc_tf32r(fmaxf(h[j + 2] + bb.z, 0.f)); h[j + 3] = enc_tf32r(fmaxf(h[j + 3] + bb.w, 0.f));
+          }
           tmem_st32(d + lane_base + c, h);
         }
       }
@@ -136,13 +184,24 @@ __global__ void __launch_bounds__(kEncFastThreads, 1) edge_encoder_fast_kernel(c
     float y[EW];
     tmem_ld32(a + lane_base, y);
     tmem_ld32(a + lane_base + 32, y + 32);
-    {
-      const float* b = blob_f + p.mlp.b_off[nh];
+    // positions of the next tile's edges: the ids asked for at the top of this tile have arrived by now
+    if (next_valid) {
 #pragma unroll
-      for (int j = 0; j < EW; ++j) y[j] += b[j];
+      for (int d = 0; d < KIN - 1; ++d) {
+        ps_nx[d] = __ldg(p.pos + (long)s_nx * p.pos_stride + d);
+        pt_nx[d] = __ldg(p.pos + (long)t_nx * p.pos_stride + d);
+      }
+    }
+    {
+      const float4* b4 = reinterpret_cast<const float4*>(blob_f + p.mlp.b_off[nh]);
+#pragma unroll
+      for (int j = 0; j < EW; j += 4) {
+        const float4 bb = b4[j >> 2];
+        y[j] += bb.x; y[j + 1] += bb.y; y[j + 2] += bb.z; y[j + 3] += bb.w;
+      }
       if (p.mlp.has_ln) {
-        const float* gam = blob_f + p.mlp.gamma_off;
-        const float* bet = blob_f + p.mlp.beta_off;
+        const float4* gam4 = reinterpret_cast<const float4*>(blob_f + p.mlp.gamma_off);
+        const float4* bet4 = reinterpret_cast<const float4*>(blob_f + p.mlp.beta_off);
         float s4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
         for (int j = 0; j < EW; ++j) s4[j & 3] += y[j];
@@ -155,10 +214,19 @@ __global__ void __launch_bounds__(kEncFastThreads, 1) edge_encoder_fast_kernel(c
         }
         const float rstd = 1.0f / sqrtf(((q4[0] + q4[1]) + (q4[2] + q4[3])) / (float)EW + 1e-5f);
 #pragma unroll
-        for (int j = 0; j < EW; ++j) y[j] = y[j] * rstd * gam[j] + bet[j];
+        for (int j = 0; j < EW; j += 4) {
+          const float4 ga = gam4[j >> 2], be = bet4[j >> 2];
+          y[j] = y[j] * rstd * ga.x + be.x; y[j + 1] = y[j + 1] * rstd * ga.y + be.y;
+          y[j + 2] = y[j + 2] * rstd * ga.z + be.z; y[j + 3] = y[j + 3] * rstd * ga.w + be.w;
+        }
       }
     }
-    // tile image in shared memory (conflict-free 16-byte stores), then ONE coalesced TMA bulk store
+    // tile image in shared memory (conflict-free 16-byte stores), then ONE coalesced TMA bulk store.  The
+    // copy engine's read of the PREVIOUS tile's image is waited for only here, a whole tile later.
+    if (stage_busy) {
+      if (wt == 0) tma_store_wait_read();
+      enc_worker_bar(w);
+    }
 #pragma unroll
     for (int ch = 0; ch < EW / 4; ++ch) {
       float4 o = valid ? make_float4(to_tf32(y[4 * ch]), to_tf32(y[4 * ch + 1]), to_tf32(y[4 * ch + 2]),
@@ -168,13 +236,9 @@ __global__ void __launch_bounds__(kEncFastThreads, 1) edge_encoder_fast_kernel(c
     }
     fence_proxy_async_smem();
     tc_fence_before_sync();
-    enc_worker_bar(w);
-    if (wt == 0) {
-      tma_bulk_s2g(p.e_tiles + (long)tile * tile_floats, stage, (uint32_t)(tile_floats * 4));
-      tma_store_wait_read();          // the stage buffer is rewritten by the next tile
-    }
-    tc_fence_before_sync();
-    enc_worker_bar(w);
+    enc_worker_bar(w);           // also: every TMEM read of this tile retired before the next tile's tmem_st
+    if (wt == 0) tma_bulk_s2g(p.e_tiles + (long)tile * tile_floats, stage, (uint32_t)(tile_floats * 4));
+    stage_busy = true;
   }
   if (wt == 0) tma_store_wait_all();
   tc_fence_before_sync();
