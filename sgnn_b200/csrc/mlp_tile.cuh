@@ -204,16 +204,30 @@ __device__ __forceinline__ void a_tile_load_rows(void* a_tile, int col0, const f
   char* a = reinterpret_cast<char*>(a_tile);
   const int chunks = width >> 2;                   // 16-byte chunks per row
   const int total = kTileRows * chunks;
-  for (int idx = threadIdx.x; idx < total; idx += kThreads) {
-    const int r = idx / chunks, c = idx - r * chunks;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (r < rows_valid) {
-      const long g = row_index(r);
-      if (g >= 0) v = __ldg(reinterpret_cast<const float4*>(src + g * ld) + c);
+  // four independent loads in flight per thread: one load per iteration made this loop a chain of
+  // global round trips (32 iterations x ~0.45 us for a 128-wide tile, the multi-scale kernels)
+  for (int idx0 = threadIdx.x; idx0 < total; idx0 += 4 * kThreads) {
+    float4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int idx = idx0 + u * kThreads;
+      const int r = idx / chunks, c = idx - r * chunks;
+      v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (idx < total && r < rows_valid) {
+        const long g = row_index(r);
+        if (g >= 0) v[u] = __ldg(reinterpret_cast<const float4*>(src + g * ld) + c);
+      }
     }
-    v.x *= scale; v.y *= scale; v.z *= scale; v.w *= scale;
-    if constexpr (TC) v = make_float4(to_tf32(v.x), to_tf32(v.y), to_tf32(v.z), to_tf32(v.w));
-    *reinterpret_cast<float4*>(a + sw128_chunk_offset(r, (col0 >> 2) + c, kTileRows)) = v;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int idx = idx0 + u * kThreads;
+      if (idx < total) {
+        const int r = idx / chunks, c = idx - r * chunks;
+        float4 t = make_float4(v[u].x * scale, v[u].y * scale, v[u].z * scale, v[u].w * scale);
+        if constexpr (TC) t = make_float4(to_tf32(t.x), to_tf32(t.y), to_tf32(t.z), to_tf32(t.w));
+        *reinterpret_cast<float4*>(a + sw128_chunk_offset(r, (col0 >> 2) + c, kTileRows)) = t;
+      }
+    }
   }
 }
 

@@ -98,23 +98,41 @@ __device__ __forceinline__ void prologue_features(const SgnnNodeParams& p, char*
 template <bool TC>
 __device__ __forceinline__ void prologue_agg_x(const SgnnNodeParams& p, char* a_tile, long row0, int nvalid) {
   const int chunks = p.agg_w >> 2;
-  for (int idx = threadIdx.x; idx < kTileRows * chunks; idx += kThreads) {
-    const int r = idx / chunks, c = idx - r * chunks;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (r < nvalid) {
-      const long i = row0 + r;
-      const int beg = p.rowptr[i], end = p.rowptr[i + 1];
-      if (end > beg) {
-        v = __ldg(reinterpret_cast<const float4*>(p.agg + i * p.agg_w) + c);
-        const int t0 = beg >> 7, t1 = (end - 1) >> 7;
-        for (int t = t0 + 1; t <= t1; ++t) {
-          const float4 h = __ldg(reinterpret_cast<const float4*>(p.head + (long)t * p.agg_w) + c);
-          v.x += h.x; v.y += h.y; v.z += h.z; v.w += h.w;
+  const int total = kTileRows * chunks;
+  // four rows' CSR bounds, then their four agg chunks, in flight together (see a_tile_load_rows)
+  for (int idx0 = threadIdx.x; idx0 < total; idx0 += 4 * kThreads) {
+    int beg[4], end[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int idx = idx0 + u * kThreads;
+      const int r = idx / chunks;
+      beg[u] = end[u] = 0;
+      if (idx < total && r < nvalid) { beg[u] = __ldg(p.rowptr + row0 + r); end[u] = __ldg(p.rowptr + row0 + r + 1); }
+    }
+    float4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int idx = idx0 + u * kThreads;
+      const int r = idx / chunks, c = idx - r * chunks;
+      v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (end[u] > beg[u]) v[u] = __ldg(reinterpret_cast<const float4*>(p.agg + (row0 + r) * p.agg_w) + c);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int idx = idx0 + u * kThreads;
+      if (idx >= total) continue;
+      const int r = idx / chunks, c = idx - r * chunks;
+      float4 t = v[u];
+      if (end[u] > beg[u]) {
+        const int t0 = beg[u] >> 7, t1 = (end[u] - 1) >> 7;
+        for (int tt = t0 + 1; tt <= t1; ++tt) {          // CSR row straddling edge tiles
+          const float4 h = __ldg(reinterpret_cast<const float4*>(p.head + (long)tt * p.agg_w) + c);
+          t.x += h.x; t.y += h.y; t.z += h.z; t.w += h.w;
         }
       }
+      if constexpr (TC) t = make_float4(to_tf32(t.x), to_tf32(t.y), to_tf32(t.z), to_tf32(t.w));
+      *reinterpret_cast<float4*>(a_tile + sw128_chunk_offset(r, c, kTileRows)) = t;
     }
-    if constexpr (TC) v = make_float4(to_tf32(v.x), to_tf32(v.y), to_tf32(v.z), to_tf32(v.w));
-    *reinterpret_cast<float4*>(a_tile + sw128_chunk_offset(r, c, kTileRows)) = v;
   }
   a_tile_load_rows<TC>(a_tile, p.agg_w, p.x_in, p.x_w, p.x_w, nvalid, [row0](int r) { return row0 + r; });
 }

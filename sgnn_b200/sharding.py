@@ -175,13 +175,20 @@ def exchange_rows(comm: Comm, plan: GhostPlan, owned_rows: torch.Tensor) -> Tupl
 @torch.no_grad()
 def sharded_rollout(simulator, positions_owned: torch.Tensor, nsteps: int, comm: Comm,
                     n_layers: int, skin: Optional[float] = None, refresh_every: int = 10,
-                    return_edges: bool = False):
+                    return_edges: bool = False, use_graph: bool = True):
     """Autoregressive rollout of this rank's slab.
 
     positions_owned [n_owned, S, dim]: the initial window of the owned particles (global ids
     lo..hi-1 in order).  Returns (pred [nsteps, n_owned, dim], strain [nsteps, n_owned]) and, when
     return_edges, the step-0 edge list of the owned receivers as GLOBAL-id-relative local pairs
-    (src_local - n_left + lo is the global id; see tests)."""
+    (src_local - n_left + lo is the global id; see tests).
+
+    Between two ghost refreshes the local system has a fixed size, so its step (neighbour search +
+    network, 21 launches) runs on ONE window buffer [n_local, S + 1, dim] with fixed addresses -- frames
+    [0, S) in, frame S out, then the window is shifted by a small device copy -- and is captured into a
+    CUDA graph once per refresh and replayed every step (use_graph).  Launching the 21 kernels from
+    Python costs ~0.5 ms per step, as much as the step itself on an eighth of a 1M-particle system
+    (8 GPUs, r01n: 1.41 ms per step launched eagerly)."""
     dev = positions_owned.device
     no, s, dim = positions_owned.shape
     radius = float(simulator._connectivity_radius)
@@ -197,26 +204,42 @@ def sharded_rollout(simulator, positions_owned: torch.Tensor, nsteps: int, comm:
         plan = GhostPlan(comm, window[:, -1, 0], g)
         gl, gr = exchange_rows(comm, plan, window)                     # full windows of the ghosts
         nl, nr, nloc = plan.n_left, plan.n_right, plan.n_local
-        buf = torch.empty(nloc, s + m, dim, dtype=torch.float32, device=dev)
-        buf[:nl, :s], buf[nl:nl + no, :s], buf[nl + no:, :s] = gl, window, gr
+        win = torch.empty(nloc, s + 1, dim, dtype=torch.float32, device=dev)
+        win[:nl, :s], win[nl:nl + no, :s], win[nl + no:, :s] = gl, window, gr
+        shift = torch.empty(nloc, s, dim, dtype=torch.float32, device=dev)
         types = torch.zeros(nloc, dtype=torch.int64, device=dev)
         ptr = torch.tensor([0, nloc], dtype=torch.int32, device=dev)
         st_buf = torch.empty(nloc, dtype=torch.float32, device=dev)
+
+        def step():
+            return simulator._step(win[:, :s], None, types, next_pos=win[:, s], strain=st_buf, example_ptr=ptr)
+
+        graph = None
+        if use_graph and m > 1 and not (return_edges and edges0 is None):
+            simulator._prepare(nloc, dev)                              # kernel plans / buffers outside the capture
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, capture_error_mode="thread_local"):
+                step()
         for j in range(m):
-            _, csr = simulator._step(buf[:, j:j + s], None, types, next_pos=buf[:, j + s], strain=st_buf,
-                                     example_ptr=ptr)
-            if return_edges and edges0 is None:
-                ei = csr.edge_index()
-                keep = (ei[1] >= nl) & (ei[1] < nl + no)
-                edges0 = (ei[:, keep], nl)
-            new_owned = buf[nl:nl + no, j + s]
+            if graph is not None:
+                graph.replay()
+            else:
+                _, csr = step()
+                if return_edges and edges0 is None:
+                    ei = csr.edge_index()
+                    keep = (ei[1] >= nl) & (ei[1] < nl + no)
+                    edges0 = (ei[:, keep], nl)
+            new_owned = win[nl:nl + no, s]
             pred[k + j] = new_owned
             strain[k + j] = st_buf[nl:nl + no]
             if j + 1 < m:                                              # ghosts take their owners' values
                 fl, fr = exchange_rows(comm, plan, new_owned.contiguous())
-                buf[:nl, j + s] = fl
-                buf[nl + no:, j + s] = fr
-        window = buf[nl:nl + no, m:m + s].contiguous()
+                win[:nl, s] = fl
+                win[nl + no:, s] = fr
+            shift.copy_(win[:, 1:])                                    # slide the window: frames 1..S -> 0..S-1
+            win[:, :s] = shift
+        window = win[nl:nl + no, :s].contiguous()
         k += m
     if return_edges:
         return pred, strain, edges0
