@@ -100,7 +100,8 @@ int sgnn_edge_features(const float* pos, long stride, int dim, float radius, con
 
 /* debug: %globaltimer stamps of the throughput node kernel's phases (CTA 0); NULL switches it off */
 int sgnn_debug_node_timeline(unsigned long long* buf);
-int sgnn_debug_node_ws_timeline(unsigned long long* buf);   /* node_ws_kernel, >= 32 slots; SGNN_TIMELINE builds */
+int sgnn_debug_node_ws_timeline(unsigned long long* buf);
+int sgnn_debug_radius_timeline(unsigned long long* buf);    /* radius_cluster_kernel, >= 16 slots; SGNN_TIMELINE builds */   /* node_ws_kernel, >= 32 slots; SGNN_TIMELINE builds */
 
 /* self-test of the GEMM tile primitive (tests/test_gemm_tile_gpu.py)                        */
 int sgnn_debug_gemm(const float* a, const float* wimg, int k, int n, float* d, int tc, void* stream);

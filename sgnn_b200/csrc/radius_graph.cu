@@ -10,6 +10,8 @@
 // smallest indices with a bounded insertion list, which yields the same set.
 //
 // All of it is HBM/latency-bound integer work: coalesced loads, one 16-byte load per candidate.
+#include <cooperative_groups.h>
+
 #include "common.cuh"
 #include "scan.cuh"
 
@@ -31,14 +33,14 @@ __device__ __forceinline__ int f2ord(float f) {
 __device__ __forceinline__ float ord2f(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
 
 // Every thread derives the same grid from the bounding box (a few flops; no extra launch).
-__device__ __forceinline__ CellGrid make_grid(const int* __restrict__ bbox, int dim, float h0,
-                                              int n_examples, int cell_cap) {
+__device__ __forceinline__ CellGrid make_grid_bounds(const float* lo, const float* hi, int dim, float h0,
+                                                     int n_examples, int cell_cap) {
   CellGrid g;
   double h = (double)h0;
   float ext[3] = {0.f, 0.f, 0.f};
   for (int d = 0; d < 3; ++d) {
-    g.lo[d] = d < dim ? ord2f(bbox[d]) : 0.f;
-    ext[d] = d < dim ? ord2f(bbox[4 + d]) - g.lo[d] : 0.f;
+    g.lo[d] = d < dim ? lo[d] : 0.f;
+    ext[d] = d < dim ? hi[d] - g.lo[d] : 0.f;
   }
   for (int it = 0; it < 64; ++it) {
     double total = (double)n_examples;
@@ -51,6 +53,12 @@ __device__ __forceinline__ CellGrid make_grid(const int* __restrict__ bbox, int 
   }
   g.inv_h = 1.0 / h;
   return g;
+}
+__device__ __forceinline__ CellGrid make_grid(const int* __restrict__ bbox, int dim, float h0,
+                                              int n_examples, int cell_cap) {
+  float lo[3] = {0.f, 0.f, 0.f}, hi[3] = {0.f, 0.f, 0.f};
+  for (int d = 0; d < dim; ++d) { lo[d] = ord2f(bbox[d]); hi[d] = ord2f(bbox[4 + d]); }
+  return make_grid_bounds(lo, hi, dim, h0, n_examples, cell_cap);
 }
 
 __device__ __forceinline__ int cell_coord(float x, float lo, double inv_h, int nc) {
@@ -221,6 +229,233 @@ compact_kernel(int n, int slab, const int* __restrict__ rowptr, const int* __res
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Small systems (n <= 8192): the whole search as ONE kernel on ONE thread-block cluster of 16 CTAs x
+// 512 threads, one particle per thread.  At 4800 particles the nine launches of the general path are
+// nine ~2.6 us latency chains (23.5 us per rollout step under graph replay, 18 % of the step); a
+// fused kernel with software grid barriers measured slower (30 us: every barrier is two global round
+// trips).  Here the phases are separated by the hardware cluster barrier (~0.2 us) and everything the
+// phases hand to each other -- bounding-box partials, cell counters / starts, the cell-sorted particle
+// array, scan totals -- lives in distributed shared memory (a remote access is ~215 cycles against
+// ~800 for L2): cells and sorted slots are dealt to the CTAs in contiguous blocks.
+namespace cg = cooperative_groups;
+// optional phase stamps of CTA 0 / thread 0 (SGNN_TIMELINE builds; profiles/radius_timeline.py)
+__device__ unsigned long long* g_rg_timeline = nullptr;
+__device__ __forceinline__ void rg_stamp(int slot) {
+#ifdef SGNN_TIMELINE
+  if (g_rg_timeline != nullptr && blockIdx.x == 0 && threadIdx.x == 0) g_rg_timeline[slot] = (unsigned long long)clock64();
+#else
+  (void)slot;
+#endif
+}
+constexpr int kClMaxN = 8192;
+constexpr int kClThreads = 512;
+constexpr int kClCtas = 16;
+constexpr int kClCellsPerCta = 2048 + 2;       // power-of-two block of cells per CTA (>= (2 * 8192 + 1024) / 16)
+
+struct ClusterSmem {
+  float bb_lo[kClCtas][4], bb_hi[kClCtas][4];   // every CTA's partial box, written by its owner into all copies
+  int tot_cells[kClCtas], tot_cnt[kClCtas];     // block totals of the two scans, same scheme
+  float w_lo[kClThreads / 32][4], w_hi[kClThreads / 32][4];
+  int cell_start[kClCellsPerCta];               // this CTA's block of cell counters, scanned in place
+  float4 sorted[kClThreads];                    // this CTA's block of the cell-sorted array (x, y, z, id)
+  int sorted_cell[kClThreads];
+  int cnt_s[kClThreads];                        // neighbour count / list of THIS CTA's particles (by id), written
+  int nbr_s[kClThreads][kMaxK + 1];             // remotely by whichever thread searched for them
+};
+
+__global__ void __launch_bounds__(kClThreads)
+radius_cluster_kernel(const float* __restrict__ pos, long stride, int n, int dim, const int* __restrict__ ex_ptr,
+                      int n_examples, float h0, int cell_cap, float r2, int kq, int loop,
+                      int* __restrict__ rowptr, int* __restrict__ src, int* __restrict__ tgt) {
+  extern __shared__ __align__(16) unsigned char cl_smem_raw[];
+  ClusterSmem& sm = *reinterpret_cast<ClusterSmem*>(cl_smem_raw);
+  cg::cluster_group cluster = cg::this_cluster();
+  const int rank = (int)cluster.block_rank();
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int i = rank * kClThreads + tid;
+  const bool live = i < n;
+  pdl_launch_dependents();
+  rg_stamp(0);
+  for (int k = tid; k < kClCellsPerCta; k += kClThreads) sm.cell_start[k] = 0;
+  pdl_wait();
+  rg_stamp(1);
+
+  // ---- A: bounding box.  CTA partial -> slot `rank` of every CTA's copy ----
+  float4 e = make_float4(0.f, 0.f, 0.f, __int_as_float(i));
+  if (live) {
+    e.x = pos[(long)i * stride];
+    if (dim > 1) e.y = pos[(long)i * stride + 1];
+    if (dim > 2) e.z = pos[(long)i * stride + 2];
+  }
+  {
+    float mn[3] = {live ? e.x : INFINITY, live ? e.y : INFINITY, live ? e.z : INFINITY};
+    float mx[3] = {live ? e.x : -INFINITY, live ? e.y : -INFINITY, live ? e.z : -INFINITY};
+#pragma unroll
+    for (int d = 0; d < 3; ++d)
+      for (int o = 16; o > 0; o >>= 1) {
+        mn[d] = fminf(mn[d], __shfl_xor_sync(0xffffffffu, mn[d], o));
+        mx[d] = fmaxf(mx[d], __shfl_xor_sync(0xffffffffu, mx[d], o));
+      }
+    if (lane == 0)
+      for (int d = 0; d < 3; ++d) { sm.w_lo[warp][d] = mn[d]; sm.w_hi[warp][d] = mx[d]; }
+    __syncthreads();
+    if (tid < kClCtas) {                              // thread t delivers this CTA's partial to CTA t
+      float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+      for (int w = 0; w < kClThreads / 32; ++w)
+        for (int d = 0; d < 3; ++d) { lo[d] = fminf(lo[d], sm.w_lo[w][d]); hi[d] = fmaxf(hi[d], sm.w_hi[w][d]); }
+      ClusterSmem* dst = cluster.map_shared_rank(&sm, tid);
+      for (int d = 0; d < 3; ++d) { dst->bb_lo[rank][d] = lo[d]; dst->bb_hi[rank][d] = hi[d]; }
+    }
+  }
+  rg_stamp(2);
+  cluster.sync();
+  rg_stamp(3);
+
+  // ---- B: grid, cell of every particle, rank within its cell (counter blocks dealt to the CTAs) ----
+  float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+  for (int r = 0; r < kClCtas; ++r)
+    for (int d = 0; d < 3; ++d) { lo[d] = fminf(lo[d], sm.bb_lo[r][d]); hi[d] = fmaxf(hi[d], sm.bb_hi[r][d]); }
+  const CellGrid g = make_grid_bounds(lo, hi, dim, h0, n_examples, cell_cap);
+  const int n_cells = n_examples * g.nc[0] * g.nc[1] * g.nc[2];
+  // cells per CTA, rounded up to a power of two: owner and slot of a cell are a shift and a mask (the search
+  // looks up 6 .. 18 cell starts per particle)
+  int csh = 0;
+  while ((kClCtas << csh) < n_cells) ++csh;
+  const int cpc = 1 << csh, cmask = cpc - 1;
+  int c = 0, crank = 0;
+  if (live) {
+    const float v[3] = {e.x, e.y, e.z};
+    c = example_of(ex_ptr, n_examples, i);
+    for (int d = dim - 1; d >= 0; --d) c = c * g.nc[d] + cell_coord(v[d], g.lo[d], g.inv_h, g.nc[d]);
+    crank = atomicAdd(cluster.map_shared_rank(&sm.cell_start[c & cmask], c >> csh), 1);
+  }
+  rg_stamp(4);
+  cluster.sync();
+  rg_stamp(5);
+
+  // ---- C: cell starts: block-local exclusive scan, block totals to everybody, offsets ----
+  {
+    const int chunk = (cpc + kClThreads - 1) / kClThreads;
+    const int k0 = min(tid * chunk, cpc), k1 = min(k0 + chunk, cpc);
+    int sum = 0;
+    for (int k = k0; k < k1; ++k) sum += sm.cell_start[k];
+    int total;
+    int run = block_exclusive_scan(sum, total);
+    for (int k = k0; k < k1; ++k) { const int t = sm.cell_start[k]; sm.cell_start[k] = run; run += t; }
+    if (tid < kClCtas) cluster.map_shared_rank(&sm, tid)->tot_cells[rank] = total;
+  }
+  cluster.sync();
+  {
+    int off = 0, mine = 0;
+    for (int r = 0; r < kClCtas; ++r) { const int t = sm.tot_cells[r]; if (r < rank) off += t; if (r == rank) mine = t; }
+    for (int k = tid; k < cpc; k += kClThreads) sm.cell_start[k] += off;
+    if (tid == 0) sm.cell_start[cpc] = off + mine;             // start of the next CTA's first cell
+  }
+  rg_stamp(6);
+  cluster.sync();
+  rg_stamp(7);
+
+  // ---- D: particles in cell order, slot s lives in CTA s / 512 ----
+  if (live) {
+    const int s = *cluster.map_shared_rank(&sm.cell_start[c & cmask], c >> csh) + crank;
+    ClusterSmem* dst = cluster.map_shared_rank(&sm, s / kClThreads);
+    dst->sorted[s % kClThreads] = e;
+    dst->sorted_cell[s % kClThreads] = c;
+  }
+  rg_stamp(8);
+  cluster.sync();
+  rg_stamp(9);
+
+  // ---- E: neighbours of the i-th particle in cell order (same rule and order as neighbor_one) ----
+  if (live) {
+    const float4 q = sm.sorted[tid];
+    const int pid = __float_as_int(q.w);
+    int cc = sm.sorted_cell[tid];
+    const int cx = cc % g.nc[0]; cc /= g.nc[0];
+    const int cy = cc % g.nc[1]; cc /= g.nc[1];
+    const int cz = cc % g.nc[2];
+    const int ex = cc / g.nc[2];
+    auto start_of = [&](int cell) -> int {          // cell in [0, n_cells]
+      if (cell >= n_cells) return n;
+      return *cluster.map_shared_rank(&sm.cell_start[cell & cmask], cell >> csh);
+    };
+    int best[kMaxK + 1];
+    int nb = 0;
+    const int zlo = dim > 2 ? max(cz - 1, 0) : 0, zhi = dim > 2 ? min(cz + 1, g.nc[2] - 1) : 0;
+    const int ylo = dim > 1 ? max(cy - 1, 0) : 0, yhi = dim > 1 ? min(cy + 1, g.nc[1] - 1) : 0;
+    const int xlo = max(cx - 1, 0), xhi = min(cx + 1, g.nc[0] - 1);
+    // bounds of all (up to nine) cell rows first: independent remote loads, one latency instead of nine
+    int rs0[9], rs1[9];
+#pragma unroll
+    for (int u = 0; u < 9; ++u) {
+      const int z = zlo + u / 3, y = ylo + u % 3;
+      rs0[u] = rs1[u] = 0;
+      if (z <= zhi && y <= yhi) {
+        const int row = ((ex * g.nc[2] + z) * g.nc[1] + y) * g.nc[0];
+        rs0[u] = start_of(row + xlo);
+        rs1[u] = start_of(row + xhi + 1);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 9; ++u) {
+      for (int s = rs0[u]; s < rs1[u]; s += 4) {       // four candidates in flight
+        float4 o4[4];
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+          const int sv = min(s + v, rs1[u] - 1);
+          o4[v] = cluster.map_shared_rank(&sm, sv / kClThreads)->sorted[sv % kClThreads];
+        }
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+          if (s + v >= rs1[u]) continue;
+          const float4 o = o4[v];
+          const int j = __float_as_int(o.w);
+          if (nb == kq && j > best[nb - 1]) continue;
+          float diff = o.x - q.x;
+          float d2 = __fmaf_rn(diff, diff, 0.0f);
+          if (dim > 1) { diff = o.y - q.y; d2 = __fmaf_rn(diff, diff, d2); }
+          if (dim > 2) { diff = o.z - q.z; d2 = __fmaf_rn(diff, diff, d2); }
+          if (!(d2 < r2)) continue;
+          int p = nb < kq ? nb++ : nb - 1;
+          while (p > 0 && best[p - 1] > j) { best[p] = best[p - 1]; --p; }
+          best[p] = j;
+        }
+      }
+    }
+    // the list goes to the CTA that owns particle `pid` (its row pointer and edges are written from there)
+    ClusterSmem* own = cluster.map_shared_rank(&sm, pid / kClThreads);
+    int kept = 0;
+    for (int u = 0; u < nb; ++u)
+      if (loop || best[u] != pid) own->nbr_s[pid % kClThreads][kept++] = best[u];
+    own->cnt_s[pid % kClThreads] = kept;
+  }
+  rg_stamp(10);
+  cluster.sync();
+  rg_stamp(11);
+
+  // ---- F: row pointers (scan in particle order) and the compacted edge list ----
+  {
+    const int v = live ? sm.cnt_s[tid] : 0;
+    int total;
+    const int prefix = block_exclusive_scan(v, total);
+    if (tid < kClCtas) cluster.map_shared_rank(&sm, tid)->tot_cnt[rank] = total;
+    cluster.sync();
+    int base = prefix;
+    for (int r = 0; r < rank; ++r) base += sm.tot_cnt[r];
+    if (live) {
+      rowptr[i] = base;
+      if (i == n - 1) rowptr[n] = base + v;
+      for (int k = 0; k < v; ++k) {
+        src[base + k] = sm.nbr_s[tid][k];
+        if (tgt) tgt[base + k] = i;
+      }
+    }
+  }
+  rg_stamp(12);
+}
+
 struct RadiusWorkspace {
   int* bbox;        // 8
   int* cell_of;     // n
@@ -264,8 +499,21 @@ extern "C" size_t sgnn_radius_graph_workspace_bytes(int n, int max_neighbors) {
 }
 
 // number of kernels one sgnn_radius_graph_csr call launches (host-side launch accounting)
+// debug: device buffer of >= 16 uint64 receiving the phase stamps of radius_cluster_kernel (NULL = off)
+extern "C" int sgnn_debug_radius_timeline(unsigned long long* buf) {
+  SGNN_CUDA(cudaMemcpyToSymbol(g_rg_timeline, &buf, sizeof(buf)));
+  return SGNN_OK;
+}
+
+// single-cluster path for small systems; SGNN_RADIUS_MULTI=1 keeps every size on the general path (A/B)
+static bool use_cluster_path(int n) {
+  static const bool multi = getenv("SGNN_RADIUS_MULTI") != nullptr;
+  return n <= kClMaxN && !multi;
+}
+
 extern "C" int sgnn_radius_graph_launches(int n, int max_neighbors) {
   if (n <= 0) return 0;
+  if (use_cluster_path(n)) return 1;
   const int cell_items = 2 * n + 1024 + 1;
   return 6 + (cell_items <= kScanChunk ? 1 : 3) + (n <= kScanChunk ? 1 : 3);
 }
@@ -294,6 +542,33 @@ extern "C" int sgnn_radius_graph_csr(const float* pos, long pos_stride, int n, i
   const float h0 = (float)(r * (1.0 + 1e-5)) ;     // cell edge just above r
   const int kq = loop ? max_neighbors : max_neighbors + 1;
 
+  if (use_cluster_path(n)) {
+    static bool attr_set = false;
+    if (!attr_set) {
+      SGNN_CUDA(cudaFuncSetAttribute(radius_cluster_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+      SGNN_CUDA(cudaFuncSetAttribute(radius_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)sizeof(ClusterSmem)));
+      attr_set = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(kClCtas);
+    cfg.blockDim = dim3(kClThreads);
+    cfg.dynamicSmemBytes = sizeof(ClusterSmem);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = kClCtas;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = getenv("SGNN_NO_PDL") ? 1 : 2;
+    SGNN_CUDA(cudaLaunchKernelEx(&cfg, radius_cluster_kernel, pos, pos_stride, n, dim, example_ptr, n_examples, h0,
+                                 w.cell_cap, r2, kq, loop, rowptr, src, tgt));
+    SGNN_LAUNCH_CHECK();
+    return SGNN_OK;
+  }
   SGNN_CUDA(sgnn_launch(bbox_init_kernel, dim3(sgnn_ceil_div(w.cell_cap + 2, 1024)), dim3(256), 0, st, w.bbox,
                         w.cell_count, w.cell_cap + 2));
   const int nb256 = sgnn_ceil_div(n, 256);

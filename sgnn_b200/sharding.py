@@ -215,13 +215,18 @@ def sharded_rollout(simulator, positions_owned: torch.Tensor, nsteps: int, comm:
             return simulator._step(win[:, :s], None, types, next_pos=win[:, s], strain=st_buf, example_ptr=ptr)
 
         graph = None
-        if use_graph and m > 1 and not (return_edges and edges0 is None):
-            simulator._prepare(nloc, dev)                              # kernel plans / buffers outside the capture
-            torch.cuda.synchronize()
-            graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(graph, capture_error_mode="thread_local"):
-                step()
         for j in range(m):
+            if j == 1 and use_graph and m > 2:
+                # the refresh's first step ran eagerly (lazy initialisation, kernel plans for this size,
+                # the step-0 edge list); the remaining ones replay one captured step
+                graph = torch.cuda.CUDAGraph()
+                cap = torch.cuda.Stream(device=dev)                    # (torch.cuda.graph() would also empty the
+                cap.wait_stream(torch.cuda.current_stream())           #  allocator cache at every refresh)
+                with torch.cuda.stream(cap):
+                    graph.capture_begin(capture_error_mode="thread_local")
+                    step()
+                    graph.capture_end()
+                torch.cuda.current_stream().wait_stream(cap)
             if graph is not None:
                 graph.replay()
             else:
