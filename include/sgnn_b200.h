@@ -34,6 +34,7 @@ int sgnn_device_info(int* sm_count, int* cc_major, int* cc_minor);
  *   rowptr [n+1], src/tgt [n*(K + !loop)] : outputs; E = rowptr[n] stays on the device     */
 size_t sgnn_radius_graph_workspace_bytes(int n, int max_neighbors);
 int sgnn_radius_graph_launches(int n, int max_neighbors);   /* kernels launched per call */
+int sgnn_radius_graph_mode(int mode);   /* 0: general path (default); 1: one 16-CTA cluster kernel for n <= 8192; returns the old mode */
 int sgnn_radius_graph_csr(const float* pos, long pos_stride, int n, int dim, const int* example_ptr,
                           int n_examples, double r, int max_neighbors, int loop, void* workspace,
                           size_t workspace_bytes, int* rowptr, int* src, int* tgt, void* stream);

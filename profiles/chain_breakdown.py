@@ -27,6 +27,8 @@ def main():
     ap.add_argument("--ny", type=int, default=40)
     ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--reps", type=int, default=10)
+    ap.add_argument("--mode", default="one_step", choices=["one_step", "autoregressive"],
+                    help="autoregressive: full step only (skipping kernels would degenerate the geometry)")
     args = ap.parse_args()
     from sgnn_b200 import engine as ENG
     from sgnn_b200.single_scale import evaluate as EV
@@ -34,7 +36,7 @@ def main():
     traj, stats, radius = bench.make_case(seed=7, nx=args.nx, ny=args.ny, nsteps=args.steps)
     sim = bench.make_sim(stats, radius, dev)
     n, S = args.nx * args.ny, bench.S
-    plan = EV.RolloutPlan(sim, n, S + args.steps, S, 2, "one_step", dev, use_graph=False)
+    plan = EV.RolloutPlan(sim, n, S + args.steps, S, 2, args.mode, dev, use_graph=False)
     plan.traj.copy_(traj["positions"].to(dev))
     plan.launch_steps(0, 2)
     torch.cuda.synchronize()
@@ -59,6 +61,10 @@ def main():
 
     print(f"N={n}  us per step under graph replay (best of {args.reps})")
     print(f"  full step            {timed([]):8.2f}")
+    if args.mode == "autoregressive":
+        _, rg = sim._engine(n, dev)
+        print("  edges after the rollout", int(rg.csr.rowptr[-1].item()))
+        return
     for f in FAMILIES:
         print(f"  only {f:15s} {timed([x for x in FAMILIES if x != f]):8.2f}")
     for f in FAMILIES:

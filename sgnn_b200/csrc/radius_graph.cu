@@ -505,10 +505,24 @@ extern "C" int sgnn_debug_radius_timeline(unsigned long long* buf) {
   return SGNN_OK;
 }
 
-// single-cluster path for small systems; SGNN_RADIUS_MULTI=1 keeps every size on the general path (A/B)
+// Which path small systems take.  Measured at 4800 particles under graph replay (profiles/README.md, r01o): the
+// single-cluster kernel takes 18.6 us against 23.5 us for the nine launches on a regular, static geometry
+// (teacher-forced steps), but in an autoregressive rollout -- irregular cells, 30 k instead of 24 k edges -- the
+// whole step is 7 us SLOWER with it: a cluster is at most 16 SMs, and 4800 searches on 10 SMs lose against 38
+// CTAs on 38 SMs once the search phase is the long one.  So the general path is the default and the cluster
+// kernel is opt-in: SGNN_RADIUS_CLUSTER=1 or sgnn_radius_graph_mode(1).
+static int g_radius_mode = -1;
 static bool use_cluster_path(int n) {
-  static const bool multi = getenv("SGNN_RADIUS_MULTI") != nullptr;
-  return n <= kClMaxN && !multi;
+  if (g_radius_mode < 0) g_radius_mode = getenv("SGNN_RADIUS_CLUSTER") != nullptr ? 1 : 0;
+  return g_radius_mode == 1 && n <= kClMaxN;
+}
+
+// 0 = general nine-launch path for every size (default), 1 = single-cluster kernel for n <= 8192; returns the old mode
+extern "C" int sgnn_radius_graph_mode(int mode) {
+  if (g_radius_mode < 0) g_radius_mode = getenv("SGNN_RADIUS_CLUSTER") != nullptr ? 1 : 0;
+  const int old = g_radius_mode;
+  if (mode == 0 || mode == 1) g_radius_mode = mode;
+  return old;
 }
 
 extern "C" int sgnn_radius_graph_launches(int n, int max_neighbors) {

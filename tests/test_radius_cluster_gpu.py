@@ -1,15 +1,19 @@
-"""GPU: the single-cluster neighbour search (n <= 8192: one launch, phases separated by the hardware
-cluster barrier, hand-offs through distributed shared memory) against the oracle and the general
-nine-launch path -- edge sets must be bit-exact."""
-import os
-import subprocess
-import sys
-
+"""GPU: the opt-in single-cluster neighbour search (sgnn_radius_graph_mode(1); n <= 8192: one launch,
+phases separated by the hardware cluster barrier, hand-offs through distributed shared memory) against
+the oracle -- edge sets must be bit-exact, as on the default nine-launch path."""
 import numpy as np
 import pytest
 import torch
 
 pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(autouse=True)
+def cluster_mode():
+    from sgnn_b200 import _lib as L
+    old = L.lib().sgnn_radius_graph_mode(1)
+    yield
+    L.lib().sgnn_radius_graph_mode(old)
 
 
 def _edges(rg, pos, counts, r):
@@ -53,22 +57,13 @@ def test_shapes_vs_oracle(n, dim, counts, k, loop):
     assert np.array_equal(got, radius_graph_np(pos, 1.3, counts, loop, k))
 
 
-def test_general_path_still_matches_for_small_systems():
-    """SGNN_RADIUS_MULTI=1 (read once per process) keeps small systems on the nine-launch path."""
-    code = "\n".join([
-        "import numpy as np, torch",
-        "from sgnn_b200 import _lib as L",
-        "from sgnn_b200.engine import RadiusGraph",
-        "from sgnn_b200.single_scale.learned_simulator import example_ptr_of",
-        "from oracle.radius import radius_graph_np",
-        "assert L.lib().sgnn_radius_graph_launches(4800, 20) > 1",
-        "pos = np.random.default_rng(1).uniform(0, 40, (4800, 2)).astype(np.float32)",
-        "rg = RadiusGraph(4800, 20, True, torch.device('cuda'))",
-        "p = torch.as_tensor(pos).cuda()",
-        "csr = rg.build(p, 2, 2, example_ptr_of([4800], p.device), 1.2)",
-        "assert np.array_equal(csr.edge_index().cpu().numpy(), radius_graph_np(pos, 1.2, [4800], True, 20))",
-        "print('ok')"])
-    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    out = subprocess.run([sys.executable, "-c", code], cwd=root, env=dict(os.environ, SGNN_RADIUS_MULTI="1"),
-                         capture_output=True, text=True, timeout=300)
-    assert out.returncode == 0 and "ok" in out.stdout, out.stderr[-2000:]
+def test_default_is_the_general_path():
+    from oracle.radius import radius_graph_np
+    from sgnn_b200 import _lib as L
+    from sgnn_b200.engine import RadiusGraph
+    L.lib().sgnn_radius_graph_mode(0)
+    assert L.lib().sgnn_radius_graph_launches(4800, 20) > 1
+    pos = np.random.default_rng(1).uniform(0, 40, (4800, 2)).astype(np.float32)
+    rg = RadiusGraph(4800, 20, True, torch.device("cuda"))
+    got = _edges(rg, torch.as_tensor(pos).cuda(), [4800], 1.2)
+    assert np.array_equal(got, radius_graph_np(pos, 1.2, [4800], True, 20))
