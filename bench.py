@@ -191,7 +191,7 @@ def measure_edge_layer(sim, n, dev, reps=50):
     eng, rg = sim._engine(n, dev)
     ep, _, es = eng.blocks[0]
     csr = rg.csr
-    e = int(csr.rowptr[-1].item())
+    e = int(csr.rowptr[csr.n_nodes].item())
     for _ in range(5):
         ep.launch(csr, eng.e_tiles[es], eng.pq, eng.agg, eng.head)
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -223,7 +223,7 @@ def large_config(pk, dev, nx=2048, ny=512):
     prof = E.profile_summary()
     E.PROFILE = None
     eng, rg = sim._engine(n, dev)
-    e = int(rg.csr.rowptr[-1].item())
+    e = int(rg.csr.rowptr[rg.csr.n_nodes].item())
     step_ms = a.elapsed_time(b)
     out = {"particles": n, "edges": e, "ms_per_step": step_ms, "particle_steps_per_s": n / (step_ms * 1e-3),
            "kernels_ms": {k: {"launches": v[0], "mean_ms": v[1]} for k, v in prof.items()},

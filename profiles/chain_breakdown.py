@@ -63,7 +63,7 @@ def main():
     print(f"  full step            {timed([]):8.2f}")
     if args.mode == "autoregressive":
         _, rg = sim._engine(n, dev)
-        print("  edges after the rollout", int(rg.csr.rowptr[-1].item()))
+        print("  edges after the rollout", int(rg.csr.rowptr[rg.csr.n_nodes].item()))
         return
     for f in FAMILIES:
         print(f"  only {f:15s} {timed([x for x in FAMILIES if x != f]):8.2f}")

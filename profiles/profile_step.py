@@ -43,7 +43,7 @@ def main():
         torch.cuda.synchronize()
         print(f"step {k}: {a.elapsed_time(b):.3f} ms")
     _, rg = sim._engine(n, dev)
-    print("N", n, "E", int(rg.csr.rowptr[-1].item()))
+    print("N", n, "E", int(rg.csr.rowptr[rg.csr.n_nodes].item()))
 
 
 if __name__ == "__main__":

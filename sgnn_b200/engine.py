@@ -52,7 +52,7 @@ class Csr:
 
     def edge_index(self) -> torch.Tensor:
         """[2,E] int64 (one host sync: reads E)."""
-        e = int(self.rowptr[-1].item())
+        e = int(self.rowptr[self.n_nodes].item())
         return torch.stack([self.src[:e].long(), self.tgt[:e].long()])
 
 
@@ -68,16 +68,22 @@ class RadiusGraph:
         self.ws_bytes = nbytes
 
     def build(self, pos: torch.Tensor, pos_stride: int, dim: int, example_ptr: torch.Tensor,
-              radius: float):
-        """pos: tensor whose data_ptr is particle 0's most recent position."""
+              radius: float, n: Optional[int] = None):
+        """pos: tensor whose data_ptr is particle 0's most recent position.  n: particles of this call
+        (<= the capacity the buffers were sized for; the sharded rollout's local system changes size
+        at every ghost refresh)."""
+        n = self.n if n is None else n
+        if n > self.n:
+            raise L.SgnnError(f"RadiusGraph sized for {self.n} particles, got {n}")
+        self.csr.n_nodes = n
         if "radius_graph" in SKIP:
             return self.csr
         with _timed("radius_graph"):
           L.check(L.lib().sgnn_radius_graph_csr(
-            C.c_void_p(pos.data_ptr()), C.c_long(pos_stride), self.n, dim, L.ptr(example_ptr),
+            C.c_void_p(pos.data_ptr()), C.c_long(pos_stride), n, dim, L.ptr(example_ptr),
             example_ptr.numel() - 1, C.c_double(radius), self.k, int(self.loop), L.ptr(self.ws),
             C.c_size_t(self.ws_bytes), L.ptr(self.csr.rowptr), L.ptr(self.csr.src),
-            L.ptr(self.csr.tgt), L.stream_ptr()), launches=L.lib().sgnn_radius_graph_launches(self.n, self.k))
+            L.ptr(self.csr.tgt), L.stream_ptr()), launches=L.lib().sgnn_radius_graph_launches(n, self.k))
         return self.csr
 
 
@@ -301,10 +307,13 @@ class EpdEngine:
     def forward(self, *, pos_seq, pos_seq_stride: int, seq_len: int, csrs: List[Csr],
                 radii: List[float], vel_mean, vel_std, wall_max: float, wall_div: float,
                 types=None, emb=None, acc_mean=None, acc_std=None, next_pos=None,
-                next_pos_stride: int = 0, strain_out=None, feat_out=None, edge_feat_out=None):
+                next_pos_stride: int = 0, strain_out=None, feat_out=None, edge_feat_out=None,
+                n_active: Optional[int] = None):
         """Launches the whole forward on the current stream.  pos_seq: tensor whose data_ptr is
         particle 0's oldest frame of the window.  Returns the raw network output buffer."""
-        n, dim = self.n, self.dim
+        n, dim = (self.n if n_active is None else n_active), self.dim
+        if n > self.n:
+            raise L.SgnnError(f"engine sized for {self.n} nodes, got {n}")
         last_off = (seq_len - 1) * dim * 4
         last_pos_ptr = pos_seq.data_ptr() + last_off
         for k, (enc, csr) in enumerate(zip(self.edge_enc, csrs)):

@@ -211,6 +211,9 @@ def sharded_rollout(simulator, positions_owned: torch.Tensor, nsteps: int, comm:
         ptr = torch.tensor([0, nloc], dtype=torch.int32, device=dev)
         st_buf = torch.empty(nloc, dtype=torch.float32, device=dev)
 
+        if k == 0:       # kernel plans and latent buffers with headroom: the local system changes size at every refresh
+            simulator._reserve(nloc + max(nloc // 16, 1024), dev)
+
         def step():
             return simulator._step(win[:, :s], None, types, next_pos=win[:, s], strain=st_buf, example_ptr=ptr)
 

@@ -75,18 +75,28 @@ class LearnedSimulator(nn.Module):
             self._stats_dev = (device, {k: {kk: f(vv) for kk, vv in v.items()} for k, v in s.items()})
         return self._stats_dev[1]
 
-    def _engine(self, n: int, device):
-        """(EpdEngine, RadiusGraph) for n particles; rebuilt when parameters change."""
-        key = (n, device, self.precision)
+    def _engine(self, n: int, device, capacity: int = 0):
+        """(EpdEngine, RadiusGraph) able to run n particles; rebuilt when parameters change.  An engine
+        sized for somewhat more particles is reused (run with n_active = n): building one packs every
+        weight image and allocates all latent buffers, which the sharded rollout cannot afford at every
+        ghost refresh (_reserve)."""
         ver = params_version(self.parameters())
+        key = (n, device, self.precision)
         hit = self._engines.get(key)
         if hit is None or hit[0] != ver:
+            for (cap, d, pr), h in self._engines.items():
+                if d == device and pr == self.precision and h[0] == ver and n <= cap <= n + max(n // 4, 4096):
+                    return h[1], h[2]
+        if hit is None or hit[0] != ver:
+            size = max(n, capacity)
+            key = (size, device, self.precision)
+            old = self._engines.get(key)
             epd = self._encode_process_decode
             blocks = [(g.edge_fn, g.node_fn, 0, l) for l, g in enumerate(epd._processor.gnn_stacks)]
-            rg = hit[2] if hit is not None else RadiusGraph(n, MAX_NUM_NEIGHBORS, True, device)
+            rg = old[2] if old is not None else RadiusGraph(size, MAX_NUM_NEIGHBORS, True, device)
             eng = EpdEngine(epd._encoder.node_fn, [epd._encoder.edge_fn], blocks, epd._decoder.node_fn,
                             k_node_in=self._nnode_in, dim=self._particle_dimensions,
-                            latent=self._latent_dim, n_nodes=n, edge_caps=[rg.csr.max_edges],
+                            latent=self._latent_dim, n_nodes=size, edge_caps=[rg.csr.max_edges],
                             precision=self.precision, device=device)
             hit = (ver, eng, rg)
             self._engines.pop(key, None)
@@ -94,6 +104,11 @@ class LearnedSimulator(nn.Module):
                 self._engines.pop(next(iter(self._engines)))
             self._engines[key] = hit
         return hit[1], hit[2]
+
+    def _reserve(self, capacity: int, device):
+        """Kernel plans and buffers for up to `capacity` particles (reused for any smaller system)."""
+        self._stats(device)
+        self._engine(capacity, device, capacity)
 
     def _prepare(self, n: int, device):
         """Build / refresh kernel plans outside a CUDA-graph capture."""
@@ -117,9 +132,9 @@ class LearnedSimulator(nn.Module):
         if example_ptr is None:
             example_ptr = example_ptr_of(nparticles_per_example, dev)
         stride = seq.stride(0)
-        csr = rg.build(seq[0, s - 1], stride, dim, example_ptr, float(self._connectivity_radius))
+        csr = rg.build(seq[0, s - 1], stride, dim, example_ptr, float(self._connectivity_radius), n=n)
         use_emb = self._nparticle_types > 1
-        eng.forward(pos_seq=seq, pos_seq_stride=stride, seq_len=s, csrs=[csr],
+        eng.forward(pos_seq=seq, pos_seq_stride=stride, seq_len=s, csrs=[csr], n_active=n,
                     radii=[float(self._connectivity_radius)], vel_mean=st["velocity"]["mean"],
                     vel_std=st["velocity"]["std"], wall_max=float(self._connectivity_radius),
                     wall_div=1.0, types=particle_types if use_emb else None,

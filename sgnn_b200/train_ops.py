@@ -40,7 +40,7 @@ class TrainGraph:
 
     @staticmethod
     def from_csr(csr) -> "TrainGraph":
-        e = int(csr.rowptr[-1].item())          # the one host sync of a training step
+        e = int(csr.rowptr[csr.n_nodes].item())   # the one host sync of a training step
         return TrainGraph(csr.rowptr, csr.src, csr.tgt, csr.n_nodes, e)
 
     def by_source(self):
