@@ -219,9 +219,10 @@ def sharded_rollout(simulator, positions_owned: torch.Tensor, nsteps: int, comm:
 
         graph = None
         for j in range(m):
-            if j == 1 and use_graph and m > 2:
-                # the refresh's first step ran eagerly (lazy initialisation, kernel plans for this size,
-                # the step-0 edge list); the remaining ones replay one captured step
+            if use_graph and graph is None and m - j > 1 and (j == 1 or (j == 0 and k > 0)):
+                # the very first step of the rollout runs eagerly (lazy initialisation, the step-0 edge list);
+                # every other step replays the step captured once per refresh
+                simulator._prepare(nloc, dev)                          # never build kernel plans inside a capture
                 graph = torch.cuda.CUDAGraph()
                 cap = torch.cuda.Stream(device=dev)                    # (torch.cuda.graph() would also empty the
                 cap.wait_stream(torch.cuda.current_stream())           #  allocator cache at every refresh)

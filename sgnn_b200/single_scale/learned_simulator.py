@@ -112,6 +112,7 @@ class LearnedSimulator(nn.Module):
 
     def _prepare(self, n: int, device):
         """Build / refresh kernel plans outside a CUDA-graph capture."""
+        self._stats(device)
         self._engine(n, device)
 
     def _check_positions(self, position_sequence):
