@@ -7,15 +7,16 @@
 // Split of the first Linear: the receiver term is per NODE (P = x W1a^T + b1, written by the node
 // kernel, read here with near-broadcast loads because edges are receiver-sorted); the sender term
 // and the edge term go through the tensor core as ONE K = 128 product [e0 | x_src] [W1c | W1b]^T.
-// The x_src rows are gathered by the TMA unit (tile::gather4 on a tensor map over the TF32-rounded
-// node latents) straight into the swizzled operand layout: no thread issues a gather load, the L1
-// pipe -- the busiest unit of the previous kernel (profiles/README.md r01f: 64 %) -- carries only
-// the P loads and the segmented-sum scratch.
+// The x_src rows are gathered with cp.async (16 bytes per lane, per-lane addresses) straight into the
+// swizzled operand layout by two producer warps, so the epilogue warps issue no gather load; TMA
+// tile::gather4 does the same job and is kept behind a debug flag, but it was slower end to end
+// (profiles/README.md r01h).  The per-receiver sums are an in-register segmented shuffle scan
+// over the 32 rows a warp holds (no shared-memory scratch).
 //
 // Roles (640 threads, one persistent CTA per SM; registers re-split with setmaxnreg):
 //   warps 0-15  four epilogue groups of 128 threads; group g owns TMEM columns [128g, 128g + 128)
 //               (accumulator 0 / hidden activations in place, accumulator 1) and every 4th tile
-//   warps 16,19 producers: a tile's e0 image by TMA bulk copy and its x_src K-blocks by TMA gather4
+//   warps 16,19 producers: a tile's e0 image by TMA bulk copy and its x_src K-blocks by cp.async
 //               into one of two 64 KB tile stages
 //   warps 17,18 one thread each issues the tcgen05.mma of the first / the second GEMM, so that the
 //               second GEMM of tile t never waits behind the loads of tile t + 1
@@ -36,10 +37,6 @@ constexpr int kWsSlotBytes = kTileRows * kKBlockBytes;     // 16 KB: 128 rows x 
 constexpr int kWsStageBytes = 4 * kWsSlotBytes;            // one tile: e0 K-blocks 0,1 then x_src K-blocks 0,1
 constexpr int kWsStages = 2;
 constexpr int kWsVecBytes = 1024;                          // resident part of the blob's vector region
-constexpr int kWsScrRows = 16;
-constexpr int kWsScrStride = 36;
-constexpr int kWsScrFloats = kWsScrRows * kWsScrStride;
-constexpr int kWsScrStride2 = 68;                          // 8-row passes over all 64 columns: 64 + 4 pad (8 x 68 <= 16 x 36)
 
 struct WsGroup {
   uint64_t acc0_ready, hid_ready, acc1_ready, region_free;
@@ -55,18 +52,17 @@ struct WsMisc {
   int pad;
   WsGroup g[kWsGroups];
 };
-// Shared memory: [vectors 1 KB | weight images | 2 tile stages | scan scratch | barriers + pieces].
+// Shared memory: [vectors 1 KB | weight images | 2 tile stages | barriers + pieces].
 // Only the first kWsVecBytes of the blob's 8 KB vector region are used by this layer (b2, gamma,
 // beta) and only they are staged; the images follow at their blob offset minus kWsImgShift.
 constexpr int kWsImgShift = SGNN_VEC_REGION_BYTES - kWsVecBytes;
 struct WsSmem {
-  int ring, scratch, misc, total;
+  int ring, misc, total;
 };
 __host__ __device__ inline WsSmem edge_ws_smem(int blob_bytes) {
   WsSmem s;
   s.ring = align_up(blob_bytes - kWsImgShift, 1024);
-  s.scratch = s.ring + kWsStages * kWsStageBytes;
-  s.misc = align_up(s.scratch + 16 * kWsScrFloats * 4, 16);
+  s.misc = align_up(s.ring + kWsStages * kWsStageBytes, 16);
   s.total = s.misc + (int)sizeof(WsMisc) + 1024;
   return s;
 }
@@ -266,7 +262,7 @@ __device__ __forceinline__ void ws_mma1(const SgnnEdgeLayerParams& p, uint32_t s
 __device__ __forceinline__ float2 f2(float a, float b) { return make_float2(a, b); }
 
 __device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const float* blob_f, WsMisc* misc,
-                                            float* scr, int g, int wt, int n_my, int n_edges, uint32_t tmem) {
+                                            int g, int wt, int n_my, int n_edges, uint32_t tmem) {
   constexpr int W = kWsW;
   constexpr unsigned FULL = 0xffffffffu;
   const int lane = wt & 31, wq = wt >> 5;
@@ -555,8 +551,7 @@ edge_layer_ws_kernel(const SgnnEdgeLayerParams p, const __grid_constant__ CUtens
   if (warp < 16) {
     asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kWsEpiRegs));
     mbar_wait(&misc->bar_w, 0);
-    float* scr = reinterpret_cast<float*>(smem + L.scratch) + warp * kWsScrFloats;
-    ws_epilogue(p, reinterpret_cast<const float*>(smem), misc, scr, warp >> 2, tid & 127, n_my, n_edges, tmem);
+    ws_epilogue(p, reinterpret_cast<const float*>(smem), misc, warp >> 2, tid & 127, n_my, n_edges, tmem);
   } else {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kWsAuxRegs));
   }
