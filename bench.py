@@ -265,7 +265,7 @@ def _train_config(dev, rank, world, steps, warmup, samples, matmul):
     from sgnn_b200 import training
     batch, stats, radius = make_train_batch(dev, samples, seed0=100 + 1000 * rank)
     sim = make_sim(stats, radius, dev).train()
-    opt = torch.optim.Adam(sim.parameters(), lr=1e-4)
+    opt = torch.optim.Adam(sim.parameters(), lr=1e-4, fused=True)
     reducer = training.FlatGradAllReduce(sim.parameters()) if world > 1 else None
     n_glob = batch["positions"].shape[0] * world
     gen = torch.Generator(device=dev).manual_seed(2 + rank)
@@ -291,7 +291,8 @@ def _train_config(dev, rank, world, steps, warmup, samples, matmul):
             "particles_per_step_global": n_glob, "samples_per_s": samples * world * 1e3 / ms,
             "loss_first": losses[0].item() * world, "loss_last": losses[-1].item() * world,
             "collective": "one flat fp32 gradient allreduce (NCCL)" if world > 1 else "none (1 GPU)",
-            "gemm": "cuBLAS " + matmul, "graph_ops": "sgnn_b200 CUDA (deterministic gather / segment-sum / LayerNorm)"}
+            "gemm": "cuBLAS " + matmul + " (forward, input gradients); weight / bias gradients: sgnn_b200 split-row fp32 kernel",
+            "graph_ops": "sgnn_b200 CUDA (deterministic gather / segment-sum / LayerNorm)", "optimizer": "Adam (fused)"}
 
 
 def multiscale_config(dev, rank, steps=5):

@@ -93,6 +93,13 @@ int sgnn_layer_norm_fwd(const float* x, long n_rows, int width, const float* gam
 int sgnn_layer_norm_bwd(const float* dy, const float* x, const float* mean, const float* rstd,
                         const float* gamma, long n_rows, int width, float* dx, float* dgamma, float* dbeta,
                         void* workspace, size_t workspace_bytes, void* stream);
+/* Weight and bias gradients of a Linear layer of the training path (autograd of every build_mlp Linear,
+ * graph_network.py:21-58): dw[out][in] = sum_r dy[r][out] x[r][in], db[out] = sum_r dy[r][out] (db may be
+ * NULL).  dy [n_rows, out_features] and x [n_rows, in_features] are contiguous row-major fp32.  Rows are
+ * split over the grid, partial tiles are added in a fixed order: deterministic.                      */
+size_t sgnn_linear_wgrad_workspace_bytes(long n_rows, int out_features, int in_features);
+int sgnn_linear_wgrad(const float* dy, const float* x, long n_rows, int out_features, int in_features,
+                      float* dw, float* db, void* workspace, size_t workspace_bytes, void* stream);
 int sgnn_node_features(const float* pos_seq, long stride, int n, int seq_len, int dim,
                        const float* vel_mean, const float* vel_std, float wall_offset, float wall_max,
                        float wall_div, float* out, long ld_out, void* stream);

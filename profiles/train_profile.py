@@ -18,7 +18,7 @@ def main():
     dev = torch.device("cuda", 0)
     batch, stats, radius = bench.make_train_batch(dev, 8, seed0=100)
     sim = bench.make_sim(stats, radius, dev).train()
-    opt = torch.optim.Adam(sim.parameters(), lr=1e-4)
+    opt = torch.optim.Adam(sim.parameters(), lr=1e-4, fused=True)
     gen = torch.Generator(device=dev).manual_seed(2)
     n = batch["positions"].shape[0]
     for _ in range(3):

@@ -78,6 +78,7 @@ def lib():
         _lib.sgnn_edge_encoder_smem_bytes.restype = C.c_size_t
         _lib.sgnn_node_smem_bytes.restype = C.c_size_t
         _lib.sgnn_layer_norm_bwd_workspace_bytes.restype = C.c_size_t
+        _lib.sgnn_linear_wgrad_workspace_bytes.restype = C.c_size_t
     return _lib
 
 

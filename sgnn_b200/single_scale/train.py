@@ -140,7 +140,7 @@ def train(simulator, metadata: dict, device, config: dict, log_every: int = 10, 
     """Training loop (train.py:185-428).  Returns (last step, lowest validation loss)."""
     rank = dist.get_rank() if dist.is_initialized() else 0
     world = dist.get_world_size() if dist.is_initialized() else 1
-    optimizer = torch.optim.Adam(simulator.parameters(), lr=config["lr_init"])
+    optimizer = torch.optim.Adam(simulator.parameters(), lr=config["lr_init"], fused=True)   # one kernel per step instead of ~10 foreach launches
     step, lowest = 0, float("inf")
     if config.get("model_file") is not None:
         simulator, step, optimizer, lowest = load_model(simulator, device, config)

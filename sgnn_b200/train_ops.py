@@ -143,6 +143,87 @@ class _LayerNorm(torch.autograd.Function):
         return dx, dgamma, dbeta, None
 
 
+_wgrad_ws = {}          # device -> persistent workspace (kernels of one stream run in order: safe to reuse)
+
+
+def _wgrad_workspace(nbytes: int, device) -> torch.Tensor:
+    ws = _wgrad_ws.get(device)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.empty(max(nbytes, 1 << 24), dtype=torch.uint8, device=device)
+        _wgrad_ws[device] = ws
+    return ws
+
+
+class _Linear(torch.autograd.Function):
+    """y = x W^T + b.  Forward and input gradient are plain library GEMMs; the weight and bias gradients
+    -- 64 x 64 outputs summed over up to 200 k rows, which cuBLAS runs inside one or two CTAs -- come from
+    csrc/train_linear.cu (rows split over the grid, fixed-order reduction: deterministic)."""
+
+    @staticmethod
+    def forward(ctx, x, w, b):
+        ctx.save_for_backward(x, w)
+        ctx.has_bias = b is not None
+        return F.linear(x, w, b)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w = ctx.saved_tensors
+        if dy.dtype != torch.float32 or not dy.is_contiguous():
+            dy = _f32(dy)
+        dx = dy @ w if ctx.needs_input_grad[0] else None
+        dw = db = None
+        if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
+            xc = x if (x.dtype == torch.float32 and x.is_contiguous()) else _f32(x)
+            n, k = xc.shape
+            m = dy.shape[1]
+            dev = dy.device
+            dw = torch.empty(m, k, dtype=torch.float32, device=dev)
+            db = torch.empty(m, dtype=torch.float32, device=dev) if ctx.has_bias else None
+            fn, fn_bytes = _wgrad_fns()
+            ws = _wgrad_workspace(fn_bytes(n, m, k), dev)
+            L.check(fn(dy.data_ptr(), xc.data_ptr(), n, m, k, dw.data_ptr(), db.data_ptr() if db is not None else None,
+                       ws.data_ptr(), ws.numel(), torch.cuda.current_stream().cuda_stream), launches=2)
+        return dx, dw, db
+
+
+_wgrad_fn = None
+
+
+def _wgrad_fns():
+    """The two C entries with their argtypes declared once (this call sits on the backward path of 41 Linears
+    per step: no per-call ctypes object construction)."""
+    global _wgrad_fn
+    if _wgrad_fn is None:
+        lib = L.lib()
+        f, g = lib.sgnn_linear_wgrad, lib.sgnn_linear_wgrad_workspace_bytes
+        f.argtypes = [C.c_void_p, C.c_void_p, C.c_long, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                      C.c_size_t, C.c_void_p]
+        g.argtypes = [C.c_long, C.c_int, C.c_int]
+        _wgrad_fn = (f, g)
+    return _wgrad_fn
+
+
+def linear(x: torch.Tensor, w: torch.Tensor, b: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """F.linear on [rows, in] activations with the weight gradient on the CUDA path above."""
+    if x.dim() != 2 or not x.is_cuda or not (torch.is_grad_enabled() and (w.requires_grad or (b is not None and b.requires_grad))):
+        return F.linear(x, w, b)
+    return _Linear.apply(x, w, b)
+
+
+def apply_mlp(seq_mlp, h, skip_first_linear: bool = False):
+    """A build_mlp Sequential (Linear / activation children) with its Linears through linear()."""
+    skip = skip_first_linear
+    for m in seq_mlp.children():
+        if isinstance(m, torch.nn.Linear):
+            if skip:
+                skip = False
+                continue
+            h = linear(h, m.weight, m.bias)
+        else:
+            h = m(h)
+    return h
+
+
 def layer_norm(ln: torch.nn.LayerNorm, h: torch.Tensor) -> torch.Tensor:
     """ln(h) for a reference nn.LayerNorm module on [rows, width] activations."""
     w = h.shape[-1]
@@ -154,7 +235,7 @@ def layer_norm(ln: torch.nn.LayerNorm, h: torch.Tensor) -> torch.Tensor:
 
 def mlp_ln(seq: torch.nn.Sequential, h: torch.Tensor) -> torch.Tensor:
     """Sequential(build_mlp, LayerNorm) as the encoders use it."""
-    return layer_norm(seq[1], seq[0](h))
+    return layer_norm(seq[1], apply_mlp(seq[0], h))
 
 
 def gather_add(p, q, graph):
@@ -192,13 +273,7 @@ def edge_features(last_pos: torch.Tensor, pos_stride: int, dim: int, radius: flo
 
 def _rest_of_mlp(seq_mlp, h):
     """Apply everything after the first Linear of a build_mlp Sequential (Act-0, NN-1, ...)."""
-    first = True
-    for m in seq_mlp.children():
-        if first and isinstance(m, torch.nn.Linear):
-            first = False
-            continue
-        h = m(h)
-    return h
+    return apply_mlp(seq_mlp, h, skip_first_linear=True)
 
 
 def interaction_block(edge_fn, node_fn, x, e, graph: TrainGraph):
@@ -206,14 +281,14 @@ def interaction_block(edge_fn, node_fn, x, e, graph: TrainGraph):
     Returns (x + node update, e + e): the reference's update() hands back its input edge latent."""
     nn_in = x.shape[1]
     w1 = linears_of(edge_fn[0])[0]
-    p = F.linear(x, w1.weight[:, :nn_in], w1.bias)                # x_target block (+ bias)
-    q = F.linear(x, w1.weight[:, nn_in:2 * nn_in])                # x_source block
-    pre = F.linear(e, w1.weight[:, 2 * nn_in:]) + gather_add(p, q, graph)
+    p = linear(x, w1.weight[:, :nn_in], w1.bias)                # x_target block (+ bias)
+    q = linear(x, w1.weight[:, nn_in:2 * nn_in])                # x_source block
+    pre = linear(e, w1.weight[:, 2 * nn_in:]) + gather_add(p, q, graph)
     msg = layer_norm(edge_fn[1], _rest_of_mlp(edge_fn[0], pre))   # ... -> LayerNorm
     agg = segment_sum(msg, graph)
     v1 = linears_of(node_fn[0])[0]
     na = agg.shape[1]
-    pre_n = F.linear(agg, v1.weight[:, :na]) + F.linear(x, v1.weight[:, na:], v1.bias)
+    pre_n = linear(agg, v1.weight[:, :na]) + linear(x, v1.weight[:, na:], v1.bias)
     upd = layer_norm(node_fn[1], _rest_of_mlp(node_fn[0], pre_n))
     return x + upd, e + e
 
@@ -225,4 +300,4 @@ def epd_forward(node_encoder, edge_encoders: List, blocks: List, decoder, nf, ef
     es = [mlp_ln(enc, ef) for enc, ef in zip(edge_encoders, efs)]
     for edge_fn, node_fn, k in blocks:
         x, es[k] = interaction_block(edge_fn, node_fn, x, es[k], graphs[k])
-    return decoder(x)
+    return apply_mlp(decoder, x) if isinstance(decoder, torch.nn.Sequential) else decoder(x)

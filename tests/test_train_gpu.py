@@ -139,6 +139,44 @@ def test_layer_norm_kernels_match_aten(width, rows):
     assert torch.equal(x.grad, got[1]) and torch.equal(ln.weight.grad, got[2]) and torch.equal(ln.bias.grad, got[3])
 
 
+@pytest.mark.parametrize("rows,m,k", [(0, 64, 64), (1, 64, 64), (33, 64, 64), (20011, 64, 64), (4097, 64, 30),
+                                      (3001, 64, 3), (2500, 2, 64), (1500, 128, 128), (777, 96, 130), (1000, 7, 5),
+                                      (150000, 64, 64)])
+@pytest.mark.parametrize("bias", [True, False])
+def test_linear_weight_gradient_kernel(rows, m, k, bias):
+    """csrc/train_linear.cu: dW = dy^T x and db = column sums of dy against fp64, input gradient against
+    F.linear's, weight slices (non-contiguous views) as the interaction blocks pass them, bit-reproducible."""
+    import torch.nn.functional as F
+    from sgnn_b200 import train_ops as T
+    g = torch.Generator().manual_seed(rows + 7 * m + k)
+    full = torch.randn(m, k + 5, generator=g).cuda().requires_grad_()
+    b = torch.randn(m, generator=g).cuda().requires_grad_() if bias else None
+    x = (torch.randn(rows, k, generator=g) + 0.25).cuda().requires_grad_()
+    up = torch.randn(rows, m, generator=g).cuda()
+
+    def run():
+        full.grad = x.grad = None
+        if b is not None:
+            b.grad = None
+        y = T.linear(x, full[:, 2:2 + k], b)
+        (y * up).sum().backward()
+        return y.detach(), x.grad.clone(), full.grad.clone(), (b.grad.clone() if b is not None else None)
+
+    y, dx, dw, db = run()
+    assert torch.equal(y, F.linear(x.detach(), full.detach()[:, 2:2 + k], b.detach() if b is not None else None))
+    w64 = full.detach().double()[:, 2:2 + k]
+    want_dw = up.double().t() @ x.detach().double()
+    scale = max(1.0, float(want_dw.abs().max())) if rows else 1.0
+    assert (dw[:, 2:2 + k].double() - want_dw).abs().max().item() <= 2e-6 * scale + 1e-5
+    assert dw[:, :2].abs().max().item() == 0 and dw[:, 2 + k:].abs().max().item() == 0
+    assert torch.allclose(dx.double(), up.double() @ w64, rtol=1e-5, atol=1e-4)
+    if bias:
+        want_db = up.double().sum(0)
+        assert (db.double() - want_db).abs().max().item() <= 1e-5 * max(1.0, rows ** 0.5)
+    again = run()
+    assert torch.equal(again[2], dw) and (db is None or torch.equal(again[3], db))
+
+
 def test_tf32_matmul_mode_of_train_step_stays_close():
     """training.train_step(matmul="tf32"): same loss to 1e-3 relative, the global flag is restored."""
     from sgnn_b200 import training
