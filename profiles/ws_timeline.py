@@ -35,6 +35,6 @@ for flags in [int(a) for a in (sys.argv[1:] or ["0"])]:
     for i in list(range(0, 12)) + list(range(100, 112)):
         r = [(int(x) - t0) / 1.9e3 if int(x) else float("nan") for x in t[i]]   # SM clocks at ~1.9 GHz -> us
         print(f"tile {i:3d} g{i % 4}: region free {r[0]:8.2f} | stage full {r[1]:8.2f} | MMA0 issued {r[2]:8.2f} | hid_ready seen "
-              f"{r[5]:8.2f} || epilogue: acc0 seen {r[6]:8.2f} | tile done {r[7]:8.2f} || producer 0: e0 slots free {r[8]:8.2f} "
+              f"{r[5]:8.2f} || epilogue: acc0 seen {r[6]:8.2f} | acc1 seen {r[3]:8.2f} | LayerNorm done {r[4]:8.2f} | sums written {r[11]:8.2f} | tile done {r[7]:8.2f} || producer 0: e0 slots free {r[8]:8.2f} "
               f"gather slot free {r[9]:8.2f} issued {r[10]:8.2f} | producer 1: free {r[13]:8.2f} issued {r[14]:8.2f}")
 L.check(L.lib().sgnn_debug_ws_flags(0))

@@ -87,8 +87,8 @@ __device__ __forceinline__ void ws_stamp(int tile_i, int k) {
 }
 
 // ---------------------------------------------------------------------------------- producers
-// Two warps fill a stage: `part` 0 = sender K-block 0, `part` 1 = the tile's e0 image (one 32 KB TMA
-// bulk copy) + sender K-block 1.  Sender rows are gathered with cp.async (16 bytes per lane, 8 lanes
+// Two warps fill a stage: `part` 0 = sender K-block 0, `part` 1 = sender K-block 1; the tile's e0 image
+// (one 32 KB TMA bulk copy) is issued by the two in turn.  Sender rows are gathered with cp.async (16 bytes per lane, 8 lanes
 // per 128-byte row segment, 4 rows per instruction, L2 -> shared memory without registers), written
 // straight into the SWIZZLE_128B operand layout; every lane's copies arrive on the stage's mbarrier.
 // TMA tile::gather4 does the same job in one instruction per 4 rows but takes its operands from
@@ -139,8 +139,11 @@ __device__ __forceinline__ void ws_producer(const SgnnEdgeLayerParams& p, const 
       for (int c = 0; c < 4; ++c) rows_nx[c] = (i + 1 < n_my && e0 + c * 32 + lane < n_edges) ? __ldg(p.src + e0 + c * 32 + lane) : 0;
     }
     const int st = i & 1, use = i >> 1;
+    // The tile's e0 image (two waits, expect_tx, one bulk copy: ~0.65 us of a producer's 2.2 us per tile in the
+    // 1M timeline, r01p) is issued by the two producers in turn, so neither carries it on every tile.
+    const bool do_e0 = part == st;
     if (use > 0) {      // a K-block slot is free as soon as ITS four MMAs are done: refills start mid-tile
-      if (part == 1) {
+      if (do_e0) {
         mbar_wait_spin(&misc->empty[st][0], (uint32_t)(use - 1) & 1u);
         mbar_wait_spin(&misc->empty[st][1], (uint32_t)(use - 1) & 1u);
       }
@@ -150,12 +153,12 @@ __device__ __forceinline__ void ws_producer(const SgnnEdgeLayerParams& p, const 
     uint64_t* full = &misc->full[st];
     char* dst = stage + (2 + part) * kWsSlotBytes;
     if (use > 0 && (flags & 3)) mbar_wait_spin(&misc->empty[st][2 + part], (uint32_t)(use - 1) & 1u);
-    if (part == 1 || (flags & 3)) {
+    if (do_e0 || (flags & 3)) {
       if (elect_one()) {
-        uint32_t tx = part == 1 ? 2 * kWsSlotBytes : 0;
+        uint32_t tx = do_e0 ? 2 * kWsSlotBytes : 0;
         if (flags & 3) tx += kWsSlotBytes;
         mbar_arrive_expect_tx(full, tx);
-        if (part == 1)
+        if (do_e0)
           tma_bulk_g2s(stage, reinterpret_cast<const char*>(p.e_tiles) + tile * (2 * kWsSlotBytes), 2 * kWsSlotBytes, full);
         if (flags & 1)
           tma_bulk_g2s(dst, reinterpret_cast<const char*>(p.e_tiles) + tile * (2 * kWsSlotBytes) + part * kWsSlotBytes,
@@ -191,8 +194,8 @@ __device__ __forceinline__ void ws_producer(const SgnnEdgeLayerParams& p, const 
     ws_stamp(i, 10 + 4 * part);
     if (!(flags & 3)) {
       cp_async_arrive_noinc(full);       // counts once this lane's copies have landed
-    } else if (part == 1 || lane != 0) {
-      mbar_arrive(full);                 // same arrival count as the cp.async path (part 0: lane 0 arrived with expect_tx)
+    } else if (do_e0 || lane != 0) {
+      mbar_arrive(full);                 // same arrival count as the cp.async path (the warp without e0: lane 0 arrived with expect_tx)
     }
   }
 }

@@ -16,10 +16,11 @@
 // fp32 FFMA on purpose: the gradient parity tests pin the fp32 path against the reference in fp64.
 // Bytes: reads 4 (M + K) per row once (M x K beyond 64 x 64: each tile re-reads its operand slabs);
 // flops: 2 * 64 * 64 per row and tile -- 16 flops per byte, above the fp32 SIMT ridge of B200
-// (~72 TFLOP/s / 6.5 TB/s = 11).  Measured (profiles/README.md r01p): 40 TFLOP/s at 1M rows, 29 at 190 k
-// rows (53 us against 293 us for torch.mm + sum), both thread layouts alike: every FFMA operand comes out
-// of shared memory (16 floats per 64 FFMA and lane), so the shared-memory pipe and the FFMA pipe are
-// loaded about equally and neither reaches its peak.
+// (~72 TFLOP/s / 6.5 TB/s = 11).  Measured (profiles/README.md r01p): 45 TFLOP/s at 1M rows, 33 at 190 k
+// rows (47 us against 293 us for torch.mm + sum).  Every FFMA operand comes out of shared memory (16
+// floats per 64 FMA and lane = 16 pipe cycles per warp and row, as many as 64 FFMA take to issue), so the
+// product is issued as packed FFMA2 and the shared-memory pipe is the loaded unit; what is left between
+// the measured rate and that bound is the per-chunk hand-off (wait, barrier, 16 cp.async per thread).
 #include "common.cuh"
 
 namespace sgnn {
@@ -102,12 +103,14 @@ linear_wgrad_kernel(const float* __restrict__ dy, const float* __restrict__ x, l
     __syncthreads();
   }
 
-  float acc[8][4 * JH];
+  // accumulators as fp32 pairs: one packed FFMA2 (two IEEE fp32 FMAs, same results as two FFMA) per pair
+  // halves the issue slots of the product, which leaves the shared-memory pipe as the only loaded unit
+  float2 acc[8][2 * JH];
   float bsum = 0.f;
 #pragma unroll
   for (int i = 0; i < 8; ++i)
 #pragma unroll
-    for (int j = 0; j < 4 * JH; ++j) acc[i][j] = 0.f;
+    for (int j = 0; j < 2 * JH; ++j) acc[i][j] = make_float2(0.f, 0.f);
 
 #pragma unroll
   for (int s = 0; s < kWgStages - 1; ++s) {
@@ -135,16 +138,19 @@ linear_wgrad_kernel(const float* __restrict__ dy, const float* __restrict__ x, l
       const float4 a0 = *reinterpret_cast<const float4*>(ds + r * kWgTile);
       const float4 a1 = *reinterpret_cast<const float4*>(ds + r * kWgTile + 32);
       const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-      float b[4 * JH];
+      float2 b[2 * JH];
 #pragma unroll
       for (int h = 0; h < JH; ++h) {
         const float4 bv = *reinterpret_cast<const float4*>(xs + r * kWgTile + 32 * h);
-        b[4 * h] = bv.x; b[4 * h + 1] = bv.y; b[4 * h + 2] = bv.z; b[4 * h + 3] = bv.w;
+        b[2 * h] = make_float2(bv.x, bv.y);
+        b[2 * h + 1] = make_float2(bv.z, bv.w);
       }
 #pragma unroll
-      for (int i = 0; i < 8; ++i)
+      for (int i = 0; i < 8; ++i) {
+        const float2 aa = make_float2(a[i], a[i]);
 #pragma unroll
-        for (int j = 0; j < 4 * JH; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+        for (int j = 0; j < 2 * JH; ++j) acc[i][j] = __ffma2_rn(aa, b[j], acc[i][j]);
+      }
     }
     if (BIAS && tid < kWgTile) {
       const float* dc = sm[c % kWgStages][0] + tid;
@@ -166,11 +172,11 @@ linear_wgrad_kernel(const float* __restrict__ dy, const float* __restrict__ x, l
       const int k = k0 + h * 32 + 4 * tx;
       if (vec_out && k + 3 < K) {
         *reinterpret_cast<float4*>(out + (long)m * K + k) =
-            make_float4(acc[i][4 * h], acc[i][4 * h + 1], acc[i][4 * h + 2], acc[i][4 * h + 3]);
+            make_float4(acc[i][2 * h].x, acc[i][2 * h].y, acc[i][2 * h + 1].x, acc[i][2 * h + 1].y);
       } else {
 #pragma unroll
         for (int j = 0; j < 4; ++j)
-          if (k + j < K) out[(long)m * K + k + j] = acc[i][4 * h + j];
+          if (k + j < K) out[(long)m * K + k + j] = (j & 1) ? acc[i][2 * h + (j >> 1)].y : acc[i][2 * h + (j >> 1)].x;
       }
     }
   }
@@ -248,13 +254,16 @@ extern "C" int sgnn_linear_wgrad(const float* dy, const float* x, long n_rows, i
   const int vec_x = (K & 3) == 0 && ((uintptr_t)x & 15) == 0;
   float* part = (float*)workspace;
   const dim3 grid(p.splits, p.tiles);
-  // 128 threads: same throughput as the 64-thread layout on long inputs, ~15 % faster on 38 400 rows
-  if (db)
-    linear_wgrad_kernel<128, true><<<grid, 128, 0, st>>>(dy, x, n_rows, M, K, p.chunks_per_split, vec_dy, vec_x, part,
-                                                         p.part_stride);
-  else
-    linear_wgrad_kernel<128, false><<<grid, 128, 0, st>>>(dy, x, n_rows, M, K, p.chunks_per_split, vec_dy, vec_x, part,
-                                                          p.part_stride);
+  // Thread layout (r01p, wgrad_micro): 8 x 8 outputs per thread is ~10 % faster once every CTA walks many
+  // chunks (190 k rows: 47 vs 52 us; 1M rows: 183 vs 205 us); 8 x 4 with twice the warps wins on short
+  // slabs, where latency rather than shared-memory bandwidth decides (38 400 rows: 18.3 vs 20.1 us).
+  const bool wide = p.chunks_per_split >= 8;
+#define WG_LAUNCH(NT, B)                                                                                          \
+  linear_wgrad_kernel<NT, B><<<grid, NT, 0, st>>>(dy, x, n_rows, M, K, p.chunks_per_split, vec_dy, vec_x, part,   \
+                                                  p.part_stride)
+  if (wide) { if (db) WG_LAUNCH(64, true); else WG_LAUNCH(64, false); }
+  else      { if (db) WG_LAUNCH(128, true); else WG_LAUNCH(128, false); }
+#undef WG_LAUNCH
   SGNN_LAUNCH_CHECK();
   const int n_w = M * K, n_b = db ? M : 0;
   linear_wgrad_finish_kernel<<<(n_w + n_b + 31) / 32, dim3(32, 32), 0, st>>>(part, p.part_stride, p.splits, n_w, n_b,
