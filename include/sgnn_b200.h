@@ -80,6 +80,12 @@ int sgnn_gather_add_rows(const float* P, long ldp, const float* Q, long ldq, con
                          const int* src, int n_edges, int width, float* out, void* stream);
 int sgnn_segment_sum_rows(const float* m, const int* rowptr, const int* perm, int n_rows, int width,
                           float* out, void* stream);
+/* variants for the fused first Linear of the edge MLP (train_ops._EdgePre): out[e] += P[tgt[e]] + Q[src[e]],
+ * and segment sums written into a column block of a wider matrix (row stride ld_out floats).        */
+int sgnn_gather_add_rows_acc(const float* P, long ldp, const float* Q, long ldq, const int* tgt,
+                             const int* src, int n_edges, int width, float* out, void* stream);
+int sgnn_segment_sum_rows_ld(const float* m, const int* rowptr, const int* perm, int n_rows, int width,
+                             float* out, long ld_out, void* stream);
 int sgnn_gather_rows(const float* rows, long ld, const int* idx, int n_out, int width, float* out,
                      void* stream);
 

@@ -14,7 +14,8 @@
 
 namespace sgnn {
 
-// one warp per edge row; width multiple of 4
+// one warp per edge row; width multiple of 4; ACC: out[e] += ... (the edge term of the first Linear is there already)
+template <bool ACC>
 __global__ void __launch_bounds__(256)
 gather_add_kernel(const float* __restrict__ P, long ldp, const float* __restrict__ Q, long ldq,
                   const int* __restrict__ tgt, const int* __restrict__ src, int n_edges, int width,
@@ -27,7 +28,12 @@ gather_add_kernel(const float* __restrict__ P, long ldp, const float* __restrict
     float4* o = reinterpret_cast<float4*>(out + e * width);
     for (int c = lane; c < chunks; c += 32) {
       const float4 a = __ldg(p + c), b = __ldg(q + c);
-      o[c] = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+      float4 r = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+      if (ACC) {
+        const float4 z = o[c];
+        r = make_float4(z.x + r.x, z.y + r.y, z.z + r.z, z.w + r.w);
+      }
+      o[c] = r;
     }
   }
 }
@@ -35,7 +41,7 @@ gather_add_kernel(const float* __restrict__ P, long ldp, const float* __restrict
 // one warp per segment, rows summed in order (deterministic); empty segments give zeros
 __global__ void __launch_bounds__(256)
 segment_sum_kernel(const float* __restrict__ m, const int* __restrict__ rowptr,
-                   const int* __restrict__ perm, int n_rows, int width, float* __restrict__ out) {
+                   const int* __restrict__ perm, int n_rows, int width, float* __restrict__ out, long ld_out) {
   const int lane = threadIdx.x & 31;
   const int chunks = width >> 2;
   for (long i = (long)blockIdx.x * 8 + (threadIdx.x >> 5); i < n_rows; i += (long)gridDim.x * 8) {
@@ -47,7 +53,7 @@ segment_sum_kernel(const float* __restrict__ m, const int* __restrict__ rowptr,
         const float4 v = __ldg(reinterpret_cast<const float4*>(m + r * width) + c);
         s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
       }
-      reinterpret_cast<float4*>(out + i * width)[c] = s;
+      reinterpret_cast<float4*>(out + i * ld_out)[c] = s;
     }
   }
 }
@@ -112,24 +118,44 @@ static int warp_grid(long rows) {
 
 using namespace sgnn;
 
-extern "C" int sgnn_gather_add_rows(const float* P, long ldp, const float* Q, long ldq, const int* tgt,
-                                    const int* src, int n_edges, int width, float* out, void* stream) {
+static int gather_add_launch(const float* P, long ldp, const float* Q, long ldq, const int* tgt, const int* src,
+                             int n_edges, int width, float* out, bool acc, void* stream) {
   SGNN_CHECK_ARG(width > 0 && width % 4 == 0 && ldp % 4 == 0 && ldq % 4 == 0,
                  "gather_add_rows: widths must be multiples of 4");
   if (n_edges <= 0) return SGNN_OK;
-  gather_add_kernel<<<warp_grid(n_edges), 256, 0, (cudaStream_t)stream>>>(P, ldp, Q, ldq, tgt, src, n_edges,
-                                                                         width, out);
+  if (acc)
+    gather_add_kernel<true><<<warp_grid(n_edges), 256, 0, (cudaStream_t)stream>>>(P, ldp, Q, ldq, tgt, src, n_edges,
+                                                                                 width, out);
+  else
+    gather_add_kernel<false><<<warp_grid(n_edges), 256, 0, (cudaStream_t)stream>>>(P, ldp, Q, ldq, tgt, src, n_edges,
+                                                                                  width, out);
+  SGNN_LAUNCH_CHECK();
+  return SGNN_OK;
+}
+
+extern "C" int sgnn_gather_add_rows(const float* P, long ldp, const float* Q, long ldq, const int* tgt,
+                                    const int* src, int n_edges, int width, float* out, void* stream) {
+  return gather_add_launch(P, ldp, Q, ldq, tgt, src, n_edges, width, out, false, stream);
+}
+
+extern "C" int sgnn_gather_add_rows_acc(const float* P, long ldp, const float* Q, long ldq, const int* tgt,
+                                        const int* src, int n_edges, int width, float* out, void* stream) {
+  return gather_add_launch(P, ldp, Q, ldq, tgt, src, n_edges, width, out, true, stream);
+}
+
+extern "C" int sgnn_segment_sum_rows_ld(const float* m, const int* rowptr, const int* perm, int n_rows, int width,
+                                        float* out, long ld_out, void* stream) {
+  SGNN_CHECK_ARG(width > 0 && width % 4 == 0 && ld_out % 4 == 0 && ld_out >= width,
+                 "segment_sum_rows: width and ld_out must be multiples of 4");
+  if (n_rows <= 0) return SGNN_OK;
+  segment_sum_kernel<<<warp_grid(n_rows), 256, 0, (cudaStream_t)stream>>>(m, rowptr, perm, n_rows, width, out, ld_out);
   SGNN_LAUNCH_CHECK();
   return SGNN_OK;
 }
 
 extern "C" int sgnn_segment_sum_rows(const float* m, const int* rowptr, const int* perm, int n_rows,
                                      int width, float* out, void* stream) {
-  SGNN_CHECK_ARG(width > 0 && width % 4 == 0, "segment_sum_rows: width must be a multiple of 4");
-  if (n_rows <= 0) return SGNN_OK;
-  segment_sum_kernel<<<warp_grid(n_rows), 256, 0, (cudaStream_t)stream>>>(m, rowptr, perm, n_rows, width, out);
-  SGNN_LAUNCH_CHECK();
-  return SGNN_OK;
+  return sgnn_segment_sum_rows_ld(m, rowptr, perm, n_rows, width, out, width, stream);
 }
 
 extern "C" int sgnn_gather_rows(const float* rows, long ld, const int* idx, int n_out, int width,

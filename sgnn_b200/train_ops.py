@@ -174,15 +174,7 @@ class _Linear(torch.autograd.Function):
         dw = db = None
         if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
             xc = x if (x.dtype == torch.float32 and x.is_contiguous()) else _f32(x)
-            n, k = xc.shape
-            m = dy.shape[1]
-            dev = dy.device
-            dw = torch.empty(m, k, dtype=torch.float32, device=dev)
-            db = torch.empty(m, dtype=torch.float32, device=dev) if ctx.has_bias else None
-            fn, fn_bytes = _wgrad_fns()
-            ws = _wgrad_workspace(fn_bytes(n, m, k), dev)
-            L.check(fn(dy.data_ptr(), xc.data_ptr(), n, m, k, dw.data_ptr(), db.data_ptr() if db is not None else None,
-                       ws.data_ptr(), ws.numel(), torch.cuda.current_stream().cuda_stream), launches=2)
+            dw, db = _wgrad(dy, xc, ctx.has_bias)
         return dx, dw, db
 
 
@@ -208,6 +200,68 @@ def linear(x: torch.Tensor, w: torch.Tensor, b: Optional[torch.Tensor] = None) -
     if x.dim() != 2 or not x.is_cuda or not (torch.is_grad_enabled() and (w.requires_grad or (b is not None and b.requires_grad))):
         return F.linear(x, w, b)
     return _Linear.apply(x, w, b)
+
+
+def _wgrad(dy: torch.Tensor, x: torch.Tensor, bias: bool):
+    """(dW [out, in], db [out] or None) of y = x W^T (+ b) for contiguous fp32 dy [rows, out], x [rows, in]."""
+    n, k = x.shape
+    m = dy.shape[1]
+    dev = dy.device
+    dw = torch.empty(m, k, dtype=torch.float32, device=dev)
+    db = torch.empty(m, dtype=torch.float32, device=dev) if bias else None
+    fn, fn_bytes = _wgrad_fns()
+    ws = _wgrad_workspace(fn_bytes(n, m, k), dev)
+    L.check(fn(dy.data_ptr(), x.data_ptr(), n, m, k, dw.data_ptr(), db.data_ptr() if bias else None,
+               ws.data_ptr(), ws.numel(), torch.cuda.current_stream().cuda_stream), launches=2)
+    return dw, db
+
+
+class _EdgePre(torch.autograd.Function):
+    """Pre-activation of the edge MLP's first Linear on cat([x_i, x_j, e]) without the concatenation
+    (graph_network.py:173,197): pre[k] = e[k] Wc^T + b + (x Wa^T)[tgt[k]] + (x Wb^T)[src[k]] with
+    W = [Wa | Wb | Wc].  One node-level GEMM for both x terms, the gather added in place; the backward
+    sums dpre per receiver and per sender into the two halves of one [N, 2H] matrix, so x sees one
+    input-gradient GEMM and W one assembled gradient instead of three sliced ones."""
+
+    @staticmethod
+    def forward(ctx, x, e, w, b, graph: TrainGraph):
+        x, e = _f32(x), _f32(e)
+        ni, h = x.shape[1], w.shape[0]
+        wst = torch.cat([w[:, :ni], w[:, ni:2 * ni]], 0)              # [2H, ni]: rows of Wa, then rows of Wb
+        pq = x @ wst.t()                                              # [N, 2H] = [P | Q]
+        wc = w[:, 2 * ni:]
+        pre = torch.addmm(b, e, wc.t()) if b is not None else e @ wc.t()
+        L.check(L.lib().sgnn_gather_add_rows_acc(L.ptr(pq), C.c_long(2 * h), C.c_void_p(pq.data_ptr() + 4 * h),
+                                                 C.c_long(2 * h), L.ptr(graph.tgt), L.ptr(graph.src), graph.e, h,
+                                                 L.ptr(pre), L.stream_ptr()))
+        ctx.save_for_backward(x, e, w, wst)
+        ctx.graph, ctx.has_bias = graph, b is not None
+        return pre
+
+    @staticmethod
+    def backward(ctx, dpre):
+        x, e, w, wst = ctx.saved_tensors
+        g = ctx.graph
+        if dpre.dtype != torch.float32 or not dpre.is_contiguous():
+            dpre = _f32(dpre)
+        ni, h = x.shape[1], w.shape[0]
+        dwc, db = _wgrad(dpre, e, ctx.has_bias)
+        de = dpre @ w[:, 2 * ni:] if ctx.needs_input_grad[1] else None
+        dpq = torch.empty(g.n, 2 * h, dtype=torch.float32, device=dpre.device)
+        perm, rp = g.by_source()
+        lib, st = L.lib(), L.stream_ptr()
+        L.check(lib.sgnn_segment_sum_rows_ld(L.ptr(dpre), L.ptr(g.rowptr), None, g.n, h, L.ptr(dpq),
+                                             C.c_long(2 * h), st))
+        L.check(lib.sgnn_segment_sum_rows_ld(L.ptr(dpre), L.ptr(rp), L.ptr(perm), g.n, h,
+                                             C.c_void_p(dpq.data_ptr() + 4 * h), C.c_long(2 * h), st))
+        dwst, _ = _wgrad(dpq, x, False)                               # [2H, ni]
+        dx = dpq @ wst if ctx.needs_input_grad[0] else None
+        dw = torch.cat([dwst[:h], dwst[h:], dwc], 1)
+        return dx, de, dw, db, None
+
+
+def edge_pre(x, e, w, b, graph: TrainGraph):
+    return _EdgePre.apply(x, e, w, b, graph)
 
 
 def apply_mlp(seq_mlp, h, skip_first_linear: bool = False):
@@ -281,14 +335,16 @@ def interaction_block(edge_fn, node_fn, x, e, graph: TrainGraph):
     Returns (x + node update, e + e): the reference's update() hands back its input edge latent."""
     nn_in = x.shape[1]
     w1 = linears_of(edge_fn[0])[0]
-    p = linear(x, w1.weight[:, :nn_in], w1.bias)                # x_target block (+ bias)
-    q = linear(x, w1.weight[:, nn_in:2 * nn_in])                # x_source block
-    pre = linear(e, w1.weight[:, 2 * nn_in:]) + gather_add(p, q, graph)
+    if w1.weight.shape[1] > 2 * nn_in and x.is_cuda:
+        pre = edge_pre(x, e, w1.weight, w1.bias, graph)
+    else:
+        p = linear(x, w1.weight[:, :nn_in], w1.bias)                # x_target block (+ bias)
+        q = linear(x, w1.weight[:, nn_in:2 * nn_in])                # x_source block
+        pre = linear(e, w1.weight[:, 2 * nn_in:]) + gather_add(p, q, graph)
     msg = layer_norm(edge_fn[1], _rest_of_mlp(edge_fn[0], pre))   # ... -> LayerNorm
     agg = segment_sum(msg, graph)
     v1 = linears_of(node_fn[0])[0]
-    na = agg.shape[1]
-    pre_n = linear(agg, v1.weight[:, :na]) + linear(x, v1.weight[:, na:], v1.bias)
+    pre_n = linear(torch.cat([agg, x], 1), v1.weight, v1.bias)    # the reference's cat([aggregated, x]) + Linear
     upd = layer_norm(node_fn[1], _rest_of_mlp(node_fn[0], pre_n))
     return x + upd, e + e
 

@@ -177,6 +177,36 @@ def test_linear_weight_gradient_kernel(rows, m, k, bias):
     assert torch.equal(again[2], dw) and (db is None or torch.equal(again[3], db))
 
 
+@pytest.mark.parametrize("n,deg,ni,ne,h,bias", [(500, 4, 64, 64, 64, True), (301, 7, 32, 64, 128, True),
+                                                (64, 1, 64, 32, 64, False)])
+def test_fused_edge_first_linear_matches_concatenation(n, deg, ni, ne, h, bias):
+    """train_ops.edge_pre against Linear(cat([x_i, x_j, e])) in fp64 (forward and all four gradients)."""
+    from sgnn_b200 import train_ops as T
+    from sgnn_b200.engine import Csr
+    g = torch.Generator().manual_seed(n + deg)
+    tgt = torch.randint(0, n, (n * deg,), generator=g)
+    src = torch.randint(0, n, (n * deg,), generator=g)
+    csr, _ = Csr.from_edge_index(torch.stack([src, tgt]).cuda(), n)
+    graph = T.TrainGraph.from_csr(csr)
+    x = torch.randn(n, ni, generator=g).cuda().requires_grad_()
+    e = torch.randn(graph.e, ne, generator=g).cuda().requires_grad_()
+    w = (0.2 * torch.randn(h, 2 * ni + ne, generator=g)).cuda().requires_grad_()
+    b = torch.randn(h, generator=g).cuda().requires_grad_() if bias else None
+    up = torch.randn(graph.e, h, generator=g).cuda()
+    pre = T.edge_pre(x, e, w, b, graph)
+    (pre * up).sum().backward()
+    x64, e64, w64 = (t.detach().double().requires_grad_() for t in (x, e, w))
+    b64 = b.detach().double().requires_grad_() if bias else None
+    cat = torch.cat([x64[graph.tgt.long()], x64[graph.src.long()], e64], 1)
+    want = torch.nn.functional.linear(cat, w64, b64)
+    (want * up.double()).sum().backward()
+    pairs = [(pre.detach(), want.detach(), "pre"), (x.grad, x64.grad, "dx"), (e.grad, e64.grad, "de"),
+             (w.grad, w64.grad, "dw")] + ([(b.grad, b64.grad, "db")] if bias else [])
+    for a, c, name in pairs:
+        tol = 2e-5 * max(1.0, float(c.abs().max()))
+        assert (a.double() - c).abs().max().item() <= tol, name
+
+
 def test_tf32_matmul_mode_of_train_step_stays_close():
     """training.train_step(matmul="tf32"): same loss to 1e-3 relative, the global flag is restored."""
     from sgnn_b200 import training
