@@ -17,10 +17,11 @@
 // Bytes: reads 4 (M + K) per row once (M x K beyond 64 x 64: each tile re-reads its operand slabs);
 // flops: 2 * 64 * 64 per row and tile -- 16 flops per byte, above the fp32 SIMT ridge of B200
 // (~72 TFLOP/s / 6.5 TB/s = 11).  Measured (profiles/README.md r01p): 45 TFLOP/s at 1M rows, 33 at 190 k
-// rows (47 us against 293 us for torch.mm + sum).  Every FFMA operand comes out of shared memory (16
-// floats per 64 FMA and lane = 16 pipe cycles per warp and row, as many as 64 FFMA take to issue), so the
-// product is issued as packed FFMA2 and the shared-memory pipe is the loaded unit; what is left between
-// the measured rate and that bound is the per-chunk hand-off (wait, barrier, 16 cp.async per thread).
+// rows (47 us against 293 us for torch.mm + sum).  ncu at 190 k rows (profiles/r01p_linear_wgrad_190k_ncu_raw.csv):
+// FMA pipe 56 % active, shared-memory wavefronts 38 % of peak, issue slots 42 % busy with 8 warps per SM
+// (48 KB of shared memory per CTA -> 4 CTAs of 2 warps); top stalls are fixed-latency waits and instruction
+// fetch, i.e. the kernel is latency-bound at two warps per scheduler, not pipe-bound.  The product is issued
+// as packed FFMA2 (same results as two FFMA, half the issue slots).
 #include "common.cuh"
 
 namespace sgnn {

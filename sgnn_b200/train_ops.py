@@ -143,14 +143,15 @@ class _LayerNorm(torch.autograd.Function):
         return dx, dgamma, dbeta, None
 
 
-_wgrad_ws = {}          # device -> persistent workspace (kernels of one stream run in order: safe to reuse)
+_wgrad_ws = {}          # (device, stream) -> persistent workspace: kernels of one stream run in order, so reuse is safe
 
 
 def _wgrad_workspace(nbytes: int, device) -> torch.Tensor:
-    ws = _wgrad_ws.get(device)
+    key = (device, torch.cuda.current_stream(device).cuda_stream)
+    ws = _wgrad_ws.get(key)
     if ws is None or ws.numel() < nbytes:
         ws = torch.empty(max(nbytes, 1 << 24), dtype=torch.uint8, device=device)
-        _wgrad_ws[device] = ws
+        _wgrad_ws[key] = ws
     return ws
 
 
