@@ -27,8 +27,14 @@
 namespace sgnn {
 
 constexpr int kWgTile = 64;                 // output tile is kWgTile x kWgTile
-constexpr int kWgRows = 32;                 // rows per chunk
-constexpr int kWgStages = 3;
+#ifndef WG_ROWS
+#define WG_ROWS 32
+#endif
+#ifndef WG_STAGES
+#define WG_STAGES 3
+#endif
+constexpr int kWgRows = WG_ROWS;            // rows per chunk
+constexpr int kWgStages = WG_STAGES;
 constexpr int kWgMaxSplits = 148 * 4;       // 48 KB of shared memory per CTA -> 4 CTAs per SM
 constexpr int kWgChunksPerSplit = 2;
 
