@@ -181,14 +181,23 @@ __device__ __forceinline__ void ws_producer(const SgnnEdgeLayerParams& p, const 
       __syncwarp();
     } else {
       const uint32_t d0 = smem_u32(dst);
+      // Row offsets in 16-byte units, computed by the lane that LOADED the id, so that the per-copy chain is
+      // shuffle -> one IMAD.WIDE onto the 64-bit base -> LDGSTS.  Shuffling the ids and scaling afterwards
+      // compiled to a 6-instruction dependent chain per copy through one register pair (48-register budget).
+      // (Measured equal at 1M, r01p: the copies are paced by the LSU queue, ~60 cycles per LDGSTS.128.)
+      uint32_t off16[4];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) off16[c] = (uint32_t)rows[c] * (uint32_t)(2 * kWsW * 4 / 16);
+      const char* xb = xbase;
+      asm volatile("" : "+l"(xb));                   // keep the 64-bit base in a register pair (not re-derived from the constant bank per copy)
 #pragma unroll
       for (int jb = 0; jb < 32; jb += 4) {           // shuffles first, then the copies: the volatile copies pin the order
-        int row[4];
+        uint32_t o[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) row[u] = __shfl_sync(FULL, rows[(jb + u) >> 3], (4 * (jb + u) + rg) & 31);
+        for (int u = 0; u < 4; ++u) o[u] = __shfl_sync(FULL, off16[(jb + u) >> 3], (4 * (jb + u) + rg) & 31);
 #pragma unroll
         for (int u = 0; u < 4; ++u)
-          cp_async16(d0 + (jb + u) * 512 + (((jb + u) & 1) ? d_odd : d_even), xbase + (long)row[u] * (2 * kWsW * 4));
+          cp_async16(d0 + (jb + u) * 512 + (((jb + u) & 1) ? d_odd : d_even), xb + (size_t)o[u] * 16);
       }
     }
     ws_stamp(i, 10 + 4 * part);
