@@ -188,6 +188,20 @@ __device__ __forceinline__ void mbar_wait_spin(uint64_t* bar, uint32_t parity) {
 // leave the issue slots and the instruction fetch to the working ones), poll in the latency regime (a
 // CTA owns one or two tiles -- 4800-particle steps -- and its kernel is ONE serial chain of five such
 // waits: in-kernel stamps put ~0.4 us of wake-up latency on every suspended wait, r01n).
+// 256-bit global accesses (sm_100: LDG / STG .ENL2.256): one full 32-byte sector per lane and instruction.
+// The address must be 32-byte aligned.
+__device__ __forceinline__ void ldg256_nc(const float* src, float* v) {
+  asm volatile("ld.global.nc.v8.f32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
+               : "l"(src));
+}
+__device__ __forceinline__ void stg256(float* dst, float a, float b, float c, float d, float e, float f, float g,
+                                       float h) {
+  asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(dst), "f"(a), "f"(b), "f"(c), "f"(d),
+               "f"(e), "f"(f), "f"(g), "f"(h)
+               : "memory");
+}
+
 __device__ __forceinline__ void mbar_wait_mode(uint64_t* bar, uint32_t parity, bool poll) {
   if (poll) mbar_wait_spin(bar, parity);
   else mbar_wait_sleep(bar, parity);

@@ -72,7 +72,7 @@ __device__ __forceinline__ void ws_group_bar(int g) {
   asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "r"(kThreads) : "memory");
 }
 
-// measurement switches (sgnn_debug_ws_flags; results are WRONG when set): bit 0 = sender K-blocks by
+// measurement switches (sgnn_debug_ws_flags; results are WRONG when set; bits 3, 4: see the epilogue): bit 0 = sender K-blocks by
 // plain bulk copy instead of gather4 (same bytes), bit 2 = epilogue stops after reading acc1
 __device__ int g_ws_flags = 0;
 // timeline of the MMA issuer of CTA 0 (SGNN_TIMELINE builds only): per tile 16 SM-clock stamps
@@ -339,12 +339,12 @@ __device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const 
     // ---- P[tgt]: W fp32 per row; consecutive rows share receivers, so a warp touches few lines ----
     float pr[W];
     {
-      const float4* prow = reinterpret_cast<const float4*>(p.pq + (long)(valid ? t : 0) * 2 * W);
+      // measurement switch bit 3: every row reads receiver 0 (one L1 line per load instruction instead of one per
+      // distinct receiver of the warp); wrong results
+      // 32-byte loads: half the load instructions, each touching one L1 line per distinct receiver of the warp
+      const float* prow = p.pq + (long)((valid && !(g_ws_flags & 8)) ? t : 0) * 2 * W;
 #pragma unroll
-      for (int j = 0; j < W / 4; ++j) {
-        const float4 a = __ldg(prow + j);
-        pr[4 * j] = a.x; pr[4 * j + 1] = a.y; pr[4 * j + 2] = a.z; pr[4 * j + 3] = a.w;
-      }
+      for (int j = 0; j < W / 8; ++j) ldg256_nc(prow + 8 * j, pr + 8 * j);
     }
 
     // ---- hidden = relu(acc0 + P), rounded to TF32, back into the same TMEM columns ----
@@ -447,27 +447,41 @@ __device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const 
       const int maxlen = __reduce_max_sync(FULL, is_end ? cnt_i : 0);
 #pragma unroll 1
       for (int d = 1; d < maxlen; d <<= 1) {
-        const bool take = lane - d >= seg0;
+        const float tk = lane - d >= seg0 ? 1.0f : 0.0f;
+        const float2 tk2 = f2(tk, tk);
 #pragma unroll
-        for (int j = 0; j < W; ++j) {
-          const float up = __shfl_up_sync(FULL, y[j], d);
-          if (take) y[j] += up;
+        for (int j = 0; j < W; j += 2) {           // two shuffles + ONE packed FMA: y += up * {1, 0} (exact; a predicated
+          const float2 up = f2(__shfl_up_sync(FULL, y[j], d), __shfl_up_sync(FULL, y[j + 1], d));   // add costs two)
+          const float2 r = __ffma2_rn(up, tk2, f2(y[j], y[j + 1]));
+          y[j] = r.x; y[j + 1] = r.y;
         }
       }
-      if (is_end) {
+      if (is_end && !(g_ws_flags & 16)) {          // measurement switch bit 4: no agg rows written (wrong results)
         const bool head_piece = first_cont && seg0 == 0;                        // continues the previous warp's receiver
         const bool tail_piece = cont_next && !one_piece && lane == nrows - 1;   // continues in the next warp
-        float* dst = tail_piece ? &wk->pieces[(2 * wq + 1) * W]
-                                : (head_piece ? &wk->pieces[(2 * wq) * W] : p.agg + (long)t * W);
         const float cnt = (float)cnt_i;
         const float4* g4 = reinterpret_cast<const float4*>(blob_f + p.mlp.gamma_off);
         const float4* be4 = reinterpret_cast<const float4*>(blob_f + p.mlp.beta_off);
+        const float2 c2 = f2(cnt, cnt);
 #pragma unroll
-        for (int j = 0; j < W / 4; ++j) {
-          const float4 ga = g4[j], be = be4[j];
-          reinterpret_cast<float4*>(dst)[j] =
-              make_float4(fmaf(y[4 * j], ga.x, cnt * be.x), fmaf(y[4 * j + 1], ga.y, cnt * be.y),
-                          fmaf(y[4 * j + 2], ga.z, cnt * be.z), fmaf(y[4 * j + 3], ga.w, cnt * be.w));
+        for (int j = 0; j < W / 4; ++j) {          // packed fp32x2 (same roundings as fmaf(y, gamma, cnt * beta)): every
+          const float4 ga = g4[j], be = be4[j];    // instruction of this block costs ~7 cycles of a contended scheduler
+          const float2 a = __ffma2_rn(f2(y[4 * j], y[4 * j + 1]), f2(ga.x, ga.y), __fmul2_rn(c2, f2(be.x, be.y)));
+          const float2 b = __ffma2_rn(f2(y[4 * j + 2], y[4 * j + 3]), f2(ga.z, ga.w), __fmul2_rn(c2, f2(be.z, be.w)));
+          y[4 * j] = a.x; y[4 * j + 1] = a.y; y[4 * j + 2] = b.x; y[4 * j + 3] = b.y;
+        }
+        if (!tail_piece && !head_piece && !(g_ws_flags & 32)) {   // (measurement switch bit 5: rows go to shared memory)
+          // a receiver's agg row leaves as eight 32-byte stores: every store fills a whole sector (sixteen
+          // 16-byte stores per row cost 19 % of the kernel at 1M: r01p, switch bit 4)
+          float* dst = p.agg + (long)t * W;
+#pragma unroll
+          for (int j = 0; j < W / 8; ++j)
+            stg256(dst + 8 * j, y[8 * j], y[8 * j + 1], y[8 * j + 2], y[8 * j + 3], y[8 * j + 4], y[8 * j + 5],
+                   y[8 * j + 6], y[8 * j + 7]);
+        } else {
+          float4* dst = reinterpret_cast<float4*>(&wk->pieces[(2 * wq + (tail_piece ? 1 : 0)) * W]);
+#pragma unroll
+          for (int j = 0; j < W / 4; ++j) dst[j] = make_float4(y[4 * j], y[4 * j + 1], y[4 * j + 2], y[4 * j + 3]);
         }
       }
     }
