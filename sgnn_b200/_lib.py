@@ -79,6 +79,16 @@ def lib():
         _lib.sgnn_node_smem_bytes.restype = C.c_size_t
         _lib.sgnn_layer_norm_bwd_workspace_bytes.restype = C.c_size_t
         _lib.sgnn_linear_wgrad_workspace_bytes.restype = C.c_size_t
+        # training-path entries are called ~100 times per step from Python: declared argument types spare the
+        # per-call type inference of ctypes (the call sites keep passing c_void_p / c_long / ints / None)
+        vp, lg, it, fl, sz = C.c_void_p, C.c_long, C.c_int, C.c_float, C.c_size_t
+        _lib.sgnn_gather_add_rows.argtypes = [vp, lg, vp, lg, vp, vp, it, it, vp, vp]
+        _lib.sgnn_gather_add_rows_acc.argtypes = [vp, lg, vp, lg, vp, vp, it, it, vp, vp]
+        _lib.sgnn_segment_sum_rows.argtypes = [vp, vp, vp, it, it, vp, vp]
+        _lib.sgnn_segment_sum_rows_ld.argtypes = [vp, vp, vp, it, it, vp, lg, vp]
+        _lib.sgnn_gather_rows.argtypes = [vp, lg, vp, it, it, vp, vp]
+        _lib.sgnn_layer_norm_fwd.argtypes = [vp, lg, it, vp, vp, fl, vp, vp, vp, vp]
+        _lib.sgnn_layer_norm_bwd.argtypes = [vp, vp, vp, vp, vp, lg, it, vp, vp, vp, vp, sz, vp]
     return _lib
 
 
