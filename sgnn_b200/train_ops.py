@@ -198,7 +198,8 @@ def _wgrad_fns():
 
 def linear(x: torch.Tensor, w: torch.Tensor, b: Optional[torch.Tensor] = None) -> torch.Tensor:
     """F.linear on [rows, in] activations with the weight gradient on the CUDA path above."""
-    if x.dim() != 2 or not x.is_cuda or not (torch.is_grad_enabled() and (w.requires_grad or (b is not None and b.requires_grad))):
+    L.require_cuda(x, "linear input")       # no CPU path: the training step runs on the GPU or not at all
+    if x.dim() != 2 or not (torch.is_grad_enabled() and (w.requires_grad or (b is not None and b.requires_grad))):
         return F.linear(x, w, b)
     return _Linear.apply(x, w, b)
 
@@ -336,7 +337,7 @@ def interaction_block(edge_fn, node_fn, x, e, graph: TrainGraph):
     Returns (x + node update, e + e): the reference's update() hands back its input edge latent."""
     nn_in = x.shape[1]
     w1 = linears_of(edge_fn[0])[0]
-    if w1.weight.shape[1] > 2 * nn_in and x.is_cuda:
+    if w1.weight.shape[1] > 2 * nn_in:
         pre = edge_pre(x, e, w1.weight, w1.bias, graph)
     else:
         p = linear(x, w1.weight[:, :nn_in], w1.bias)                # x_target block (+ bias)
