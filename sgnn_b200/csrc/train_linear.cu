@@ -20,7 +20,7 @@
 // rows (47 us against 293 us for torch.mm + sum).  ncu at 190 k rows (profiles/r01p_linear_wgrad_190k_ncu_raw.csv):
 // FMA pipe 56 % active, shared-memory wavefronts 38 % of peak, issue slots 42 % busy with 8 warps per SM
 // (48 KB of shared memory per CTA -> 4 CTAs of 2 warps); top stalls are fixed-latency waits and instruction
-// fetch, i.e. the kernel is latency-bound at two warps per scheduler, not pipe-bound.  The product is issued
+// fetch.  Ring shapes (32 x 2, 16 x 4, 16 x 3) and 6 or 8 resident CTAs per SM all measured the same (r01p).  The product is issued
 // as packed FFMA2 (same results as two FFMA, half the issue slots).
 #include "common.cuh"
 
@@ -35,7 +35,10 @@ constexpr int kWgTile = 64;                 // output tile is kWgTile x kWgTile
 #endif
 constexpr int kWgRows = WG_ROWS;            // rows per chunk
 constexpr int kWgStages = WG_STAGES;
-constexpr int kWgMaxSplits = 148 * 4;       // 48 KB of shared memory per CTA -> 4 CTAs per SM
+#ifndef WG_CTAS
+#define WG_CTAS 4
+#endif
+constexpr int kWgMaxSplits = 148 * WG_CTAS;   // 48 KB of shared memory per CTA -> 4 CTAs per SM
 constexpr int kWgChunksPerSplit = 2;
 
 __device__ __forceinline__ void wg_cp16(float* dst, const float* src, bool ok) {
