@@ -57,7 +57,8 @@ class NodeParams(C.Structure):
                 ("pq_bias_off", C.c_int), ("pq_out", C.c_void_p), ("dec", Mlp),
                 ("dec_wlast_off", C.c_int), ("dec_out", C.c_void_p), ("acc_mean", C.c_void_p),
                 ("acc_std", C.c_void_p), ("next_pos", C.c_void_p), ("next_pos_stride", C.c_long),
-                ("strain_out", C.c_void_p), ("xr_in", C.c_void_p), ("xr_ld", C.c_long)]
+                ("strain_out", C.c_void_p), ("xr_in", C.c_void_p), ("xr_ld", C.c_long),
+                ("n_types", C.c_int)]
 
 
 _lib = None

@@ -84,7 +84,9 @@ __device__ __forceinline__ void prologue_features(const SgnnNodeParams& p, char*
     if (p.feat_out) p.feat_out[i * p.k_in + k] = wd;
     a_store_scalar<TC>(a_tile, row, k++, wd);
     if (p.emb) {
-      const float* e = p.emb + p.types[i] * p.emb_dim;
+      long ty = p.types[i];      // nn.Embedding raises on ids outside the table; here they are clamped
+      if (p.n_types > 0) ty = ty < 0 ? 0 : (ty >= p.n_types ? p.n_types - 1 : ty);
+      const float* e = p.emb + ty * p.emb_dim;
       for (int j = 0; j < p.emb_dim; ++j) {
         if (p.feat_out) p.feat_out[i * p.k_in + k] = e[j];
         a_store_scalar<TC>(a_tile, row, k++, e[j]);

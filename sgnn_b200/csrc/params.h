@@ -133,6 +133,7 @@ typedef struct {
   float* strain_out;      /* [n] */
   const float* xr_in;     /* AGG_X, optional: x_in rounded to TF32 (row i at xr_in + i * xr_ld), as written */
   long xr_ld;             /* by a node kernel with tail PX into the Q half of pq; enables node_ws_kernel    */
+  int n_types;            /* rows of `emb`; type ids are clamped to [0, n_types) (0: not clamped)           */
 } SgnnNodeParams;
 
 #ifdef __cplusplus

@@ -253,14 +253,15 @@ class EpdEngine:
     """
 
     def __init__(self, node_encoder, edge_encoders, blocks, decoder, *, k_node_in: int, dim: int,
-                 latent: int, n_nodes: int, edge_caps: List[int], precision: str, device):
+                 latent: int, n_nodes: int, edge_caps: List[int], precision: str, device,
+                 has_embedding: bool = False):
         if precision not in ("tf32", "fp32"):
             raise ValueError("precision must be 'tf32' (tensor cores) or 'fp32' (FFMA parity mode)")
         L.device_info()
         tc = precision == "tf32"
         self.tc, self.n, self.dim, self.latent, self.device = tc, n_nodes, dim, latent, device
         self.edge_enc = [EdgeEncoderPlan(seq, dim + 1, tc, device) for seq in edge_encoders]
-        self.gather = self._gather_mode(node_encoder, blocks, k_node_in, latent, tc)
+        self.gather = (not has_embedding) and self._gather_mode(node_encoder, blocks, k_node_in, latent, tc)
         self.blocks = []
         for bi, (edge_fn, node_fn, es, layer) in enumerate(blocks):
             nedge = self.edge_enc[es].out
@@ -286,8 +287,9 @@ class EpdEngine:
     def _gather_mode(self, node_encoder, blocks, k_node_in: int, latent: int, tc: bool) -> bool:
         """True when every edge layer can take its sender rows by TMA gather (edge_layer_ws.cu): all
         widths 64, one hidden layer in the edge MLPs, and every node kernel that feeds an edge layer
-        is the 64-wide tensor-core kernel (the only one with tail PX).  SGNN_EDGE_PQ=1 forces the
-        P/Q formulation (A/B measurements)."""
+        is the 64-wide tensor-core kernel (the only one with tail PX).  A particle-type embedding in the
+        node features keeps the P/Q formulation: only the generic node encoder builds those columns, and
+        it has no tail PX.  SGNN_EDGE_PQ=1 forces the P/Q formulation (A/B measurements)."""
         if not tc or latent != 64 or os.environ.get("SGNN_EDGE_PQ") or os.environ.get("SGNN_EDGE_GENERIC") \
                 or os.environ.get("SGNN_NODE_GENERIC"):
             return False
@@ -329,7 +331,8 @@ class EpdEngine:
             n, pos_seq=pos_seq, pos_seq_stride=pos_seq_stride, seq_len=seq_len, dim=dim,
             vel_mean=vel_mean, vel_std=vel_std, wall_offset=2.0, wall_max=wall_max, wall_div=wall_div,
             types=types if emb is not None else None, emb=emb,
-            emb_dim=0 if emb is None else emb.shape[1], feat_out=feat_out,
+            emb_dim=0 if emb is None else emb.shape[1], n_types=0 if emb is None else emb.shape[0],
+            feat_out=feat_out,
             x_out=self.x[x_cur] if keep_x else None, pq_out=self.pq)
         for bi, (ep, npn, es) in enumerate(self.blocks):
             csr = csrs[es]

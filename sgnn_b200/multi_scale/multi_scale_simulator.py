@@ -114,7 +114,8 @@ class MultiScaleSimulator(nn.Module):
             eng = EpdEngine(g.grid_node_encoder, [g.g2m_edge_encoder, g.m2m_edge_encoder, g.m2g_edge_encoder],
                             blocks, g.prediction_head, k_node_in=self._nnode_in,
                             dim=self._kinematic_dimensions, latent=self._latent_dim, n_nodes=n,
-                            edge_caps=list(caps), precision=self.precision, device=device)
+                            edge_caps=list(caps), precision=self.precision, device=device,
+                            has_embedding=self._nparticle_types > 1)
             hit = (ver, eng)
             self._engines = {key: hit}
         return hit[1]
@@ -147,6 +148,12 @@ class MultiScaleSimulator(nn.Module):
         st = self._stats(dev)
         rg, rc = self._radii()
         use_emb = self._nparticle_types > 1
+        if use_emb:      # the kernel indexes the embedding table with these ids (clamped to the table there)
+            L.require_cuda(particle_types, "particle_types")
+            if particle_types.dtype != torch.int64 or not particle_types.is_contiguous():
+                particle_types = particle_types.to(torch.int64).contiguous()
+            if particle_types.numel() != n:
+                raise ValueError(f"particle_types has {particle_types.numel()} entries for {n} particles")
         stride = seq.stride(0)
         eng.forward(pos_seq=seq, pos_seq_stride=stride, seq_len=s, csrs=csrs, radii=[rg, rc, rg],
                     vel_mean=st["velocity"]["mean"], vel_std=st["velocity"]["std"], wall_max=rg,

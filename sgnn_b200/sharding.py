@@ -228,7 +228,7 @@ def sharded_rollout(simulator, positions_owned: torch.Tensor, nsteps: int, comm:
                 cap.wait_stream(torch.cuda.current_stream())           #  allocator cache at every refresh)
                 with torch.cuda.stream(cap):
                     graph.capture_begin(capture_error_mode="thread_local")
-                    step()
+                    held = step()      # noqa: F841 -- the engine / edge set whose pointers the graph replays stay alive with it
                     graph.capture_end()
                 torch.cuda.current_stream().wait_stream(cap)
             if graph is not None:

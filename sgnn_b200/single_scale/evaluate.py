@@ -19,6 +19,7 @@ from .learned_simulator import LearnedSimulator, example_ptr_of
 EROSIONAL_PARTICLE_ID = -1      # evaluate.py:16
 RMSE_PRINT_INTERVAL = 3         # evaluate.py:20
 VERBOSE = True
+MAX_CACHED_PLANS = 4            # each plan owns a trajectory buffer, a CUDA graph and the engine it captured
 
 
 def rollout_rmse(pred: np.ndarray, gt: np.ndarray) -> np.ndarray:
@@ -52,12 +53,15 @@ class RolloutPlan:
         self.use_graph = use_graph
         self.version = None
         self.launches_per_replay = 0
+        self.captured = None      # (engine, edge set(s)) whose device pointers are baked into `graph`
 
     def launch_steps(self, lo: int, hi: int):
+        used = None
         for k in range(lo, hi):
-            self.sim._step(self.traj[:, k:k + self.s], None, self.types,
-                           next_pos=self.pred[:, k + self.s], strain=self.strain[k],
-                           example_ptr=self.example_ptr)
+            used = self.sim._step(self.traj[:, k:k + self.s], None, self.types,
+                                  next_pos=self.pred[:, k + self.s], strain=self.strain[k],
+                                  example_ptr=self.example_ptr)
+        return used
 
     def run(self):
         """All steps on the current stream (graph replay when captured)."""
@@ -75,9 +79,12 @@ class RolloutPlan:
             g = torch.cuda.CUDAGraph()
             before = L.launch_count
             with torch.cuda.graph(g):
-                self.launch_steps(0, self.nsteps)
+                used = self.launch_steps(0, self.nsteps)
             self.launches_per_replay = L.launch_count - before
-            self.graph, self.version = g, ver
+            # The graph replays raw pointers into the engine's weight blobs / latent buffers and the edge-set
+            # buffers.  The simulator's engine cache is bounded and evicts; the plan therefore OWNS what it
+            # captured, so a replay can never touch freed or re-used allocator memory.
+            self.graph, self.version, self.captured = g, ver, used
         self.graph.replay()
         L.launch_count += self.launches_per_replay
 
@@ -85,9 +92,13 @@ class RolloutPlan:
 def get_plan(sim, n, t, s, dim, mode, device, use_graph=True) -> RolloutPlan:
     cache = sim.__dict__.setdefault("_rollout_plans", {})
     key = (n, t, s, dim, mode, str(device), use_graph, getattr(sim, "_graph_token", 0))
-    if key not in cache:
-        cache[key] = RolloutPlan(sim, n, t, s, dim, mode, device, use_graph)
-    return cache[key]
+    plan = cache.pop(key, None)
+    if plan is None:
+        plan = RolloutPlan(sim, n, t, s, dim, mode, device, use_graph)
+        while len(cache) >= MAX_CACHED_PLANS:          # least recently used first (dicts keep insertion order)
+            cache.pop(next(iter(cache)))
+    cache[key] = plan
+    return plan
 
 
 @torch.no_grad()

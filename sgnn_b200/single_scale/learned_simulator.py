@@ -97,7 +97,8 @@ class LearnedSimulator(nn.Module):
             eng = EpdEngine(epd._encoder.node_fn, [epd._encoder.edge_fn], blocks, epd._decoder.node_fn,
                             k_node_in=self._nnode_in, dim=self._particle_dimensions,
                             latent=self._latent_dim, n_nodes=size, edge_caps=[rg.csr.max_edges],
-                            precision=self.precision, device=device)
+                            precision=self.precision, device=device,
+                            has_embedding=self._nparticle_types > 1)
             hit = (ver, eng, rg)
             self._engines.pop(key, None)
             while len(self._engines) >= 2:                 # bounded cache: shapes change at halo refreshes
@@ -135,6 +136,15 @@ class LearnedSimulator(nn.Module):
         stride = seq.stride(0)
         csr = rg.build(seq[0, s - 1], stride, dim, example_ptr, float(self._connectivity_radius), n=n)
         use_emb = self._nparticle_types > 1
+        if use_emb:
+            # the kernel indexes the embedding table with these ids: int64, on the device, contiguous.  Ids
+            # outside [0, ntypes) are clamped by the kernel (nn.Embedding would raise; a fault on the device
+            # cannot be raised as an exception without a host sync)
+            L.require_cuda(particle_types, "particle_types")
+            if particle_types.dtype != torch.int64 or not particle_types.is_contiguous():
+                particle_types = particle_types.to(torch.int64).contiguous()
+            if particle_types.numel() != n:
+                raise ValueError(f"particle_types has {particle_types.numel()} entries for {n} particles")
         eng.forward(pos_seq=seq, pos_seq_stride=stride, seq_len=s, csrs=[csr], n_active=n,
                     radii=[float(self._connectivity_radius)], vel_mean=st["velocity"]["mean"],
                     vel_std=st["velocity"]["std"], wall_max=float(self._connectivity_radius),

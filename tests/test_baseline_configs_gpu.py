@@ -1,0 +1,218 @@
+"""GPU parity of the PRODUCT kernels on the BASELINE.json configurations themselves (not on reduced
+fixtures): the same code path bench.py times (GATHER-mode tensor-core kernels, CUDA-graph rollout)
+against the CPU oracle on the same seeded inputs.
+
+Tolerance policy (stated; SURVEY.md section 7.2 "Tolerance policy"):
+  * edge sets: bit-exact -- at every checked step the CUDA neighbour search on the CUDA trajectory's
+    own frame equals the oracle's search on that same frame
+  * one step (teacher-forced on the CUDA trajectory's window, oracle network in fp64):
+        |pos - pos64| <= ONE_STEP[precision] * acc_std
+    (the integrator scales the normalised acceleration by acc_std; ONE_STEP is the bound on the
+    normalised acceleration: 3x the largest error observed on these configs, see the table printed
+    by the test)
+  * autoregressive rollout vs the oracle's fp64 rollout: the one-step bound times the error growth
+    of the DYNAMICS, taken from the reference arithmetic itself: G(k) = envelope of
+    gap(k) / gap(0), gap(k) = max|oracle_fp32(k) - oracle_fp64(k)|
+        |pos(k) - pos64(k)| <= ONE_STEP[precision] * acc_std * G(k)
+"""
+import functools
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+S, H, LAYERS, NX, NY = 11, 64, 5, 120, 40
+# bound on the normalised acceleration after ONE step (see module docstring)
+ONE_STEP = {"fp32": 2e-5, "tf32": 3e-3}
+
+
+def _case(regime, nsteps, seed=0, nx=NX, ny=NY):
+    from sgnn_b200 import synthetic
+    spacing, radius = synthetic.spacing_for(regime)
+    traj = synthetic.taylor_trajectory(nx, ny, spacing, nframes=S + nsteps, seed=seed)
+    stats = synthetic.normalization_stats(synthetic.metadata_from(traj["positions"]), 0.02 * spacing / 0.5)
+    return traj, stats, radius
+
+
+def _sim(stats, radius, precision):
+    from sgnn_b200.single_scale import LearnedSimulator
+    torch.manual_seed(1)
+    sim = LearnedSimulator(2, (S - 1) * 2 + 1, 3, H, LAYERS, 1, H, radius, stats, 1, 9,
+                           device="cuda", precision=precision)
+    return sim.cuda().eval()
+
+
+@functools.lru_cache(maxsize=None)
+def _oracle_rollouts(regime, nsteps):
+    """fp32 and fp64 rollouts of the oracle (shared by the precision parametrisation)."""
+    from oracle import sgnn_oracle as O
+    traj, stats, radius = _case(regime, nsteps)
+    sim = _sim(stats, radius, "tf32")
+    sd = {k: v.detach().cpu() for k, v in sim.state_dict().items()}
+    pos, types = traj["positions"], traj["particle_types"]
+    with torch.no_grad():
+        p32, _, _ = O.rollout(sd, pos, types, nsteps, radius, stats, S)
+        p64, s64, _ = O.rollout(O.cast_sd(sd, torch.float64), pos.double(), types, nsteps, radius,
+                                O.cast_stats(stats, torch.float64), S)
+    gap = (p32.double() - p64).abs().amax(dim=(1, 2)).numpy()
+    growth = np.maximum.accumulate(gap / gap[0])
+    return sd, p64, s64, gap, growth
+
+
+# ---------------------------------------------------------------------------------- configs[1]
+@pytest.mark.parametrize("regime", ["A", "B"])
+@pytest.mark.parametrize("precision", ["tf32", "fp32"])
+def test_config2_100_step_rollout(regime, precision):
+    """BASELINE configs[1]: N=4800, 100-step autoregressive rollout through evaluate.rollout (one CUDA
+    graph, the path bench.py times) against the oracle (reference: single_scale/evaluate.py:117-160)."""
+    from oracle import sgnn_oracle as O
+    from sgnn_b200.single_scale import evaluate as EV
+    EV.VERBOSE = False
+    nsteps = 100
+    traj, stats, radius = _case(regime, nsteps)
+    sd, p64, s64, gap, growth = _oracle_rollouts(regime, nsteps)
+    sim = _sim(stats, radius, precision)
+    pos, types = traj["positions"].cuda(), traj["particle_types"].cuda()
+    n = pos.shape[0]
+    out = EV.rollout(sim, pos, types, torch.tensor(n), traj["strains"].cuda(), nsteps, 2, "cuda", S)
+    again = EV.rollout(sim, pos, types, torch.tensor(n), traj["strains"].cuda(), nsteps, 2, "cuda", S)
+    assert np.array_equal(out["predicted_rollout"], again["predicted_rollout"])      # graph replay, bit-reproducible
+    pred = torch.from_numpy(out["predicted_rollout"])                                # [nsteps, N, 2]
+    acc_std = stats["acceleration"]["std"].max().item()
+    full = torch.cat([traj["positions"][:, :S], pred.permute(1, 0, 2)], dim=1)      # the CUDA trajectory
+    sd64, st64 = O.cast_sd(sd, torch.float64), O.cast_stats(stats, torch.float64)
+    rows = []
+    for k in list(range(0, nsteps, 10)) + [nsteps - 1]:
+        # one step, teacher-forced on the CUDA trajectory's own window
+        win = full[:, k:k + S]
+        with torch.no_grad():
+            want, want_strain, ei = O.predict_positions(sd64, win.double(), [n], traj["particle_types"], radius, st64)
+        a, b = sim._compute_graph_connectivity(win[:, -1].contiguous().cuda(), torch.tensor([n]), radius)
+        assert torch.equal(torch.stack([a, b]).cpu(), ei), f"edge set differs at step {k}"
+        one = (pred[k].double() - want).abs().max().item()
+        strain_err = float(np.abs(out["predicted_strain"][k] - want_strain.numpy()).max())
+        auto = (pred[k].double() - p64[k]).abs().max().item()
+        tol_auto = ONE_STEP[precision] * acc_std * growth[k]
+        rows.append((k, ei.shape[1], one / acc_std, strain_err, auto, tol_auto, gap[k]))
+    print(f"\nconfig 2 regime {regime} {precision}: acc_std {acc_std:.3e}")
+    print("step  edges  one-step|dacc_n|  |dstrain|  auto|dpos|   bound      oracle fp32-fp64 gap")
+    for r in rows:
+        print("%4d %6d   %.3e      %.3e  %.3e  %.3e  %.3e" % r)
+    for k, _, one_n, strain_err, auto, tol_auto, _ in rows:
+        assert one_n <= ONE_STEP[precision], (k, one_n)
+        assert strain_err <= ONE_STEP[precision], (k, strain_err)
+        assert auto <= tol_auto, (k, auto, tol_auto)
+
+
+# ---------------------------------------------------------------------------------- configs[3]
+MS_ONE_STEP = {"fp32": 5e-5, "tf32": 6e-3}     # H=128, nmlp=2, 7 blocks: K twice as long, two more GEMMs per MLP
+
+
+@pytest.mark.parametrize("precision", ["tf32", "fp32"])
+def test_config4_multi_scale_rollout(precision):
+    """BASELINE configs[3]: multi-scale, N=4800 at the hard-coded 0.5 spacing, scales=2, window=2,
+    layers=5, hidden=128, nmlp=2, 10-step rollout (CUDA graph) vs oracle.sgnn_oracle_ms
+    (reference: multi_scale_evaluate.py:164-220, multi_scale_gnn.py:277-325)."""
+    from oracle import sgnn_oracle as O, sgnn_oracle_ms as OM
+    from sgnn_b200 import synthetic
+    from sgnn_b200.multi_scale import MultiScaleConfig, MultiScaleGraph, MultiScaleSimulator
+    from sgnn_b200.multi_scale.multi_scale_evaluate import evaluate_multi_scale_rollout
+    nsteps = 10
+    traj = synthetic.taylor_trajectory(NX, NY, 0.5, nframes=S + nsteps, seed=0)
+    stats = synthetic.normalization_stats(synthetic.metadata_from(traj["positions"]), 0.02)
+    torch.manual_seed(1)
+    sim = MultiScaleSimulator(2, (S - 1) * 2 + 1, 3, 128, 128, LAYERS, 2, stats, 1, 9, num_scales=2,
+                              window_size=2, radius_multiplier=2.0, device="cuda", precision=precision).cuda().eval()
+    pos = traj["positions"].cuda()
+    n = pos.shape[0]
+    graph = MultiScaleGraph(MultiScaleConfig(2, 2, 2.0)).create_all_edges(pos[:, 0].contiguous())
+    want_graph = OM.create_all_edges(traj["positions"][:, 0], 2, 2, 2.0)
+    counts = {}
+    for key in ("grid2mesh_edges", "mesh2mesh_edges", "mesh2grid_edges"):
+        assert torch.equal(graph[key].cpu(), want_graph[key]), key
+        counts[key] = graph[key].shape[1]
+    assert counts == {"grid2mesh_edges": 10561, "mesh2mesh_edges": 10324, "mesh2grid_edges": 10561}
+    sim.set_static_graph(graph)
+    out = evaluate_multi_scale_rollout(sim, pos, traj["particle_types"].cuda(), torch.tensor([n]),
+                                       traj["strains"].cuda(), nsteps, 2, "cuda", S)
+    pred = torch.from_numpy(out["predicted_rollout"])
+    sd = {k: v.detach().cpu() for k, v in sim.state_dict().items()}
+    sd64, st64 = O.cast_sd(sd, torch.float64), O.cast_stats(stats, torch.float64)
+    with torch.no_grad():
+        p32, _ = OM.rollout(sd, traj["positions"], traj["particle_types"], nsteps, want_graph, stats, S, 2)
+        p64, _ = OM.rollout(sd64, traj["positions"].double(), traj["particle_types"], nsteps, want_graph, st64, S, 2)
+    gap = (p32.double() - p64).abs().amax(dim=(1, 2)).numpy()
+    growth = np.maximum.accumulate(gap / gap[0])
+    acc_std = stats["acceleration"]["std"].max().item()
+    full = torch.cat([traj["positions"][:, :S], pred.permute(1, 0, 2)], dim=1)
+    rows = []
+    for k in range(nsteps):
+        with torch.no_grad():
+            want, want_strain = OM.predict_positions(sd64, full[:, k:k + S].double(), traj["particle_types"],
+                                                     want_graph, st64, 2)
+        one = (pred[k].double() - want).abs().max().item() / acc_std
+        strain_err = float(np.abs(out["predicted_strain"][k] - want_strain.numpy()).max())
+        auto = (pred[k].double() - p64[k]).abs().max().item()
+        rows.append((k, one, strain_err, auto, MS_ONE_STEP[precision] * acc_std * growth[k], gap[k]))
+    print(f"\nconfig 4 multi-scale {precision}: acc_std {acc_std:.3e}")
+    print("step  one-step|dacc_n|  |dstrain|  auto|dpos|   bound      oracle fp32-fp64 gap")
+    for r in rows:
+        print("%4d   %.3e      %.3e  %.3e  %.3e  %.3e" % r)
+    for k, one, strain_err, auto, tol, _ in rows:
+        assert one <= MS_ONE_STEP[precision], (k, one)
+        assert strain_err <= MS_ONE_STEP[precision], (k, strain_err)
+        assert auto <= tol, (k, auto, tol)
+
+
+# ---------------------------------------------------------------------------------- configs[2]
+def test_config3_train_step_8x4800():
+    """BASELINE configs[2]: one training forward + backward on 8 samples x 4800 particles against the
+    oracle's autograd in fp64 (reference: single_scale/train.py:230-280).  Bar per parameter tensor:
+    |g - g64| <= 20 * |g32 - g64| + 1e-6 * max|g64| (the reference arithmetic's own fp32-vs-fp64 gap)."""
+    from oracle import sgnn_oracle as O
+    samples = 8
+    pos, nxt, strain = [], [], []
+    for k in range(samples):
+        traj, stats, radius = _case("A", 1, seed=100 + k)
+        pos.append(traj["positions"][:, :S]); nxt.append(traj["positions"][:, S]); strain.append(traj["strains"][S])
+    pos, nxt, strain = torch.cat(pos), torch.cat(nxt), torch.cat(strain)
+    n = pos.shape[0]
+    counts = torch.full((samples,), n // samples, dtype=torch.int64)
+    types = torch.zeros(n, dtype=torch.int64)
+    noise = O.random_walk_noise(pos, 0.02 * 25.0, torch.Generator().manual_seed(2))
+    sim = _sim(stats, radius, "tf32").train()
+    pa, ta, ps = sim.predict_accelerations(nxt.cuda(), noise.cuda(), pos.cuda(), counts.cuda(), types.cuda())
+    loss = (((pa - ta) ** 2).sum(-1) + (ps - strain.cuda()) ** 2).mean()
+    sim.zero_grad()
+    loss.backward()
+    sd = {k: v.detach().cpu() for k, v in sim.state_dict().items()}
+
+    def oracle_grads(dtype):
+        sdd = {k: v.clone().requires_grad_(v.is_floating_point()) for k, v in O.cast_sd(sd, dtype).items()}
+        opa, ota, ops, ei = O.predict_accelerations(sdd, nxt.to(dtype), noise.to(dtype), pos.to(dtype), counts, types,
+                                                    radius, O.cast_stats(stats, dtype))
+        ol = O.train_loss(opa, ota, ops, strain.to(dtype))
+        ol.backward()
+        return ol.item(), {k: v.grad for k, v in sdd.items() if v.requires_grad and v.grad is not None}, ei, opa
+
+    l64, g64, ei, pa64 = oracle_grads(torch.float64)
+    l32, g32, _, _ = oracle_grads(torch.float32)
+    assert abs(loss.item() - l64) <= 1e-4 * max(1.0, l64), (loss.item(), l64)
+    assert (pa.detach().cpu().double() - pa64.detach()).abs().max().item() <= 5e-5
+    worst = 0.0
+    seen = 0
+    for k, p in sim.named_parameters():
+        if k not in g64:
+            assert p.grad is None or float(p.grad.abs().max()) == 0.0, k
+            continue
+        gap = (g32[k].double() - g64[k]).abs().max().item()
+        gmax = g64[k].abs().max().item()
+        err = (p.grad.cpu().double() - g64[k]).abs().max().item()
+        worst = max(worst, err / (20 * gap + 1e-6 * gmax + 1e-12))
+        assert err <= 20 * gap + 1e-6 * gmax + 1e-12, (k, err, gap, gmax)
+        seen += 1
+    assert seen == len(g64)
+    print(f"\nconfig 3 train step: N={n} E={ei.shape[1]} loss {loss.item():.6f} (fp64 {l64:.6f}); "
+          f"worst gradient error / bar = {worst:.3f} over {seen} tensors")
