@@ -23,6 +23,7 @@ struct CellGrid {
   float lo[3];
   double inv_h;
   int nc[3];
+  int bad;      // the bounding box is not finite (diverged rollout, Inf / NaN input): no edges are emitted
 };
 
 // order-preserving float <-> int encoding for atomicMin/atomicMax
@@ -32,26 +33,47 @@ __device__ __forceinline__ int f2ord(float f) {
 }
 __device__ __forceinline__ float ord2f(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
 
-// Every thread derives the same grid from the bounding box (a few flops; no extra launch).
+// Every thread derives the same grid from the bounding box (a few flops; no extra launch).  The grid is
+// valid for ANY input: cells per axis are formed in double and clamped to [1, cell_cap] before the int
+// cast (an extent of 1e30 or Inf would overflow it), the cell edge grows until the grid fits the cap, and
+// a non-finite box (NaN positions never enter it, Inf ones do) marks the grid `bad`: one cell per example,
+// in-range cell indices, and the search emits no edges instead of walking every particle of the example.
 __device__ __forceinline__ CellGrid make_grid_bounds(const float* lo, const float* hi, int dim, float h0,
                                                      int n_examples, int cell_cap) {
   CellGrid g;
   double h = (double)h0;
-  float ext[3] = {0.f, 0.f, 0.f};
+  double ext[3] = {0.0, 0.0, 0.0};
+  g.bad = 0;
   for (int d = 0; d < 3; ++d) {
-    g.lo[d] = d < dim ? lo[d] : 0.f;
-    ext[d] = d < dim ? hi[d] - g.lo[d] : 0.f;
+    g.lo[d] = 0.f;
+    if (d < dim) {
+      const bool fin = isfinite(lo[d]) && isfinite(hi[d]);
+      if (!fin && !(lo[d] > hi[d])) g.bad = 1;      // (lo > hi: no particle at all -- an empty box, not a bad one)
+      if (fin && hi[d] >= lo[d]) {
+        g.lo[d] = lo[d];
+        ext[d] = (double)hi[d] - (double)lo[d];
+      }
+    }
   }
-  for (int it = 0; it < 64; ++it) {
+  if (!(h > 0.0) || !isfinite(h)) g.bad = 1;
+  const double cap = (double)(cell_cap > 0 ? cell_cap : 1);
+  bool fits = false;
+  for (int it = 0; it < 400 && !g.bad; ++it) {      // 1.25^64 covers sane inputs; doubling afterwards covers FLT_MAX
     double total = (double)n_examples;
     for (int d = 0; d < 3; ++d) {
-      g.nc[d] = d < dim ? (int)floor((double)ext[d] / h) + 1 : 1;
-      total *= (double)g.nc[d];
+      double q = d < dim ? floor(ext[d] / h) + 1.0 : 1.0;
+      q = q < 1.0 ? 1.0 : (q > cap ? cap + 1.0 : q);
+      g.nc[d] = (int)q;
+      total *= q;
     }
-    if (total <= (double)cell_cap) break;
-    h *= 1.25;
+    if (total <= cap) { fits = true; break; }
+    h *= it < 64 ? 1.25 : 2.0;
   }
-  g.inv_h = 1.0 / h;
+  if (!fits) {
+    g.nc[0] = g.nc[1] = g.nc[2] = 1;
+    if (!g.bad && (double)n_examples > cap) g.bad = 1;
+  }
+  g.inv_h = g.bad ? 0.0 : 1.0 / h;
   return g;
 }
 __device__ __forceinline__ CellGrid make_grid(const int* __restrict__ bbox, int dim, float h0,
@@ -164,6 +186,7 @@ __device__ __forceinline__ void neighbor_one(int t, int dim, const CellGrid& g, 
                                              int* __restrict__ nbr) {
   const float4 q = sorted[t];
   const int i = __float_as_int(q.w);
+  if (g.bad) { cnt[i] = 0; return; }
   int c = cell_of[i];
   const int cx = c % g.nc[0]; c /= g.nc[0];
   const int cy = c % g.nc[1]; c /= g.nc[1];
@@ -400,6 +423,7 @@ radius_cluster_kernel(const float* __restrict__ pos, long stride, int n, int dim
     }
 #pragma unroll
     for (int u = 0; u < 9; ++u) {
+      if (g.bad) break;                                // non-finite bounding box: no edges (see make_grid_bounds)
       for (int s = rs0[u]; s < rs1[u]; s += 4) {       // four candidates in flight
         float4 o4[4];
 #pragma unroll
