@@ -6,14 +6,15 @@ Tolerance policy (stated; SURVEY.md section 7.2 "Tolerance policy"):
   * edge sets: bit-exact -- at every checked step the CUDA neighbour search on the CUDA trajectory's
     own frame equals the oracle's search on that same frame
   * one step (teacher-forced on the CUDA trajectory's window, oracle network in fp64):
-        |pos - pos64| <= ONE_STEP[precision] * acc_std
+        |pos - pos64| <= ONE_STEP[precision] * acc_std + ulp32(max|pos|)
     (the integrator scales the normalised acceleration by acc_std; ONE_STEP is the bound on the
-    normalised acceleration: 3x the largest error observed on these configs, see the table printed
-    by the test)
+    normalised acceleration: ~3x the largest error observed on these configs, see the table printed
+    by the test; the second term is the fp32 quantum of the position the kernel stores -- at
+    |x| ~ 1500 it is 1.2e-4, ten times the fp32 path's network error)
   * autoregressive rollout vs the oracle's fp64 rollout: the one-step bound times the error growth
     of the DYNAMICS, taken from the reference arithmetic itself: G(k) = envelope of
     gap(k) / gap(0), gap(k) = max|oracle_fp32(k) - oracle_fp64(k)|
-        |pos(k) - pos64(k)| <= ONE_STEP[precision] * acc_std * G(k)
+        |pos(k) - pos64(k)| <= (ONE_STEP[precision] * acc_std + ulp32(max|pos|)) * G(k)
 """
 import functools
 
@@ -25,7 +26,7 @@ pytestmark = pytest.mark.gpu
 
 S, H, LAYERS, NX, NY = 11, 64, 5, 120, 40
 # bound on the normalised acceleration after ONE step (see module docstring)
-ONE_STEP = {"fp32": 2e-5, "tf32": 3e-3}
+ONE_STEP = {"fp32": 5e-6, "tf32": 3e-3}      # observed: 1.0e-6 / 2.0e-3 (strain channel), profiles/r02a_parity_baseline_configs.txt
 
 
 def _case(regime, nsteps, seed=0, nx=NX, ny=NY):
@@ -81,6 +82,7 @@ def test_config2_100_step_rollout(regime, precision):
     assert np.array_equal(out["predicted_rollout"], again["predicted_rollout"])      # graph replay, bit-reproducible
     pred = torch.from_numpy(out["predicted_rollout"])                                # [nsteps, N, 2]
     acc_std = stats["acceleration"]["std"].max().item()
+    ulp = float(np.spacing(np.float32(traj["positions"].abs().max().item())))
     full = torch.cat([traj["positions"][:, :S], pred.permute(1, 0, 2)], dim=1)      # the CUDA trajectory
     sd64, st64 = O.cast_sd(sd, torch.float64), O.cast_stats(stats, torch.float64)
     rows = []
@@ -94,20 +96,20 @@ def test_config2_100_step_rollout(regime, precision):
         one = (pred[k].double() - want).abs().max().item()
         strain_err = float(np.abs(out["predicted_strain"][k] - want_strain.numpy()).max())
         auto = (pred[k].double() - p64[k]).abs().max().item()
-        tol_auto = ONE_STEP[precision] * acc_std * growth[k]
-        rows.append((k, ei.shape[1], one / acc_std, strain_err, auto, tol_auto, gap[k]))
-    print(f"\nconfig 2 regime {regime} {precision}: acc_std {acc_std:.3e}")
-    print("step  edges  one-step|dacc_n|  |dstrain|  auto|dpos|   bound      oracle fp32-fp64 gap")
+        tol_one = ONE_STEP[precision] * acc_std + ulp
+        rows.append((k, ei.shape[1], one, tol_one, strain_err, auto, tol_one * growth[k], gap[k]))
+    print(f"\nconfig 2 regime {regime} {precision}: acc_std {acc_std:.3e} ulp32(max|pos|) {ulp:.3e}")
+    print("step  edges  one-step|dpos|  bound      |dstrain|  auto|dpos|   bound      oracle fp32-fp64 gap")
     for r in rows:
-        print("%4d %6d   %.3e      %.3e  %.3e  %.3e  %.3e" % r)
-    for k, _, one_n, strain_err, auto, tol_auto, _ in rows:
-        assert one_n <= ONE_STEP[precision], (k, one_n)
+        print("%4d %6d   %.3e    %.3e  %.3e  %.3e  %.3e  %.3e" % r)
+    for k, _, one, tol_one, strain_err, auto, tol_auto, _ in rows:
+        assert one <= tol_one, (k, one, tol_one)
         assert strain_err <= ONE_STEP[precision], (k, strain_err)
         assert auto <= tol_auto, (k, auto, tol_auto)
 
 
 # ---------------------------------------------------------------------------------- configs[3]
-MS_ONE_STEP = {"fp32": 5e-5, "tf32": 6e-3}     # H=128, nmlp=2, 7 blocks: K twice as long, two more GEMMs per MLP
+MS_ONE_STEP = {"fp32": 5e-6, "tf32": 3e-3}   # observed: 7.0e-7 / 9.7e-4;     # H=128, nmlp=2, 7 blocks: K twice as long, two more GEMMs per MLP
 
 
 @pytest.mark.parametrize("precision", ["tf32", "fp32"])
@@ -146,22 +148,24 @@ def test_config4_multi_scale_rollout(precision):
     gap = (p32.double() - p64).abs().amax(dim=(1, 2)).numpy()
     growth = np.maximum.accumulate(gap / gap[0])
     acc_std = stats["acceleration"]["std"].max().item()
+    ulp = float(np.spacing(np.float32(traj["positions"].abs().max().item())))
+    tol_one = MS_ONE_STEP[precision] * acc_std + ulp
     full = torch.cat([traj["positions"][:, :S], pred.permute(1, 0, 2)], dim=1)
     rows = []
     for k in range(nsteps):
         with torch.no_grad():
             want, want_strain = OM.predict_positions(sd64, full[:, k:k + S].double(), traj["particle_types"],
                                                      want_graph, st64, 2)
-        one = (pred[k].double() - want).abs().max().item() / acc_std
+        one = (pred[k].double() - want).abs().max().item()
         strain_err = float(np.abs(out["predicted_strain"][k] - want_strain.numpy()).max())
         auto = (pred[k].double() - p64[k]).abs().max().item()
-        rows.append((k, one, strain_err, auto, MS_ONE_STEP[precision] * acc_std * growth[k], gap[k]))
-    print(f"\nconfig 4 multi-scale {precision}: acc_std {acc_std:.3e}")
-    print("step  one-step|dacc_n|  |dstrain|  auto|dpos|   bound      oracle fp32-fp64 gap")
+        rows.append((k, one, strain_err, auto, tol_one * growth[k], gap[k]))
+    print(f"\nconfig 4 multi-scale {precision}: acc_std {acc_std:.3e} ulp32(max|pos|) {ulp:.3e} one-step bound {tol_one:.3e}")
+    print("step  one-step|dpos|  |dstrain|  auto|dpos|   bound      oracle fp32-fp64 gap")
     for r in rows:
         print("%4d   %.3e      %.3e  %.3e  %.3e  %.3e" % r)
     for k, one, strain_err, auto, tol, _ in rows:
-        assert one <= MS_ONE_STEP[precision], (k, one)
+        assert one <= tol_one, (k, one, tol_one)
         assert strain_err <= MS_ONE_STEP[precision], (k, strain_err)
         assert auto <= tol, (k, auto, tol)
 
