@@ -99,6 +99,14 @@ int sgnn_layer_norm_fwd(const float* x, long n_rows, int width, const float* gam
 int sgnn_layer_norm_bwd(const float* dy, const float* x, const float* mean, const float* rstd,
                         const float* gamma, long n_rows, int width, float* dx, float* dgamma, float* dbeta,
                         void* workspace, size_t workspace_bytes, void* stream);
+/* No counterpart in the reference: added for callers that cannot
+ * call cudaMalloc (CUDA graph capture, tight serving loops).  Same result as sgnn_layer_norm_bwd, but the
+ * per-CTA dgamma / dbeta partials live in a static __device__ array inside the library (592 KiB per GPU,
+ * sized for the maximum width 128; wider rows are rejected) instead of a caller workspace.  Allocates
+ * nothing.  All calls on one device share that array: calls that overlap on the GPU race.             */
+int sgnn_layer_norm_bwd_static(const float* dy, const float* x, const float* mean, const float* rstd,
+                               const float* gamma, long n_rows, int width, float* dx, float* dgamma,
+                               float* dbeta, void* stream);
 /* Weight and bias gradients of a Linear layer of the training path (autograd of every build_mlp Linear,
  * graph_network.py:21-58): dw[out][in] = sum_r dy[r][out] x[r][in], db[out] = sum_r dy[r][out] (db may be
  * NULL).  dy [n_rows, out_features] and x [n_rows, in_features] are contiguous row-major fp32.  Rows are

@@ -90,6 +90,7 @@ def lib():
         _lib.sgnn_gather_rows.argtypes = [vp, lg, vp, it, it, vp, vp]
         _lib.sgnn_layer_norm_fwd.argtypes = [vp, lg, it, vp, vp, fl, vp, vp, vp, vp]
         _lib.sgnn_layer_norm_bwd.argtypes = [vp, vp, vp, vp, vp, lg, it, vp, vp, vp, vp, sz, vp]
+        _lib.sgnn_layer_norm_bwd_static.argtypes = [vp, vp, vp, vp, vp, lg, it, vp, vp, vp, vp]
     return _lib
 
 

@@ -130,6 +130,15 @@ static int ln_blocks(long n_rows, int width) {
   return b < 1 ? 1 : (int)b;
 }
 
+// Scratch of sgnn_layer_norm_bwd_static: the per-CTA (dgamma, dbeta) partials of the widest supported row
+// (kLnMaxBlocks * 2 * kLnStaticMaxWidth floats = 592 KiB), resident on every GPU that loads the library.
+// Host code must not pass this name to a kernel (it is the host-side shadow of the symbol): the entry point
+// resolves the device address with cudaGetSymbolAddress, once per device.
+constexpr int kLnStaticMaxWidth = 128;
+constexpr int kLnStaticMaxDevices = 64;
+static __device__ __align__(256) float g_ln_bwd_scratch[kLnMaxBlocks * 2 * kLnStaticMaxWidth];
+static float* g_ln_bwd_scratch_addr[kLnStaticMaxDevices];       // device address per device ordinal, NULL = not resolved
+
 }  // namespace sgnn
 
 using namespace sgnn;
@@ -173,4 +182,28 @@ extern "C" int sgnn_layer_norm_bwd(const float* dy, const float* x, const float*
   ln_bwd_finish_kernel<<<sgnn_ceil_div(2 * width, 32), dim3(32, 8), 0, st>>>(part, grid, width, dgamma, dbeta);
   SGNN_LAUNCH_CHECK();
   return SGNN_OK;
+}
+
+// Variant of sgnn_layer_norm_bwd for callers that cannot allocate (CUDA graph capture, serving loops): the
+// partials live in g_ln_bwd_scratch instead of a caller workspace.  Calls no cudaMalloc / cudaFree.  Every
+// call on a device shares the array: calls that overlap on the GPU (two streams) race.  Nothing in it has to
+// start at zero -- each CTA of a launch overwrites its own slot and the finish kernel reads those slots only.
+extern "C" int sgnn_layer_norm_bwd_static(const float* dy, const float* x, const float* mean, const float* rstd,
+                                          const float* gamma, long n_rows, int width, float* dx, float* dgamma,
+                                          float* dbeta, void* stream) {
+  SGNN_CHECK_ARG(width <= kLnStaticMaxWidth,
+                 "layer_norm_bwd_static: width %d exceeds the static scratch (max width %d, %zu bytes)", width,
+                 kLnStaticMaxWidth, sizeof(float) * (size_t)kLnMaxBlocks * 2 * kLnStaticMaxWidth);
+  SGNN_CHECK_ARG(sgnn_layer_norm_supported(width), "layer_norm_bwd_static: width must be 32, 64 or 128, got %d", width);
+  int dev = -1;
+  SGNN_CUDA(cudaGetDevice(&dev));
+  SGNN_CHECK_ARG(dev >= 0 && dev < kLnStaticMaxDevices, "layer_norm_bwd_static: device ordinal %d out of range", dev);
+  float* part = __atomic_load_n(&g_ln_bwd_scratch_addr[dev], __ATOMIC_ACQUIRE);
+  if (part == nullptr) {                       // set-up, once per device, with that device current
+    SGNN_CUDA(cudaGetSymbolAddress((void**)&part, g_ln_bwd_scratch));
+    SGNN_CHECK_ARG(part != nullptr, "layer_norm_bwd_static: cudaGetSymbolAddress returned NULL");
+    __atomic_store_n(&g_ln_bwd_scratch_addr[dev], part, __ATOMIC_RELEASE);
+  }
+  return sgnn_layer_norm_bwd(dy, x, mean, rstd, gamma, n_rows, width, dx, dgamma, dbeta, part,
+                             sizeof(float) * (size_t)kLnMaxBlocks * 2 * kLnStaticMaxWidth, stream);
 }
