@@ -6,6 +6,7 @@ the window with torch.cat.  Here the rollout reuses the single-scale RolloutPlan
 particle-major trajectory buffer, the decoder kernel writes frame k+S in place, all steps captured
 in one CUDA graph; per-step RMSE is computed on the device after the loop and read back once.
 """
+import time
 from typing import Any, Dict
 
 import numpy as np
@@ -58,3 +59,39 @@ def evaluate_multi_scale_rollout(simulator: MultiScaleSimulator, positions: torc
         "run_time": 0.0,                                            # set by the caller (:243)
         "inference_mode": inference_mode,
     }
+
+
+def validate_multi_scale_simulator(simulator: MultiScaleSimulator, data_path: str, metadata: Dict[str, Any], device,
+                                   input_sequence_length: int = 3, inference_mode: str = "autoregressive",
+                                   num_scales: int = 3, window_size: int = 3, radius_multiplier: float = 2.0,
+                                   verbose: bool = True) -> Dict[str, float]:
+    """Rollout every trajectory of `data_path` with its own static graph and average the final-step
+    losses (reference multi_scale_evaluate.py:18-136; same metric keys)."""
+    from .static_graph_data_loader import MultiScaleTaylorImpactTrajectoriesDataset
+    dataset = MultiScaleTaylorImpactTrajectoriesDataset(data_path, num_scales=num_scales, window_size=window_size,
+                                                        radius_multiplier=radius_multiplier, device=device)
+    was_training = simulator.training
+    simulator.eval()
+    simulator.to(device)
+    total, position, strain, one_step, times = [], [], [], [], []
+    nsteps = metadata["sequence_length"] - input_sequence_length
+    for i, traj in enumerate(dataset):
+        simulator.set_static_graph(traj["graph"])
+        torch.cuda.synchronize()
+        t0 = time.time()
+        out = evaluate_multi_scale_rollout(simulator, traj["positions"], traj["particle_type"],
+                                           traj["n_particles_per_example"], traj["strains"], nsteps,
+                                           metadata["dim"], device, input_sequence_length, inference_mode)
+        times.append(time.time() - t0)
+        position.append(float(out["rmse_position"][-1]))
+        strain.append(float(out["rmse_strain"][-1]))
+        total.append(position[-1] + strain[-1])
+        one_step.append(float(out["rmse_position"][0] + out["rmse_strain"][0]))
+        if verbose:
+            print(f"     Example {i + 1} - Loss total: {total[-1]:.6f}, Position: {position[-1]:.6f}, "
+                  f"Strain: {strain[-1]:.6f}, Time: {times[-1]:.2f}s")
+    if was_training:
+        simulator.train()
+    return {"val/loss_total": float(np.mean(total)), "val/loss_position": float(np.mean(position)),
+            "val/loss_strain": float(np.mean(strain)), "val/loss_oneStep": float(np.mean(one_step)),
+            "val/mean_time": float(np.mean(times)), "val/std_time": float(np.std(times))}
