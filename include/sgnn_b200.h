@@ -114,6 +114,27 @@ int sgnn_layer_norm_bwd_static(const float* dy, const float* x, const float* mea
 size_t sgnn_linear_wgrad_workspace_bytes(long n_rows, int out_features, int in_features);
 int sgnn_linear_wgrad(const float* dy, const float* x, long n_rows, int out_features, int in_features,
                       float* dw, float* db, void* workspace, size_t workspace_bytes, void* stream);
+/* Training step as hand-written kernels (sgnn_b200/train_engine.py; csrc/train_mlp.cu): the autograd of every
+ * build_mlp Sequential + LayerNorm under loss.backward() (graph_network.py:21-58,86-96,139-222; train.py:230-280).
+ *   sgnn_train_pack      all forward / transposed weight images of a step (hi = TF32 part, lo = remainder), one launch
+ *   sgnn_train_mlp_fwd   Linear or Linear-ReLU-Linear[-LayerNorm] over row tiles on tcgen05, keeping h1, the LayerNorm
+ *                        input and statistics; gathered P[tgt] + Q[src] terms of the edge MLP's first Linear
+ *   sgnn_train_mlp_bwd   dpre = (dy W2) * (h1 > 0), dx = dpre W1 routed to two destinations (store / accumulate)
+ *                        -- the interaction layer's input-gradient chain ("sgnn_interaction_layer_bwd" of SURVEY 8(b))
+ *   sgnn_layer_norm_bwd_rows  LayerNorm backward with the upstream rows gathered by an index (backward of the
+ *                        sum-aggregation) and the row count read on the device ("sgnn_mlp_ln_bwd")
+ *   sgnn_linear_wgrad_ex weight / bias gradients on operand column blocks, device-side row count, scaled result
+ *                        written into a column block of a wider gradient                                      */
+int sgnn_train_pack(const SgnnPackDesc* descs_dev, int n_descs, float* img_hi, float* img_lo, void* stream);
+int sgnn_train_mlp_fwd(const SgnnTrainFwd* p, void* stream);
+int sgnn_train_mlp_bwd(const SgnnTrainBwd* p, void* stream);
+int sgnn_layer_norm_bwd_rows(const float* dy, const int* dy_index, const float* x, const float* mean,
+                             const float* rstd, const float* gamma, long max_rows, const int* n_rows_dev, int width,
+                             float* dx, float* dgamma, float* dbeta, void* workspace, size_t workspace_bytes,
+                             void* stream);
+int sgnn_linear_wgrad_ex(const float* dy, long ld_dy, const float* x, long ld_x, long max_rows, const int* n_rows_dev,
+                         int out_features, int in_features, float* dw, long ld_dw, float scale, float* db,
+                         void* workspace, size_t workspace_bytes, void* stream);
 int sgnn_node_features(const float* pos_seq, long stride, int n, int seq_len, int dim,
                        const float* vel_mean, const float* vel_std, float wall_offset, float wall_max,
                        float wall_div, float* out, long ld_out, void* stream);

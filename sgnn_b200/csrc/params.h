@@ -136,6 +136,107 @@ typedef struct {
   int n_types;            /* rows of `emb`; type ids are clamped to [0, n_types) (0: not clamped)           */
 } SgnnNodeParams;
 
+
+/* ---- training path: row-tile kernels with activations kept for the backward pass (csrc/train_mlp.cu) ----
+ * One launch = one Linear (n_linear 1) or Linear-ReLU-Linear[-LayerNorm] (n_linear 2) of build_mlp
+ * (graph_network.py:21-58) over `rows` rows, row-major fp32 in and out.  The row count may live on the
+ * device (n_rows_dev: the edge count rowptr[n] of this step), so that a whole training step has no host
+ * read and can be captured in a CUDA graph; buffers are sized by max_rows.
+ * Weights are K-major SWIZZLE_128B images made by sgnn_train_pack (hi = TF32-rounded value, lo = the
+ * remainder).  split = 1 runs every product as hi*hi + lo*hi + hi*lo (fp32-grade accuracy on the
+ * tensor cores), split = 0 as hi*hi only (plain TF32). */
+enum { SGNN_TPRO_ROWS = 0, SGNN_TPRO_ROWS2 = 1, SGNN_TPRO_EDGE_FEATURES = 2 };
+
+typedef struct {
+  int max_rows;
+  const int* n_rows_dev;   /* NULL: max_rows rows; else min(*n_rows_dev, max_rows), read on the device   */
+  int prologue;
+  const float* a0;         /* ROWS / ROWS2: input columns [0, k0): row r at a0 + r * ld0, times scale0    */
+  long ld0;
+  int k0;
+  float scale0;
+  const float* a1;         /* ROWS2: input columns [k0, k0 + k1) (k0 a multiple of 64)                   */
+  long ld1;
+  int k1;
+  const float* pos;        /* EDGE_FEATURES: (pos[src] - pos[tgt]) / radius and its norm, dim + 1 columns */
+  long pos_stride;
+  int dim;
+  float radius;
+  const int* src;          /* [rows] sender / receiver of each row (EDGE_FEATURES, add_p / add_q)         */
+  const int* tgt;
+  float* feat_out;         /* EDGE_FEATURES: [max_rows, dim + 1] copy of the features (weight gradient)   */
+  const float* add_p;      /* optional: first Linear's output += add_p[tgt[r]] + add_q[src[r]]            */
+  const float* add_q;      /* (the x_i / x_j column blocks of the edge MLP, graph_network.py:173,197)     */
+  long ld_add;
+  int kpad;                /* input width rounded up to 32                                                */
+  int hidden;              /* output width of the first Linear (multiple of 16, <= 128)                  */
+  int out;                 /* output width of the second Linear (<= 128)                                  */
+  int n_linear;
+  int has_ln;
+  int split;
+  const float* w1_hi;      /* image N = hidden, K = kpad                                                  */
+  const float* w1_lo;
+  const float* w2_hi;      /* image N = out rounded up to 16, K = hidden                                  */
+  const float* w2_lo;
+  const float* b1;         /* bias of the first Linear, added to columns [0, b1_cols)                     */
+  int b1_cols;
+  const float* b2;
+  const float* gamma;
+  const float* beta;
+  const float* res;        /* optional residual added to the output: row r at res + r * ld_res            */
+  long ld_res;
+  float* h1;               /* out [rows, hidden]: ReLU output of the first Linear (n_linear 2)            */
+  float* y2;               /* out [rows, out]: input of the LayerNorm (has_ln)                            */
+  float* mean;             /* out [rows]                                                                  */
+  float* rstd;             /* out [rows]                                                                  */
+  float* y;                /* out: row r at y + r * ld_y; width out (n_linear 2) or hidden (n_linear 1)   */
+  long ld_y;
+} SgnnTrainFwd;
+
+/* Backward of the same block from dy = gradient of the LAST Linear's output (after the LayerNorm backward,
+ * sgnn_layer_norm_bwd_rows):  n_linear 2: dpre = (dy W2) * (h1 > 0), written for the weight gradients;
+ * n_linear 1: dpre = dy.  Then optionally dx = dpre W1, routed by columns to two destinations. */
+typedef struct {
+  int max_rows;
+  const int* n_rows_dev;
+  const float* dy;
+  long ld_dy;
+  int k_dy;                /* width of dy; its images use K = k_dy rounded up to 32                       */
+  int n_linear;
+  int hidden;              /* n_linear 2: width of h1 / dpre                                              */
+  const float* h1;
+  float* dpre;             /* out [rows, hidden] (n_linear 2)                                             */
+  const float* w2t_hi;     /* image of W2^T: N = hidden, K = pad32(k_dy)                                  */
+  const float* w2t_lo;
+  int want_dx;
+  int kx;                  /* width of dx = k0 + k1, multiple of 16                                       */
+  const float* w1t_hi;     /* image of W1^T: N = kx, K = hidden (n_linear 2) or pad32(k_dy) (n_linear 1)  */
+  const float* w1t_lo;
+  float* dx0;              /* columns [0, k0) (k0 a multiple of 32)                                       */
+  long ld_dx0;
+  int k0;
+  int acc0;                /* 1: dx0 += ...; 0: dx0 = ...                                                 */
+  float* dx1;              /* columns [k0, k0 + k1)                                                       */
+  long ld_dx1;
+  int k1;
+  int acc1;
+  const float* add1;       /* optional [rows, k1] added into dx1 (gradient arriving over the residual)    */
+  long ld_add1;
+  int split;
+} SgnnTrainBwd;
+
+/* One block of a weight image of the training step: image element (row0 + r, col0 + c), r < n, c < k, of an
+ * image with n_pad rows gets scale * src[r * stride_n + c * stride_k] (stride swap = transposed image; several
+ * blocks may fill one image, e.g. [Wa; Wb]).  Images are zeroed once at set-up: padding is never written. */
+typedef struct {
+  const float* src;
+  long stride_n, stride_k;
+  int n, k, row0, col0, n_pad, pad_;
+  float scale;
+  int pad2_;
+  long dst_off;            /* float offset of the image in the hi and the lo image buffers                */
+} SgnnPackDesc;
+
 #ifdef __cplusplus
 }
 #endif

@@ -92,7 +92,8 @@ __device__ __forceinline__ void wg_load_chunk(float* dst, const float* __restric
 template <int NT, bool BIAS>
 __global__ void __launch_bounds__(NT)
 linear_wgrad_kernel(const float* __restrict__ dy, const float* __restrict__ x, long n_rows, int M, int K,
-                    int chunks_per_split, int vec_dy, int vec_x, float* __restrict__ part, long part_stride) {
+                    int chunks_per_split, int vec_dy, int vec_x, float* __restrict__ part, long part_stride,
+                    long ld_dy, long ld_x, const int* __restrict__ n_rows_dev) {
   constexpr int JH = NT == 64 ? 2 : 1;              // groups of 4 columns per thread
   constexpr int TXB = NT == 64 ? 3 : 4;             // log2 of threads along the columns
   __shared__ __align__(16) float sm[kWgStages][2][kWgRows * kWgTile];
@@ -101,6 +102,12 @@ linear_wgrad_kernel(const float* __restrict__ dy, const float* __restrict__ x, l
   const int mt = blockIdx.y / k_tiles, kt = blockIdx.y - mt * k_tiles;
   const int m0 = mt * kWgTile, k0 = kt * kWgTile;
   const int wm = M - m0 < kWgTile ? M - m0 : kWgTile, wk = K - k0 < kWgTile ? K - k0 : kWgTile;
+  if (n_rows_dev != nullptr) {               // row count on the device: the slabs are cut here, over the whole grid
+    const long nd = *n_rows_dev;
+    n_rows = nd < 0 ? 0 : (nd < n_rows ? nd : n_rows);
+    const long ch = (n_rows + kWgRows - 1) / kWgRows;
+    chunks_per_split = (int)((ch + gridDim.x - 1) / gridDim.x);
+  }
   const long n_chunks = (n_rows + kWgRows - 1) / kWgRows;
   const long c_beg = (long)blockIdx.x * chunks_per_split;
   long c_end = c_beg + chunks_per_split;
@@ -125,8 +132,8 @@ linear_wgrad_kernel(const float* __restrict__ dy, const float* __restrict__ x, l
 #pragma unroll
   for (int s = 0; s < kWgStages - 1; ++s) {
     if (s < n_my) {
-      wg_load_chunk<NT>(sm[s][0], dy, M, n_rows, (c_beg + s) * kWgRows, m0, wm, vec_dy);
-      wg_load_chunk<NT>(sm[s][1], x, K, n_rows, (c_beg + s) * kWgRows, k0, wk, vec_x);
+      wg_load_chunk<NT>(sm[s][0], dy, ld_dy, n_rows, (c_beg + s) * kWgRows, m0, wm, vec_dy);
+      wg_load_chunk<NT>(sm[s][1], x, ld_x, n_rows, (c_beg + s) * kWgRows, k0, wk, vec_x);
     }
     wg_commit();
   }
@@ -136,8 +143,8 @@ linear_wgrad_kernel(const float* __restrict__ dy, const float* __restrict__ x, l
     {
       const int cn = c + kWgStages - 1, st = cn % kWgStages;
       if (cn < n_my) {
-        wg_load_chunk<NT>(sm[st][0], dy, M, n_rows, (c_beg + cn) * kWgRows, m0, wm, vec_dy);
-        wg_load_chunk<NT>(sm[st][1], x, K, n_rows, (c_beg + cn) * kWgRows, k0, wk, vec_x);
+        wg_load_chunk<NT>(sm[st][0], dy, ld_dy, n_rows, (c_beg + cn) * kWgRows, m0, wm, vec_dy);
+        wg_load_chunk<NT>(sm[st][1], x, ld_x, n_rows, (c_beg + cn) * kWgRows, k0, wk, vec_x);
       }
       wg_commit();
     }
@@ -197,7 +204,7 @@ linear_wgrad_kernel(const float* __restrict__ dy, const float* __restrict__ x, l
 // adding its splits in increasing order, then a fixed tree over the lanes.
 __global__ void __launch_bounds__(1024)
 linear_wgrad_finish_kernel(const float* __restrict__ part, long part_stride, int n_splits, int n_w, int n_b,
-                           float* __restrict__ dw, float* __restrict__ db) {
+                           float* __restrict__ dw, float* __restrict__ db, int K = 0, long ld_dw = 0, float scale = 1.0f) {
   __shared__ float red[32][33];
   const int e = blockIdx.x * 32 + threadIdx.x, sl = threadIdx.y;
   const int total = n_w + n_b;
@@ -212,8 +219,9 @@ linear_wgrad_finish_kernel(const float* __restrict__ part, long part_stride, int
     __syncthreads();
   }
   if (sl == 0 && e < total) {
-    if (e < n_w) dw[e] = red[0][threadIdx.x];
-    else db[e - n_w] = red[0][threadIdx.x];
+    if (e >= n_w) db[e - n_w] = red[0][threadIdx.x];
+    else if (K == 0) dw[e] = red[0][threadIdx.x];
+    else dw[(long)(e / K) * ld_dw + (e % K)] = red[0][threadIdx.x] * scale;      // a column block of a wider gradient
   }
 }
 
@@ -270,7 +278,7 @@ extern "C" int sgnn_linear_wgrad(const float* dy, const float* x, long n_rows, i
   const bool wide = p.chunks_per_split >= 8;
 #define WG_LAUNCH(NT, B)                                                                                          \
   linear_wgrad_kernel<NT, B><<<grid, NT, 0, st>>>(dy, x, n_rows, M, K, p.chunks_per_split, vec_dy, vec_x, part,   \
-                                                  p.part_stride)
+                                                  p.part_stride, M, K, nullptr)
   if (wide) { if (db) WG_LAUNCH(64, true); else WG_LAUNCH(64, false); }
   else      { if (db) WG_LAUNCH(128, true); else WG_LAUNCH(128, false); }
 #undef WG_LAUNCH
@@ -278,6 +286,38 @@ extern "C" int sgnn_linear_wgrad(const float* dy, const float* x, long n_rows, i
   const int n_w = M * K, n_b = db ? M : 0;
   linear_wgrad_finish_kernel<<<(n_w + n_b + 31) / 32, dim3(32, 32), 0, st>>>(part, p.part_stride, p.splits, n_w, n_b,
                                                                             dw, db);
+  SGNN_LAUNCH_CHECK();
+  return SGNN_OK;
+}
+
+// sgnn_linear_wgrad for the graph-captured training step: operands with leading dimensions (column blocks of
+// wider matrices), the row count min(max_rows, *n_rows_dev) read on the device (NULL: max_rows; the slabs are
+// then cut on the device over the grid planned for max_rows), and the result written as scale * dW into a
+// column block of a wider gradient (row stride ld_dw).  Workspace: sgnn_linear_wgrad_workspace_bytes(max_rows, ..).
+extern "C" int sgnn_linear_wgrad_ex(const float* dy, long ld_dy, const float* x, long ld_x, long max_rows,
+                                    const int* n_rows_dev, int out_features, int in_features, float* dw, long ld_dw,
+                                    float scale, float* db, void* workspace, size_t workspace_bytes, void* stream) {
+  const int M = out_features, K = in_features;
+  SGNN_CHECK_ARG(M > 0 && K > 0 && max_rows > 0, "linear_wgrad_ex: bad shape rows=%ld out=%d in=%d", max_rows, M, K);
+  SGNN_CHECK_ARG(ld_dy >= M && ld_x >= K && ld_dw >= K, "linear_wgrad_ex: leading dimensions too small");
+  SGNN_CHECK_ARG(workspace_bytes >= sgnn_linear_wgrad_workspace_bytes(max_rows, M, K), "linear_wgrad_ex: workspace too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  const WgPlan p = wg_plan(max_rows, M, K);
+  const int vec_dy = (M & 3) == 0 && (ld_dy & 3) == 0 && ((uintptr_t)dy & 15) == 0;
+  const int vec_x = (K & 3) == 0 && (ld_x & 3) == 0 && ((uintptr_t)x & 15) == 0;
+  float* part = (float*)workspace;
+  const dim3 grid(p.splits, p.tiles);
+  const bool wide = p.chunks_per_split >= 32;      // planned for the capacity: the live row count is usually a fraction of it
+#define WG_LAUNCH(NT, B)                                                                                          \
+  linear_wgrad_kernel<NT, B><<<grid, NT, 0, st>>>(dy, x, max_rows, M, K, p.chunks_per_split, vec_dy, vec_x, part, \
+                                                  p.part_stride, ld_dy, ld_x, n_rows_dev)
+  if (wide) { if (db) WG_LAUNCH(64, true); else WG_LAUNCH(64, false); }
+  else      { if (db) WG_LAUNCH(128, true); else WG_LAUNCH(128, false); }
+#undef WG_LAUNCH
+  SGNN_LAUNCH_CHECK();
+  const int n_w = M * K, n_b = db ? M : 0;
+  linear_wgrad_finish_kernel<<<(n_w + n_b + 31) / 32, dim3(32, 32), 0, st>>>(part, p.part_stride, p.splits, n_w, n_b,
+                                                                            dw, db, K, ld_dw, scale);
   SGNN_LAUNCH_CHECK();
   return SGNN_OK;
 }

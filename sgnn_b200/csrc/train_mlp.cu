@@ -1,0 +1,580 @@
+// Training-path MLP blocks on the tensor cores: forward WITH the activations the backward needs, and the
+// backward's chain of input-gradient products.  Reference: every build_mlp Sequential + LayerNorm of the
+// single-scale network under loss.backward() (sgnn/single_scale/graph_network.py:21-58,86-96,139-147,
+// 178-222; sgnn/single_scale/train.py:230-280).
+//
+//   forward   h1 = relu(A W1^T + b1 [+ P[tgt] + Q[src]]),  y2 = h1 W2^T + b2,  y = LN(y2) [+ res]
+//             (n_linear 1: y = A W1^T + b1 -- the per-node P | Q product of an edge block)
+//   backward  dpre = (dy W2) * (h1 > 0)  [n_linear 1: dpre = dy],  dx = dpre W1 (routed to two destinations)
+//
+// A CTA of 128 threads owns 128-row tiles (persistent loop, row count read on the device); thread t owns
+// row t in every epilogue: TMEM lane t <-> row t, bias / ReLU / LayerNorm / the ReLU mask are thread-local.
+// The products are tcgen05.mma kind::tf32 with both operands in shared memory (K-major SWIZZLE_128B) and
+// fp32 accumulators in TMEM -- the same tile machinery as the inference kernels (mlp_tile.cuh).
+//
+// Precision.  TF32 keeps 10 mantissa bits; the gradient parity tests pin the training step against the
+// reference in fp64 with a bar of 20 x the reference's own fp32-vs-fp64 gap.  With split = 1 every operand is
+// cut into hi = tf32(v) and lo = v - hi (exact in fp32) and every product runs as lo*hi + hi*lo + hi*hi on the
+// tensor pipe: the dropped lo*lo term is 2^-22 relative, i.e. fp32-grade results at a third of the TF32 rate --
+// still far above what the rows' HBM traffic allows (a 128 x 64 x 64 product is 0.14 us of tensor time per SM,
+// its rows take ~1.5 us of the SM's HBM share).  split = 0 is plain TF32.
+//
+// Bytes per row (H = 64, fp32): forward of an edge block reads 256 (e0) + 512 (gathered P, Q rows, L2) and
+// writes 256 x 3 (h1, y2, y) + 8; its backward reads 256 x 2 (dy, h1) and writes 256 (dpre) + 256 (de0 +=).
+#include "mlp_tile.cuh"
+#include "params.h"
+
+namespace sgnn {
+
+constexpr int kTrKChunk = 64;       // the A operand is staged in chunks of at most 64 columns
+
+struct TrMisc {
+  uint64_t bar_w, bar_mma;
+  uint32_t tmem_slot;
+  int pad;
+};
+
+template <bool SPLIT>
+__device__ __forceinline__ void tr_store4(char* a_hi, char* a_lo, uint32_t off, float4 v) {
+  const float4 h = make_float4(to_tf32(v.x), to_tf32(v.y), to_tf32(v.z), to_tf32(v.w));
+  *reinterpret_cast<float4*>(a_hi + off) = h;
+  if constexpr (SPLIT)
+    *reinterpret_cast<float4*>(a_lo + off) = make_float4(v.x - h.x, v.y - h.y, v.z - h.z, v.w - h.w);
+}
+
+// 32 columns [col, col + 32) of this thread's row into the A tile(s)
+template <bool SPLIT>
+__device__ __forceinline__ void tr_a_store32(char* a_hi, char* a_lo, int col, const float* v) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+    tr_store4<SPLIT>(a_hi, a_lo, sw128_chunk_offset(threadIdx.x, col / 4 + j, kTileRows),
+                     make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]));
+}
+
+// Cooperative load of columns [c0, c0 + width) of rows [row0, row0 + rows_valid) of a row-major matrix into
+// columns [0, wpad) of the A tile(s) (zero padded to wpad, a multiple of 32; rows past rows_valid zero).
+template <bool SPLIT>
+__device__ __forceinline__ void tr_a_load(char* a_hi, char* a_lo, const float* __restrict__ src, long ld, long row0,
+                                          int c0, int width, int wpad, int rows_valid, float scale) {
+  const bool vec = (width & 3) == 0 && (ld & 3) == 0 && (c0 & 3) == 0 && ((uintptr_t)src & 15) == 0;
+  if (vec) {
+    const int chunks = wpad >> 2, wch = width >> 2;
+    const int total = kTileRows * chunks;
+    for (int idx0 = threadIdx.x; idx0 < total; idx0 += 4 * kThreads) {
+      float4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int idx = idx0 + u * kThreads;
+        const int r = idx / chunks, c = idx - r * chunks;
+        v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (idx < total && r < rows_valid && c < wch)
+          v[u] = __ldg(reinterpret_cast<const float4*>(src + (row0 + r) * ld + c0) + c);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int idx = idx0 + u * kThreads;
+        if (idx < total) {
+          const int r = idx / chunks, c = idx - r * chunks;
+          tr_store4<SPLIT>(a_hi, a_lo, sw128_chunk_offset(r, c, kTileRows),
+                           make_float4(v[u].x * scale, v[u].y * scale, v[u].z * scale, v[u].w * scale));
+        }
+      }
+    }
+  } else {
+    const int total = kTileRows * wpad;
+    for (int idx = threadIdx.x; idx < total; idx += kThreads) {
+      const int r = idx / wpad, c = idx - r * wpad;
+      float v = 0.f;
+      if (r < rows_valid && c < width) v = __ldg(src + (row0 + r) * ld + c0 + c) * scale;
+      const float h = to_tf32(v);
+      const uint32_t off = sw128_offset(r, c, kTileRows);
+      *reinterpret_cast<float*>(a_hi + off) = h;
+      if constexpr (SPLIT) *reinterpret_cast<float*>(a_lo + off) = v - h;
+    }
+  }
+}
+
+// D[128 x n] (+)= A[128 x k] W[n x k]^T on the tensor pipe; with SPLIT the two cross terms go first.
+// All threads call; completion through gemm_wait<true>.
+template <bool SPLIT>
+__device__ __forceinline__ void tr_gemm(TileAcc<true>& acc, const char* a_hi, const char* a_lo, const char* w_hi,
+                                        const char* w_lo, int k, int n, int acc_col, bool accumulate) {
+  if (threadIdx.x < 32) {
+    tc_fence_after_sync();
+    if (elect_one()) {
+      const uint32_t d = acc.tmem_base + (uint32_t)acc_col;
+      if constexpr (SPLIT) {
+        umma_gemm_tf32(d, smem_u32(a_lo), smem_u32(w_hi), k, n, accumulate);
+        umma_gemm_tf32(d, smem_u32(a_hi), smem_u32(w_lo), k, n, true);
+        umma_gemm_tf32(d, smem_u32(a_hi), smem_u32(w_hi), k, n, true);
+      } else {
+        umma_gemm_tf32(d, smem_u32(a_hi), smem_u32(w_hi), k, n, accumulate);
+      }
+    }
+    __syncwarp();
+  }
+}
+
+__device__ __forceinline__ int tr_rows(int max_rows, const int* n_rows_dev) {
+  if (n_rows_dev == nullptr) return max_rows;
+  const int n = *n_rows_dev;
+  return n < 0 ? 0 : (n > max_rows ? max_rows : n);
+}
+
+// stage `bytes` (multiple of 16) with bulk copies on a barrier whose expect_tx the caller has set
+__device__ __forceinline__ void tr_stage(char* dst, const float* src, int bytes, uint64_t* bar) {
+  for (int off = 0; off < bytes; off += 32768)
+    tma_bulk_g2s(dst + off, reinterpret_cast<const char*>(src) + off, (uint32_t)(bytes - off < 32768 ? bytes - off : 32768),
+                 bar);
+}
+
+struct TrFwdSmem {
+  int w1, w2, a, a_bytes, misc, total;
+};
+__host__ __device__ inline TrFwdSmem tr_fwd_smem(int kpad, int hidden, int out, int n_linear, int split) {
+  TrFwdSmem s;
+  const int out_pad = (out + 15) & ~15;
+  s.w1 = hidden * kpad * 4;
+  s.w2 = n_linear == 2 ? out_pad * hidden * 4 : 0;
+  int aw = kpad < kTrKChunk ? kpad : kTrKChunk;
+  if (n_linear == 2 && hidden > aw) aw = hidden;
+  s.a_bytes = kTileRows * aw * 4;
+  s.a = (s.w1 + s.w2) * (split ? 2 : 1);
+  s.misc = s.a + s.a_bytes * (split ? 2 : 1);
+  s.total = s.misc + (int)sizeof(TrMisc) + 1024;
+  return s;
+}
+
+template <bool SPLIT>
+__global__ void __launch_bounds__(kThreads)
+train_fwd_kernel(const SgnnTrainFwd p) {
+  char* smem = smem_base_1024();
+  const TrFwdSmem L = tr_fwd_smem(p.kpad, p.hidden, p.out, p.n_linear, SPLIT);
+  const int out_pad = (p.out + 15) & ~15;
+  char* w1h = smem;
+  char* w1l = SPLIT ? w1h + L.w1 : w1h;
+  char* w2h = w1h + L.w1 * (SPLIT ? 2 : 1);
+  char* w2l = SPLIT ? w2h + L.w2 : w2h;
+  char* a_hi = smem + L.a;
+  char* a_lo = SPLIT ? a_hi + L.a_bytes : a_hi;
+  TrMisc* misc = reinterpret_cast<TrMisc*>(smem + L.misc);
+  const int tid = threadIdx.x;
+
+  if (tid == 0) {
+    mbar_init(&misc->bar_w, 1);
+    mbar_fence_init();
+    mbar_arrive_expect_tx(&misc->bar_w, (uint32_t)((L.w1 + L.w2) * (SPLIT ? 2 : 1)));
+    tr_stage(w1h, p.w1_hi, L.w1, &misc->bar_w);
+    if (SPLIT) tr_stage(w1l, p.w1_lo, L.w1, &misc->bar_w);
+    if (L.w2) {
+      tr_stage(w2h, p.w2_hi, L.w2, &misc->bar_w);
+      if (SPLIT) tr_stage(w2l, p.w2_lo, L.w2, &misc->bar_w);
+    }
+  }
+  TileAcc<true> acc;
+  const int acc1 = p.hidden;                                     // accumulator of the second Linear
+  acc_setup<true>(acc, pow2_cols(p.hidden + (p.n_linear == 2 ? out_pad : 0)), &misc->bar_mma, &misc->tmem_slot, nullptr);
+  mbar_wait(&misc->bar_w, 0);
+
+  const int rows = tr_rows(p.max_rows, p.n_rows_dev);
+  const int n_tiles = (rows + kTileRows - 1) / kTileRows;
+  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const long row0 = (long)tile * kTileRows;
+    const int rows_valid = rows - row0 < kTileRows ? (int)(rows - row0) : kTileRows;
+    const long r = row0 + tid;
+    const bool valid = tid < rows_valid;
+    int tg = 0, sr = 0;
+    if (valid && p.tgt != nullptr) { tg = __ldg(p.tgt + r); sr = __ldg(p.src + r); }
+
+    // ---- first Linear, K staged in chunks of 64 columns ----
+    for (int kc = 0; kc < p.kpad; kc += kTrKChunk) {
+      const int kw = p.kpad - kc < kTrKChunk ? p.kpad - kc : kTrKChunk;
+      if (p.prologue == SGNN_TPRO_EDGE_FEATURES) {
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = 0.f;
+        if (valid) {
+          float sq = 0.f;
+          for (int d = 0; d < p.dim; ++d) {
+            const float f = __fdiv_rn(__fsub_rn(__ldg(p.pos + (long)sr * p.pos_stride + d),
+                                                __ldg(p.pos + (long)tg * p.pos_stride + d)), p.radius);
+            v[d] = f;
+            sq = __fadd_rn(sq, __fmul_rn(f, f));
+          }
+          v[p.dim] = sqrtf(sq);
+          if (p.feat_out != nullptr)
+            for (int d = 0; d <= p.dim; ++d) p.feat_out[r * (p.dim + 1) + d] = v[d];
+        }
+        tr_a_store32<SPLIT>(a_hi, a_lo, 0, v);
+      } else if (p.prologue == SGNN_TPRO_ROWS2 && kc >= p.k0) {
+        tr_a_load<SPLIT>(a_hi, a_lo, p.a1, p.ld1, row0, kc - p.k0, p.k1 - (kc - p.k0) < kw ? p.k1 - (kc - p.k0) : kw, kw,
+                         rows_valid, 1.0f);
+      } else {
+        tr_a_load<SPLIT>(a_hi, a_lo, p.a0, p.ld0, row0, kc, p.k0 - kc < kw ? p.k0 - kc : kw, kw, rows_valid, p.scale0);
+      }
+      a_tile_publish<true>();
+      const int woff = (kc / kKBlock) * p.hidden * kKBlockBytes;
+      tr_gemm<SPLIT>(acc, a_hi, a_lo, w1h + woff, w1l + woff, kw, p.hidden, 0, kc > 0);
+      gemm_wait<true>(acc);
+    }
+
+    // ---- bias (+ gathered receiver / sender terms), ReLU, keep h1, feed the second Linear ----
+    for (int c = 0; c < p.hidden; c += 32) {
+      float v[32];
+      acc_load32<true>(acc, c, v);
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (p.b1 != nullptr && c + j < p.b1_cols) v[j] += __ldg(p.b1 + c + j);
+      if (p.add_p != nullptr && valid) {
+        const float4* pp = reinterpret_cast<const float4*>(p.add_p + (long)tg * p.ld_add + c);
+        const float4* qq = reinterpret_cast<const float4*>(p.add_q + (long)sr * p.ld_add + c);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float4 a = __ldg(pp + j), b = __ldg(qq + j);
+          v[4 * j] += a.x + b.x; v[4 * j + 1] += a.y + b.y; v[4 * j + 2] += a.z + b.z; v[4 * j + 3] += a.w + b.w;
+        }
+      }
+      if (p.n_linear == 2) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = valid ? fmaxf(v[j], 0.f) : 0.f;
+        if (valid) {
+          float4* h = reinterpret_cast<float4*>(p.h1 + r * p.hidden + c);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) h[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        }
+        tr_a_store32<SPLIT>(a_hi, a_lo, c, v);
+      } else if (valid) {
+        float4* y = reinterpret_cast<float4*>(p.y + r * p.ld_y + c);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) y[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+      }
+    }
+    if (p.n_linear != 2) {
+      tc_fence_before_sync();
+      __syncthreads();                      // every thread has read its accumulator before the next tile's MMAs
+      continue;
+    }
+    a_tile_publish<true>();
+    tr_gemm<SPLIT>(acc, a_hi, a_lo, w2h, w2l, p.hidden, out_pad, acc1, false);
+    gemm_wait<true>(acc);
+
+    // ---- second Linear's bias, LayerNorm (statistics kept), residual, output ----
+    float mean = 0.f, rstd = 1.f;
+    if (p.has_ln) {
+      float s4[4] = {0.f, 0.f, 0.f, 0.f};
+      for (int c = 0; c < p.out; c += 32) {
+        float v[32];
+        acc_load32<true>(acc, acc1 + c, v);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) s4[j & 3] += v[j] + __ldg(p.b2 + c + j);
+      }
+      mean = ((s4[0] + s4[1]) + (s4[2] + s4[3])) / (float)p.out;
+      float q4[4] = {0.f, 0.f, 0.f, 0.f};
+      for (int c = 0; c < p.out; c += 32) {
+        float v[32];
+        acc_load32<true>(acc, acc1 + c, v);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const float d = v[j] + __ldg(p.b2 + c + j) - mean;
+          q4[j & 3] = fmaf(d, d, q4[j & 3]);
+        }
+      }
+      rstd = 1.0f / sqrtf(((q4[0] + q4[1]) + (q4[2] + q4[3])) / (float)p.out + 1e-5f);
+      if (valid) { p.mean[r] = mean; p.rstd[r] = rstd; }
+    }
+    for (int c = 0; c < out_pad; c += 32) {
+      float v[32];
+      acc_load32<true>(acc, acc1 + c, v);
+      if (!valid) continue;
+      if (p.has_ln) {                       // out is a multiple of 32 here (checked by the launcher)
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] += __ldg(p.b2 + c + j);
+        float4* y2 = reinterpret_cast<float4*>(p.y2 + r * p.out + c);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) y2[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = (v[j] - mean) * rstd * __ldg(p.gamma + c + j) + __ldg(p.beta + c + j);
+        if (p.res != nullptr) {
+          const float4* rs = reinterpret_cast<const float4*>(p.res + r * p.ld_res + c);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 a = __ldg(rs + j);
+            v[4 * j] += a.x; v[4 * j + 1] += a.y; v[4 * j + 2] += a.z; v[4 * j + 3] += a.w;
+          }
+        }
+        float4* y = reinterpret_cast<float4*>(p.y + r * p.ld_y + c);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) y[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+      } else {
+        for (int j = 0; j < 32 && c + j < p.out; ++j) p.y[r * p.ld_y + c + j] = v[j] + __ldg(p.b2 + c + j);
+      }
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+  }
+  acc_teardown<true>(acc);
+}
+
+// ------------------------------------------------------------------------------------------ backward
+struct TrBwdSmem {
+  int w2t, w1t, a, a_bytes, misc, total;
+};
+__host__ __device__ inline TrBwdSmem tr_bwd_smem(int k_dy, int n_linear, int hidden, int want_dx, int kx, int split) {
+  TrBwdSmem s;
+  const int kdp = (k_dy + 31) & ~31;
+  const int k2 = n_linear == 2 ? hidden : kdp;             // K of the dx product
+  s.w2t = n_linear == 2 ? hidden * kdp * 4 : 0;
+  s.w1t = want_dx ? kx * k2 * 4 : 0;
+  int aw = kdp < kTrKChunk ? kdp : kTrKChunk;
+  if (n_linear == 2 && hidden > aw) aw = hidden;
+  s.a_bytes = kTileRows * aw * 4;
+  s.a = (s.w2t + s.w1t) * (split ? 2 : 1);
+  s.misc = s.a + s.a_bytes * (split ? 2 : 1);
+  s.total = s.misc + (int)sizeof(TrMisc) + 1024;
+  return s;
+}
+
+template <bool SPLIT>
+__global__ void __launch_bounds__(kThreads)
+train_bwd_kernel(const SgnnTrainBwd p) {
+  char* smem = smem_base_1024();
+  const TrBwdSmem L = tr_bwd_smem(p.k_dy, p.n_linear, p.hidden, p.want_dx, p.kx, SPLIT);
+  const int kdp = (p.k_dy + 31) & ~31;
+  const int k2 = p.n_linear == 2 ? p.hidden : kdp;
+  char* w2h = smem;
+  char* w2l = SPLIT ? w2h + L.w2t : w2h;
+  char* w1h = w2h + L.w2t * (SPLIT ? 2 : 1);
+  char* w1l = SPLIT ? w1h + L.w1t : w1h;
+  char* a_hi = smem + L.a;
+  char* a_lo = SPLIT ? a_hi + L.a_bytes : a_hi;
+  TrMisc* misc = reinterpret_cast<TrMisc*>(smem + L.misc);
+  const int tid = threadIdx.x;
+
+  if (tid == 0) {
+    mbar_init(&misc->bar_w, 1);
+    mbar_fence_init();
+    mbar_arrive_expect_tx(&misc->bar_w, (uint32_t)((L.w2t + L.w1t) * (SPLIT ? 2 : 1)));
+    if (L.w2t) {
+      tr_stage(w2h, p.w2t_hi, L.w2t, &misc->bar_w);
+      if (SPLIT) tr_stage(w2l, p.w2t_lo, L.w2t, &misc->bar_w);
+    }
+    if (L.w1t) {
+      tr_stage(w1h, p.w1t_hi, L.w1t, &misc->bar_w);
+      if (SPLIT) tr_stage(w1l, p.w1t_lo, L.w1t, &misc->bar_w);
+    }
+  }
+  TileAcc<true> acc;
+  const int accx = p.n_linear == 2 ? p.hidden : 0;               // accumulator of the dx product
+  acc_setup<true>(acc, pow2_cols(accx + (p.want_dx ? p.kx : 0) > 32 ? accx + (p.want_dx ? p.kx : 0) : 32),
+                  &misc->bar_mma, &misc->tmem_slot, nullptr);
+  mbar_wait(&misc->bar_w, 0);
+
+  const int rows = tr_rows(p.max_rows, p.n_rows_dev);
+  const int n_tiles = (rows + kTileRows - 1) / kTileRows;
+  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const long row0 = (long)tile * kTileRows;
+    const int rows_valid = rows - row0 < kTileRows ? (int)(rows - row0) : kTileRows;
+    const long r = row0 + tid;
+    const bool valid = tid < rows_valid;
+
+    if (p.n_linear == 2) {
+      // ---- dh = dy W2 (K = width of dy, staged in chunks), ReLU mask, dpre kept ----
+      for (int kc = 0; kc < kdp; kc += kTrKChunk) {
+        const int kw = kdp - kc < kTrKChunk ? kdp - kc : kTrKChunk;
+        tr_a_load<SPLIT>(a_hi, a_lo, p.dy, p.ld_dy, row0, kc, p.k_dy - kc < kw ? p.k_dy - kc : kw, kw, rows_valid, 1.0f);
+        a_tile_publish<true>();
+        const int woff = (kc / kKBlock) * p.hidden * kKBlockBytes;
+        tr_gemm<SPLIT>(acc, a_hi, a_lo, w2h + woff, w2l + woff, kw, p.hidden, 0, kc > 0);
+        gemm_wait<true>(acc);
+      }
+      for (int c = 0; c < p.hidden; c += 32) {
+        float v[32];
+        acc_load32<true>(acc, c, v);
+        if (valid) {
+          const float4* h = reinterpret_cast<const float4*>(p.h1 + r * p.hidden + c);
+          float4* dp = reinterpret_cast<float4*>(p.dpre + r * p.hidden + c);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 a = __ldg(h + j);
+            v[4 * j] = a.x > 0.f ? v[4 * j] : 0.f;
+            v[4 * j + 1] = a.y > 0.f ? v[4 * j + 1] : 0.f;
+            v[4 * j + 2] = a.z > 0.f ? v[4 * j + 2] : 0.f;
+            v[4 * j + 3] = a.w > 0.f ? v[4 * j + 3] : 0.f;
+            dp[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = 0.f;
+        }
+        if (p.want_dx) tr_a_store32<SPLIT>(a_hi, a_lo, c, v);
+      }
+      if (!p.want_dx) {
+        tc_fence_before_sync();
+        __syncthreads();
+        continue;
+      }
+      a_tile_publish<true>();
+      tr_gemm<SPLIT>(acc, a_hi, a_lo, w1h, w1l, p.hidden, p.kx, accx, false);
+      gemm_wait<true>(acc);
+    } else {
+      // ---- dx = dy W1 directly (K = width of dy, staged in chunks) ----
+      for (int kc = 0; kc < kdp; kc += kTrKChunk) {
+        const int kw = kdp - kc < kTrKChunk ? kdp - kc : kTrKChunk;
+        tr_a_load<SPLIT>(a_hi, a_lo, p.dy, p.ld_dy, row0, kc, p.k_dy - kc < kw ? p.k_dy - kc : kw, kw, rows_valid, 1.0f);
+        a_tile_publish<true>();
+        const int woff = (kc / kKBlock) * p.kx * kKBlockBytes;
+        tr_gemm<SPLIT>(acc, a_hi, a_lo, w1h + woff, w1l + woff, kw, p.kx, accx, kc > 0);
+        gemm_wait<true>(acc);
+      }
+    }
+    (void)k2;
+    // ---- route dx by columns: [0, k0) -> dx0, [k0, k0 + k1) -> dx1 ----
+    for (int c = 0; c < p.kx; c += 32) {
+      float v[32];
+      acc_load32<true>(acc, accx + c, v);
+      if (!valid) continue;
+      const bool second = c >= p.k0;
+      float* dst = second ? p.dx1 + r * p.ld_dx1 + (c - p.k0) : p.dx0 + r * p.ld_dx0 + c;
+      const bool accum = second ? p.acc1 != 0 : p.acc0 != 0;
+      const int wlim = (second ? p.k0 + p.k1 : p.k0) - c;          // columns of this chunk that exist (>= 16)
+      if (second && p.add1 != nullptr) {
+        const float4* ad = reinterpret_cast<const float4*>(p.add1 + r * p.ld_add1 + (c - p.k0));
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (4 * j < wlim) {
+            const float4 a = __ldg(ad + j);
+            v[4 * j] += a.x; v[4 * j + 1] += a.y; v[4 * j + 2] += a.z; v[4 * j + 3] += a.w;
+          }
+      }
+      float4* d4 = reinterpret_cast<float4*>(dst);
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (4 * j < wlim) {
+          float4 o = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          if (accum) {
+            const float4 z = d4[j];
+            o = make_float4(o.x + z.x, o.y + z.y, o.z + z.z, o.w + z.w);
+          }
+          d4[j] = o;
+        }
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+  }
+  acc_teardown<true>(acc);
+}
+
+// ------------------------------------------------------------------------------------------ weight images
+// All images of a training step in ONE launch (the weights change every step): blockIdx.y = descriptor.
+__global__ void __launch_bounds__(256)
+train_pack_kernel(const SgnnPackDesc* __restrict__ descs, float* __restrict__ img_hi, float* __restrict__ img_lo) {
+  const SgnnPackDesc d = descs[blockIdx.y];
+  const int total = d.n * d.k;
+  for (int idx = blockIdx.x * 256 + threadIdx.x; idx < total; idx += gridDim.x * 256) {
+    const int r = idx / d.k, c = idx - r * d.k;
+    const float v = __ldg(d.src + r * d.stride_n + c * d.stride_k) * d.scale;
+    const float h = to_tf32(v);
+    const uint32_t off = sw128_offset(d.row0 + r, d.col0 + c, d.n_pad) >> 2;
+    img_hi[d.dst_off + off] = h;
+    img_lo[d.dst_off + off] = v - h;
+  }
+}
+
+static int tr_sm_count() {
+  static int sms = 0;
+  if (sms == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+      sms = 148;
+  }
+  return sms;
+}
+
+}  // namespace sgnn
+
+using namespace sgnn;
+
+static bool al16(const void* p) { return ((uintptr_t)p & 15) == 0; }
+
+extern "C" int sgnn_train_pack(const SgnnPackDesc* descs_dev, int n_descs, float* img_hi, float* img_lo, void* stream) {
+  if (n_descs <= 0) return SGNN_OK;
+  train_pack_kernel<<<dim3(16, n_descs), 256, 0, (cudaStream_t)stream>>>(descs_dev, img_hi, img_lo);
+  SGNN_LAUNCH_CHECK();
+  return SGNN_OK;
+}
+
+extern "C" int sgnn_train_mlp_fwd(const SgnnTrainFwd* p, void* stream) {
+  SGNN_CHECK_ARG(p->n_linear == 1 || p->n_linear == 2, "train_mlp_fwd: n_linear must be 1 or 2");
+  SGNN_CHECK_ARG(p->kpad > 0 && p->kpad % 32 == 0 && p->kpad <= 256, "train_mlp_fwd: bad kpad %d", p->kpad);
+  SGNN_CHECK_ARG(p->hidden >= 16 && p->hidden % 32 == 0 && p->hidden <= 128, "train_mlp_fwd: hidden %d must be 32, 64, 96 or 128",
+                 p->hidden);
+  SGNN_CHECK_ARG(p->n_linear == 1 || (p->out >= 1 && p->out <= 128), "train_mlp_fwd: bad out %d", p->out);
+  SGNN_CHECK_ARG(!p->has_ln || (p->n_linear == 2 && p->out % 32 == 0), "train_mlp_fwd: LayerNorm needs out %% 32 == 0");
+  SGNN_CHECK_ARG(p->n_linear == 2 || p->hidden % 32 == 0, "train_mlp_fwd: single Linear needs width %% 32 == 0");
+  SGNN_CHECK_ARG(p->prologue != SGNN_TPRO_ROWS2 || (p->k0 % kTrKChunk == 0 && p->k0 + p->k1 <= p->kpad),
+                 "train_mlp_fwd: ROWS2 needs k0 %% 64 == 0");
+  SGNN_CHECK_ARG(p->prologue != SGNN_TPRO_EDGE_FEATURES || (p->kpad == 32 && p->dim >= 1 && p->dim <= 3 && p->src && p->tgt),
+                 "train_mlp_fwd: EDGE_FEATURES needs kpad 32, dim 1..3 and the edge lists");
+  SGNN_CHECK_ARG(p->add_p == nullptr || (p->add_q && p->src && p->tgt && p->ld_add % 4 == 0 && al16(p->add_p) && al16(p->add_q)),
+                 "train_mlp_fwd: gathered terms need both matrices, the edge lists and 16-byte alignment");
+  SGNN_CHECK_ARG(al16(p->y) && p->ld_y % 4 == 0 && (p->h1 == nullptr || al16(p->h1)) && (p->y2 == nullptr || al16(p->y2)) &&
+                     (p->res == nullptr || (al16(p->res) && p->ld_res % 4 == 0)),
+                 "train_mlp_fwd: outputs must be 16-byte aligned with leading dimensions %% 4 == 0");
+  SGNN_CHECK_ARG(p->n_linear == 1 || p->h1 != nullptr, "train_mlp_fwd: h1 output missing");
+  SGNN_CHECK_ARG(!p->has_ln || (p->y2 && p->mean && p->rstd && p->gamma && p->beta), "train_mlp_fwd: LayerNorm outputs missing");
+  if (p->max_rows <= 0) return SGNN_OK;
+  const TrFwdSmem s = tr_fwd_smem(p->kpad, p->hidden, p->out, p->n_linear, p->split);
+  SGNN_CHECK_ARG(s.total <= 227 * 1024, "train_mlp_fwd: needs %d bytes of shared memory", s.total);
+  const int tiles = (p->max_rows + kTileRows - 1) / kTileRows;
+  int per_sm = (227 * 1024) / s.total;
+  const int tmem_cols = pow2_cols(p->hidden + (p->n_linear == 2 ? ((p->out + 15) & ~15) : 0));
+  if (per_sm > 512 / tmem_cols) per_sm = 512 / tmem_cols;      // resident CTAs share the SM's 512 TMEM columns
+  if (per_sm > 4) per_sm = 4;
+  int grid = tr_sm_count() * per_sm;
+  if (grid > tiles) grid = tiles;
+  if (p->split) {
+    SGNN_ENSURE_SMEM(train_fwd_kernel<true>, s.total);
+    train_fwd_kernel<true><<<grid, kThreads, s.total, (cudaStream_t)stream>>>(*p);
+  } else {
+    SGNN_ENSURE_SMEM(train_fwd_kernel<false>, s.total);
+    train_fwd_kernel<false><<<grid, kThreads, s.total, (cudaStream_t)stream>>>(*p);
+  }
+  SGNN_LAUNCH_CHECK();
+  return SGNN_OK;
+}
+
+extern "C" int sgnn_train_mlp_bwd(const SgnnTrainBwd* p, void* stream) {
+  SGNN_CHECK_ARG(p->n_linear == 1 || p->n_linear == 2, "train_mlp_bwd: n_linear must be 1 or 2");
+  SGNN_CHECK_ARG(p->k_dy >= 1 && p->k_dy <= 256, "train_mlp_bwd: bad k_dy %d", p->k_dy);
+  SGNN_CHECK_ARG(p->n_linear == 1 || (p->hidden % 32 == 0 && p->hidden >= 32 && p->hidden <= 128 && p->h1 && p->dpre &&
+                                      al16(p->h1) && al16(p->dpre)),
+                 "train_mlp_bwd: hidden %d must be 32..128 (multiple of 32) with h1 / dpre given", p->hidden);
+  SGNN_CHECK_ARG(p->n_linear == 2 || p->want_dx, "train_mlp_bwd: a single Linear has only the dx product");
+  if (p->want_dx) {
+    SGNN_CHECK_ARG(p->kx == p->k0 + p->k1 && p->kx % 16 == 0 && p->kx <= 128 && p->k0 % 32 == 0 && p->k0 > 0,
+                   "train_mlp_bwd: dx widths k0 %d k1 %d", p->k0, p->k1);
+    SGNN_CHECK_ARG(p->dx0 && al16(p->dx0) && p->ld_dx0 % 4 == 0 && (p->k1 == 0 || (p->dx1 && al16(p->dx1) && p->ld_dx1 % 4 == 0 && p->k1 % 16 == 0)),
+                   "train_mlp_bwd: dx destinations must be 16-byte aligned");
+    SGNN_CHECK_ARG(p->add1 == nullptr || (al16(p->add1) && p->ld_add1 % 4 == 0), "train_mlp_bwd: add1 alignment");
+  }
+  if (p->max_rows <= 0) return SGNN_OK;
+  const TrBwdSmem s = tr_bwd_smem(p->k_dy, p->n_linear, p->hidden, p->want_dx, p->kx, p->split);
+  SGNN_CHECK_ARG(s.total <= 227 * 1024, "train_mlp_bwd: needs %d bytes of shared memory", s.total);
+  const int tiles = (p->max_rows + kTileRows - 1) / kTileRows;
+  int per_sm = (227 * 1024) / s.total;
+  const int cols_needed = (p->n_linear == 2 ? p->hidden : 0) + (p->want_dx ? p->kx : 0);
+  const int tmem_cols = pow2_cols(cols_needed > 32 ? cols_needed : 32);
+  if (per_sm > 512 / tmem_cols) per_sm = 512 / tmem_cols;
+  if (per_sm > 4) per_sm = 4;
+  int grid = tr_sm_count() * per_sm;
+  if (grid > tiles) grid = tiles;
+  if (p->split) {
+    SGNN_ENSURE_SMEM(train_bwd_kernel<true>, s.total);
+    train_bwd_kernel<true><<<grid, kThreads, s.total, (cudaStream_t)stream>>>(*p);
+  } else {
+    SGNN_ENSURE_SMEM(train_bwd_kernel<false>, s.total);
+    train_bwd_kernel<false><<<grid, kThreads, s.total, (cudaStream_t)stream>>>(*p);
+  }
+  SGNN_LAUNCH_CHECK();
+  return SGNN_OK;
+}

@@ -58,8 +58,13 @@ template <int LPR>
 __global__ void __launch_bounds__(kLnThreads)
 ln_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ mean,
               const float* __restrict__ rstd, const float* __restrict__ gamma, long n_rows,
-              float* __restrict__ dx, float* __restrict__ part) {
+              float* __restrict__ dx, float* __restrict__ part, const int* __restrict__ dy_index = nullptr,
+              const int* __restrict__ n_rows_dev = nullptr) {
   constexpr int W = 4 * LPR, RPW = 32 / LPR;
+  if (n_rows_dev != nullptr) {                // training step under a CUDA graph: the row count lives on the device
+    const long nd = *n_rows_dev;
+    n_rows = nd < 0 ? 0 : (nd < n_rows ? nd : n_rows);
+  }
   __shared__ float4 s_dg[kLnThreads], s_db[kLnThreads];
   const int lane = threadIdx.x & 31, sub = lane % LPR, rw = lane / LPR;
   const float4 g = __ldg(reinterpret_cast<const float4*>(gamma) + sub);
@@ -72,7 +77,9 @@ ln_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ x, const f
     float m = 0.f, rs = 0.f;
     if (ok) {
       v = __ldcs(reinterpret_cast<const float4*>(x) + r * LPR + sub);
-      d = __ldcs(reinterpret_cast<const float4*>(dy) + r * LPR + sub);
+      const long rd = dy_index != nullptr ? (long)__ldg(dy_index + r) : r;      // dy rows gathered (edges: dagg[tgt])
+      d = dy_index != nullptr ? __ldg(reinterpret_cast<const float4*>(dy) + rd * LPR + sub)
+                              : __ldcs(reinterpret_cast<const float4*>(dy) + rd * LPR + sub);
       m = __ldg(mean + r);
       rs = __ldg(rstd + r);
     }
@@ -206,4 +213,30 @@ extern "C" int sgnn_layer_norm_bwd_static(const float* dy, const float* x, const
   }
   return sgnn_layer_norm_bwd(dy, x, mean, rstd, gamma, n_rows, width, dx, dgamma, dbeta, part,
                              sizeof(float) * (size_t)kLnMaxBlocks * 2 * kLnStaticMaxWidth, stream);
+}
+
+// sgnn_layer_norm_bwd for the graph-captured training step: row r of the upstream gradient is dy[dy_index[r]]
+// (NULL: dy[r]) -- the backward of the sum-aggregation's gather folded into this pass -- and the row count is
+// min(max_rows, *n_rows_dev) read on the device (NULL: max_rows).
+extern "C" int sgnn_layer_norm_bwd_rows(const float* dy, const int* dy_index, const float* x, const float* mean,
+                                        const float* rstd, const float* gamma, long max_rows, const int* n_rows_dev,
+                                        int width, float* dx, float* dgamma, float* dbeta, void* workspace,
+                                        size_t workspace_bytes, void* stream) {
+  SGNN_CHECK_ARG(sgnn_layer_norm_supported(width), "layer_norm_bwd_rows: width must be 32, 64 or 128, got %d", width);
+  SGNN_CHECK_ARG(workspace_bytes >= sgnn_layer_norm_bwd_workspace_bytes(width), "layer_norm_bwd_rows: workspace too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (max_rows <= 0) {
+    SGNN_CUDA(cudaMemsetAsync(dgamma, 0, sizeof(float) * width, st));
+    SGNN_CUDA(cudaMemsetAsync(dbeta, 0, sizeof(float) * width, st));
+    return SGNN_OK;
+  }
+  const int grid = ln_blocks(max_rows, width);
+  float* part = (float*)workspace;
+  if (width == 32) ln_bwd_kernel<8><<<grid, kLnThreads, 0, st>>>(dy, x, mean, rstd, gamma, max_rows, dx, part, dy_index, n_rows_dev);
+  else if (width == 64) ln_bwd_kernel<16><<<grid, kLnThreads, 0, st>>>(dy, x, mean, rstd, gamma, max_rows, dx, part, dy_index, n_rows_dev);
+  else ln_bwd_kernel<32><<<grid, kLnThreads, 0, st>>>(dy, x, mean, rstd, gamma, max_rows, dx, part, dy_index, n_rows_dev);
+  SGNN_LAUNCH_CHECK();
+  ln_bwd_finish_kernel<<<sgnn_ceil_div(2 * width, 32), dim3(32, 8), 0, st>>>(part, grid, width, dgamma, dbeta);
+  SGNN_LAUNCH_CHECK();
+  return SGNN_OK;
 }

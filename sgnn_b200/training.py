@@ -52,12 +52,9 @@ class FlatGradAllReduce:
             off += n
         dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=self.group)
         off = 0
-        for p in self.params:
+        for p in self.params:          # hand the reduced buffer out as views: no copy back
             n = p.numel()
-            if p.grad is None:
-                p.grad = self.flat[off:off + n].view_as(p).clone()
-            else:
-                p.grad.copy_(self.flat[off:off + n].view_as(p))
+            p.grad = self.flat[off:off + n].view_as(p)
             off += n
 
 
@@ -67,6 +64,23 @@ def global_particle_count(n_local: int, device, group=None) -> int:
     t = torch.tensor([n_local], dtype=torch.int64, device=device)
     dist.all_reduce(t, group=group)
     return int(t.item())
+
+
+def make_optimizer(params, lr: float, device=None) -> torch.optim.Adam:
+    """Adam as the reference builds it (train.py:199) in the form a captured step needs: fused, capturable,
+    learning rate held in a device tensor (set_lr updates it in place)."""
+    params = list(params)
+    dev = params[0].device if device is None else device
+    return torch.optim.Adam(params, lr=torch.tensor(float(lr), dtype=torch.float32, device=dev), fused=True,
+                            capturable=True)
+
+
+def set_lr(optimizer, lr: float):
+    for g in optimizer.param_groups:
+        if isinstance(g["lr"], torch.Tensor):
+            g["lr"].fill_(float(lr))
+        else:
+            g["lr"] = float(lr)
 
 
 class matmul_precision:
@@ -90,11 +104,13 @@ class matmul_precision:
 def train_step(simulator, optimizer, batch: Dict[str, torch.Tensor], noise_std: float,
                w_pos: float = 1.0, w_strain: float = 1.0, reducer: Optional[FlatGradAllReduce] = None,
                n_global: Optional[int] = None, noise: Optional[torch.Tensor] = None,
-               generator: Optional[torch.Generator] = None, matmul: str = "fp32") -> torch.Tensor:
+               generator: Optional[torch.Generator] = None, matmul: str = "fp32", engine=None) -> torch.Tensor:
     """One optimisation step on this rank's shard.  batch: positions [N,S,dim], particle_type [N],
     n_particles_per_example [B], next_position [N,dim], next_strain [N] (the tensors the
     reference's collate_fn emits, taylor_impact_data_loader.py:243-284), already on the device.
     Returns this rank's contribution to the global mean loss (sum over ranks = the loss)."""
+    if engine is not None:          # hand-written forward / backward / allreduce / Adam under one CUDA graph
+        return engine.step(batch, noise_std, noise=noise, generator=generator, n_global=n_global)
     pos = batch["positions"]
     if noise is None:
         noise = noise_utils.get_random_walk_noise_for_position_sequence(pos, noise_std, generator)
