@@ -125,6 +125,11 @@ int sgnn_linear_wgrad(const float* dy, const float* x, long n_rows, int out_feat
  *                        sum-aggregation) and the row count read on the device ("sgnn_mlp_ln_bwd")
  *   sgnn_linear_wgrad_ex weight / bias gradients on operand column blocks, device-side row count, scaled result
  *                        written into a column block of a wider gradient                                      */
+/* Edges of a receiver-sorted CSR grouped by sender (deterministic, no full sort): backward of propagate's sender
+ * gather (graph_network.py:173); edge count read on the device.                                              */
+size_t sgnn_csr_by_source_workspace_bytes(int n_nodes);
+int sgnn_csr_by_source(const int* src, const int* n_edges_dev, int max_edges, int n_nodes, int* rp_src, int* perm_src,
+                       void* workspace, size_t workspace_bytes, void* stream);
 int sgnn_train_pack(const SgnnPackDesc* descs_dev, int n_descs, float* img_hi, float* img_lo, void* stream);
 int sgnn_train_mlp_fwd(const SgnnTrainFwd* p, void* stream);
 int sgnn_train_mlp_bwd(const SgnnTrainBwd* p, void* stream);

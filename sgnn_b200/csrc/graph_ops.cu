@@ -11,6 +11,7 @@
 //   node / edge features                                   learned_simulator.py:257-312,
 //                                                          multi_scale_simulator.py:173-238
 #include "common.cuh"
+#include "scan.cuh"
 
 namespace sgnn {
 
@@ -108,6 +109,41 @@ edge_features_kernel(const float* __restrict__ pos, long stride, int dim, float 
   out[e * (dim + 1) + dim] = sqrtf(sq);
 }
 
+// ---- edges grouped by SENDER (the transposed CSR), built without a sort of the whole edge list ----
+// count: senders' out-degrees (integer atomics: order-independent); scan -> rp; fill: every edge takes a slot of
+// its sender's segment in arrival order; order: each sender's few slots (<= ~40) are sorted by edge id, so the
+// result -- and every sum taken over it -- is the same on every run.
+__global__ void __launch_bounds__(256)
+by_source_count_kernel(const int* __restrict__ src, const int* __restrict__ n_edges_dev, int max_edges, int n_nodes,
+                       int* __restrict__ count) {
+  const int e_total = min(max(*n_edges_dev, 0), max_edges);
+  for (int e = blockIdx.x * 256 + threadIdx.x; e < e_total; e += gridDim.x * 256) {
+    const int j = src[e];
+    if (j >= 0 && j < n_nodes) atomicAdd(count + j, 1);
+  }
+}
+__global__ void __launch_bounds__(256)
+by_source_fill_kernel(const int* __restrict__ src, const int* __restrict__ n_edges_dev, int max_edges, int n_nodes,
+                      const int* __restrict__ rp, int* __restrict__ cursor, int* __restrict__ perm) {
+  const int e_total = min(max(*n_edges_dev, 0), max_edges);
+  for (int e = blockIdx.x * 256 + threadIdx.x; e < e_total; e += gridDim.x * 256) {
+    const int j = src[e];
+    if (j >= 0 && j < n_nodes) perm[rp[j] + atomicAdd(cursor + j, 1)] = e;
+  }
+}
+__global__ void __launch_bounds__(256)
+by_source_order_kernel(const int* __restrict__ rp, int n_nodes, int* __restrict__ perm) {
+  const int j = blockIdx.x * 256 + threadIdx.x;
+  if (j >= n_nodes) return;
+  const int beg = rp[j], end = rp[j + 1];
+  for (int a = beg + 1; a < end; ++a) {              // insertion sort of a short segment
+    const int v = perm[a];
+    int b = a - 1;
+    while (b >= beg && perm[b] > v) { perm[b + 1] = perm[b]; --b; }
+    perm[b + 1] = v;
+  }
+}
+
 static int warp_grid(long rows) {
   long g = (rows + 7) / 8;
   if (g > 148L * 64) g = 148L * 64;
@@ -184,6 +220,35 @@ extern "C" int sgnn_edge_features(const float* pos, long stride, int dim, float 
   if (n_edges <= 0) return SGNN_OK;
   edge_features_kernel<<<sgnn_ceil_div(n_edges, 256), 256, 0, (cudaStream_t)stream>>>(pos, stride, dim, radius,
                                                                                      src, tgt, n_edges, out);
+  SGNN_LAUNCH_CHECK();
+  return SGNN_OK;
+}
+
+// Edges of a receiver-sorted CSR grouped by sender: rp_src [n_nodes + 1], perm_src [max_edges] (edge ids, ascending
+// inside a sender's segment).  Backward of the sender gather of PyG's propagate (graph_network.py:173): the
+// scatter-add over senders becomes sgnn_segment_sum_rows over (rp_src, perm_src).  The edge count is read on the
+// device (n_edges_dev, e.g. rowptr + n_nodes).  Workspace: sgnn_csr_by_source_workspace_bytes(n_nodes).
+extern "C" size_t sgnn_csr_by_source_workspace_bytes(int n_nodes) {
+  return sizeof(int) * ((size_t)2 * (n_nodes + 2) + scan_tmp_ints(n_nodes + 1) + 8);
+}
+extern "C" int sgnn_csr_by_source(const int* src, const int* n_edges_dev, int max_edges, int n_nodes, int* rp_src,
+                                  int* perm_src, void* workspace, size_t workspace_bytes, void* stream) {
+  SGNN_CHECK_ARG(n_nodes > 0 && max_edges > 0, "csr_by_source: empty graph");
+  SGNN_CHECK_ARG(workspace_bytes >= sgnn_csr_by_source_workspace_bytes(n_nodes), "csr_by_source: workspace too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  int* count = (int*)workspace;
+  int* cursor = count + (n_nodes + 2);
+  int* tmp = cursor + (n_nodes + 2);
+  SGNN_CUDA(cudaMemsetAsync(count, 0, sizeof(int) * 2 * (size_t)(n_nodes + 2), st));
+  int grid = sgnn_ceil_div(max_edges, 256);
+  if (grid > 148 * 8) grid = 148 * 8;
+  by_source_count_kernel<<<grid, 256, 0, st>>>(src, n_edges_dev, max_edges, n_nodes, count);
+  SGNN_LAUNCH_CHECK();
+  const int rc = exclusive_scan_i32(count, rp_src, n_nodes, tmp, st);
+  if (rc != SGNN_OK) return rc;
+  by_source_fill_kernel<<<grid, 256, 0, st>>>(src, n_edges_dev, max_edges, n_nodes, rp_src, cursor, perm_src);
+  SGNN_LAUNCH_CHECK();
+  by_source_order_kernel<<<sgnn_ceil_div(n_nodes, 256), 256, 0, st>>>(rp_src, n_nodes, perm_src);
   SGNN_LAUNCH_CHECK();
   return SGNN_OK;
 }

@@ -93,7 +93,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_chunk_kernel(const int* __r
   }
 }
 
-__global__ void scan_add_kernel(int* __restrict__ out, int n, const int* __restrict__ sums,
+static __global__ void scan_add_kernel(int* __restrict__ out, int n, const int* __restrict__ sums,
                                 int nblocks) {
   pdl_launch_dependents();
   pdl_wait();

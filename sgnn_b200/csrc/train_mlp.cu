@@ -27,11 +27,21 @@
 namespace sgnn {
 
 constexpr int kTrKChunk = 64;       // the A operand is staged in chunks of at most 64 columns
+// 256 threads per CTA: threads t and t + 128 own the SAME row (TMEM lane t & 127 -- a warp reaches the lane
+// quadrant 32 * (warp % 4)) and alternate over its 32-column chunks.  With one CTA per SM (the hi / lo operand
+// tiles and images take 130-190 KB) 128 threads meant ONE warp per scheduler: ncu showed 15 % issue utilisation
+// with every dependent-issue and shared-memory latency exposed (profiles/README.md, r02b).
+constexpr int kTrThreads = 256;
+__device__ __forceinline__ int tr_row() { return (int)threadIdx.x & (kTileRows - 1); }
+__device__ __forceinline__ int tr_half() { return (int)threadIdx.x >> 7; }
+__device__ __forceinline__ int tr_log2(int x) { return 31 - __clz(x); }
 
 struct TrMisc {
   uint64_t bar_w, bar_mma;
   uint32_t tmem_slot;
   int pad;
+  int tgt[kTileRows], src[kTileRows];
+  float2 red[2][kTileRows];           // LayerNorm: (mean, sum of squared deviations) of each half of a row
 };
 
 template <bool SPLIT>
@@ -47,7 +57,7 @@ template <bool SPLIT>
 __device__ __forceinline__ void tr_a_store32(char* a_hi, char* a_lo, int col, const float* v) {
 #pragma unroll
   for (int j = 0; j < 8; ++j)
-    tr_store4<SPLIT>(a_hi, a_lo, sw128_chunk_offset(threadIdx.x, col / 4 + j, kTileRows),
+    tr_store4<SPLIT>(a_hi, a_lo, sw128_chunk_offset(tr_row(), col / 4 + j, kTileRows),
                      make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]));
 }
 
@@ -58,32 +68,32 @@ __device__ __forceinline__ void tr_a_load(char* a_hi, char* a_lo, const float* _
                                           int c0, int width, int wpad, int rows_valid, float scale) {
   const bool vec = (width & 3) == 0 && (ld & 3) == 0 && (c0 & 3) == 0 && ((uintptr_t)src & 15) == 0;
   if (vec) {
-    const int chunks = wpad >> 2, wch = width >> 2;
+    const int chunks = wpad >> 2, wch = width >> 2, sh = tr_log2(chunks);        // wpad is 32 or 64
     const int total = kTileRows * chunks;
-    for (int idx0 = threadIdx.x; idx0 < total; idx0 += 4 * kThreads) {
+    for (int idx0 = threadIdx.x; idx0 < total; idx0 += 4 * kTrThreads) {
       float4 v[4];
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        const int idx = idx0 + u * kThreads;
-        const int r = idx / chunks, c = idx - r * chunks;
+        const int idx = idx0 + u * kTrThreads;
+        const int r = idx >> sh, c = idx & (chunks - 1);
         v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (idx < total && r < rows_valid && c < wch)
           v[u] = __ldg(reinterpret_cast<const float4*>(src + (row0 + r) * ld + c0) + c);
       }
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        const int idx = idx0 + u * kThreads;
+        const int idx = idx0 + u * kTrThreads;
         if (idx < total) {
-          const int r = idx / chunks, c = idx - r * chunks;
+          const int r = idx >> sh, c = idx & (chunks - 1);
           tr_store4<SPLIT>(a_hi, a_lo, sw128_chunk_offset(r, c, kTileRows),
                            make_float4(v[u].x * scale, v[u].y * scale, v[u].z * scale, v[u].w * scale));
         }
       }
     }
   } else {
-    const int total = kTileRows * wpad;
-    for (int idx = threadIdx.x; idx < total; idx += kThreads) {
-      const int r = idx / wpad, c = idx - r * wpad;
+    const int total = kTileRows * wpad, sh = tr_log2(wpad);
+    for (int idx = threadIdx.x; idx < total; idx += kTrThreads) {
+      const int r = idx >> sh, c = idx & (wpad - 1);
       float v = 0.f;
       if (r < rows_valid && c < width) v = __ldg(src + (row0 + r) * ld + c0 + c) * scale;
       const float h = to_tf32(v);
@@ -115,6 +125,12 @@ __device__ __forceinline__ void tr_gemm(TileAcc<true>& acc, const char* a_hi, co
   }
 }
 
+// 32 accumulator columns of this thread's row (lane quadrant of the warp: warp % 4)
+__device__ __forceinline__ void tr_acc_load32(const TileAcc<true>& acc, int col, float* v) {
+  const uint32_t lane_base = (uint32_t)(((threadIdx.x >> 5) & 3) * 32) << 16;
+  tmem_ld32(acc.tmem_base + lane_base + (uint32_t)col, v);
+}
+
 __device__ __forceinline__ int tr_rows(int max_rows, const int* n_rows_dev) {
   if (n_rows_dev == nullptr) return max_rows;
   const int n = *n_rows_dev;
@@ -128,8 +144,83 @@ __device__ __forceinline__ void tr_stage(char* dst, const float* src, int bytes,
                  bar);
 }
 
+// ---- exact fp32 staging tiles (same swizzled layout as the operands) -------------------------------------
+// Row-owner accesses to global memory touch 32 different 128-byte lines per warp instruction (32 L1 wavefronts
+// for 512 bytes); everything a thread reads or writes per ROW therefore goes through a shared-memory tile: the
+// row owner uses conflict-free 16-byte shared accesses, the global side is a cooperative loop in which a warp
+// covers whole contiguous rows (4 wavefronts per 512 bytes).
+__device__ __forceinline__ void tr_row_store32(char* t, int col, const float* v) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+    *reinterpret_cast<float4*>(t + sw128_chunk_offset(tr_row(), col / 4 + j, kTileRows)) =
+        make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+}
+__device__ __forceinline__ void tr_row_load32(const char* t, int col, float* v) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const float4 a = *reinterpret_cast<const float4*>(t + sw128_chunk_offset(tr_row(), col / 4 + j, kTileRows));
+    v[4 * j] = a.x; v[4 * j + 1] = a.y; v[4 * j + 2] = a.z; v[4 * j + 3] = a.w;
+  }
+}
+// tile[r][0:width) = a[ia[r]][0:width) (+ b[ib[r]][0:width)), rows >= rows_valid untouched; width % 4 == 0.
+// ia / ib: shared-memory index arrays (NULL: row0 + r).  Eight 16-byte loads in flight per thread.
+__device__ __forceinline__ void tr_tile_gather(char* t, const float* __restrict__ a, const float* __restrict__ b, long ld,
+                                               const int* ia, const int* ib, long row0, int width, int rows_valid) {
+  const int chunks = width >> 2, sh = tr_log2(chunks);          // width is 32, 64 or 128
+  const int total = rows_valid * chunks;
+  constexpr int U = 4;
+  for (int idx0 = threadIdx.x; idx0 < total; idx0 += U * kTrThreads) {
+    float4 va[U], vb[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int idx = idx0 + u * kTrThreads;
+      va[u] = vb[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (idx < total) {
+        const int r = idx >> sh, c = idx & (chunks - 1);
+        va[u] = __ldg(reinterpret_cast<const float4*>(a + (ia ? (long)ia[r] : row0 + r) * ld) + c);
+        if (b != nullptr) vb[u] = __ldg(reinterpret_cast<const float4*>(b + (ib ? (long)ib[r] : row0 + r) * ld) + c);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int idx = idx0 + u * kTrThreads;
+      if (idx < total) {
+        const int r = idx >> sh, c = idx & (chunks - 1);
+        *reinterpret_cast<float4*>(t + sw128_chunk_offset(r, c, kTileRows)) =
+            make_float4(va[u].x + vb[u].x, va[u].y + vb[u].y, va[u].z + vb[u].z, va[u].w + vb[u].w);
+      }
+    }
+  }
+}
+// dst[row0 + r][0:width) (=|+=) tile[r] (+ tile_lo[r]) (+ add[row0 + r]); coalesced; width % 4 == 0
+__device__ __forceinline__ void tr_tile_store(float* __restrict__ dst, long ld, long row0, const char* t, const char* t_lo,
+                                              int width, int rows_valid, bool accumulate, const float* __restrict__ add,
+                                              long ld_add) {
+  const int chunks = width >> 2, sh = tr_log2(chunks);
+  const int total = rows_valid * chunks;
+  for (int idx = threadIdx.x; idx < total; idx += kTrThreads) {
+    const int r = idx >> sh, c = idx & (chunks - 1);
+    const uint32_t off = sw128_chunk_offset(r, c, kTileRows);
+    float4 v = *reinterpret_cast<const float4*>(t + off);
+    if (t_lo != nullptr) {
+      const float4 l = *reinterpret_cast<const float4*>(t_lo + off);
+      v = make_float4(v.x + l.x, v.y + l.y, v.z + l.z, v.w + l.w);
+    }
+    if (add != nullptr) {
+      const float4 a = __ldg(reinterpret_cast<const float4*>(add + (row0 + r) * ld_add) + c);
+      v = make_float4(v.x + a.x, v.y + a.y, v.z + a.z, v.w + a.w);
+    }
+    float4* d = reinterpret_cast<float4*>(dst + (row0 + r) * ld) + c;
+    if (accumulate) {
+      const float4 z = *d;
+      v = make_float4(v.x + z.x, v.y + z.y, v.z + z.z, v.w + z.w);
+    }
+    *d = v;
+  }
+}
+
 struct TrFwdSmem {
-  int w1, w2, a, a_bytes, misc, total;
+  int w1, w2, a, a_bytes, g, g_bytes, misc, total;
 };
 __host__ __device__ inline TrFwdSmem tr_fwd_smem(int kpad, int hidden, int out, int n_linear, int split) {
   TrFwdSmem s;
@@ -140,13 +231,16 @@ __host__ __device__ inline TrFwdSmem tr_fwd_smem(int kpad, int hidden, int out, 
   if (n_linear == 2 && hidden > aw) aw = hidden;
   s.a_bytes = kTileRows * aw * 4;
   s.a = (s.w1 + s.w2) * (split ? 2 : 1);
-  s.misc = s.a + s.a_bytes * (split ? 2 : 1);
+  s.g = s.a + s.a_bytes * (split ? 2 : 1);
+  const int gw = n_linear == 2 ? (hidden > out ? hidden : ((out + 31) & ~31)) : hidden;
+  s.g_bytes = kTileRows * gw * 4;
+  s.misc = s.g + s.g_bytes;
   s.total = s.misc + (int)sizeof(TrMisc) + 1024;
   return s;
 }
 
 template <bool SPLIT>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kTrThreads)
 train_fwd_kernel(const SgnnTrainFwd p) {
   char* smem = smem_base_1024();
   const TrFwdSmem L = tr_fwd_smem(p.kpad, p.hidden, p.out, p.n_linear, SPLIT);
@@ -158,7 +252,7 @@ train_fwd_kernel(const SgnnTrainFwd p) {
   char* a_hi = smem + L.a;
   char* a_lo = SPLIT ? a_hi + L.a_bytes : a_hi;
   TrMisc* misc = reinterpret_cast<TrMisc*>(smem + L.misc);
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, row = tr_row(), half = tr_half();
 
   if (tid == 0) {
     mbar_init(&misc->bar_w, 1);
@@ -176,20 +270,24 @@ train_fwd_kernel(const SgnnTrainFwd p) {
   acc_setup<true>(acc, pow2_cols(p.hidden + (p.n_linear == 2 ? out_pad : 0)), &misc->bar_mma, &misc->tmem_slot, nullptr);
   mbar_wait(&misc->bar_w, 0);
 
+  char* g_t = smem + L.g;                                         // exact fp32 staging tile
   const int rows = tr_rows(p.max_rows, p.n_rows_dev);
   const int n_tiles = (rows + kTileRows - 1) / kTileRows;
+  const bool gathered = p.add_p != nullptr;
   for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const long row0 = (long)tile * kTileRows;
     const int rows_valid = rows - row0 < kTileRows ? (int)(rows - row0) : kTileRows;
-    const long r = row0 + tid;
-    const bool valid = tid < rows_valid;
+    const long r = row0 + row;
+    const bool valid = row < rows_valid;
     int tg = 0, sr = 0;
     if (valid && p.tgt != nullptr) { tg = __ldg(p.tgt + r); sr = __ldg(p.src + r); }
+    if (half == 0) { misc->tgt[row] = tg; misc->src[row] = sr; }
 
     // ---- first Linear, K staged in chunks of 64 columns ----
     for (int kc = 0; kc < p.kpad; kc += kTrKChunk) {
       const int kw = p.kpad - kc < kTrKChunk ? p.kpad - kc : kTrKChunk;
       if (p.prologue == SGNN_TPRO_EDGE_FEATURES) {
+       if (half == 0) {
         float v[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = 0.f;
@@ -206,6 +304,7 @@ train_fwd_kernel(const SgnnTrainFwd p) {
             for (int d = 0; d <= p.dim; ++d) p.feat_out[r * (p.dim + 1) + d] = v[d];
         }
         tr_a_store32<SPLIT>(a_hi, a_lo, 0, v);
+       }
       } else if (p.prologue == SGNN_TPRO_ROWS2 && kc >= p.k0) {
         tr_a_load<SPLIT>(a_hi, a_lo, p.a1, p.ld1, row0, kc - p.k0, p.k1 - (kc - p.k0) < kw ? p.k1 - (kc - p.k0) : kw, kw,
                          rows_valid, 1.0f);
@@ -215,101 +314,100 @@ train_fwd_kernel(const SgnnTrainFwd p) {
       a_tile_publish<true>();
       const int woff = (kc / kKBlock) * p.hidden * kKBlockBytes;
       tr_gemm<SPLIT>(acc, a_hi, a_lo, w1h + woff, w1l + woff, kw, p.hidden, 0, kc > 0);
+      // while the last chunk's product runs: receiver + sender terms of the rows, gathered with whole-row requests
+      if (gathered && kc + kTrKChunk >= p.kpad)
+        tr_tile_gather(g_t, p.add_p, p.add_q, p.ld_add, misc->tgt, misc->src, row0, p.hidden, rows_valid);
       gemm_wait<true>(acc);
     }
+    if (gathered) __syncthreads();
 
-    // ---- bias (+ gathered receiver / sender terms), ReLU, keep h1, feed the second Linear ----
-    for (int c = 0; c < p.hidden; c += 32) {
+    // ---- bias (+ gathered terms), ReLU, feed the second Linear; h1 leaves from the operand tile ----
+    for (int c = half * 32; c < p.hidden; c += 64) {
       float v[32];
-      acc_load32<true>(acc, c, v);
+      tr_acc_load32(acc, c, v);
 #pragma unroll
       for (int j = 0; j < 32; ++j)
         if (p.b1 != nullptr && c + j < p.b1_cols) v[j] += __ldg(p.b1 + c + j);
-      if (p.add_p != nullptr && valid) {
-        const float4* pp = reinterpret_cast<const float4*>(p.add_p + (long)tg * p.ld_add + c);
-        const float4* qq = reinterpret_cast<const float4*>(p.add_q + (long)sr * p.ld_add + c);
+      if (gathered && valid) {
+        float gsum[32];
+        tr_row_load32(g_t, c, gsum);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const float4 a = __ldg(pp + j), b = __ldg(qq + j);
-          v[4 * j] += a.x + b.x; v[4 * j + 1] += a.y + b.y; v[4 * j + 2] += a.z + b.z; v[4 * j + 3] += a.w + b.w;
-        }
+        for (int j = 0; j < 32; ++j) v[j] += gsum[j];
       }
       if (p.n_linear == 2) {
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = valid ? fmaxf(v[j], 0.f) : 0.f;
-        if (valid) {
-          float4* h = reinterpret_cast<float4*>(p.h1 + r * p.hidden + c);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) h[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-        }
         tr_a_store32<SPLIT>(a_hi, a_lo, c, v);
-      } else if (valid) {
-        float4* y = reinterpret_cast<float4*>(p.y + r * p.ld_y + c);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) y[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+      } else {
+        tr_row_store32(g_t, c, v);
       }
     }
     if (p.n_linear != 2) {
       tc_fence_before_sync();
-      __syncthreads();                      // every thread has read its accumulator before the next tile's MMAs
+      __syncthreads();
+      tr_tile_store(p.y, p.ld_y, row0, g_t, nullptr, p.hidden, rows_valid, false, nullptr, 0);
+      __syncthreads();                      // staging tile and accumulator free for the next tile
       continue;
     }
     a_tile_publish<true>();
     tr_gemm<SPLIT>(acc, a_hi, a_lo, w2h, w2l, p.hidden, out_pad, acc1, false);
+    // h1 = hi (+ lo) from the operand tiles while the second product runs (plain TF32 mode keeps the rounded value)
+    tr_tile_store(p.h1, p.hidden, row0, a_hi, SPLIT ? a_lo : nullptr, p.hidden, rows_valid, false, nullptr, 0);
     gemm_wait<true>(acc);
+    __syncthreads();                        // everybody is done reading the operand tiles: they become staging space
 
-    // ---- second Linear's bias, LayerNorm (statistics kept), residual, output ----
-    float mean = 0.f, rstd = 1.f;
-    if (p.has_ln) {
+    // ---- second Linear's bias, LayerNorm (statistics kept), output ----
+    if (p.has_ln) {                         // out is a multiple of 64 here: each half of the row owns out / 2 columns
+      const float n_loc = 0.5f * (float)p.out;
       float s4[4] = {0.f, 0.f, 0.f, 0.f};
-      for (int c = 0; c < p.out; c += 32) {
+      for (int c = half * 32; c < p.out; c += 64) {
         float v[32];
-        acc_load32<true>(acc, acc1 + c, v);
+        tr_acc_load32(acc, acc1 + c, v);
 #pragma unroll
         for (int j = 0; j < 32; ++j) s4[j & 3] += v[j] + __ldg(p.b2 + c + j);
       }
-      mean = ((s4[0] + s4[1]) + (s4[2] + s4[3])) / (float)p.out;
+      const float m_loc = ((s4[0] + s4[1]) + (s4[2] + s4[3])) / n_loc;
       float q4[4] = {0.f, 0.f, 0.f, 0.f};
-      for (int c = 0; c < p.out; c += 32) {
+      for (int c = half * 32; c < p.out; c += 64) {
         float v[32];
-        acc_load32<true>(acc, acc1 + c, v);
+        tr_acc_load32(acc, acc1 + c, v);
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
-          const float d = v[j] + __ldg(p.b2 + c + j) - mean;
+          const float d = v[j] + __ldg(p.b2 + c + j) - m_loc;
           q4[j & 3] = fmaf(d, d, q4[j & 3]);
         }
       }
-      rstd = 1.0f / sqrtf(((q4[0] + q4[1]) + (q4[2] + q4[3])) / (float)p.out + 1e-5f);
-      if (valid) { p.mean[r] = mean; p.rstd[r] = rstd; }
-    }
-    for (int c = 0; c < out_pad; c += 32) {
-      float v[32];
-      acc_load32<true>(acc, acc1 + c, v);
-      if (!valid) continue;
-      if (p.has_ln) {                       // out is a multiple of 32 here (checked by the launcher)
+      misc->red[half][row] = make_float2(m_loc, (q4[0] + q4[1]) + (q4[2] + q4[3]));
+      __syncthreads();
+      const float2 oth = misc->red[half ^ 1][row];          // pairwise combination of the two halves' moments
+      const float dm = oth.x - m_loc;
+      const float mean = 0.5f * (m_loc + oth.x);
+      const float m2 = ((q4[0] + q4[1]) + (q4[2] + q4[3])) + oth.y + dm * dm * (0.5f * n_loc);
+      const float rstd = 1.0f / sqrtf(m2 / (float)p.out + 1e-5f);
+      if (valid && half == 0) { p.mean[r] = mean; p.rstd[r] = rstd; }
+      for (int c = half * 32; c < p.out; c += 64) {
+        float v[32];
+        tr_acc_load32(acc, acc1 + c, v);
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] += __ldg(p.b2 + c + j);
-        float4* y2 = reinterpret_cast<float4*>(p.y2 + r * p.out + c);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) y2[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        tr_row_store32(a_hi, c, v);         // y2, the LayerNorm's input
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = (v[j] - mean) * rstd * __ldg(p.gamma + c + j) + __ldg(p.beta + c + j);
-        if (p.res != nullptr) {
-          const float4* rs = reinterpret_cast<const float4*>(p.res + r * p.ld_res + c);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float4 a = __ldg(rs + j);
-            v[4 * j] += a.x; v[4 * j + 1] += a.y; v[4 * j + 2] += a.z; v[4 * j + 3] += a.w;
-          }
-        }
-        float4* y = reinterpret_cast<float4*>(p.y + r * p.ld_y + c);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) y[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-      } else {
-        for (int j = 0; j < 32 && c + j < p.out; ++j) p.y[r * p.ld_y + c + j] = v[j] + __ldg(p.b2 + c + j);
+        tr_row_store32(g_t, c, v);          // y (the residual is added on the way out)
       }
+      tc_fence_before_sync();
+      __syncthreads();
+      tr_tile_store(p.y2, p.out, row0, a_hi, nullptr, p.out, rows_valid, false, nullptr, 0);
+      tr_tile_store(p.y, p.ld_y, row0, g_t, nullptr, p.out, rows_valid, false, p.res, p.ld_res);
+    } else {
+      for (int c = half * 32; c < out_pad; c += 64) {
+        float v[32];
+        tr_acc_load32(acc, acc1 + c, v);
+        if (valid)
+          for (int j = 0; j < 32 && c + j < p.out; ++j) p.y[r * p.ld_y + c + j] = v[j] + __ldg(p.b2 + c + j);
+      }
+      tc_fence_before_sync();
     }
-    tc_fence_before_sync();
     __syncthreads();
   }
   acc_teardown<true>(acc);
@@ -317,7 +415,7 @@ train_fwd_kernel(const SgnnTrainFwd p) {
 
 // ------------------------------------------------------------------------------------------ backward
 struct TrBwdSmem {
-  int w2t, w1t, a, a_bytes, misc, total;
+  int w2t, w1t, a, a_bytes, g, g_bytes, misc, total;
 };
 __host__ __device__ inline TrBwdSmem tr_bwd_smem(int k_dy, int n_linear, int hidden, int want_dx, int kx, int split) {
   TrBwdSmem s;
@@ -329,13 +427,16 @@ __host__ __device__ inline TrBwdSmem tr_bwd_smem(int k_dy, int n_linear, int hid
   if (n_linear == 2 && hidden > aw) aw = hidden;
   s.a_bytes = kTileRows * aw * 4;
   s.a = (s.w2t + s.w1t) * (split ? 2 : 1);
-  s.misc = s.a + s.a_bytes * (split ? 2 : 1);
+  s.g = s.a + s.a_bytes * (split ? 2 : 1);
+  s.g_bytes = kTileRows * kTrKChunk * 4;                   // h1 tile, then the second half of dx
+  if (n_linear == 2 && hidden > kTrKChunk) s.g_bytes = kTileRows * hidden * 4;
+  s.misc = s.g + s.g_bytes;
   s.total = s.misc + (int)sizeof(TrMisc) + 1024;
   return s;
 }
 
 template <bool SPLIT>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kTrThreads)
 train_bwd_kernel(const SgnnTrainBwd p) {
   char* smem = smem_base_1024();
   const TrBwdSmem L = tr_bwd_smem(p.k_dy, p.n_linear, p.hidden, p.want_dx, p.kx, SPLIT);
@@ -348,7 +449,7 @@ train_bwd_kernel(const SgnnTrainBwd p) {
   char* a_hi = smem + L.a;
   char* a_lo = SPLIT ? a_hi + L.a_bytes : a_hi;
   TrMisc* misc = reinterpret_cast<TrMisc*>(smem + L.misc);
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, row = tr_row(), half = tr_half();
 
   if (tid == 0) {
     mbar_init(&misc->bar_w, 1);
@@ -369,52 +470,45 @@ train_bwd_kernel(const SgnnTrainBwd p) {
                   &misc->bar_mma, &misc->tmem_slot, nullptr);
   mbar_wait(&misc->bar_w, 0);
 
+  char* g_t = smem + L.g;
   const int rows = tr_rows(p.max_rows, p.n_rows_dev);
   const int n_tiles = (rows + kTileRows - 1) / kTileRows;
   for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const long row0 = (long)tile * kTileRows;
     const int rows_valid = rows - row0 < kTileRows ? (int)(rows - row0) : kTileRows;
-    const long r = row0 + tid;
-    const bool valid = tid < rows_valid;
+    const bool valid = row < rows_valid;
 
     if (p.n_linear == 2) {
-      // ---- dh = dy W2 (K = width of dy, staged in chunks), ReLU mask, dpre kept ----
+      // ---- dh = dy W2 (K = width of dy, staged in chunks), ReLU mask from the h1 tile, dpre kept ----
       for (int kc = 0; kc < kdp; kc += kTrKChunk) {
         const int kw = kdp - kc < kTrKChunk ? kdp - kc : kTrKChunk;
         tr_a_load<SPLIT>(a_hi, a_lo, p.dy, p.ld_dy, row0, kc, p.k_dy - kc < kw ? p.k_dy - kc : kw, kw, rows_valid, 1.0f);
         a_tile_publish<true>();
         const int woff = (kc / kKBlock) * p.hidden * kKBlockBytes;
         tr_gemm<SPLIT>(acc, a_hi, a_lo, w2h + woff, w2l + woff, kw, p.hidden, 0, kc > 0);
+        if (kc + kTrKChunk >= kdp)          // while the product runs: this tile of h1, whole rows per request
+          tr_tile_gather(g_t, p.h1, nullptr, p.hidden, nullptr, nullptr, row0, p.hidden, rows_valid);
         gemm_wait<true>(acc);
       }
-      for (int c = 0; c < p.hidden; c += 32) {
-        float v[32];
-        acc_load32<true>(acc, c, v);
-        if (valid) {
-          const float4* h = reinterpret_cast<const float4*>(p.h1 + r * p.hidden + c);
-          float4* dp = reinterpret_cast<float4*>(p.dpre + r * p.hidden + c);
+      __syncthreads();
+      for (int c = half * 32; c < p.hidden; c += 64) {
+        float v[32], h[32];
+        tr_acc_load32(acc, c, v);
+        tr_row_load32(g_t, c, h);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float4 a = __ldg(h + j);
-            v[4 * j] = a.x > 0.f ? v[4 * j] : 0.f;
-            v[4 * j + 1] = a.y > 0.f ? v[4 * j + 1] : 0.f;
-            v[4 * j + 2] = a.z > 0.f ? v[4 * j + 2] : 0.f;
-            v[4 * j + 3] = a.w > 0.f ? v[4 * j + 3] : 0.f;
-            dp[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = 0.f;
-        }
-        if (p.want_dx) tr_a_store32<SPLIT>(a_hi, a_lo, c, v);
+        for (int j = 0; j < 32; ++j) v[j] = (valid && h[j] > 0.f) ? v[j] : 0.f;
+        tr_a_store32<SPLIT>(a_hi, a_lo, c, v);
+        if (!SPLIT) tr_row_store32(g_t, c, v);      // plain TF32: the operand tile holds rounded values, dpre leaves exact
       }
+      a_tile_publish<true>();
+      if (p.want_dx) tr_gemm<SPLIT>(acc, a_hi, a_lo, w1h, w1l, p.hidden, p.kx, accx, false);
+      if (SPLIT) tr_tile_store(p.dpre, p.hidden, row0, a_hi, a_lo, p.hidden, rows_valid, false, nullptr, 0);
+      else tr_tile_store(p.dpre, p.hidden, row0, g_t, nullptr, p.hidden, rows_valid, false, nullptr, 0);
       if (!p.want_dx) {
         tc_fence_before_sync();
         __syncthreads();
         continue;
       }
-      a_tile_publish<true>();
-      tr_gemm<SPLIT>(acc, a_hi, a_lo, w1h, w1l, p.hidden, p.kx, accx, false);
       gemm_wait<true>(acc);
     } else {
       // ---- dx = dy W1 directly (K = width of dy, staged in chunks) ----
@@ -428,37 +522,18 @@ train_bwd_kernel(const SgnnTrainBwd p) {
       }
     }
     (void)k2;
-    // ---- route dx by columns: [0, k0) -> dx0, [k0, k0 + k1) -> dx1 ----
-    for (int c = 0; c < p.kx; c += 32) {
+    __syncthreads();                        // operand and staging tiles are free: dx is staged there
+    // ---- dx by columns: [0, k0) -> dx0 through the operand tile, [k0, k0 + k1) -> dx1 through the staging tile ----
+    for (int c = half * 32; c < p.kx; c += 64) {
       float v[32];
-      acc_load32<true>(acc, accx + c, v);
-      if (!valid) continue;
-      const bool second = c >= p.k0;
-      float* dst = second ? p.dx1 + r * p.ld_dx1 + (c - p.k0) : p.dx0 + r * p.ld_dx0 + c;
-      const bool accum = second ? p.acc1 != 0 : p.acc0 != 0;
-      const int wlim = (second ? p.k0 + p.k1 : p.k0) - c;          // columns of this chunk that exist (>= 16)
-      if (second && p.add1 != nullptr) {
-        const float4* ad = reinterpret_cast<const float4*>(p.add1 + r * p.ld_add1 + (c - p.k0));
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-          if (4 * j < wlim) {
-            const float4 a = __ldg(ad + j);
-            v[4 * j] += a.x; v[4 * j + 1] += a.y; v[4 * j + 2] += a.z; v[4 * j + 3] += a.w;
-          }
-      }
-      float4* d4 = reinterpret_cast<float4*>(dst);
-#pragma unroll
-      for (int j = 0; j < 8; ++j)
-        if (4 * j < wlim) {
-          float4 o = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-          if (accum) {
-            const float4 z = d4[j];
-            o = make_float4(o.x + z.x, o.y + z.y, o.z + z.z, o.w + z.w);
-          }
-          d4[j] = o;
-        }
+      tr_acc_load32(acc, accx + c, v);
+      if (c < p.k0) tr_row_store32(a_hi, c, v);
+      else tr_row_store32(g_t, c - p.k0, v);
     }
     tc_fence_before_sync();
+    __syncthreads();
+    tr_tile_store(p.dx0, p.ld_dx0, row0, a_hi, nullptr, p.k0, rows_valid, p.acc0 != 0, nullptr, 0);
+    if (p.k1 > 0) tr_tile_store(p.dx1, p.ld_dx1, row0, g_t, nullptr, p.k1, rows_valid, p.acc1 != 0, p.add1, p.ld_add1);
     __syncthreads();
   }
   acc_teardown<true>(acc);
@@ -509,7 +584,8 @@ extern "C" int sgnn_train_mlp_fwd(const SgnnTrainFwd* p, void* stream) {
   SGNN_CHECK_ARG(p->hidden >= 16 && p->hidden % 32 == 0 && p->hidden <= 128, "train_mlp_fwd: hidden %d must be 32, 64, 96 or 128",
                  p->hidden);
   SGNN_CHECK_ARG(p->n_linear == 1 || (p->out >= 1 && p->out <= 128), "train_mlp_fwd: bad out %d", p->out);
-  SGNN_CHECK_ARG(!p->has_ln || (p->n_linear == 2 && p->out % 32 == 0), "train_mlp_fwd: LayerNorm needs out %% 32 == 0");
+  SGNN_CHECK_ARG(!p->has_ln || (p->n_linear == 2 && (p->out == 64 || p->out == 128)), "train_mlp_fwd: LayerNorm needs out 64 or 128");
+  SGNN_CHECK_ARG(p->hidden == 32 || p->hidden == 64 || p->hidden == 128, "train_mlp_fwd: hidden must be 32, 64 or 128");
   SGNN_CHECK_ARG(p->n_linear == 2 || p->hidden % 32 == 0, "train_mlp_fwd: single Linear needs width %% 32 == 0");
   SGNN_CHECK_ARG(p->prologue != SGNN_TPRO_ROWS2 || (p->k0 % kTrKChunk == 0 && p->k0 + p->k1 <= p->kpad),
                  "train_mlp_fwd: ROWS2 needs k0 %% 64 == 0");
@@ -534,10 +610,10 @@ extern "C" int sgnn_train_mlp_fwd(const SgnnTrainFwd* p, void* stream) {
   if (grid > tiles) grid = tiles;
   if (p->split) {
     SGNN_ENSURE_SMEM(train_fwd_kernel<true>, s.total);
-    train_fwd_kernel<true><<<grid, kThreads, s.total, (cudaStream_t)stream>>>(*p);
+    train_fwd_kernel<true><<<grid, kTrThreads, s.total, (cudaStream_t)stream>>>(*p);
   } else {
     SGNN_ENSURE_SMEM(train_fwd_kernel<false>, s.total);
-    train_fwd_kernel<false><<<grid, kThreads, s.total, (cudaStream_t)stream>>>(*p);
+    train_fwd_kernel<false><<<grid, kTrThreads, s.total, (cudaStream_t)stream>>>(*p);
   }
   SGNN_LAUNCH_CHECK();
   return SGNN_OK;
@@ -550,6 +626,9 @@ extern "C" int sgnn_train_mlp_bwd(const SgnnTrainBwd* p, void* stream) {
                                       al16(p->h1) && al16(p->dpre)),
                  "train_mlp_bwd: hidden %d must be 32..128 (multiple of 32) with h1 / dpre given", p->hidden);
   SGNN_CHECK_ARG(p->n_linear == 2 || p->want_dx, "train_mlp_bwd: a single Linear has only the dx product");
+  SGNN_CHECK_ARG(p->n_linear == 1 || p->hidden == 64 || p->hidden == 128, "train_mlp_bwd: hidden must be 64 or 128");
+  SGNN_CHECK_ARG(!p->want_dx || ((p->k0 == 64 || p->k0 == 32 || p->k0 == 128) && (p->k1 == 0 || p->k1 == 64 || p->k1 == 32)),
+                 "train_mlp_bwd: dx widths must be powers of two (32..128)");
   if (p->want_dx) {
     SGNN_CHECK_ARG(p->kx == p->k0 + p->k1 && p->kx % 16 == 0 && p->kx <= 128 && p->k0 % 32 == 0 && p->k0 > 0,
                    "train_mlp_bwd: dx widths k0 %d k1 %d", p->k0, p->k1);
@@ -570,10 +649,10 @@ extern "C" int sgnn_train_mlp_bwd(const SgnnTrainBwd* p, void* stream) {
   if (grid > tiles) grid = tiles;
   if (p->split) {
     SGNN_ENSURE_SMEM(train_bwd_kernel<true>, s.total);
-    train_bwd_kernel<true><<<grid, kThreads, s.total, (cudaStream_t)stream>>>(*p);
+    train_bwd_kernel<true><<<grid, kTrThreads, s.total, (cudaStream_t)stream>>>(*p);
   } else {
     SGNN_ENSURE_SMEM(train_bwd_kernel<false>, s.total);
-    train_bwd_kernel<false><<<grid, kThreads, s.total, (cudaStream_t)stream>>>(*p);
+    train_bwd_kernel<false><<<grid, kTrThreads, s.total, (cudaStream_t)stream>>>(*p);
   }
   SGNN_LAUNCH_CHECK();
   return SGNN_OK;

@@ -67,7 +67,7 @@ def load_model(simulator, device, config: dict):
     simulator.load(str(mp))
     simulator.to(device)
     state = torch.load(str(sp), map_location="cpu")
-    optimizer = torch.optim.Adam(simulator.parameters())
+    optimizer = training.make_optimizer(simulator.parameters(), 1e-3, device)
     optimizer.load_state_dict(state["optimizer_state"])
     gts = state["global_train_state"]
     return simulator, int(gts["step"]), optimizer, float(gts.get("lowest_eval_loss", float("inf")))
@@ -85,13 +85,14 @@ def train(simulator: MultiScaleSimulator, metadata: dict, device, config: dict, 
     """Training loop (reference :79-287).  Returns (last step, lowest validation loss)."""
     rank = dist.get_rank() if dist.is_initialized() else 0
     world = dist.get_world_size() if dist.is_initialized() else 1
-    optimizer = torch.optim.Adam(simulator.parameters(), lr=config["lr_init"], fused=True)
+    simulator.to(device)
+    optimizer = training.make_optimizer(simulator.parameters(), config["lr_init"], device)
     step, lowest = 0, float("inf")
     if config.get("model_file"):
         try:
             simulator, step, optimizer, lowest = load_model(simulator, device, config)
-            for g in optimizer.param_groups:
-                g["lr"] = training.learning_rate(step, config["lr_init"], config["lr_decay"], config["lr_decay_steps"])
+            training.set_lr(optimizer, training.learning_rate(step, config["lr_init"], config["lr_decay"],
+                                                              config["lr_decay_steps"]))
             if rank == 0:
                 print(f"Resumed training from step {step}")
         except FileNotFoundError as e:           # reference :107-112: start fresh
@@ -119,8 +120,7 @@ def train(simulator: MultiScaleSimulator, metadata: dict, device, config: dict, 
                                        config["loss_weight_position"], config["loss_weight_strain"],
                                        reducer=reducer, n_global=n_glob, generator=gen)
             lr_new = training.learning_rate(step, config["lr_init"], config["lr_decay"], config["lr_decay_steps"])
-            for g in optimizer.param_groups:
-                g["lr"] = lr_new
+            training.set_lr(optimizer, lr_new)
             if step % log_every == 0:
                 if world > 1:
                     dist.all_reduce(loss)

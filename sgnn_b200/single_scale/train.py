@@ -10,6 +10,9 @@ train_state-best-{step:06}.pt with {'optimizer_state', 'global_train_state': {'s
     NCCL allreduce, sgnn_b200/training.py); rank 0 validates and writes checkpoints;
   * a resumed run continues from the restored step and learning rate (the reference resets `step`
     to 0 after loading, train.py:221 -- SURVEY.md 8(f) rank 4);
+  * the optimisation step runs as ONE CUDA graph of hand-written kernels (sgnn_b200/train_engine.py: weight
+    images, neighbour search, forward, loss, backward, gradient allreduce, Adam) whenever the model is one the
+    engine covers and every batch has the same particle count; otherwise through torch.autograd (train_ops.py);
   * the loss scalar is read back every `log_every` steps only, not every step;
   * Weights & Biases logging is not wired (no network); `log` is accepted and ignored.
 """
@@ -26,7 +29,7 @@ import torch.distributed as dist
 import yaml
 
 from .. import data as data_mod
-from .. import training
+from .. import train_engine, training
 from . import evaluate, learned_simulator
 
 
@@ -122,7 +125,7 @@ def load_model(simulator, device, config: dict):
     simulator.load(str(mp))
     simulator.to(device)                       # before the optimizer: load_state_dict casts its state to the parameters' device
     state = torch.load(str(sp), map_location="cpu")
-    optimizer = torch.optim.Adam(simulator.parameters())
+    optimizer = training.make_optimizer(simulator.parameters(), 1e-3, device)
     optimizer.load_state_dict(state["optimizer_state"])
     gts = state["global_train_state"]
     return simulator, int(gts["step"]), optimizer, float(gts.get("lowest_eval_loss", float("inf")))
@@ -140,14 +143,16 @@ def train(simulator, metadata: dict, device, config: dict, log_every: int = 10, 
     """Training loop (train.py:185-428).  Returns (last step, lowest validation loss)."""
     rank = dist.get_rank() if dist.is_initialized() else 0
     world = dist.get_world_size() if dist.is_initialized() else 1
-    optimizer = torch.optim.Adam(simulator.parameters(), lr=config["lr_init"], fused=True)   # one kernel per step instead of ~10 foreach launches
+    simulator.to(device)
+    optimizer = training.make_optimizer(simulator.parameters(), config["lr_init"], device)   # fused, capturable, lr on the device
     step, lowest = 0, float("inf")
     if config.get("model_file") is not None:
         simulator, step, optimizer, lowest = load_model(simulator, device, config)
-        for g in optimizer.param_groups:
-            g["lr"] = training.learning_rate(step, config["lr_init"], config["lr_decay"], config["lr_decay_steps"])
+        training.set_lr(optimizer, training.learning_rate(step, config["lr_init"], config["lr_decay"],
+                                                          config["lr_decay_steps"]))
     simulator.train()
-    simulator.to(device)
+    engines = {}                                   # particle count -> TrainEngine (captured step), at most two alive
+    use_engine = config.get("train_engine", True) and train_engine.supports(simulator)
     loader = data_mod.get_data_loader_by_samples(
         str(Path(config["data_path"]) / "train.npz"), config["input_sequence_length"], config["batch_size"],
         shuffle=True, device=device, seed=seed, rank=rank, world=world)
@@ -160,12 +165,21 @@ def train(simulator, metadata: dict, device, config: dict, log_every: int = 10, 
             step += 1
             batch = {**b["input"], **b["output"]}
             n_glob = training.global_particle_count(batch["positions"].shape[0], device) if world > 1 else None
+            eng = None
+            if use_engine:
+                n_loc = batch["positions"].shape[0]
+                eng = engines.get(n_loc)
+                if eng is None:
+                    while len(engines) >= 2:
+                        engines.pop(next(iter(engines)))
+                    eng = engines[n_loc] = train_engine.TrainEngine(
+                        simulator, optimizer, n_loc, device, w_pos=config["loss_weight_position"],
+                        w_strain=config["loss_weight_strain"])
             loss = training.train_step(simulator, optimizer, batch, config["noise_std"],
                                        config["loss_weight_position"], config["loss_weight_strain"],
-                                       reducer=reducer, n_global=n_glob, generator=gen)
+                                       reducer=reducer, n_global=n_glob, generator=gen, engine=eng)
             lr_new = training.learning_rate(step, config["lr_init"], config["lr_decay"], config["lr_decay_steps"])
-            for g in optimizer.param_groups:
-                g["lr"] = lr_new
+            training.set_lr(optimizer, lr_new)
             if step % log_every == 0:
                 if world > 1:
                     dist.all_reduce(loss)

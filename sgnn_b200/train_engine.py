@@ -127,6 +127,21 @@ class _Images:
         return off
 
 
+class _Timed:
+    def __init__(self, store, name):
+        self.store, self.name = store, name
+
+    def __enter__(self):
+        if self.store is not None:
+            self.ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+            self.ev[0].record()
+
+    def __exit__(self, *a):
+        if self.store is not None:
+            self.ev[1].record()
+            self.store.setdefault(self.name, []).append(self.ev)
+
+
 class TrainEngine:
     """One training step of `sim` on n particles per rank (module docstring).
 
@@ -170,8 +185,7 @@ class TrainEngine:
         csr = self.rg.csr
         self.cap = cap = csr.max_edges
         self.n_edges_dev = csr.rowptr.data_ptr() + 4 * n                  # int32 rowptr[n], read by every edge kernel
-        self.ar_cap = torch.arange(cap, dtype=torch.int32, device=dev)
-        self.ar_n1 = torch.arange(n + 1, dtype=torch.int32, device=dev)
+        self.ws_src = torch.empty(self.lib.sgnn_csr_by_source_workspace_bytes(n), dtype=torch.uint8, device=dev)
         self.perm_src = torch.zeros(cap, dtype=torch.int32, device=dev)
         self.rp_src = torch.zeros(n + 1, dtype=torch.int32, device=dev)
 
@@ -231,6 +245,7 @@ class TrainEngine:
         lib = self.lib
         vp, lg, it, fl, sz = C.c_void_p, C.c_long, C.c_int, C.c_float, C.c_size_t
         lib.sgnn_train_pack.argtypes = [vp, it, vp, vp, vp]
+        lib.sgnn_csr_by_source.argtypes = [vp, vp, it, it, vp, vp, vp, sz, vp]
         lib.sgnn_train_mlp_fwd.argtypes = [vp, vp]
         lib.sgnn_train_mlp_bwd.argtypes = [vp, vp]
         lib.sgnn_layer_norm_bwd_rows.argtypes = [vp, vp, vp, vp, vp, vp, lg, vp, it, vp, vp, vp, vp, sz, vp]
@@ -288,7 +303,24 @@ class TrainEngine:
         return self.img_hi.data_ptr() + 4 * off, self.img_lo.data_ptr() + 4 * off
 
     # ------------------------------------------------------------------ launches
-    def _fwd(self, **kw):
+    profile = None          # set to {} to collect CUDA-event pairs per kernel family (un-captured steps only)
+
+    def _timed(self, name):
+        return _Timed(self.profile, name)
+
+    def profile_summary(self):
+        """{family: (launch groups, total ms)} of the last profiled step; call after torch.cuda.synchronize()."""
+        return {k: (len(v), sum(a.elapsed_time(b) for a, b in v)) for k, v in (self.profile or {}).items()}
+
+    def _fwd(self, tag="fwd", **kw):
+        with self._timed(tag):
+            self._fwd_launch(**kw)
+
+    def _bwd(self, tag="bwd", **kw):
+        with self._timed(tag):
+            self._bwd_launch(**kw)
+
+    def _fwd_launch(self, **kw):
         p = TrainFwd()
         p.scale0 = 1.0
         p.split = self.split
@@ -298,7 +330,7 @@ class TrainEngine:
             setattr(p, k, v)
         L.check(self.lib.sgnn_train_mlp_fwd(C.addressof(p), self._stream()))
 
-    def _bwd(self, **kw):
+    def _bwd_launch(self, **kw):
         p = TrainBwd()
         p.split = self.split
         for k, v in kw.items():
@@ -314,19 +346,22 @@ class TrainEngine:
                db: Optional[torch.Tensor] = None):
         """dW[:, col0:col0+k] = scale * dy^T x (and db = column sums of dy) into the parameter's .grad view."""
         ptr = lambda t: t if isinstance(t, int) else t.data_ptr()      # noqa: E731
-        L.check(self.lib.sgnn_linear_wgrad_ex(ptr(dy), ld_dy, ptr(x), ld_x, rows, rows_dev, m, k,
+        with self._timed("wgrad_edges" if rows_dev is not None else "wgrad_nodes"):
+          L.check(self.lib.sgnn_linear_wgrad_ex(ptr(dy), ld_dy, ptr(x), ld_x, rows, rows_dev, m, k,
                                               dw.data_ptr() + 4 * col0, dw.shape[1], scale,
                                               None if db is None else db.data_ptr(), self.ws.data_ptr(),
                                               self.ws.numel(), self._stream()), launches=2)
 
     def _ln_bwd(self, dy, index, act, ln, rows, rows_dev, dx):
-        L.check(self.lib.sgnn_layer_norm_bwd_rows(dy.data_ptr(), index, act["y2"].data_ptr(), act["mean"].data_ptr(),
+        with self._timed("ln_bwd_edges" if rows_dev is not None else "ln_bwd_nodes"):
+          L.check(self.lib.sgnn_layer_norm_bwd_rows(dy.data_ptr(), index, act["y2"].data_ptr(), act["mean"].data_ptr(),
                                                   act["rstd"].data_ptr(), ln.weight.data_ptr(), rows, rows_dev, self.h,
                                                   dx.data_ptr(), ln.weight.grad.data_ptr(), ln.bias.grad.data_ptr(),
                                                   self.ws.data_ptr(), self.ws.numel(), self._stream()), launches=2)
 
     def _segsum(self, m, rowptr, perm, out, ld_out):
-        L.check(self.lib.sgnn_segment_sum_rows_ld(m.data_ptr(), rowptr.data_ptr(), None if perm is None else perm.data_ptr(),
+        with self._timed("segment_sum"):
+          L.check(self.lib.sgnn_segment_sum_rows_ld(m.data_ptr(), rowptr.data_ptr(), None if perm is None else perm.data_ptr(),
                                                   self.n, self.h, out, ld_out, self._stream()))
 
     # ------------------------------------------------------------------ the step
@@ -337,17 +372,19 @@ class TrainEngine:
         st = self.sim._stats(self.dev)
         win = self.window
         s = win.shape[1]
-        L.check(self.lib.sgnn_train_pack(self.descs.data_ptr(), self.n_descs, self.img_hi.data_ptr(),
-                                         self.img_lo.data_ptr(), self._stream()))
+        with self._timed("pack_weights"):
+            L.check(self.lib.sgnn_train_pack(self.descs.data_ptr(), self.n_descs, self.img_hi.data_ptr(),
+                                             self.img_lo.data_ptr(), self._stream()))
         # noisy window, target, neighbour search on the noisy last frame (learned_simulator.py:461-470)
         torch.add(self.pos_in, self.noise, out=win)
         last = win[0, s - 1]
-        self.rg.build(last, win.stride(0), dim, self.example_ptr, self.radius)
+        with self._timed("neighbour_search"):
+            self.rg.build(last, win.stride(0), dim, self.example_ptr, self.radius)
         # edges sorted by sender (stable): the backward of the sender gather is a segmented sum in edge order
-        keys = torch.where(self.ar_cap < csr.rowptr[n], csr.src, n)
-        skeys, perm = torch.sort(keys, stable=True)
-        self.perm_src.copy_(perm)
-        self.rp_src.copy_(torch.searchsorted(skeys, self.ar_n1))
+        with self._timed("group_by_sender"):
+            L.check(self.lib.sgnn_csr_by_source(csr.src.data_ptr(), ed, cap, n, self.rp_src.data_ptr(),
+                                                self.perm_src.data_ptr(), self.ws_src.data_ptr(), self.ws_src.numel(),
+                                                self._stream()), launches=5)
         L.check(self.lib.sgnn_node_features(win.data_ptr(), win.stride(0), n, s, dim, st["velocity"]["mean"].data_ptr(),
                                             st["velocity"]["std"].data_ptr(), 2.0, self.radius, 1.0, self.nf.data_ptr(),
                                             self.k_node, self._stream()))
@@ -355,14 +392,14 @@ class TrainEngine:
         m = self.mlp["ne"]
         hi, lo = self._img(m["w1"]); hi2, lo2 = self._img(m["w2"])
         a = self.act_ne
-        self._fwd(max_rows=n, prologue=TPRO_ROWS, a0=self.nf, ld0=self.k_node, k0=self.k_node, kpad=pad32(self.k_node),
+        self._fwd(tag="fwd_node_encoder", max_rows=n, prologue=TPRO_ROWS, a0=self.nf, ld0=self.k_node, k0=self.k_node, kpad=pad32(self.k_node),
                   hidden=h, out=h, n_linear=2, has_ln=1, w1_hi=hi, w1_lo=lo, w2_hi=hi2, w2_lo=lo2, b1=m["a"].bias,
                   b1_cols=h, b2=m["b"].bias, gamma=m["ln"].weight, beta=m["ln"].bias, h1=a["h1"], y2=a["y2"],
                   mean=a["mean"], rstd=a["rstd"], y=self.x[0], ld_y=h)
         m = self.mlp["ee"]
         hi, lo = self._img(m["w1"]); hi2, lo2 = self._img(m["w2"])
         a = self.act_ee
-        self._fwd(max_rows=cap, n_rows_dev=ed, prologue=TPRO_EDGE_FEATURES, pos=last.data_ptr(), pos_stride=win.stride(0),
+        self._fwd(tag="fwd_edge_encoder", max_rows=cap, n_rows_dev=ed, prologue=TPRO_EDGE_FEATURES, pos=last.data_ptr(), pos_stride=win.stride(0),
                   dim=dim, radius=self.radius, src=csr.src, tgt=csr.tgt, feat_out=self.ef, kpad=32, hidden=h, out=h,
                   n_linear=2, has_ln=1, w1_hi=hi, w1_lo=lo, w2_hi=hi2, w2_lo=lo2, b1=m["a"].bias, b1_cols=h,
                   b2=m["b"].bias, gamma=m["ln"].weight, beta=m["ln"].bias, h1=a["h1"], y2=a["y2"], mean=a["mean"],
@@ -370,17 +407,17 @@ class TrainEngine:
         for l in range(len(self.layers)):
             me, mn, ae, an = self.mlp_e[l], self.mlp_n[l], self.act_e[l], self.act_n[l]
             hi, lo = self._img(me["pq"])
-            self._fwd(max_rows=n, prologue=TPRO_ROWS, a0=self.x[l], ld0=h, k0=h, kpad=h, hidden=2 * h, out=2 * h,
+            self._fwd(tag="fwd_pq", max_rows=n, prologue=TPRO_ROWS, a0=self.x[l], ld0=h, k0=h, kpad=h, hidden=2 * h, out=2 * h,
                       n_linear=1, w1_hi=hi, w1_lo=lo, b1=me["a"].bias, b1_cols=h, y=self.pq[l], ld_y=2 * h)
             hi, lo = self._img(me["w1"]); hi2, lo2 = self._img(me["w2"])
-            self._fwd(max_rows=cap, n_rows_dev=ed, prologue=TPRO_ROWS, a0=self.e0, ld0=h, k0=h, kpad=h, src=csr.src,
+            self._fwd(tag="fwd_edge_mlp", max_rows=cap, n_rows_dev=ed, prologue=TPRO_ROWS, a0=self.e0, ld0=h, k0=h, kpad=h, src=csr.src,
                       tgt=csr.tgt, add_p=self.pq[l], add_q=self.pq[l].data_ptr() + 4 * h, ld_add=2 * h, hidden=h, out=h,
                       n_linear=2, has_ln=1, w1_hi=hi, w1_lo=lo, w2_hi=hi2, w2_lo=lo2, b2=me["b"].bias,
                       gamma=me["ln"].weight, beta=me["ln"].bias, h1=ae["h1"], y2=ae["y2"], mean=ae["mean"],
                       rstd=ae["rstd"], y=self.msg, ld_y=h)
             self._segsum(self.msg, csr.rowptr, None, self.agg[l].data_ptr(), h)
             hi, lo = self._img(mn["w1"]); hi2, lo2 = self._img(mn["w2"])
-            self._fwd(max_rows=n, prologue=TPRO_ROWS2, a0=self.agg[l], ld0=h, k0=h, a1=self.x[l], ld1=h, k1=h,
+            self._fwd(tag="fwd_node_mlp", max_rows=n, prologue=TPRO_ROWS2, a0=self.agg[l], ld0=h, k0=h, a1=self.x[l], ld1=h, k1=h,
                       kpad=2 * h, hidden=h, out=h, n_linear=2, has_ln=1, w1_hi=hi, w1_lo=lo, w2_hi=hi2, w2_lo=lo2,
                       b1=mn["a"].bias, b1_cols=h, b2=mn["b"].bias, gamma=mn["ln"].weight, beta=mn["ln"].bias,
                       res=self.x[l], ld_res=h, h1=an["h1"], y2=an["y2"], mean=an["mean"], rstd=an["rstd"],
@@ -388,7 +425,7 @@ class TrainEngine:
         md = self.mlp["dec"]
         xl = self.x[-1]
         hi, lo = self._img(md["w1"]); hi2, lo2 = self._img(md["w2"])
-        self._fwd(max_rows=n, prologue=TPRO_ROWS, a0=xl, ld0=h, k0=h, kpad=h, hidden=h, out=dim + 1, n_linear=2,
+        self._fwd(tag="fwd_decoder", max_rows=n, prologue=TPRO_ROWS, a0=xl, ld0=h, k0=h, kpad=h, hidden=h, out=dim + 1, n_linear=2,
                   has_ln=0, w1_hi=hi, w1_lo=lo, w2_hi=hi2, w2_lo=lo2, b1=md["a"].bias, b1_cols=h, b2=md["b"].bias,
                   h1=self.h1_d, y=self.pred, ld_y=4)
 
@@ -405,7 +442,7 @@ class TrainEngine:
         # ---- backward ----
         dx, dx_new = self.dx
         hi, lo = self._img(md["w2t"]); hi1, lo1 = self._img(md["w1t"])
-        self._bwd(max_rows=n, dy=self.dpred, ld_dy=4, k_dy=dim + 1, n_linear=2, hidden=h, h1=self.h1_d, dpre=self.dpre_n,
+        self._bwd(tag="bwd_decoder", max_rows=n, dy=self.dpred, ld_dy=4, k_dy=dim + 1, n_linear=2, hidden=h, h1=self.h1_d, dpre=self.dpre_n,
                   w2t_hi=hi, w2t_lo=lo, want_dx=1, kx=h, w1t_hi=hi1, w1t_lo=lo1, dx0=dx, ld_dx0=h, k0=h)
         self._wgrad(self.dpred, 4, self.h1_d, h, n, None, dim + 1, h, md["b"].weight.grad, 0, db=md["b"].bias.grad)
         self._wgrad(self.dpre_n, h, xl, h, n, None, h, h, md["a"].weight.grad, 0, db=md["a"].bias.grad)
@@ -415,7 +452,7 @@ class TrainEngine:
             # node update: x' = x + LN(MLP([agg | x]))
             self._ln_bwd(dx, None, an, mn["ln"], n, None, self.dy2_n)
             hi, lo = self._img(mn["w2t"]); hi1, lo1 = self._img(mn["w1t"])
-            self._bwd(max_rows=n, dy=self.dy2_n, ld_dy=h, k_dy=h, n_linear=2, hidden=h, h1=an["h1"], dpre=self.dpre_n,
+            self._bwd(tag="bwd_node_mlp", max_rows=n, dy=self.dy2_n, ld_dy=h, k_dy=h, n_linear=2, hidden=h, h1=an["h1"], dpre=self.dpre_n,
                       w2t_hi=hi, w2t_lo=lo, want_dx=1, kx=2 * h, w1t_hi=hi1, w1t_lo=lo1, dx0=self.dagg, ld_dx0=h, k0=h,
                       dx1=dx_new, ld_dx1=h, k1=h, add1=dx, ld_add1=h)
             self._wgrad(self.dy2_n, h, an["h1"], h, n, None, h, h, mn["b"].weight.grad, 0, db=mn["b"].bias.grad)
@@ -424,7 +461,7 @@ class TrainEngine:
             # messages: agg = segment sum of LN(MLP(...)); its backward gathers dagg by receiver
             self._ln_bwd(self.dagg, csr.tgt.data_ptr(), ae, me["ln"], cap, ed, self.dy2_e)
             hi, lo = self._img(me["w2t"]); hi1, lo1 = self._img(me["w1t"])
-            self._bwd(max_rows=cap, n_rows_dev=ed, dy=self.dy2_e, ld_dy=h, k_dy=h, n_linear=2, hidden=h, h1=ae["h1"],
+            self._bwd(tag="bwd_edge_mlp", max_rows=cap, n_rows_dev=ed, dy=self.dy2_e, ld_dy=h, k_dy=h, n_linear=2, hidden=h, h1=ae["h1"],
                       dpre=self.dpre_e, w2t_hi=hi, w2t_lo=lo, want_dx=1, kx=h, w1t_hi=hi1, w1t_lo=lo1, dx0=self.de0,
                       ld_dx0=h, k0=h, acc0=1)
             self._wgrad(self.dy2_e, h, ae["h1"], h, cap, ed, h, h, me["b"].weight.grad, 0, db=me["b"].bias.grad)
@@ -433,7 +470,7 @@ class TrainEngine:
             self._segsum(self.dpre_e, csr.rowptr, None, self.dpq.data_ptr(), 2 * h)
             self._segsum(self.dpre_e, self.rp_src, self.perm_src, self.dpq.data_ptr() + 4 * h, 2 * h)
             hi1, lo1 = self._img(me["pqt"])
-            self._bwd(max_rows=n, dy=self.dpq, ld_dy=2 * h, k_dy=2 * h, n_linear=1, want_dx=1, kx=h, w1t_hi=hi1,
+            self._bwd(tag="bwd_pq", max_rows=n, dy=self.dpq, ld_dy=2 * h, k_dy=2 * h, n_linear=1, want_dx=1, kx=h, w1t_hi=hi1,
                       w1t_lo=lo1, dx0=dx_new, ld_dx0=h, k0=h, acc0=1)
             self._wgrad(self.dpq, 2 * h, self.x[l], h, n, None, h, h, me["a"].weight.grad, 0)
             self._wgrad(self.dpq.data_ptr() + 4 * h, 2 * h, self.x[l], h, n, None, h, h, me["a"].weight.grad, h)
@@ -442,23 +479,26 @@ class TrainEngine:
         m, a = self.mlp["ee"], self.act_ee
         self._ln_bwd(self.de0, None, a, m["ln"], cap, ed, self.dy2_e)
         hi, lo = self._img(m["w2t"])
-        self._bwd(max_rows=cap, n_rows_dev=ed, dy=self.dy2_e, ld_dy=h, k_dy=h, n_linear=2, hidden=h, h1=a["h1"],
+        self._bwd(tag="bwd_edge_encoder", max_rows=cap, n_rows_dev=ed, dy=self.dy2_e, ld_dy=h, k_dy=h, n_linear=2, hidden=h, h1=a["h1"],
                   dpre=self.dpre_e, w2t_hi=hi, w2t_lo=lo, want_dx=0)
         self._wgrad(self.dy2_e, h, a["h1"], h, cap, ed, h, h, m["b"].weight.grad, 0, db=m["b"].bias.grad)
         self._wgrad(self.dpre_e, h, self.ef, dim + 1, cap, ed, h, dim + 1, m["a"].weight.grad, 0, db=m["a"].bias.grad)
         m, a = self.mlp["ne"], self.act_ne
         self._ln_bwd(dx, None, a, m["ln"], n, None, self.dy2_n)
         hi, lo = self._img(m["w2t"])
-        self._bwd(max_rows=n, dy=self.dy2_n, ld_dy=h, k_dy=h, n_linear=2, hidden=h, h1=a["h1"], dpre=self.dpre_n,
+        self._bwd(tag="bwd_node_encoder", max_rows=n, dy=self.dy2_n, ld_dy=h, k_dy=h, n_linear=2, hidden=h, h1=a["h1"], dpre=self.dpre_n,
                   w2t_hi=hi, w2t_lo=lo, want_dx=0)
         self._wgrad(self.dy2_n, h, a["h1"], h, n, None, h, h, m["b"].weight.grad, 0, db=m["b"].bias.grad)
         self._wgrad(self.dpre_n, h, self.nf, self.k_node, n, None, h, self.k_node, m["a"].weight.grad, 0, db=m["a"].bias.grad)
 
     def _whole_step(self):
-        self._forward_backward()
+        with self._timed("forward_backward_total"):
+            self._forward_backward()
         if self.world > 1:
-            dist.all_reduce(self.flat_grad, op=dist.ReduceOp.SUM, group=self.group)
-        self.opt.step()
+            with self._timed("allreduce"):
+                dist.all_reduce(self.flat_grad, op=dist.ReduceOp.SUM, group=self.group)
+        with self._timed("adam"):
+            self.opt.step()
 
     # ------------------------------------------------------------------ public
     def _bind(self, batch: Dict[str, torch.Tensor]):
