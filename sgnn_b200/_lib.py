@@ -30,7 +30,7 @@ class EdgeLayerParams(C.Structure):
     _fields_ = [("e_tiles", C.c_void_p), ("pq", C.c_void_p), ("src", C.c_void_p),
                 ("tgt", C.c_void_p), ("rowptr", C.c_void_p), ("n_nodes", C.c_int), ("he", C.c_int),
                 ("blob", C.c_void_p), ("blob_bytes", C.c_int), ("mlp", Mlp), ("agg", C.c_void_p),
-                ("head", C.c_void_p), ("max_tiles", C.c_int), ("wxs_off", C.c_int)]
+                ("head", C.c_void_p), ("max_tiles", C.c_int), ("wxs_off", C.c_int), ("defer_affine", C.c_int)]
 
 
 class EdgeEncoderParams(C.Structure):
@@ -58,7 +58,7 @@ class NodeParams(C.Structure):
                 ("dec_wlast_off", C.c_int), ("dec_out", C.c_void_p), ("acc_mean", C.c_void_p),
                 ("acc_std", C.c_void_p), ("next_pos", C.c_void_p), ("next_pos_stride", C.c_long),
                 ("strain_out", C.c_void_p), ("xr_in", C.c_void_p), ("xr_ld", C.c_long),
-                ("n_types", C.c_int)]
+                ("n_types", C.c_int), ("agg_affine", C.c_int), ("agg_gamma_off", C.c_int), ("agg_beta_off", C.c_int)]
 
 
 _lib = None

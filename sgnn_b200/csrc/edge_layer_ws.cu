@@ -273,6 +273,7 @@ __device__ __forceinline__ void ws_mma1(const SgnnEdgeLayerParams& p, uint32_t s
 // arithmetic for the LayerNorm, no duplicated special cases.
 __device__ __forceinline__ float2 f2(float a, float b) { return make_float2(a, b); }
 
+template <bool DEFER>
 __device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const float* blob_f, WsMisc* misc,
                                             int g, int wt, int n_my, int n_edges, uint32_t tmem) {
   constexpr int W = kWsW;
@@ -459,16 +460,32 @@ __device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const 
       if (is_end && !(g_ws_flags & 16)) {          // measurement switch bit 4: no agg rows written (wrong results)
         const bool head_piece = first_cont && seg0 == 0;                        // continues the previous warp's receiver
         const bool tail_piece = cont_next && !one_piece && lane == nrows - 1;   // continues in the next warp
-        const float cnt = (float)cnt_i;
-        const float4* g4 = reinterpret_cast<const float4*>(blob_f + p.mlp.gamma_off);
-        const float4* be4 = reinterpret_cast<const float4*>(blob_f + p.mlp.beta_off);
-        const float2 c2 = f2(cnt, cnt);
+        if constexpr (DEFER) {
+          // The node kernel applies gamma / count * beta to the receiver's complete sum.  The sums pass through one
+          // packed multiply by an opaque 1.0f: with NO arithmetic between the scan and the stores ptxas spilled 388
+          // bytes around the scan in this instantiation (64 with the affine, 68 with this), and the kernel ran 30 %
+          // SLOWER than with the affine (0.77 vs 0.59 ms at 1M, r02c).  x * 1.0f is exact.
+          float one = 1.0f;
+          asm volatile("" : "+f"(one));
+          const float2 o2 = f2(one, one);
 #pragma unroll
-        for (int j = 0; j < W / 4; ++j) {          // packed fp32x2 (same roundings as fmaf(y, gamma, cnt * beta)): every
-          const float4 ga = g4[j], be = be4[j];    // instruction of this block costs ~7 cycles of a contended scheduler
-          const float2 a = __ffma2_rn(f2(y[4 * j], y[4 * j + 1]), f2(ga.x, ga.y), __fmul2_rn(c2, f2(be.x, be.y)));
-          const float2 b = __ffma2_rn(f2(y[4 * j + 2], y[4 * j + 3]), f2(ga.z, ga.w), __fmul2_rn(c2, f2(be.z, be.w)));
-          y[4 * j] = a.x; y[4 * j + 1] = a.y; y[4 * j + 2] = b.x; y[4 * j + 3] = b.y;
+          for (int j = 0; j < W / 2; ++j) {
+            const float2 a = __fmul2_rn(f2(y[2 * j], y[2 * j + 1]), o2);
+            y[2 * j] = a.x; y[2 * j + 1] = a.y;
+          }
+        }
+        if constexpr (!DEFER) {                    // defer_affine: the node kernel applies gamma / count * beta to the
+          const float cnt = (float)cnt_i;          // receiver's complete sum (one pass per NODE row there instead of this
+          const float4* g4 = reinterpret_cast<const float4*>(blob_f + p.mlp.gamma_off);   // divergent block per edge tile:
+          const float4* be4 = reinterpret_cast<const float4*>(blob_f + p.mlp.beta_off);   // -19 % at 1M, r01p switch bit 4)
+          const float2 c2 = f2(cnt, cnt);
+#pragma unroll
+          for (int j = 0; j < W / 4; ++j) {        // packed fp32x2 (same roundings as fmaf(y, gamma, cnt * beta)): every
+            const float4 ga = g4[j], be = be4[j];  // instruction of this block costs ~7 cycles of a contended scheduler
+            const float2 a = __ffma2_rn(f2(y[4 * j], y[4 * j + 1]), f2(ga.x, ga.y), __fmul2_rn(c2, f2(be.x, be.y)));
+            const float2 b = __ffma2_rn(f2(y[4 * j + 2], y[4 * j + 3]), f2(ga.z, ga.w), __fmul2_rn(c2, f2(be.z, be.w)));
+            y[4 * j] = a.x; y[4 * j + 1] = a.y; y[4 * j + 2] = b.x; y[4 * j + 3] = b.y;
+          }
         }
         if (!tail_piece && !head_piece && !(g_ws_flags & 32)) {   // (measurement switch bit 5: rows go to shared memory)
           // a receiver's agg row leaves as eight 32-byte stores: every store fills a whole sector (sixteen
@@ -531,6 +548,7 @@ __device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const 
 }
 
 // ---------------------------------------------------------------------------------- kernel
+template <bool DEFER>
 __global__ void __launch_bounds__(kWsThreads, 1)
 edge_layer_ws_kernel(const SgnnEdgeLayerParams p, const __grid_constant__ CUtensorMap xmap) {
   constexpr int TMEM_COLS = 512;
@@ -577,7 +595,7 @@ edge_layer_ws_kernel(const SgnnEdgeLayerParams p, const __grid_constant__ CUtens
   if (warp < 16) {
     asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kWsEpiRegs));
     mbar_wait(&misc->bar_w, 0);
-    ws_epilogue(p, reinterpret_cast<const float*>(smem), misc, warp >> 2, tid & 127, n_my, n_edges, tmem);
+    ws_epilogue<DEFER>(p, reinterpret_cast<const float*>(smem), misc, warp >> 2, tid & 127, n_my, n_edges, tmem);
   } else {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kWsAuxRegs));
   }
@@ -640,7 +658,12 @@ int sgnn_edge_layer_gather_launch(const SgnnEdgeLayerParams* p, void* stream) {
   }
   int grid = p->max_tiles < sms ? p->max_tiles : sms;
   if (grid < 1) grid = 1;
-  SGNN_ENSURE_SMEM(edge_layer_ws_kernel, s.total);
-  SGNN_CUDA(sgnn_launch(edge_layer_ws_kernel, dim3(grid), dim3(kWsThreads), s.total, (cudaStream_t)stream, *p, map));
+  if (p->defer_affine) {
+    SGNN_ENSURE_SMEM(edge_layer_ws_kernel<true>, s.total);
+    SGNN_CUDA(sgnn_launch(edge_layer_ws_kernel<true>, dim3(grid), dim3(kWsThreads), s.total, (cudaStream_t)stream, *p, map));
+  } else {
+    SGNN_ENSURE_SMEM(edge_layer_ws_kernel<false>, s.total);
+    SGNN_CUDA(sgnn_launch(edge_layer_ws_kernel<false>, dim3(grid), dim3(kWsThreads), s.total, (cudaStream_t)stream, *p, map));
+  }
   return SGNN_OK;
 }

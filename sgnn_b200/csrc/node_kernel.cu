@@ -349,6 +349,8 @@ extern "C" int sgnn_node_fwd(const SgnnNodeParams* p, int use_tensor_cores, int 
     r = sgnn_node_fast_try(p, stream);
     if (r != 0) return r < 0 ? r : SGNN_OK;
   }
+  SGNN_CHECK_ARG(!p->agg_affine, "node: agg_affine (edge kernel with defer_affine) is implemented by the 64-wide "
+                 "warp-specialised node kernel only; this layer shape / switch must not defer the affine");
   SGNN_CHECK_ARG(p->tail != SGNN_TAIL_PX, "node: tail PX (gather-mode edge kernel) exists only in the 64-wide "
                  "tensor-core kernel; this layer shape / precision must use tail PQ");
   const int streamed = node_streamed(*p, use_tensor_cores);

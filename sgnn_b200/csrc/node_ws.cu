@@ -175,6 +175,8 @@ __device__ __forceinline__ void nw_epilogue(const SgnnNodeParams& p, const CUten
   const float4* b1 = reinterpret_cast<const float4*>(vec + p.mlp.b_off[1]);
   const float4* gam4 = reinterpret_cast<const float4*>(vec + p.mlp.gamma_off);
   const float4* bet4 = reinterpret_cast<const float4*>(vec + p.mlp.beta_off);
+  const float4* ag4 = reinterpret_cast<const float4*>(vec + (p.agg_affine ? p.agg_gamma_off : 0));
+  const float4* ab4 = reinterpret_cast<const float4*>(vec + (p.agg_affine ? p.agg_beta_off : 0));
   char* x_slot = smem + kNwXOff + g * kNwSlotBytes;
   const bool px = p.tail == SGNN_TAIL_PX;
   const bool poll = false;      // polling epilogue warps measured slower even with one tile per group (r01n)
@@ -206,6 +208,7 @@ __device__ __forceinline__ void nw_epilogue(const SgnnNodeParams& p, const CUten
     //      tile's serial chain, 1.8 us after the tile had landed (in-kernel stamps, r01n) -- so the partial
     //      is fetched BEFORE the wait for the tile, next to the TMA loads it does not depend on ----
     const bool has = valid && end > beg;             // no edges: the edge kernel never wrote this agg row
+    const float cnt = has ? (float)(end - beg) : 0.f;
     const int t_lo = (beg >> 7) + 1, t_hi = has ? ((end - 1) >> 7) : 0;     // later edge tiles of a straddling CSR row
     float4 hp[W / 4];
     if (t_hi >= t_lo) {
@@ -226,6 +229,11 @@ __device__ __forceinline__ void nw_epilogue(const SgnnNodeParams& p, const CUten
           float4* q = reinterpret_cast<float4*>(agg_rows + sw128_chunk_offset(wt, c, kTileRows));
           float4 a = has ? *q : make_float4(0.f, 0.f, 0.f, 0.f);
           a.x += hp[c].x; a.y += hp[c].y; a.z += hp[c].z; a.w += hp[c].w;
+          if (p.agg_affine) {                        // the edge MLP's LayerNorm affine on the complete sum
+            const float4 ga = ag4[c], be = ab4[c];
+            a.x = fmaf(a.x, ga.x, cnt * be.x); a.y = fmaf(a.y, ga.y, cnt * be.y);
+            a.z = fmaf(a.z, ga.z, cnt * be.z); a.w = fmaf(a.w, ga.w, cnt * be.w);
+          }
           *q = make_float4(nw_tf32r(a.x), nw_tf32r(a.y), nw_tf32r(a.z), nw_tf32r(a.w));
         }
       } else {                                       // rows longer than a tile (arbitrary edge lists only)
@@ -236,6 +244,11 @@ __device__ __forceinline__ void nw_epilogue(const SgnnNodeParams& p, const CUten
           for (int t = t_lo; t <= t_hi; ++t) {
             const float4 h = __ldg(reinterpret_cast<const float4*>(p.head + (long)t * W) + c);
             a.x += h.x; a.y += h.y; a.z += h.z; a.w += h.w;
+          }
+          if (p.agg_affine) {
+            const float4 ga = ag4[c], be = ab4[c];
+            a.x = fmaf(a.x, ga.x, cnt * be.x); a.y = fmaf(a.y, ga.y, cnt * be.y);
+            a.z = fmaf(a.z, ga.z, cnt * be.z); a.w = fmaf(a.w, ga.w, cnt * be.w);
           }
           *q = make_float4(nw_tf32r(a.x), nw_tf32r(a.y), nw_tf32r(a.z), nw_tf32r(a.w));
         }
@@ -539,6 +552,7 @@ int sgnn_node_ws_try(const SgnnNodeParams* p, void* stream) {
       !nw_vec_resident(p->mlp.gamma_off, kNwW) || !nw_vec_resident(p->mlp.beta_off, kNwW))
     return 0;
   if (!nw_img_resident(p->mlp.w_off[0], 2 * wb) || !nw_img_resident(p->mlp.w_off[1], wb)) return 0;
+  if (p->agg_affine && (!nw_vec_resident(p->agg_gamma_off, kNwW) || !nw_vec_resident(p->agg_beta_off, kNwW))) return 0;
   if (p->blob_bytes < SGNN_VEC_REGION_BYTES + kNwImgBytes) return 0;
   if (p->tail == SGNN_TAIL_PX) {
     if (p->pq_hidden != kNwW || !p->pq_out || !nw_vec_resident(p->pq_bias_off, kNwW) || !nw_img_resident(p->wp_off, wb))

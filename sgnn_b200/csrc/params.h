@@ -50,6 +50,9 @@ typedef struct {
   int wxs_off;            /* 0: PQ mode.  > 0: GATHER mode -- byte offset of the W1b image; the Q half */
                           /* of `pq` then holds the TF32-rounded node latents x (node tail            */
                           /* SGNN_TAIL_PX) and the sender term x_src W1b^T is part of the first GEMM  */
+  int defer_affine;       /* GATHER mode, 1: agg / head hold the plain sums of the normalised messages; the    */
+                          /* LayerNorm affine (gamma * sum + count * beta) is applied by the node kernel      */
+                          /* (SgnnNodeParams.agg_affine)                                                       */
 } SgnnEdgeLayerParams;
 
 /* Edge encoder: features from positions -> MLP -> LN -> e0 tiles.  Reference:
@@ -134,6 +137,9 @@ typedef struct {
   const float* xr_in;     /* AGG_X, optional: x_in rounded to TF32 (row i at xr_in + i * xr_ld), as written */
   long xr_ld;             /* by a node kernel with tail PX into the Q half of pq; enables node_ws_kernel    */
   int n_types;            /* rows of `emb`; type ids are clamped to [0, n_types) (0: not clamped)           */
+  int agg_affine;         /* AGG_X, 1: agg / head are plain sums (edge kernel with defer_affine); the row becomes    */
+  int agg_gamma_off;      /* gamma * (agg + head) + (rowptr[i+1] - rowptr[i]) * beta with the EDGE MLP's LayerNorm  */
+  int agg_beta_off;       /* parameters at these float offsets of the blob (node_ws_kernel only)                    */
 } SgnnNodeParams;
 
 

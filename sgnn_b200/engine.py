@@ -159,7 +159,7 @@ class EdgeLayerPlan:
     the first Linear's columns are [x_target | x_source | e] (graph_network.py:197)."""
 
     def __init__(self, edge_fn: torch.nn.Sequential, nnode: int, nedge: int, scale: float, tc: bool,
-                 device, gather: bool = False):
+                 device, gather: bool = False, defer_affine: bool = False):
         lins, ln = linears_of(edge_fn[0]), edge_fn[1]
         assert lins[0].in_features == 2 * nnode + nedge
         b = BlobBuilder(device, tc)
@@ -167,6 +167,7 @@ class EdgeLayerPlan:
         fill_mlp(b, self.p.mlp, lins, ln, first_cols=(2 * nnode, nedge), first_scale=scale,
                  first_bias=False)
         self.gather = gather
+        self.p.defer_affine = int(gather and defer_affine)
         if gather:      # sender columns of W1: multiplied inside the edge kernel (TMA-gathered x_src rows)
             self.p.wxs_off = b.add_image(lins[0].weight, 0, lins[0].out_features, nnode, nnode, pad32(nnode))
         self.blob, nbytes = b.finish()
@@ -197,7 +198,7 @@ class NodePlan:
     def __init__(self, prologue: int, k_in: int, body: Optional[torch.nn.Sequential], tc: bool,
                  device, nnode_next: int = 0, pq_from: Optional[torch.nn.Sequential] = None,
                  decoder: Optional[torch.nn.Sequential] = None, residual: bool = False,
-                 body_has_ln: bool = True, px: bool = False):
+                 body_has_ln: bool = True, px: bool = False, agg_ln: Optional[torch.nn.LayerNorm] = None):
         b = BlobBuilder(device, tc)
         p = self.p = L.NodeParams()
         p.prologue, p.k_in, p.k_pad = prologue, k_in, pad32(k_in)
@@ -211,6 +212,9 @@ class NodePlan:
             fill_mlp(b, p.mlp, lins, ln, first_kpad=p.k_pad)
             p.has_mlp = 1
             width = p.mlp.out
+        if agg_ln is not None:      # the edge kernel left plain sums (defer_affine): gamma * sum + count * beta applied here
+            p.agg_affine = 1
+            p.agg_gamma_off, p.agg_beta_off = b.add_vector(agg_ln.weight), b.add_vector(agg_ln.bias)
         p.tail = L.TAIL_NONE
         if pq_from is not None:
             w1 = linears_of(pq_from[0])[0]
@@ -262,14 +266,18 @@ class EpdEngine:
         self.tc, self.n, self.dim, self.latent, self.device = tc, n_nodes, dim, latent, device
         self.edge_enc = [EdgeEncoderPlan(seq, dim + 1, tc, device) for seq in edge_encoders]
         self.gather = (not has_embedding) and self._gather_mode(node_encoder, blocks, k_node_in, latent, tc)
+        # gather mode: the edge kernel writes plain sums of the normalised messages and the warp-specialised node
+        # kernel applies the edge LayerNorm's affine to each receiver's complete sum (SGNN_EDGE_AFFINE=1: old split)
+        self.defer_affine = self.gather and not (os.environ.get("SGNN_EDGE_AFFINE") or os.environ.get("SGNN_NODE_FAST"))
         self.blocks = []
         for bi, (edge_fn, node_fn, es, layer) in enumerate(blocks):
             nedge = self.edge_enc[es].out
-            ep = EdgeLayerPlan(edge_fn, latent, nedge, float(2 ** layer), tc, device, gather=self.gather)
+            ep = EdgeLayerPlan(edge_fn, latent, nedge, float(2 ** layer), tc, device, gather=self.gather,
+                               defer_affine=self.defer_affine)
             nxt = blocks[bi + 1][0] if bi + 1 < len(blocks) else None
             npn = NodePlan(L.PRO_AGG_X, ep.out + latent, node_fn, tc, device, nnode_next=latent,
                            pq_from=nxt, decoder=None if nxt is not None else decoder, residual=True,
-                           px=self.gather)
+                           px=self.gather, agg_ln=edge_fn[1] if self.defer_affine else None)
             self.blocks.append((ep, npn, es))
         self.node_enc = NodePlan(L.PRO_FEATURES, k_node_in, node_encoder, tc, device,
                                  nnode_next=latent, pq_from=blocks[0][0], px=self.gather)
