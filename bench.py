@@ -113,6 +113,87 @@ def cpu_reference_rollout(nsteps, threads):
     return time.perf_counter() - t0
 
 
+def cpu_legs(threads):
+    """SURVEY.md 8(d) CPU legs on the box's host cores (oracle port, torch CPU fp32): (i) BASELINE configs[0]
+    exactly -- one train step (forward + backward + Adam) and a 10-step rollout at N=4800; (ii) the
+    Encode-Process-Decode forward alone; (iii) the neighbour search alone, oracle C port and a scipy cKDTree
+    stand-in; (iv) one step of configs[4] on a bounded 262,144-particle sample."""
+    import numpy as np
+    from oracle import sgnn_oracle as O
+    torch.set_num_threads(threads)
+    traj, stats, radius = make_case(seed=0, nsteps=10)
+    sim = make_sim(stats, radius, "cpu")
+    sd = {k: v.detach().clone() for k, v in sim.state_dict().items()}
+    pos, types = traj["positions"], traj["particle_types"]
+    n = pos.shape[0]
+    out = {"cores": threads, "particles": n}
+    # (i) train step + 10-step rollout
+    leaves = {k: v.clone().requires_grad_(v.is_floating_point()) for k, v in sd.items()}
+    opt = torch.optim.Adam([v for v in leaves.values() if v.requires_grad], lr=1e-4)
+    noise = O.random_walk_noise(pos[:, :S], 0.5, torch.Generator().manual_seed(1))
+    t0 = time.perf_counter()
+    pa, ta, ps, _ = O.predict_accelerations(leaves, pos[:, S], noise, pos[:, :S], [n], types, radius, stats)
+    O.train_loss(pa, ta, ps, traj["strains"][S]).backward()
+    opt.step()
+    out["config1_train_step_s"] = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    with torch.no_grad():
+        O.rollout(sd, pos, types, 10, radius, stats, S)
+    out["config1_rollout_10_steps_s"] = time.perf_counter() - t0
+    # (ii) network alone, (iii) search alone
+    with torch.no_grad():
+        t0 = time.perf_counter()
+        ei = O.graph_connectivity(pos[:, S - 1], [n], radius)
+        out["neighbour_search_oracle_c_s"] = time.perf_counter() - t0
+        nf, ef = O.single_scale_features(pos[:, :S], ei, radius, stats, types, sd.get("_particle_type_embedding.weight"))
+        O.encode_process_decode(sd, "_encode_process_decode.", nf, ei, ef)
+        t0 = time.perf_counter()
+        for _ in range(3):
+            O.encode_process_decode(sd, "_encode_process_decode.", nf, ei, ef)
+        out["epd_forward_s"] = (time.perf_counter() - t0) / 3
+    try:
+        from scipy.spatial import cKDTree
+        p32 = pos[:, S - 1].numpy().astype(np.float64)
+        t0 = time.perf_counter()
+        cKDTree(p32).query_ball_point(p32, radius, workers=threads)
+        out["neighbour_search_ckdtree_s"] = time.perf_counter() - t0
+    except Exception as ex:
+        out["neighbour_search_ckdtree_s"] = repr(ex)
+    # (iv) one step of a bounded sample of configs[4]
+    try:
+        traj, stats, radius = make_case(seed=7, nx=1024, ny=256, nsteps=1)
+        with torch.no_grad():
+            t0 = time.perf_counter()
+            O.predict_positions(sd, traj["positions"][:, :S], [1024 * 256], traj["particle_types"], radius, stats)
+            dt = time.perf_counter() - t0
+        out["config5_sample"] = {"particles": 1024 * 256, "step_s": dt, "particle_steps_per_s": 1024 * 256 / dt}
+    except Exception as ex:
+        out["config5_sample"] = {"error": repr(ex)}
+    return out
+
+
+def measure_tf32_peak(dev, n=8192, reps=5):
+    """Dense TF32 throughput of this GPU (cuBLAS through torch.matmul, fp32 storage, allow_tf32): best of `reps`
+    (burst) -- the denominator of `tensor_frac` (the driver's MEASURED_PEAKS.json has bf16 only)."""
+    saved = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    try:
+        a = torch.randn(n, n, device=dev)
+        b = torch.randn(n, n, device=dev)
+        torch.matmul(a, b)
+        best = float("inf")
+        for _ in range(reps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            torch.matmul(a, b)
+            e1.record()
+            torch.cuda.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        return 2.0 * n ** 3 / (best * 1e-3) / 1e12
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = saved
+
+
 def run_reference(args):
     """--impl reference: the reference's CPU path (oracle port) timed on the host cores."""
     rank = int(os.environ.get("RANK", "0"))
@@ -168,14 +249,16 @@ def roofline_entry(ms, n, e, pk, traffic=None, kernel="edge_layer_ws_kernel"):
     by, fl = edge_layer_alg(n, e)
     if traffic is None:
         traffic = ncu_traffic(kernel, n)
-    tf32_peak = pk["bf16_tflops"] / 2.0            # TF32 dense = 1/2 BF16 (nominal ratio)
+    tf32_peak = pk.get("tf32_tflops") or pk["bf16_tflops"] / 2.0     # measured in this run (measure_tf32_peak), else 1/2 BF16
     t_hbm, t_tc = by / (pk["hbm_gbs"] * 1e9), fl / (tf32_peak * 1e12)
     achieved = by / (ms * 1e-3) / 1e9
     return {"kernel": kernel, "bound": "hbm" if t_hbm >= t_tc else "tensor",
             "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"],
             "traffic": traffic, "peak_source": pk["source"], "ms_per_launch": ms,
             "alg_bytes_per_launch": by, "alg_flops_per_launch": fl,
-            "tensor_frac": fl / (ms * 1e-3) / 1e12 / tf32_peak, "edges": e, "nodes": n}
+            "tensor_frac": fl / (ms * 1e-3) / 1e12 / tf32_peak, "tensor_peak_tflops": tf32_peak,
+            "tensor_peak_source": "measured in this run (cuBLAS TF32 8192^3, burst)" if pk.get("tf32_tflops") else "nominal 1/2 bf16",
+            "edges": e, "nodes": n}
 
 
 def edge_kernel_name(eng):
@@ -228,6 +311,17 @@ def large_config(pk, dev, nx=2048, ny=512):
     out = {"particles": n, "edges": e, "ms_per_step": step_ms, "particle_steps_per_s": n / (step_ms * 1e-3),
            "kernels_ms": {k: {"launches": v[0], "mean_ms": v[1]} for k, v in prof.items()},
            "roofline": roofline_entry(prof["edge_layer"][1], n, e, pk, kernel=edge_kernel_name(eng))}
+    # SURVEY.md 8(d) accounting (fp32 latents, fused layer): 260 E + 512 N bytes per processor layer,
+    # 1560 E + 3192 N per step; times from the same CUDA events
+    pair_ms = prof["edge_layer"][1] + prof["node_layer"][1]
+    by_layer, by_step = 260 * e + 512 * n, 1560 * e + 3192 * n
+    out["roofline_layer_pair"] = {"kernels": "edge layer + node layer (one processor layer)", "bound": "hbm",
+                                  "alg_bytes": by_layer, "ms": pair_ms, "achieved": by_layer / (pair_ms * 1e-3) / 1e9,
+                                  "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": by_layer / (pair_ms * 1e-3) / 1e9 / pk["hbm_gbs"],
+                                  "edge_kernel_alone_frac": by_layer / (prof["edge_layer"][1] * 1e-3) / 1e9 / pk["hbm_gbs"]}
+    out["roofline_step"] = {"kernels": "whole step (search, encoders, 5 layers, decoder)", "bound": "hbm",
+                            "alg_bytes": by_step, "ms": step_ms, "achieved": by_step / (step_ms * 1e-3) / 1e9,
+                            "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": by_step / (step_ms * 1e-3) / 1e9 / pk["hbm_gbs"]}
     del plan, sim
     torch.cuda.empty_cache()
     return out
@@ -376,17 +470,31 @@ def multiscale_config(dev, rank, steps=5):
             "finite": bool(torch.isfinite(plan.traj).all().item())}
 
 
-def sharded_config(dev, rank, world, nx=2048, ny=512, nsteps=20, refresh=10):
-    """BASELINE configs[4]: >= 1M particles, rollout sharded by spatial slab, one ghost-frame
-    exchange per step over NCCL P2P (sgnn_b200/sharding.py).  Timed on the device, max over ranks."""
+def sharded_config(dev, rank, world, nx=2048, ny=512, nsteps=20, refresh=10, check_steps=3, weak=False):
+    """BASELINE configs[4]: >= 1M particles, rollout sharded by spatial slab, one ghost-frame exchange per step over
+    NCCL P2P (sgnn_b200/sharding.py).  Timed on the device, max over ranks.  weak=True scales the bar with the
+    ranks (nx * world columns: >= 1M particles PER GPU).  Parity under real NCCL: every rank also steps the WHOLE
+    system on its own GPU for `check_steps` steps (strong-scaled run only) and compares its slab: owned-receiver edge
+    sets of step 0 must be equal, positions are reported as max |delta|."""
     import torch.distributed as dist
     from sgnn_b200 import sharding as SH
-    traj, stats, radius = make_case(seed=7, nx=nx, ny=ny, nsteps=1)
-    sim = make_sim(stats, radius, dev)
-    n = nx * ny
+    from sgnn_b200.single_scale import evaluate as EV
+    nx_tot = nx * world if weak else nx
+    n = nx_tot * ny
     lo, hi = SH.slab_bounds(n, world)[rank]
-    init = traj["positions"][lo:hi, :S].to(dev).contiguous()
-    del traj
+    if weak:       # a rank only ever needs its slab plus the halo: generate a padded x-range of the bar
+        pad = 16
+        c0, c1 = max(lo // ny - pad, 0), min(hi // ny + pad, nx_tot)
+        traj, stats, radius = make_case(seed=7, nx=nx, ny=ny, nsteps=1)          # statistics of the base bar
+        spacing, _ = synthetic.spacing_for(REGIME)
+        full = synthetic.taylor_trajectory(c1 - c0, ny, spacing, nframes=S + 1, seed=7 + rank)["positions"]
+        full[:, :, 0] += spacing * c0                                            # shift to the slab's columns
+        init = full[(lo - c0 * ny):(hi - c0 * ny), :S].to(dev).contiguous()
+        del full
+    else:
+        traj, stats, radius = make_case(seed=7, nx=nx, ny=ny, nsteps=1)
+        init = traj["positions"][lo:hi, :S].to(dev).contiguous()
+    sim = make_sim(stats, radius, dev)
     comm = SH.DistComm()
     SH.sharded_rollout(sim, init, 3, comm, n_layers=LAYERS, refresh_every=refresh)         # warm-up
     dist.barrier()
@@ -400,12 +508,97 @@ def sharded_config(dev, rank, world, nx=2048, ny=512, nsteps=20, refresh=10):
     dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ok = torch.tensor([float(torch.isfinite(pred).all().item())], device=dev)
     dist.all_reduce(ok, op=dist.ReduceOp.MIN)
-    return {"particles": n, "ranks": world, "steps": nsteps, "ms_per_step": ms.item() / nsteps,
-            "particle_steps_per_s": n * nsteps / (ms.item() * 1e-3), "finite": bool(ok.item()),
-            "exchange": "ghost region of L*r + skin, one new-frame P2P exchange per step (NCCL)",
-            "refresh_every": refresh,
-            "includes": "ghost selection + full-window exchange + graph capture at every refresh (host syncs), "
-                        "neighbour search; steps between refreshes replay one CUDA graph"}
+    out = {"particles": n, "ranks": world, "steps": nsteps, "ms_per_step": ms.item() / nsteps,
+           "particle_steps_per_s": n * nsteps / (ms.item() * 1e-3), "finite": bool(ok.item()),
+           "scaling": "weak (nx x ranks columns)" if weak else "strong (fixed 1,048,576 particles)",
+           "exchange": "ghost region of L*r + skin, one new-frame P2P exchange per step (NCCL)",
+           "refresh_every": refresh,
+           "includes": "ghost selection + full-window exchange + graph capture at every refresh (host syncs), "
+                       "neighbour search; steps between refreshes replay one CUDA graph"}
+    if not weak and check_steps > 0:
+        # parity: the same steps on the whole system, on this rank's own GPU
+        pred_s, _, edges = SH.sharded_rollout(sim, init, check_steps, comm, n_layers=LAYERS, refresh_every=refresh,
+                                              return_edges=True)
+        whole = traj["positions"][:, :S].to(dev)
+        res = EV.rollout(sim, torch.cat([whole, whole[:, :check_steps]], 1), traj["particle_types"].to(dev),
+                         torch.tensor(n), torch.zeros(S + check_steps, n, device=dev), check_steps, 2, dev, S)
+        ref = torch.from_numpy(res["predicted_rollout"]).to(dev)[:, lo:hi]
+        dmax = (pred_s - ref).abs().amax(dim=(1, 2))
+        a0, b0 = sim._compute_graph_connectivity(whole[:, -1].contiguous(), torch.tensor([n]), radius)
+        keep = (b0 >= lo) & (b0 < hi)
+        want = torch.stack([a0[keep], b0[keep]])
+        ei, nl = edges
+        got = ei - nl + lo                                  # local -> global ids
+        same = bool(got.shape == want.shape and torch.equal(got, want))
+        t = torch.tensor([dmax.max().item(), 0.0 if same else 1.0], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        out["parity_vs_unsharded"] = {"steps": check_steps, "max_abs_dpos_over_ranks": t[0].item(),
+                                      "owned_edge_sets_equal_step0": t[1].item() == 0.0,
+                                      "how": "every rank rolls the whole 1M system out on its own GPU and compares its slab"}
+        del whole, ref
+    del sim
+    torch.cuda.empty_cache()
+    return out
+
+
+def batched_config(dev, batches=(8, 32), steps=3):
+    """Saturation throughput: B independent trajectories stepped as ONE system through the public API's
+    nparticles_per_example (learned_simulator.py:104-117 of the reference batches examples the same way); the
+    100-step rollout of B x 4800 particles is one CUDA graph.  Batch 1 leaves > 80 % of the GPU idle."""
+    from sgnn_b200.single_scale import evaluate as EV
+    out = {}
+    for bsz in batches:
+        trajs = [make_case(seed=50 + k) for k in range(min(bsz, 4))]
+        stats, radius = trajs[0][1], trajs[0][2]
+        pos = torch.cat([trajs[k % len(trajs)][0]["positions"] for k in range(bsz)]).to(dev)
+        n1 = NX * NY
+        sim = make_sim(stats, radius, dev)
+        npe = torch.full((bsz,), n1, dtype=torch.int64, device=dev)
+        types = torch.zeros(bsz * n1, dtype=torch.int64, device=dev)
+        strains = torch.zeros(pos.shape[1], bsz * n1, device=dev)
+        nsteps = pos.shape[1] - S
+        for _ in range(2):
+            EV.rollout(sim, pos, types, npe, strains, nsteps, 2, dev, S)
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        a.record()
+        for _ in range(steps):
+            res = EV.rollout(sim, pos, types, npe, strains, nsteps, 2, dev, S)
+        b.record()
+        torch.cuda.synchronize()
+        wall = time.perf_counter() - t0
+        out[str(bsz)] = {"particles": bsz * n1, "ms_per_100_step_rollout_e2e": 1e3 * wall / steps,
+                         "particle_steps_per_s_e2e": bsz * n1 * nsteps * steps / wall,
+                         "finite": bool(torch.isfinite(torch.as_tensor(res["predicted_rollout"])).all())}
+        del sim, pos
+        torch.cuda.empty_cache()
+    return out
+
+
+def fp32_config(dev, traj, stats, radius, steps=3):
+    """The headline workload in precision="fp32" (FFMA kernels: the reference's own arithmetic, the tight-parity mode)."""
+    from sgnn_b200.single_scale import evaluate as EV
+    sim = make_sim(stats, radius, dev, precision="fp32")
+    n, t, dim = traj["positions"].shape
+    pos = traj["positions"].to(dev)
+    plan = EV.get_plan(sim, n, t, S, dim, "autoregressive", dev, True)
+    plan.types.copy_(traj["particle_types"].to(dev))
+    for _ in range(2):
+        plan.traj[:, :S].copy_(pos[:, :S])
+        plan.run()
+    torch.cuda.synchronize()
+    tot = 0.0
+    for _ in range(steps):
+        plan.traj[:, :S].copy_(pos[:, :S])
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        plan.run()
+        b.record()
+        torch.cuda.synchronize()
+        tot += a.elapsed_time(b)
+    ms = tot / steps
+    return {"precision": "fp32 (FFMA)", "ms_per_100_step_rollout": ms, "particle_steps_per_s": n * (t - S) / (ms * 1e-3)}
 
 
 def run_gpu(args):
@@ -424,6 +617,10 @@ def run_gpu(args):
     L.lib()
     EV.VERBOSE = False
     pk = peaks()
+    try:
+        pk["tf32_tflops"] = measure_tf32_peak(dev)
+    except Exception:
+        pk["tf32_tflops"] = None
     traj, stats, radius = make_case(seed=rank)
     sim = make_sim(stats, radius, dev)
     n, t, dim = traj["positions"].shape
@@ -495,9 +692,14 @@ def run_gpu(args):
         cores = os.cpu_count() or 1
         cpu_steps = 5
         cpu_value = None
+        legs = None
         if world == 1:          # N=1 only: with N ranks alive the host cores are not the oracle's alone
             cpu_reference_rollout(1, cores)
             cpu_value = n * cpu_steps / cpu_reference_rollout(cpu_steps, cores)
+            try:
+                legs = cpu_legs(cores)
+            except Exception as ex:
+                legs = {"error": repr(ex)}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps, "higher_is_better": True,
@@ -509,7 +711,8 @@ def run_gpu(args):
             "roofline": roof,
             "cpu_baseline": {"value": cpu_value, "unit": UNIT, "cores": cores, "kind": "port",
                              "sample": (f"{cpu_steps} of {ROLLOUT_STEPS} rollout steps, N={n}, regime {REGIME}"
-                                        if world == 1 else "measured at --gpus 1 only")},
+                                        if world == 1 else "measured at --gpus 1 only"),
+                             "legs": legs},
         }
         if world == 1 and not args.no_large:
             try:
@@ -525,23 +728,52 @@ def run_gpu(args):
             except Exception as ex:           # report, never hide
                 line["large"] = {"error": repr(ex)}
     if not args.no_extra:
-        # every rank takes part (the train step has a collective); rank 0 reports
+        # every rank takes part (the train step and the sharded rollout have collectives); rank 0 reports
         try:
             tr = train_config(dev, rank, world)
         except Exception as ex:
             tr = {"error": repr(ex)}
-        try:
-            ms = multiscale_config(dev, rank) if rank == 0 else None
-        except Exception as ex:
-            ms = {"error": repr(ex)}
-        sh = None
+        ms = fp = bt = None
+        if rank == 0:
+            try:
+                ms = multiscale_config(dev, rank)
+            except Exception as ex:
+                ms = {"error": repr(ex)}
+            try:
+                fp = fp32_config(dev, traj, stats, radius)
+            except Exception as ex:
+                fp = {"error": repr(ex)}
+            if world == 1:
+                try:
+                    bt = batched_config(dev)
+                except Exception as ex:
+                    bt = {"error": repr(ex)}
+        sh = shw = None
         if world > 1:
             try:
                 sh = sharded_config(dev, rank, world)
             except Exception as ex:
                 sh = {"error": repr(ex)}
+            try:
+                shw = sharded_config(dev, rank, world, weak=True, check_steps=0)
+            except Exception as ex:
+                shw = {"error": repr(ex)}
         if line is not None:
-            line["train"], line["multi_scale"], line["sharded_1m"] = tr, ms, sh
+            line["train"], line["multi_scale"], line["sharded_1m"], line["sharded_weak"] = tr, ms, sh, shw
+            line["fp32_mode"], line["batched"] = fp, bt
+            # --workload train / sharded: the same run with a communicating workload as the headline value
+            if args.workload == "train" and "error" not in tr:
+                line.update({"metric": "train_samples_per_s", "unit": "samples/s", "value": tr["samples_per_s"],
+                             "ms_per_step": tr["ms_per_train_step"], "scaling": "weak", "dtype": "tf32 hi/lo split (fp32-grade)",
+                             "config": {"workload": "single-scale training, 8 samples x 4800 particles per GPU, gradient allreduce",
+                                        "samples_per_gpu": 8, "particles_per_sample": NX * NY, "layers": LAYERS, "hidden": H},
+                             "e2e": {"value": tr["samples_per_s"], "unit": "samples/s", "h2d_bytes_per_step": 0,
+                                     "d2h_bytes_per_step": 0, "api": "sgnn_b200.training.train_step (device-resident data loader)"}})
+            if args.workload == "sharded" and sh is not None and "error" not in sh:
+                line.update({"metric": "sharded_rollout_particle_steps_per_s", "value": sh["particle_steps_per_s"],
+                             "ms_per_step": sh["ms_per_step"], "scaling": "strong",
+                             "config": {"workload": "1,048,576-particle rollout sharded by spatial slab", "particles": sh["particles"],
+                                        "layers": LAYERS, "hidden": H, "refresh_every": sh["refresh_every"]}})
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -557,6 +789,9 @@ def main():
     ap.add_argument("--impl", default="sgnn_b200", choices=["sgnn_b200", "reference"])
     ap.add_argument("--no-large", action="store_true", help="skip the 1M-particle single-step section")
     ap.add_argument("--no-extra", action="store_true", help="skip the training and multi-scale sections")
+    ap.add_argument("--workload", default="rollout", choices=["rollout", "train", "sharded"],
+                    help="which measured workload is the headline `value` (rollout replicas by default; train and "
+                         "sharded communicate, so the driver's scaling efficiency then measures the collectives)")
     args = ap.parse_args()
     # stdout carries the ONE JSON line and nothing else: everything any library prints while the bench runs
     # (NCCL's version banner goes to fd 1 whatever NCCL_DEBUG_FILE says) is sent to stderr at the descriptor

@@ -74,7 +74,12 @@ __device__ __forceinline__ void ws_group_bar(int g) {
 
 // measurement switches (sgnn_debug_ws_flags; results are WRONG when set; bits 3, 4: see the epilogue): bit 0 = sender K-blocks by
 // plain bulk copy instead of gather4 (same bytes), bit 2 = epilogue stops after reading acc1
+#ifdef SGNN_TIMELINE
 __device__ int g_ws_flags = 0;
+#define WS_FLAGS g_ws_flags
+#else
+#define WS_FLAGS 0          // release builds: the wrong-answer switches do not exist
+#endif
 // timeline of the MMA issuer of CTA 0 (SGNN_TIMELINE builds only): per tile 16 SM-clock stamps
 // [region free, slot0 full, slot1 full, slot2 full, slot3 full / MMA0 committed, hid_ready seen, -, -]
 __device__ unsigned long long* g_ws_timeline = nullptr;
@@ -106,7 +111,7 @@ __device__ __forceinline__ void cp_async_arrive_noinc(uint64_t* bar) {
 __device__ __forceinline__ void ws_producer(const SgnnEdgeLayerParams& p, const CUtensorMap* xmap, char* ring,
                                             WsMisc* misc, int n_my, int n_edges, int lane, int part) {
   constexpr unsigned FULL = 0xffffffffu;
-  const int flags = g_ws_flags;
+  const int flags = WS_FLAGS;
   const int rg = lane >> 3, ch = lane & 7;            // row within a group of 4, 16-byte chunk of the K-block
   const char* xbase = reinterpret_cast<const char*>(p.pq) + (kWsW + part * kKBlock) * 4 + ch * 16;
   // destination of (row 4j + rg, chunk ch) inside the K-block image: row * 128 + ((ch ^ (row & 7)) << 4)
@@ -343,7 +348,7 @@ __device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const 
       // measurement switch bit 3: every row reads receiver 0 (one L1 line per load instruction instead of one per
       // distinct receiver of the warp); wrong results
       // 32-byte loads: half the load instructions, each touching one L1 line per distinct receiver of the warp
-      const float* prow = p.pq + (long)((valid && !(g_ws_flags & 8)) ? t : 0) * 2 * W;
+      const float* prow = p.pq + (long)((valid && !(WS_FLAGS & 8)) ? t : 0) * 2 * W;
 #pragma unroll
       for (int j = 0; j < W / 8; ++j) ldg256_nc(prow + 8 * j, pr + 8 * j);
     }
@@ -386,7 +391,7 @@ __device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const 
     tmem_ld64(t1, y);
     tc_fence_before_sync();
     mbar_arrive(&wk->region_free);
-    if (g_ws_flags & 4) {      // measurement switch: skip LayerNorm, sums and stitch (wrong results)
+    if (WS_FLAGS & 4) {      // measurement switch: skip LayerNorm, sums and stitch (wrong results)
       if (y[0] == 123.456f) p.agg[wt] = y[1];
       continue;
     }
@@ -457,7 +462,7 @@ __device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const 
           y[j] = r.x; y[j + 1] = r.y;
         }
       }
-      if (is_end && !(g_ws_flags & 16)) {          // measurement switch bit 4: no agg rows written (wrong results)
+      if (is_end && !(WS_FLAGS & 16)) {          // measurement switch bit 4: no agg rows written (wrong results)
         const bool head_piece = first_cont && seg0 == 0;                        // continues the previous warp's receiver
         const bool tail_piece = cont_next && !one_piece && lane == nrows - 1;   // continues in the next warp
         if constexpr (DEFER) {
@@ -487,7 +492,7 @@ __device__ __forceinline__ void ws_epilogue(const SgnnEdgeLayerParams& p, const 
             y[4 * j] = a.x; y[4 * j + 1] = a.y; y[4 * j + 2] = b.x; y[4 * j + 3] = b.y;
           }
         }
-        if (!tail_piece && !head_piece && !(g_ws_flags & 32)) {   // (measurement switch bit 5: rows go to shared memory)
+        if (!tail_piece && !head_piece && !(WS_FLAGS & 32)) {   // (measurement switch bit 5: rows go to shared memory)
           // a receiver's agg row leaves as eight 32-byte stores: every store fills a whole sector (sixteen
           // 16-byte stores per row cost 19 % of the kernel at 1M: r01p, switch bit 4)
           float* dst = p.agg + (long)t * W;
@@ -633,8 +638,13 @@ extern "C" int sgnn_debug_ws_timeline(void* buf) {
   return SGNN_OK;
 }
 extern "C" int sgnn_debug_ws_flags(int flags) {
+#ifdef SGNN_TIMELINE
   SGNN_CUDA(cudaMemcpyToSymbol(g_ws_flags, &flags, sizeof(flags)));
   return SGNN_OK;
+#else
+  SGNN_CHECK_ARG(flags == 0, "debug_ws_flags: the measurement switches exist in SGNN_TIMELINE builds only");
+  return SGNN_OK;
+#endif
 }
 
 int sgnn_edge_layer_gather_launch(const SgnnEdgeLayerParams* p, void* stream) {

@@ -39,7 +39,7 @@ class RolloutPlan:
     """Static buffers + captured CUDA graph of one (N, T, S, mode) rollout shape."""
 
     def __init__(self, sim: LearnedSimulator, n: int, total_frames: int, s: int, dim: int,
-                 mode: str, device, use_graph: bool = True):
+                 mode: str, device, use_graph: bool = True, n_examples: int = 1):
         self.sim, self.n, self.t, self.s, self.dim, self.mode = sim, n, total_frames, s, dim, mode
         self.nsteps = total_frames - s
         f32 = dict(dtype=torch.float32, device=device)
@@ -48,7 +48,9 @@ class RolloutPlan:
         self.pred = self.traj if mode == "autoregressive" else torch.zeros(n, total_frames, dim, **f32)
         self.strain = torch.zeros(self.nsteps, n, **f32)
         self.types = torch.zeros(n, dtype=torch.int64, device=device)
-        self.example_ptr = example_ptr_of([n], device)
+        self.example_ptr = example_ptr_of([n], device)             # one example; B + 1 boundaries for a batch of B
+        if n_examples > 1:                                          # (filled by the caller: the graph reads the buffer)
+            self.example_ptr = torch.zeros(n_examples + 1, dtype=torch.int32, device=device)
         self.graph = None
         self.use_graph = use_graph
         self.version = None
@@ -89,12 +91,12 @@ class RolloutPlan:
         L.launch_count += self.launches_per_replay
 
 
-def get_plan(sim, n, t, s, dim, mode, device, use_graph=True) -> RolloutPlan:
+def get_plan(sim, n, t, s, dim, mode, device, use_graph=True, n_examples: int = 1) -> RolloutPlan:
     cache = sim.__dict__.setdefault("_rollout_plans", {})
-    key = (n, t, s, dim, mode, str(device), use_graph, getattr(sim, "_graph_token", 0))
+    key = (n, t, s, dim, mode, str(device), use_graph, getattr(sim, "_graph_token", 0), n_examples)
     plan = cache.pop(key, None)
     if plan is None:
-        plan = RolloutPlan(sim, n, t, s, dim, mode, device, use_graph)
+        plan = RolloutPlan(sim, n, t, s, dim, mode, device, use_graph, n_examples)
         while len(cache) >= MAX_CACHED_PLANS:          # least recently used first (dicts keep insertion order)
             cache.pop(next(iter(cache)))
     cache[key] = plan
@@ -127,7 +129,13 @@ def rollout(simulator: LearnedSimulator, position: torch.Tensor, particle_types:
     particle_types = particle_types.to(dev)
     erosional = particle_types == EROSIONAL_PARTICLE_ID
     has_erosional = bool(erosional.any().item())        # one sync, before the timed loop
-    plan = get_plan(simulator, n, t, s, dim, inference_mode, dev, use_cuda_graph and not has_erosional)
+    # a [B] tensor of particle counts (B > 1) rolls B independent trajectories out as one system: examples do not
+    # interact (the neighbour search is per example, learned_simulator.py:104-117 of the reference)
+    n_examples = n_particles_per_example.numel() if isinstance(n_particles_per_example, torch.Tensor) else 1
+    plan = get_plan(simulator, n, t, s, dim, inference_mode, dev, use_cuda_graph and not has_erosional,
+                    max(n_examples, 1))
+    if n_examples > 1:
+        plan.example_ptr.copy_(example_ptr_of(n_particles_per_example, dev))
     plan.types.copy_(particle_types)
     gt_strains = strains[s:].to(dev).float()
 
