@@ -136,11 +136,18 @@ class GhostPlan:
             torch.tensor([float("inf"), float("-inf")], device=dev)
         exts = comm.allgather(ext)
         r, w = comm.rank, comm.world
-        if r > 0 and r < w - 1 and x_last_owned.numel():
-            width = float(ext[1] - ext[0])
-            if width < g:
-                raise ValueError(f"slab of rank {r} is narrower ({width:.3g}) than the halo ({g:.3g}): "
-                                 "use fewer ranks")
+        # Every rank holds the same `exts`, so every rank takes the same decision here (a ValueError on one rank only
+        # would leave the others hanging in the next collective).  Ghosts are exchanged with the two id-neighbours
+        # only: slabs two or more apart must be farther than g apart in x, and an inner slab must be wider than g.
+        lo_hi = [(float(e[0]), float(e[1])) for e in exts]
+        for a in range(w):
+            if 0 < a < w - 1 and lo_hi[a][1] - lo_hi[a][0] < g:
+                raise ValueError(f"slab of rank {a} is narrower ({lo_hi[a][1] - lo_hi[a][0]:.3g}) than the halo "
+                                 f"({g:.3g}): use fewer ranks")
+            for b in range(a + 2, w):
+                if not (lo_hi[b][0] - lo_hi[a][1] > g or lo_hi[a][0] - lo_hi[b][1] > g):
+                    raise ValueError(f"slabs of ranks {a} and {b} are closer than the halo ({g:.3g}) in x: particle ids "
+                                     "are not x-major (or the system deformed too far); re-partition before sharding")
         empty = torch.empty(0, dtype=torch.long, device=dev)
         self.send_left = select_for_neighbour(x_last_owned, float(exts[r - 1][0]), float(exts[r - 1][1]), g) \
             if r > 0 else empty
@@ -175,7 +182,8 @@ def exchange_rows(comm: Comm, plan: GhostPlan, owned_rows: torch.Tensor) -> Tupl
 @torch.no_grad()
 def sharded_rollout(simulator, positions_owned: torch.Tensor, nsteps: int, comm: Comm,
                     n_layers: int, skin: Optional[float] = None, refresh_every: int = 10,
-                    return_edges: bool = False, use_graph: bool = True):
+                    return_edges: bool = False, use_graph: bool = True,
+                    particle_types_owned: Optional[torch.Tensor] = None):
     """Autoregressive rollout of this rank's slab.
 
     positions_owned [n_owned, S, dim]: the initial window of the owned particles (global ids
@@ -208,6 +216,9 @@ def sharded_rollout(simulator, positions_owned: torch.Tensor, nsteps: int, comm:
         win[:nl, :s], win[nl:nl + no, :s], win[nl + no:, :s] = gl, window, gr
         shift = torch.empty(nloc, s, dim, dtype=torch.float32, device=dev)
         types = torch.zeros(nloc, dtype=torch.int64, device=dev)
+        if particle_types_owned is not None:                          # ghosts carry their owners' types
+            tl, tr = exchange_rows(comm, plan, particle_types_owned.to(dev).long().contiguous())
+            types[:nl], types[nl:nl + no], types[nl + no:] = tl, particle_types_owned.to(dev).long(), tr
         ptr = torch.tensor([0, nloc], dtype=torch.int32, device=dev)
         st_buf = torch.empty(nloc, dtype=torch.float32, device=dev)
 

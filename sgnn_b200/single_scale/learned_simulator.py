@@ -221,7 +221,7 @@ class LearnedSimulator(nn.Module):
         if rg is None or rg.n != n or rg.csr.rowptr.device != dev:
             rg = self.__dict__["_train_rg"] = RadiusGraph(n, MAX_NUM_NEIGHBORS, True, dev)
         csr = rg.build(noisy[0, s - 1], noisy.stride(0), dim, example_ptr_of(nparticles_per_example, dev), radius)
-        graph = T.TrainGraph.from_csr(csr)
+        graph = T.TrainGraph.from_csr(csr, copy=torch.is_grad_enabled())     # two forwards before one backward stay correct
         extra = self._particle_type_embedding(particle_types) if self._nparticle_types > 1 else None
         nf = T.node_features(noisy, st["velocity"]["mean"], st["velocity"]["std"], radius, 1.0, extra)
         ef = T.edge_features(noisy[0, s - 1], noisy.stride(0), dim, radius, graph)

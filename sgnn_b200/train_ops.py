@@ -39,8 +39,13 @@ class TrainGraph:
         self._by_src = None
 
     @staticmethod
-    def from_csr(csr) -> "TrainGraph":
+    def from_csr(csr, copy: bool = False) -> "TrainGraph":
+        """copy=True: own copies of the edge list (the autograd Functions read it again at backward time; a
+        persistent neighbour-search buffer would be overwritten by a second forward before that backward)."""
         e = int(csr.rowptr[csr.n_nodes].item())   # the one host sync of a training step
+        if copy:
+            return TrainGraph(csr.rowptr[:csr.n_nodes + 1].clone(), csr.src[:e].clone(), csr.tgt[:e].clone(),
+                              csr.n_nodes, e)
         return TrainGraph(csr.rowptr, csr.src, csr.tgt, csr.n_nodes, e)
 
     def by_source(self):

@@ -225,3 +225,40 @@ def test_tf32_matmul_mode_of_train_step_stays_close():
         losses[mode] = training.train_step(sim, opt, batch, 0.02, noise=noise, matmul=mode).item()
         assert torch.backends.cuda.matmul.allow_tf32 == before
     assert abs(losses["tf32"] - losses["fp32"]) <= 1e-3 * max(1.0, abs(losses["fp32"]))
+
+
+def test_two_forwards_before_one_backward_keep_their_graphs():
+    """predict_accelerations hands each forward its own copy of the edge list: a second forward (gradient
+    accumulation, an extra loss evaluation) must not change the gradients of the first."""
+    from sgnn_b200 import synthetic
+    from sgnn_b200.single_scale import LearnedSimulator
+    s = 6
+    spacing, radius = synthetic.spacing_for("B")
+    stats = None
+    batches = []
+    for seed in (0, 1):
+        traj = synthetic.taylor_trajectory(20, 10, spacing, nframes=s + 1, seed=seed)
+        stats = stats or synthetic.normalization_stats(synthetic.metadata_from(traj["positions"]), 0.02 * spacing / 0.5)
+        pos = traj["positions"].cuda()
+        if seed == 1:
+            pos = pos * 0.8                                   # a different edge set
+        batches.append((pos[:, :s].contiguous(), pos[:, s].contiguous()))
+    torch.manual_seed(0)
+    sim = LearnedSimulator(2, (s - 1) * 2 + 1, 3, 64, 2, 1, 64, radius, stats, 1, 9, device="cuda").cuda().train()
+    n = batches[0][0].shape[0]
+    types, counts = torch.zeros(n, dtype=torch.int64, device="cuda"), torch.tensor([n], device="cuda")
+
+    def fwd(b):
+        pa, ta, ps = sim.predict_accelerations(b[1], torch.zeros_like(b[0]), b[0], counts, types)
+        return ((pa - ta) ** 2).sum()
+
+    sim.zero_grad()
+    fwd(batches[0]).backward()
+    want = {k: p.grad.clone() for k, p in sim.named_parameters() if p.grad is not None}
+    sim.zero_grad()
+    l0 = fwd(batches[0])
+    fwd(batches[1])                                           # overwrites the persistent neighbour-search buffers
+    l0.backward()
+    for k, p in sim.named_parameters():
+        if p.grad is not None:
+            assert torch.equal(p.grad, want[k]), k
