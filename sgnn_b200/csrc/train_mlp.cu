@@ -9,8 +9,9 @@
 //
 // A CTA of 128 threads owns 128-row tiles (persistent loop, row count read on the device); thread t owns
 // row t in every epilogue: TMEM lane t <-> row t, bias / ReLU / LayerNorm / the ReLU mask are thread-local.
-// The products are tcgen05.mma kind::tf32 with both operands in shared memory (K-major SWIZZLE_128B) and
-// fp32 accumulators in TMEM -- the same tile machinery as the inference kernels (mlp_tile.cuh).
+// The products are tcgen05.mma kind::tf32 with the A operand (activations) in TENSOR MEMORY, the weight images in
+// shared memory (K-major SWIZZLE_128B) and fp32 accumulators in TMEM.  Keeping the activations out of shared
+// memory is what lets two CTAs share an SM with hi / lo operands (64 KB of images + one 32 KB staging tile each).
 //
 // Precision.  TF32 keeps 10 mantissa bits; the gradient parity tests pin the training step against the
 // reference in fp64 with a bar of 20 x the reference's own fp32-vs-fp64 gap.  With split = 1 every operand is
@@ -28,10 +29,13 @@ namespace sgnn {
 
 constexpr int kTrKChunk = 64;       // the A operand is staged in chunks of at most 64 columns
 // 256 threads per CTA: threads t and t + 128 own the SAME row (TMEM lane t & 127 -- a warp reaches the lane
-// quadrant 32 * (warp % 4)) and alternate over its 32-column chunks.  With one CTA per SM (the hi / lo operand
-// tiles and images take 130-190 KB) 128 threads meant ONE warp per scheduler: ncu showed 15 % issue utilisation
-// with every dependent-issue and shared-memory latency exposed (profiles/README.md, r02b).
+// quadrant 32 * (warp % 4)) and alternate over its 32-column chunks.  With 128 threads and one CTA per SM there
+// was ONE warp per scheduler: ncu showed 15 % issue utilisation with every dependent-issue and shared-memory
+// latency exposed (profiles/README.md, r02b).
 constexpr int kTrThreads = 256;
+// TMEM columns of a CTA: [0, 64) A hi, [64, 128) A lo, [128, 256) accumulators (two of 64, or one of 128)
+constexpr int kTrTmemCols = 256;
+constexpr int kTrAHi = 0, kTrALo = 64, kTrAcc = 128;
 __device__ __forceinline__ int tr_row() { return (int)threadIdx.x & (kTileRows - 1); }
 __device__ __forceinline__ int tr_half() { return (int)threadIdx.x >> 7; }
 __device__ __forceinline__ int tr_log2(int x) { return 31 - __clz(x); }
@@ -44,91 +48,142 @@ struct TrMisc {
   float2 red[2][kTileRows];           // LayerNorm: (mean, sum of squared deviations) of each half of a row
 };
 
-template <bool SPLIT>
-__device__ __forceinline__ void tr_store4(char* a_hi, char* a_lo, uint32_t off, float4 v) {
-  const float4 h = make_float4(to_tf32(v.x), to_tf32(v.y), to_tf32(v.z), to_tf32(v.w));
-  *reinterpret_cast<float4*>(a_hi + off) = h;
-  if constexpr (SPLIT)
-    *reinterpret_cast<float4*>(a_lo + off) = make_float4(v.x - h.x, v.y - h.y, v.z - h.z, v.w - h.w);
-}
-
-// 32 columns [col, col + 32) of this thread's row into the A tile(s)
-template <bool SPLIT>
-__device__ __forceinline__ void tr_a_store32(char* a_hi, char* a_lo, int col, const float* v) {
+// ---- exact fp32 staging tile (K-major SWIZZLE_128B addressing: conflict-free 16-byte row-owner accesses) ----
+// Everything a thread reads or writes per ROW goes through this tile: the global side is a cooperative loop in
+// which a warp covers whole contiguous rows (4 L1 wavefronts per 512 bytes instead of 32 for row-owner accesses).
+__device__ __forceinline__ void tr_row_store32(char* t, int col, const float* v) {
 #pragma unroll
   for (int j = 0; j < 8; ++j)
-    tr_store4<SPLIT>(a_hi, a_lo, sw128_chunk_offset(tr_row(), col / 4 + j, kTileRows),
-                     make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]));
+    *reinterpret_cast<float4*>(t + sw128_chunk_offset(tr_row(), col / 4 + j, kTileRows)) =
+        make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
 }
-
-// Cooperative load of columns [c0, c0 + width) of rows [row0, row0 + rows_valid) of a row-major matrix into
-// columns [0, wpad) of the A tile(s) (zero padded to wpad, a multiple of 32; rows past rows_valid zero).
-template <bool SPLIT>
-__device__ __forceinline__ void tr_a_load(char* a_hi, char* a_lo, const float* __restrict__ src, long ld, long row0,
-                                          int c0, int width, int wpad, int rows_valid, float scale) {
-  const bool vec = (width & 3) == 0 && (ld & 3) == 0 && (c0 & 3) == 0 && ((uintptr_t)src & 15) == 0;
-  if (vec) {
-    const int chunks = wpad >> 2, wch = width >> 2, sh = tr_log2(chunks);        // wpad is 32 or 64
-    const int total = kTileRows * chunks;
-    for (int idx0 = threadIdx.x; idx0 < total; idx0 += 4 * kTrThreads) {
-      float4 v[4];
+__device__ __forceinline__ void tr_row_load32(const char* t, int col, float* v) {
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int idx = idx0 + u * kTrThreads;
-        const int r = idx >> sh, c = idx & (chunks - 1);
-        v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (idx < total && r < rows_valid && c < wch)
-          v[u] = __ldg(reinterpret_cast<const float4*>(src + (row0 + r) * ld + c0) + c);
-      }
+  for (int j = 0; j < 8; ++j) {
+    const float4 a = *reinterpret_cast<const float4*>(t + sw128_chunk_offset(tr_row(), col / 4 + j, kTileRows));
+    v[4 * j] = a.x; v[4 * j + 1] = a.y; v[4 * j + 2] = a.z; v[4 * j + 3] = a.w;
+  }
+}
+// tile[r][0:width) = a[ia[r]][c0 : c0 + width) (+ b[ib[r]][..]) for r < rows_valid; width is 32, 64 or 128 and
+// c0, ld multiples of 4.  ia / ib: shared index arrays (NULL: row0 + r).  Columns [width, wpad) are zeroed.
+__device__ __forceinline__ void tr_tile_gather(char* t, const float* __restrict__ a, const float* __restrict__ b, long ld,
+                                               const int* ia, const int* ib, long row0, int c0, int width, int wpad,
+                                               int rows_valid) {
+  const int chunks = wpad >> 2, wch = width >> 2, sh = tr_log2(chunks);
+  const int total = rows_valid * chunks;
+  constexpr int U = 4;
+  for (int idx0 = threadIdx.x; idx0 < total; idx0 += U * kTrThreads) {
+    float4 va[U], vb[U];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int idx = idx0 + u * kTrThreads;
-        if (idx < total) {
-          const int r = idx >> sh, c = idx & (chunks - 1);
-          tr_store4<SPLIT>(a_hi, a_lo, sw128_chunk_offset(r, c, kTileRows),
-                           make_float4(v[u].x * scale, v[u].y * scale, v[u].z * scale, v[u].w * scale));
-        }
+    for (int u = 0; u < U; ++u) {
+      const int idx = idx0 + u * kTrThreads;
+      va[u] = vb[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      const int r = idx >> sh, c = idx & (chunks - 1);
+      if (idx < total && c < wch) {
+        va[u] = __ldg(reinterpret_cast<const float4*>(a + (ia ? (long)ia[r] : row0 + r) * ld + c0) + c);
+        if (b != nullptr) vb[u] = __ldg(reinterpret_cast<const float4*>(b + (ib ? (long)ib[r] : row0 + r) * ld + c0) + c);
       }
     }
-  } else {
-    const int total = kTileRows * wpad, sh = tr_log2(wpad);
-    for (int idx = threadIdx.x; idx < total; idx += kTrThreads) {
-      const int r = idx >> sh, c = idx & (wpad - 1);
-      float v = 0.f;
-      if (r < rows_valid && c < width) v = __ldg(src + (row0 + r) * ld + c0 + c) * scale;
-      const float h = to_tf32(v);
-      const uint32_t off = sw128_offset(r, c, kTileRows);
-      *reinterpret_cast<float*>(a_hi + off) = h;
-      if constexpr (SPLIT) *reinterpret_cast<float*>(a_lo + off) = v - h;
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int idx = idx0 + u * kTrThreads;
+      if (idx < total) {
+        const int r = idx >> sh, c = idx & (chunks - 1);
+        *reinterpret_cast<float4*>(t + sw128_chunk_offset(r, c, kTileRows)) =
+            make_float4(va[u].x + vb[u].x, va[u].y + vb[u].y, va[u].z + vb[u].z, va[u].w + vb[u].w);
+      }
     }
   }
 }
+// dst[row0 + r][0:width) (=|+=) tile[r] (+ add[row0 + r]); coalesced; width is 32, 64 or 128
+__device__ __forceinline__ void tr_tile_store(float* __restrict__ dst, long ld, long row0, const char* t, int width,
+                                              int rows_valid, bool accumulate, const float* __restrict__ add, long ld_add) {
+  const int chunks = width >> 2, sh = tr_log2(chunks);
+  const int total = rows_valid * chunks;
+  for (int idx = threadIdx.x; idx < total; idx += kTrThreads) {
+    const int r = idx >> sh, c = idx & (chunks - 1);
+    float4 v = *reinterpret_cast<const float4*>(t + sw128_chunk_offset(r, c, kTileRows));
+    if (add != nullptr) {
+      const float4 a = __ldg(reinterpret_cast<const float4*>(add + (row0 + r) * ld_add) + c);
+      v = make_float4(v.x + a.x, v.y + a.y, v.z + a.z, v.w + a.w);
+    }
+    float4* d = reinterpret_cast<float4*>(dst + (row0 + r) * ld) + c;
+    if (accumulate) {
+      const float4 z = *d;
+      v = make_float4(v.x + z.x, v.y + z.y, v.z + z.z, v.w + z.w);
+    }
+    *d = v;
+  }
+}
 
-// D[128 x n] (+)= A[128 x k] W[n x k]^T on the tensor pipe; with SPLIT the two cross terms go first.
-// All threads call; completion through gemm_wait<true>.
+// ---- tensor memory ----------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t tr_lane_base() { return (uint32_t)(((threadIdx.x >> 5) & 3) * 32) << 16; }
+// 32 accumulator columns of this thread's row (lane quadrant of the warp: warp % 4)
+__device__ __forceinline__ void tr_acc_load32(const TileAcc<true>& acc, int col, float* v) {
+  tmem_ld32(acc.tmem_base + tr_lane_base() + (uint32_t)col, v);
+}
+// 32 columns [col, col + 32) of this thread's row of the A operand: hi = tf32(v) (and lo = v - hi, exact)
 template <bool SPLIT>
-__device__ __forceinline__ void tr_gemm(TileAcc<true>& acc, const char* a_hi, const char* a_lo, const char* w_hi,
-                                        const char* w_lo, int k, int n, int acc_col, bool accumulate) {
+__device__ __forceinline__ void tr_a_store32(const TileAcc<true>& acc, int col, const float* v) {
+  float h[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) h[j] = to_tf32(v[j]);
+  tmem_st32(acc.tmem_base + tr_lane_base() + (uint32_t)(kTrAHi + col), h);
+  if constexpr (SPLIT) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) h[j] = v[j] - h[j];
+    tmem_st32(acc.tmem_base + tr_lane_base() + (uint32_t)(kTrALo + col), h);
+  }
+}
+// staging tile columns [0, kw) of every row -> A operand (rows >= rows_valid and columns >= kw as zeros), times scale
+template <bool SPLIT>
+__device__ __forceinline__ void tr_a_from_tile(const TileAcc<true>& acc, const char* t, int kw, bool valid, float scale) {
+  for (int c = tr_half() * 32; c < kw; c += 64) {
+    float v[32];
+    tr_row_load32(t, c, v);
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = valid ? v[j] * scale : 0.f;
+    tr_a_store32<SPLIT>(acc, c, v);
+  }
+}
+// the A operand is complete: tensor-memory stores -> visible to the MMAs of the elected thread
+__device__ __forceinline__ void tr_a_publish() {
+  tmem_st_wait();
+  tc_fence_before_sync();
+  __syncthreads();
+}
+
+// D[128 x n] (+)= A[128 x k] W[n x k]^T, A in tensor memory; with SPLIT the two cross terms go first.
+// All threads call; completion through gemm_wait<true>.
+__device__ __forceinline__ void tr_umma_ts(uint32_t d, uint32_t a, uint32_t w_base, int k, int n, bool accumulate) {
+  const uint32_t idesc = umma_idesc_tf32(kTileRows, n);
+  uint32_t acc = accumulate ? 1u : 0u;
+  for (int kb = 0; kb < k / kKBlock; ++kb) {
+    const uint32_t w_kb = w_base + kb * n * kKBlockBytes;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      umma_tf32_ts(d, a + kb * kKBlock + j * 8, umma_desc_sw128(w_kb + j * 32), idesc, acc);
+      acc = 1u;
+    }
+  }
+}
+template <bool SPLIT>
+__device__ __forceinline__ void tr_gemm(TileAcc<true>& acc, const char* w_hi, const char* w_lo, int k, int n,
+                                        int acc_col, bool accumulate) {
   if (threadIdx.x < 32) {
     tc_fence_after_sync();
     if (elect_one()) {
       const uint32_t d = acc.tmem_base + (uint32_t)acc_col;
       if constexpr (SPLIT) {
-        umma_gemm_tf32(d, smem_u32(a_lo), smem_u32(w_hi), k, n, accumulate);
-        umma_gemm_tf32(d, smem_u32(a_hi), smem_u32(w_lo), k, n, true);
-        umma_gemm_tf32(d, smem_u32(a_hi), smem_u32(w_hi), k, n, true);
+        tr_umma_ts(d, acc.tmem_base + kTrALo, smem_u32(w_hi), k, n, accumulate);
+        tr_umma_ts(d, acc.tmem_base + kTrAHi, smem_u32(w_lo), k, n, true);
+        tr_umma_ts(d, acc.tmem_base + kTrAHi, smem_u32(w_hi), k, n, true);
       } else {
-        umma_gemm_tf32(d, smem_u32(a_hi), smem_u32(w_hi), k, n, accumulate);
+        tr_umma_ts(d, acc.tmem_base + kTrAHi, smem_u32(w_hi), k, n, accumulate);
       }
     }
     __syncwarp();
   }
-}
-
-// 32 accumulator columns of this thread's row (lane quadrant of the warp: warp % 4)
-__device__ __forceinline__ void tr_acc_load32(const TileAcc<true>& acc, int col, float* v) {
-  const uint32_t lane_base = (uint32_t)(((threadIdx.x >> 5) & 3) * 32) << 16;
-  tmem_ld32(acc.tmem_base + lane_base + (uint32_t)col, v);
 }
 
 __device__ __forceinline__ int tr_rows(int max_rows, const int* n_rows_dev) {
@@ -144,95 +199,16 @@ __device__ __forceinline__ void tr_stage(char* dst, const float* src, int bytes,
                  bar);
 }
 
-// ---- exact fp32 staging tiles (same swizzled layout as the operands) -------------------------------------
-// Row-owner accesses to global memory touch 32 different 128-byte lines per warp instruction (32 L1 wavefronts
-// for 512 bytes); everything a thread reads or writes per ROW therefore goes through a shared-memory tile: the
-// row owner uses conflict-free 16-byte shared accesses, the global side is a cooperative loop in which a warp
-// covers whole contiguous rows (4 wavefronts per 512 bytes).
-__device__ __forceinline__ void tr_row_store32(char* t, int col, const float* v) {
-#pragma unroll
-  for (int j = 0; j < 8; ++j)
-    *reinterpret_cast<float4*>(t + sw128_chunk_offset(tr_row(), col / 4 + j, kTileRows)) =
-        make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-}
-__device__ __forceinline__ void tr_row_load32(const char* t, int col, float* v) {
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const float4 a = *reinterpret_cast<const float4*>(t + sw128_chunk_offset(tr_row(), col / 4 + j, kTileRows));
-    v[4 * j] = a.x; v[4 * j + 1] = a.y; v[4 * j + 2] = a.z; v[4 * j + 3] = a.w;
-  }
-}
-// tile[r][0:width) = a[ia[r]][0:width) (+ b[ib[r]][0:width)), rows >= rows_valid untouched; width % 4 == 0.
-// ia / ib: shared-memory index arrays (NULL: row0 + r).  Eight 16-byte loads in flight per thread.
-__device__ __forceinline__ void tr_tile_gather(char* t, const float* __restrict__ a, const float* __restrict__ b, long ld,
-                                               const int* ia, const int* ib, long row0, int width, int rows_valid) {
-  const int chunks = width >> 2, sh = tr_log2(chunks);          // width is 32, 64 or 128
-  const int total = rows_valid * chunks;
-  constexpr int U = 4;
-  for (int idx0 = threadIdx.x; idx0 < total; idx0 += U * kTrThreads) {
-    float4 va[U], vb[U];
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int idx = idx0 + u * kTrThreads;
-      va[u] = vb[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (idx < total) {
-        const int r = idx >> sh, c = idx & (chunks - 1);
-        va[u] = __ldg(reinterpret_cast<const float4*>(a + (ia ? (long)ia[r] : row0 + r) * ld) + c);
-        if (b != nullptr) vb[u] = __ldg(reinterpret_cast<const float4*>(b + (ib ? (long)ib[r] : row0 + r) * ld) + c);
-      }
-    }
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int idx = idx0 + u * kTrThreads;
-      if (idx < total) {
-        const int r = idx >> sh, c = idx & (chunks - 1);
-        *reinterpret_cast<float4*>(t + sw128_chunk_offset(r, c, kTileRows)) =
-            make_float4(va[u].x + vb[u].x, va[u].y + vb[u].y, va[u].z + vb[u].z, va[u].w + vb[u].w);
-      }
-    }
-  }
-}
-// dst[row0 + r][0:width) (=|+=) tile[r] (+ tile_lo[r]) (+ add[row0 + r]); coalesced; width % 4 == 0
-__device__ __forceinline__ void tr_tile_store(float* __restrict__ dst, long ld, long row0, const char* t, const char* t_lo,
-                                              int width, int rows_valid, bool accumulate, const float* __restrict__ add,
-                                              long ld_add) {
-  const int chunks = width >> 2, sh = tr_log2(chunks);
-  const int total = rows_valid * chunks;
-  for (int idx = threadIdx.x; idx < total; idx += kTrThreads) {
-    const int r = idx >> sh, c = idx & (chunks - 1);
-    const uint32_t off = sw128_chunk_offset(r, c, kTileRows);
-    float4 v = *reinterpret_cast<const float4*>(t + off);
-    if (t_lo != nullptr) {
-      const float4 l = *reinterpret_cast<const float4*>(t_lo + off);
-      v = make_float4(v.x + l.x, v.y + l.y, v.z + l.z, v.w + l.w);
-    }
-    if (add != nullptr) {
-      const float4 a = __ldg(reinterpret_cast<const float4*>(add + (row0 + r) * ld_add) + c);
-      v = make_float4(v.x + a.x, v.y + a.y, v.z + a.z, v.w + a.w);
-    }
-    float4* d = reinterpret_cast<float4*>(dst + (row0 + r) * ld) + c;
-    if (accumulate) {
-      const float4 z = *d;
-      v = make_float4(v.x + z.x, v.y + z.y, v.z + z.z, v.w + z.w);
-    }
-    *d = v;
-  }
-}
-
 struct TrFwdSmem {
-  int w1, w2, a, a_bytes, g, g_bytes, misc, total;
+  int w1, w2, g, g_bytes, misc, total;
 };
 __host__ __device__ inline TrFwdSmem tr_fwd_smem(int kpad, int hidden, int out, int n_linear, int split) {
   TrFwdSmem s;
   const int out_pad = (out + 15) & ~15;
   s.w1 = hidden * kpad * 4;
   s.w2 = n_linear == 2 ? out_pad * hidden * 4 : 0;
-  int aw = kpad < kTrKChunk ? kpad : kTrKChunk;
-  if (n_linear == 2 && hidden > aw) aw = hidden;
-  s.a_bytes = kTileRows * aw * 4;
-  s.a = (s.w1 + s.w2) * (split ? 2 : 1);
-  s.g = s.a + s.a_bytes * (split ? 2 : 1);
-  const int gw = n_linear == 2 ? (hidden > out ? hidden : ((out + 31) & ~31)) : hidden;
+  s.g = (s.w1 + s.w2) * (split ? 2 : 1);
+  int gw = hidden > kTrKChunk ? hidden : kTrKChunk;          // input chunk, gathered terms, h1, y2 / y, [P | Q]
   s.g_bytes = kTileRows * gw * 4;
   s.misc = s.g + s.g_bytes;
   s.total = s.misc + (int)sizeof(TrMisc) + 1024;
@@ -240,7 +216,7 @@ __host__ __device__ inline TrFwdSmem tr_fwd_smem(int kpad, int hidden, int out, 
 }
 
 template <bool SPLIT>
-__global__ void __launch_bounds__(kTrThreads)
+__global__ void __launch_bounds__(kTrThreads, 2)
 train_fwd_kernel(const SgnnTrainFwd p) {
   char* smem = smem_base_1024();
   const TrFwdSmem L = tr_fwd_smem(p.kpad, p.hidden, p.out, p.n_linear, SPLIT);
@@ -249,8 +225,7 @@ train_fwd_kernel(const SgnnTrainFwd p) {
   char* w1l = SPLIT ? w1h + L.w1 : w1h;
   char* w2h = w1h + L.w1 * (SPLIT ? 2 : 1);
   char* w2l = SPLIT ? w2h + L.w2 : w2h;
-  char* a_hi = smem + L.a;
-  char* a_lo = SPLIT ? a_hi + L.a_bytes : a_hi;
+  char* g_t = smem + L.g;
   TrMisc* misc = reinterpret_cast<TrMisc*>(smem + L.misc);
   const int tid = threadIdx.x, row = tr_row(), half = tr_half();
 
@@ -266,11 +241,10 @@ train_fwd_kernel(const SgnnTrainFwd p) {
     }
   }
   TileAcc<true> acc;
-  const int acc1 = p.hidden;                                     // accumulator of the second Linear
-  acc_setup<true>(acc, pow2_cols(p.hidden + (p.n_linear == 2 ? out_pad : 0)), &misc->bar_mma, &misc->tmem_slot, nullptr);
+  const int acc0 = kTrAcc, acc1 = kTrAcc + 64;                   // n_linear 1: one accumulator of up to 128 columns
+  acc_setup<true>(acc, kTrTmemCols, &misc->bar_mma, &misc->tmem_slot, nullptr);
   mbar_wait(&misc->bar_w, 0);
 
-  char* g_t = smem + L.g;                                         // exact fp32 staging tile
   const int rows = tr_rows(p.max_rows, p.n_rows_dev);
   const int n_tiles = (rows + kTileRows - 1) / kTileRows;
   const bool gathered = p.add_p != nullptr;
@@ -283,48 +257,53 @@ train_fwd_kernel(const SgnnTrainFwd p) {
     if (valid && p.tgt != nullptr) { tg = __ldg(p.tgt + r); sr = __ldg(p.src + r); }
     if (half == 0) { misc->tgt[row] = tg; misc->src[row] = sr; }
 
-    // ---- first Linear, K staged in chunks of 64 columns ----
+    // ---- first Linear, K staged in chunks of 64 columns: rows -> staging tile -> A operand in tensor memory ----
     for (int kc = 0; kc < p.kpad; kc += kTrKChunk) {
       const int kw = p.kpad - kc < kTrKChunk ? p.kpad - kc : kTrKChunk;
       if (p.prologue == SGNN_TPRO_EDGE_FEATURES) {
-       if (half == 0) {
-        float v[32];
+        if (half == 0) {
+          float v[32];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = 0.f;
-        if (valid) {
-          float sq = 0.f;
-          for (int d = 0; d < p.dim; ++d) {
-            const float f = __fdiv_rn(__fsub_rn(__ldg(p.pos + (long)sr * p.pos_stride + d),
-                                                __ldg(p.pos + (long)tg * p.pos_stride + d)), p.radius);
-            v[d] = f;
-            sq = __fadd_rn(sq, __fmul_rn(f, f));
+          for (int j = 0; j < 32; ++j) v[j] = 0.f;
+          if (valid) {
+            float sq = 0.f;
+            for (int d = 0; d < p.dim; ++d) {
+              const float f = __fdiv_rn(__fsub_rn(__ldg(p.pos + (long)sr * p.pos_stride + d),
+                                                  __ldg(p.pos + (long)tg * p.pos_stride + d)), p.radius);
+              v[d] = f;
+              sq = __fadd_rn(sq, __fmul_rn(f, f));
+            }
+            v[p.dim] = sqrtf(sq);
+            if (p.feat_out != nullptr)
+              for (int d = 0; d <= p.dim; ++d) p.feat_out[r * (p.dim + 1) + d] = v[d];
           }
-          v[p.dim] = sqrtf(sq);
-          if (p.feat_out != nullptr)
-            for (int d = 0; d <= p.dim; ++d) p.feat_out[r * (p.dim + 1) + d] = v[d];
+          tr_a_store32<SPLIT>(acc, 0, v);
         }
-        tr_a_store32<SPLIT>(a_hi, a_lo, 0, v);
-       }
-      } else if (p.prologue == SGNN_TPRO_ROWS2 && kc >= p.k0) {
-        tr_a_load<SPLIT>(a_hi, a_lo, p.a1, p.ld1, row0, kc - p.k0, p.k1 - (kc - p.k0) < kw ? p.k1 - (kc - p.k0) : kw, kw,
-                         rows_valid, 1.0f);
       } else {
-        tr_a_load<SPLIT>(a_hi, a_lo, p.a0, p.ld0, row0, kc, p.k0 - kc < kw ? p.k0 - kc : kw, kw, rows_valid, p.scale0);
+        if (p.prologue == SGNN_TPRO_ROWS2 && kc >= p.k0) {
+          const int w = p.k1 - (kc - p.k0) < kw ? p.k1 - (kc - p.k0) : kw;
+          tr_tile_gather(g_t, p.a1, nullptr, p.ld1, nullptr, nullptr, row0, kc - p.k0, w, kw, rows_valid);
+        } else {
+          const int w = p.k0 - kc < kw ? p.k0 - kc : kw;
+          tr_tile_gather(g_t, p.a0, nullptr, p.ld0, nullptr, nullptr, row0, kc, w, kw, rows_valid);
+        }
+        __syncthreads();
+        tr_a_from_tile<SPLIT>(acc, g_t, kw, valid, (p.prologue == SGNN_TPRO_ROWS2 && kc >= p.k0) ? 1.0f : p.scale0);
       }
-      a_tile_publish<true>();
+      tr_a_publish();                       // (also: everybody has read the staging tile)
       const int woff = (kc / kKBlock) * p.hidden * kKBlockBytes;
-      tr_gemm<SPLIT>(acc, a_hi, a_lo, w1h + woff, w1l + woff, kw, p.hidden, 0, kc > 0);
+      tr_gemm<SPLIT>(acc, w1h + woff, w1l + woff, kw, p.hidden, acc0, kc > 0);
       // while the last chunk's product runs: receiver + sender terms of the rows, gathered with whole-row requests
       if (gathered && kc + kTrKChunk >= p.kpad)
-        tr_tile_gather(g_t, p.add_p, p.add_q, p.ld_add, misc->tgt, misc->src, row0, p.hidden, rows_valid);
+        tr_tile_gather(g_t, p.add_p, p.add_q, p.ld_add, misc->tgt, misc->src, row0, 0, p.hidden, p.hidden, rows_valid);
       gemm_wait<true>(acc);
     }
     if (gathered) __syncthreads();
 
-    // ---- bias (+ gathered terms), ReLU, feed the second Linear; h1 leaves from the operand tile ----
+    // ---- bias (+ gathered terms), ReLU; h1 exact into the staging tile, hi / lo into the A operand ----
     for (int c = half * 32; c < p.hidden; c += 64) {
       float v[32];
-      tr_acc_load32(acc, c, v);
+      tr_acc_load32(acc, acc0 + c, v);
 #pragma unroll
       for (int j = 0; j < 32; ++j)
         if (p.b1 != nullptr && c + j < p.b1_cols) v[j] += __ldg(p.b1 + c + j);
@@ -337,27 +316,25 @@ train_fwd_kernel(const SgnnTrainFwd p) {
       if (p.n_linear == 2) {
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = valid ? fmaxf(v[j], 0.f) : 0.f;
-        tr_a_store32<SPLIT>(a_hi, a_lo, c, v);
-      } else {
-        tr_row_store32(g_t, c, v);
+        tr_a_store32<SPLIT>(acc, c, v);
       }
+      tr_row_store32(g_t, c, v);
     }
     if (p.n_linear != 2) {
       tc_fence_before_sync();
       __syncthreads();
-      tr_tile_store(p.y, p.ld_y, row0, g_t, nullptr, p.hidden, rows_valid, false, nullptr, 0);
+      tr_tile_store(p.y, p.ld_y, row0, g_t, p.hidden, rows_valid, false, nullptr, 0);
       __syncthreads();                      // staging tile and accumulator free for the next tile
       continue;
     }
-    a_tile_publish<true>();
-    tr_gemm<SPLIT>(acc, a_hi, a_lo, w2h, w2l, p.hidden, out_pad, acc1, false);
-    // h1 = hi (+ lo) from the operand tiles while the second product runs (plain TF32 mode keeps the rounded value)
-    tr_tile_store(p.h1, p.hidden, row0, a_hi, SPLIT ? a_lo : nullptr, p.hidden, rows_valid, false, nullptr, 0);
+    tr_a_publish();
+    tr_gemm<SPLIT>(acc, w2h, w2l, p.hidden, out_pad, acc1, false);
+    tr_tile_store(p.h1, p.hidden, row0, g_t, p.hidden, rows_valid, false, nullptr, 0);     // while the second product runs
     gemm_wait<true>(acc);
-    __syncthreads();                        // everybody is done reading the operand tiles: they become staging space
+    __syncthreads();                        // the staging tile is free again
 
     // ---- second Linear's bias, LayerNorm (statistics kept), output ----
-    if (p.has_ln) {                         // out is a multiple of 64 here: each half of the row owns out / 2 columns
+    if (p.has_ln) {                         // out is 64 or 128: each half of the row owns out / 2 columns
       const float n_loc = 0.5f * (float)p.out;
       float s4[4] = {0.f, 0.f, 0.f, 0.f};
       for (int c = half * 32; c < p.out; c += 64) {
@@ -376,6 +353,7 @@ train_fwd_kernel(const SgnnTrainFwd p) {
           const float d = v[j] + __ldg(p.b2 + c + j) - m_loc;
           q4[j & 3] = fmaf(d, d, q4[j & 3]);
         }
+        tr_row_store32(g_t, c, v);          // (y2 without its bias, for now)
       }
       misc->red[half][row] = make_float2(m_loc, (q4[0] + q4[1]) + (q4[2] + q4[3]));
       __syncthreads();
@@ -385,20 +363,32 @@ train_fwd_kernel(const SgnnTrainFwd p) {
       const float m2 = ((q4[0] + q4[1]) + (q4[2] + q4[3])) + oth.y + dm * dm * (0.5f * n_loc);
       const float rstd = 1.0f / sqrtf(m2 / (float)p.out + 1e-5f);
       if (valid && half == 0) { p.mean[r] = mean; p.rstd[r] = rstd; }
-      for (int c = half * 32; c < p.out; c += 64) {
-        float v[32];
-        tr_acc_load32(acc, acc1 + c, v);
+      float y[2][32];                       // this thread's chunks of the output (out <= 128: at most two)
 #pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] += __ldg(p.b2 + c + j);
-        tr_row_store32(a_hi, c, v);         // y2, the LayerNorm's input
+      for (int k = 0; k < 2; ++k) {
+        const int c = half * 32 + 64 * k;
+        if (c < p.out) {
+          float v[32];
+          tr_row_load32(g_t, c, v);
 #pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = (v[j] - mean) * rstd * __ldg(p.gamma + c + j) + __ldg(p.beta + c + j);
-        tr_row_store32(g_t, c, v);          // y (the residual is added on the way out)
+          for (int j = 0; j < 32; ++j) {
+            v[j] += __ldg(p.b2 + c + j);
+            y[k][j] = (v[j] - mean) * rstd * __ldg(p.gamma + c + j) + __ldg(p.beta + c + j);
+          }
+          tr_row_store32(g_t, c, v);        // y2, the LayerNorm's input
+        }
       }
       tc_fence_before_sync();
       __syncthreads();
-      tr_tile_store(p.y2, p.out, row0, a_hi, nullptr, p.out, rows_valid, false, nullptr, 0);
-      tr_tile_store(p.y, p.ld_y, row0, g_t, nullptr, p.out, rows_valid, false, p.res, p.ld_res);
+      tr_tile_store(p.y2, p.out, row0, g_t, p.out, rows_valid, false, nullptr, 0);
+      __syncthreads();
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const int c = half * 32 + 64 * k;
+        if (c < p.out) tr_row_store32(g_t, c, y[k]);
+      }
+      __syncthreads();
+      tr_tile_store(p.y, p.ld_y, row0, g_t, p.out, rows_valid, false, p.res, p.ld_res);     // (+ residual on the way out)
     } else {
       for (int c = half * 32; c < out_pad; c += 64) {
         float v[32];
@@ -415,7 +405,7 @@ train_fwd_kernel(const SgnnTrainFwd p) {
 
 // ------------------------------------------------------------------------------------------ backward
 struct TrBwdSmem {
-  int w2t, w1t, a, a_bytes, g, g_bytes, misc, total;
+  int w2t, w1t, g, g_bytes, misc, total;
 };
 __host__ __device__ inline TrBwdSmem tr_bwd_smem(int k_dy, int n_linear, int hidden, int want_dx, int kx, int split) {
   TrBwdSmem s;
@@ -423,31 +413,24 @@ __host__ __device__ inline TrBwdSmem tr_bwd_smem(int k_dy, int n_linear, int hid
   const int k2 = n_linear == 2 ? hidden : kdp;             // K of the dx product
   s.w2t = n_linear == 2 ? hidden * kdp * 4 : 0;
   s.w1t = want_dx ? kx * k2 * 4 : 0;
-  int aw = kdp < kTrKChunk ? kdp : kTrKChunk;
-  if (n_linear == 2 && hidden > aw) aw = hidden;
-  s.a_bytes = kTileRows * aw * 4;
-  s.a = (s.w2t + s.w1t) * (split ? 2 : 1);
-  s.g = s.a + s.a_bytes * (split ? 2 : 1);
-  s.g_bytes = kTileRows * kTrKChunk * 4;                   // h1 tile, then the second half of dx
-  if (n_linear == 2 && hidden > kTrKChunk) s.g_bytes = kTileRows * hidden * 4;
+  s.g = (s.w2t + s.w1t) * (split ? 2 : 1);
+  s.g_bytes = kTileRows * kTrKChunk * 4;                   // dy chunk, h1 tile, dpre, one 64-column half of dx
   s.misc = s.g + s.g_bytes;
   s.total = s.misc + (int)sizeof(TrMisc) + 1024;
   return s;
 }
 
 template <bool SPLIT>
-__global__ void __launch_bounds__(kTrThreads)
+__global__ void __launch_bounds__(kTrThreads, 2)
 train_bwd_kernel(const SgnnTrainBwd p) {
   char* smem = smem_base_1024();
   const TrBwdSmem L = tr_bwd_smem(p.k_dy, p.n_linear, p.hidden, p.want_dx, p.kx, SPLIT);
   const int kdp = (p.k_dy + 31) & ~31;
-  const int k2 = p.n_linear == 2 ? p.hidden : kdp;
   char* w2h = smem;
   char* w2l = SPLIT ? w2h + L.w2t : w2h;
   char* w1h = w2h + L.w2t * (SPLIT ? 2 : 1);
   char* w1l = SPLIT ? w1h + L.w1t : w1h;
-  char* a_hi = smem + L.a;
-  char* a_lo = SPLIT ? a_hi + L.a_bytes : a_hi;
+  char* g_t = smem + L.g;
   TrMisc* misc = reinterpret_cast<TrMisc*>(smem + L.misc);
   const int tid = threadIdx.x, row = tr_row(), half = tr_half();
 
@@ -465,12 +448,10 @@ train_bwd_kernel(const SgnnTrainBwd p) {
     }
   }
   TileAcc<true> acc;
-  const int accx = p.n_linear == 2 ? p.hidden : 0;               // accumulator of the dx product
-  acc_setup<true>(acc, pow2_cols(accx + (p.want_dx ? p.kx : 0) > 32 ? accx + (p.want_dx ? p.kx : 0) : 32),
-                  &misc->bar_mma, &misc->tmem_slot, nullptr);
+  const int acch = kTrAcc, accx = kTrAcc;                        // dh is consumed before the dx product starts: same columns
+  acc_setup<true>(acc, kTrTmemCols, &misc->bar_mma, &misc->tmem_slot, nullptr);
   mbar_wait(&misc->bar_w, 0);
 
-  char* g_t = smem + L.g;
   const int rows = tr_rows(p.max_rows, p.n_rows_dev);
   const int n_tiles = (rows + kTileRows - 1) / kTileRows;
   for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -478,62 +459,63 @@ train_bwd_kernel(const SgnnTrainBwd p) {
     const int rows_valid = rows - row0 < kTileRows ? (int)(rows - row0) : kTileRows;
     const bool valid = row < rows_valid;
 
-    if (p.n_linear == 2) {
-      // ---- dh = dy W2 (K = width of dy, staged in chunks), ReLU mask from the h1 tile, dpre kept ----
-      for (int kc = 0; kc < kdp; kc += kTrKChunk) {
-        const int kw = kdp - kc < kTrKChunk ? kdp - kc : kTrKChunk;
-        tr_a_load<SPLIT>(a_hi, a_lo, p.dy, p.ld_dy, row0, kc, p.k_dy - kc < kw ? p.k_dy - kc : kw, kw, rows_valid, 1.0f);
-        a_tile_publish<true>();
-        const int woff = (kc / kKBlock) * p.hidden * kKBlockBytes;
-        tr_gemm<SPLIT>(acc, a_hi, a_lo, w2h + woff, w2l + woff, kw, p.hidden, 0, kc > 0);
-        if (kc + kTrKChunk >= kdp)          // while the product runs: this tile of h1, whole rows per request
-          tr_tile_gather(g_t, p.h1, nullptr, p.hidden, nullptr, nullptr, row0, p.hidden, rows_valid);
-        gemm_wait<true>(acc);
-      }
+    // ---- first product: dh = dy W2 (n_linear 2) or dx = dy W1 (n_linear 1); K = width of dy, in chunks of 64 ----
+    const int n1 = p.n_linear == 2 ? p.hidden : p.kx;
+    for (int kc = 0; kc < kdp; kc += kTrKChunk) {
+      const int kw = kdp - kc < kTrKChunk ? kdp - kc : kTrKChunk;
+      const int w = p.k_dy - kc < kw ? p.k_dy - kc : kw;
+      tr_tile_gather(g_t, p.dy, nullptr, p.ld_dy, nullptr, nullptr, row0, kc, w, kw, rows_valid);
       __syncthreads();
+      tr_a_from_tile<SPLIT>(acc, g_t, kw, valid, 1.0f);
+      tr_a_publish();
+      const int woff = (kc / kKBlock) * n1 * kKBlockBytes;
+      if (p.n_linear == 2) {
+        tr_gemm<SPLIT>(acc, w2h + woff, w2l + woff, kw, n1, acch, kc > 0);
+        if (kc + kTrKChunk >= kdp)          // while the product runs: this tile of h1, whole rows per request
+          tr_tile_gather(g_t, p.h1, nullptr, p.hidden, nullptr, nullptr, row0, 0, p.hidden, p.hidden, rows_valid);
+      } else {
+        tr_gemm<SPLIT>(acc, w1h + woff, w1l + woff, kw, n1, accx, kc > 0);
+      }
+      gemm_wait<true>(acc);
+    }
+    if (p.n_linear == 2) {
+      __syncthreads();
+      // ---- ReLU mask from the h1 tile; dpre exact into the staging tile, hi / lo into the A operand ----
       for (int c = half * 32; c < p.hidden; c += 64) {
         float v[32], h[32];
-        tr_acc_load32(acc, c, v);
+        tr_acc_load32(acc, acch + c, v);
         tr_row_load32(g_t, c, h);
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = (valid && h[j] > 0.f) ? v[j] : 0.f;
-        tr_a_store32<SPLIT>(a_hi, a_lo, c, v);
-        if (!SPLIT) tr_row_store32(g_t, c, v);      // plain TF32: the operand tile holds rounded values, dpre leaves exact
+        if (p.want_dx) tr_a_store32<SPLIT>(acc, c, v);
+        tr_row_store32(g_t, c, v);
       }
-      a_tile_publish<true>();
-      if (p.want_dx) tr_gemm<SPLIT>(acc, a_hi, a_lo, w1h, w1l, p.hidden, p.kx, accx, false);
-      if (SPLIT) tr_tile_store(p.dpre, p.hidden, row0, a_hi, a_lo, p.hidden, rows_valid, false, nullptr, 0);
-      else tr_tile_store(p.dpre, p.hidden, row0, g_t, nullptr, p.hidden, rows_valid, false, nullptr, 0);
+      if (p.want_dx) tmem_st_wait();
+      tc_fence_before_sync();
+      __syncthreads();
+      if (p.want_dx) tr_gemm<SPLIT>(acc, w1h, w1l, p.hidden, p.kx, accx, false);
+      tr_tile_store(p.dpre, p.hidden, row0, g_t, p.hidden, rows_valid, false, nullptr, 0);
       if (!p.want_dx) {
-        tc_fence_before_sync();
         __syncthreads();
         continue;
       }
       gemm_wait<true>(acc);
-    } else {
-      // ---- dx = dy W1 directly (K = width of dy, staged in chunks) ----
-      for (int kc = 0; kc < kdp; kc += kTrKChunk) {
-        const int kw = kdp - kc < kTrKChunk ? kdp - kc : kTrKChunk;
-        tr_a_load<SPLIT>(a_hi, a_lo, p.dy, p.ld_dy, row0, kc, p.k_dy - kc < kw ? p.k_dy - kc : kw, kw, rows_valid, 1.0f);
-        a_tile_publish<true>();
-        const int woff = (kc / kKBlock) * p.kx * kKBlockBytes;
-        tr_gemm<SPLIT>(acc, a_hi, a_lo, w1h + woff, w1l + woff, kw, p.kx, accx, kc > 0);
-        gemm_wait<true>(acc);
+    }
+    // ---- dx by 64-column halves through the staging tile: [0, k0) -> dx0, [k0, k0 + k1) -> dx1 ----
+    for (int c0 = 0; c0 < p.kx; c0 += kTrKChunk) {
+      __syncthreads();                      // the staging tile is free
+      const int cw = p.kx - c0 < kTrKChunk ? p.kx - c0 : kTrKChunk;
+      for (int c = half * 32; c < cw; c += 64) {
+        float v[32];
+        tr_acc_load32(acc, accx + c0 + c, v);
+        tr_row_store32(g_t, c, v);
       }
+      tc_fence_before_sync();
+      __syncthreads();
+      if (c0 < p.k0) tr_tile_store(p.dx0 + c0, p.ld_dx0, row0, g_t, cw, rows_valid, p.acc0 != 0, nullptr, 0);
+      else tr_tile_store(p.dx1 + (c0 - p.k0), p.ld_dx1, row0, g_t, cw, rows_valid, p.acc1 != 0,
+                         p.add1 ? p.add1 + (c0 - p.k0) : nullptr, p.ld_add1);
     }
-    (void)k2;
-    __syncthreads();                        // operand and staging tiles are free: dx is staged there
-    // ---- dx by columns: [0, k0) -> dx0 through the operand tile, [k0, k0 + k1) -> dx1 through the staging tile ----
-    for (int c = half * 32; c < p.kx; c += 64) {
-      float v[32];
-      tr_acc_load32(acc, accx + c, v);
-      if (c < p.k0) tr_row_store32(a_hi, c, v);
-      else tr_row_store32(g_t, c - p.k0, v);
-    }
-    tc_fence_before_sync();
-    __syncthreads();
-    tr_tile_store(p.dx0, p.ld_dx0, row0, a_hi, nullptr, p.k0, rows_valid, p.acc0 != 0, nullptr, 0);
-    if (p.k1 > 0) tr_tile_store(p.dx1, p.ld_dx1, row0, g_t, nullptr, p.k1, rows_valid, p.acc1 != 0, p.add1, p.ld_add1);
     __syncthreads();
   }
   acc_teardown<true>(acc);
@@ -584,8 +566,13 @@ extern "C" int sgnn_train_mlp_fwd(const SgnnTrainFwd* p, void* stream) {
   SGNN_CHECK_ARG(p->hidden >= 16 && p->hidden % 32 == 0 && p->hidden <= 128, "train_mlp_fwd: hidden %d must be 32, 64, 96 or 128",
                  p->hidden);
   SGNN_CHECK_ARG(p->n_linear == 1 || (p->out >= 1 && p->out <= 128), "train_mlp_fwd: bad out %d", p->out);
-  SGNN_CHECK_ARG(!p->has_ln || (p->n_linear == 2 && (p->out == 64 || p->out == 128)), "train_mlp_fwd: LayerNorm needs out 64 or 128");
-  SGNN_CHECK_ARG(p->hidden == 32 || p->hidden == 64 || p->hidden == 128, "train_mlp_fwd: hidden must be 32, 64 or 128");
+  SGNN_CHECK_ARG(!p->has_ln || (p->n_linear == 2 && p->out == 64), "train_mlp_fwd: LayerNorm needs out 64");
+  SGNN_CHECK_ARG(p->hidden == 64 || (p->n_linear == 1 && p->hidden == 128), "train_mlp_fwd: hidden must be 64 (a single Linear: 64 or 128)");
+  SGNN_CHECK_ARG(p->prologue == SGNN_TPRO_EDGE_FEATURES || (p->a0 && al16(p->a0) && p->ld0 % 4 == 0 && p->k0 % 4 == 0),
+                 "train_mlp_fwd: input rows must be 16-byte aligned, leading dimension and width multiples of 4");
+  SGNN_CHECK_ARG(p->prologue != SGNN_TPRO_ROWS2 || (p->a1 && al16(p->a1) && p->ld1 % 4 == 0 && p->k1 % 4 == 0),
+                 "train_mlp_fwd: second input must be 16-byte aligned, leading dimension and width multiples of 4");
+  SGNN_CHECK_ARG(p->n_linear == 1 || p->out <= 64, "train_mlp_fwd: out must be <= 64");
   SGNN_CHECK_ARG(p->n_linear == 2 || p->hidden % 32 == 0, "train_mlp_fwd: single Linear needs width %% 32 == 0");
   SGNN_CHECK_ARG(p->prologue != SGNN_TPRO_ROWS2 || (p->k0 % kTrKChunk == 0 && p->k0 + p->k1 <= p->kpad),
                  "train_mlp_fwd: ROWS2 needs k0 %% 64 == 0");
@@ -603,9 +590,7 @@ extern "C" int sgnn_train_mlp_fwd(const SgnnTrainFwd* p, void* stream) {
   SGNN_CHECK_ARG(s.total <= 227 * 1024, "train_mlp_fwd: needs %d bytes of shared memory", s.total);
   const int tiles = (p->max_rows + kTileRows - 1) / kTileRows;
   int per_sm = (227 * 1024) / s.total;
-  const int tmem_cols = pow2_cols(p->hidden + (p->n_linear == 2 ? ((p->out + 15) & ~15) : 0));
-  if (per_sm > 512 / tmem_cols) per_sm = 512 / tmem_cols;      // resident CTAs share the SM's 512 TMEM columns
-  if (per_sm > 4) per_sm = 4;
+  if (per_sm > 512 / kTrTmemCols) per_sm = 512 / kTrTmemCols;  // resident CTAs share the SM's 512 TMEM columns
   int grid = tr_sm_count() * per_sm;
   if (grid > tiles) grid = tiles;
   if (p->split) {
@@ -626,9 +611,10 @@ extern "C" int sgnn_train_mlp_bwd(const SgnnTrainBwd* p, void* stream) {
                                       al16(p->h1) && al16(p->dpre)),
                  "train_mlp_bwd: hidden %d must be 32..128 (multiple of 32) with h1 / dpre given", p->hidden);
   SGNN_CHECK_ARG(p->n_linear == 2 || p->want_dx, "train_mlp_bwd: a single Linear has only the dx product");
-  SGNN_CHECK_ARG(p->n_linear == 1 || p->hidden == 64 || p->hidden == 128, "train_mlp_bwd: hidden must be 64 or 128");
-  SGNN_CHECK_ARG(!p->want_dx || ((p->k0 == 64 || p->k0 == 32 || p->k0 == 128) && (p->k1 == 0 || p->k1 == 64 || p->k1 == 32)),
-                 "train_mlp_bwd: dx widths must be powers of two (32..128)");
+  SGNN_CHECK_ARG(p->n_linear == 1 || p->hidden == 64, "train_mlp_bwd: hidden must be 64");
+  SGNN_CHECK_ARG(!p->want_dx || (p->k0 == 64 && (p->k1 == 0 || p->k1 == 64)), "train_mlp_bwd: dx widths must be 64 (+ 64)");
+  SGNN_CHECK_ARG(p->dy && al16(p->dy) && p->ld_dy % 4 == 0 && p->k_dy % 4 == 0,
+                 "train_mlp_bwd: dy must be 16-byte aligned, leading dimension and width multiples of 4");
   if (p->want_dx) {
     SGNN_CHECK_ARG(p->kx == p->k0 + p->k1 && p->kx % 16 == 0 && p->kx <= 128 && p->k0 % 32 == 0 && p->k0 > 0,
                    "train_mlp_bwd: dx widths k0 %d k1 %d", p->k0, p->k1);
@@ -641,10 +627,7 @@ extern "C" int sgnn_train_mlp_bwd(const SgnnTrainBwd* p, void* stream) {
   SGNN_CHECK_ARG(s.total <= 227 * 1024, "train_mlp_bwd: needs %d bytes of shared memory", s.total);
   const int tiles = (p->max_rows + kTileRows - 1) / kTileRows;
   int per_sm = (227 * 1024) / s.total;
-  const int cols_needed = (p->n_linear == 2 ? p->hidden : 0) + (p->want_dx ? p->kx : 0);
-  const int tmem_cols = pow2_cols(cols_needed > 32 ? cols_needed : 32);
-  if (per_sm > 512 / tmem_cols) per_sm = 512 / tmem_cols;
-  if (per_sm > 4) per_sm = 4;
+  if (per_sm > 512 / kTrTmemCols) per_sm = 512 / kTrTmemCols;
   int grid = tr_sm_count() * per_sm;
   if (grid > tiles) grid = tiles;
   if (p->split) {

@@ -201,7 +201,8 @@ class TrainEngine:
         self.inv_n = f(1)
         self.loss = f(1)
         # activations
-        self.nf = f(n, self.k_node)
+        self.k_node_pad = pad32(self.k_node)
+        self.nf = f(n, self.k_node_pad)             # zero-padded rows: 16-byte aligned, whole-row requests
         self.ef = f(cap, self.dim + 1)
         mk_n = lambda: {"h1": f(n, h), "y2": f(n, h), "mean": f(n), "rstd": f(n)}           # noqa: E731
         mk_e = lambda: {"h1": f(cap, h), "y2": f(cap, h), "mean": f(cap), "rstd": f(cap)}   # noqa: E731
@@ -387,12 +388,12 @@ class TrainEngine:
                                                 self._stream()), launches=5)
         L.check(self.lib.sgnn_node_features(win.data_ptr(), win.stride(0), n, s, dim, st["velocity"]["mean"].data_ptr(),
                                             st["velocity"]["std"].data_ptr(), 2.0, self.radius, 1.0, self.nf.data_ptr(),
-                                            self.k_node, self._stream()))
+                                            self.k_node_pad, self._stream()))
         # ---- forward ----
         m = self.mlp["ne"]
         hi, lo = self._img(m["w1"]); hi2, lo2 = self._img(m["w2"])
         a = self.act_ne
-        self._fwd(tag="fwd_node_encoder", max_rows=n, prologue=TPRO_ROWS, a0=self.nf, ld0=self.k_node, k0=self.k_node, kpad=pad32(self.k_node),
+        self._fwd(tag="fwd_node_encoder", max_rows=n, prologue=TPRO_ROWS, a0=self.nf, ld0=self.k_node_pad, k0=self.k_node_pad, kpad=self.k_node_pad,
                   hidden=h, out=h, n_linear=2, has_ln=1, w1_hi=hi, w1_lo=lo, w2_hi=hi2, w2_lo=lo2, b1=m["a"].bias,
                   b1_cols=h, b2=m["b"].bias, gamma=m["ln"].weight, beta=m["ln"].bias, h1=a["h1"], y2=a["y2"],
                   mean=a["mean"], rstd=a["rstd"], y=self.x[0], ld_y=h)
@@ -442,7 +443,7 @@ class TrainEngine:
         # ---- backward ----
         dx, dx_new = self.dx
         hi, lo = self._img(md["w2t"]); hi1, lo1 = self._img(md["w1t"])
-        self._bwd(tag="bwd_decoder", max_rows=n, dy=self.dpred, ld_dy=4, k_dy=dim + 1, n_linear=2, hidden=h, h1=self.h1_d, dpre=self.dpre_n,
+        self._bwd(tag="bwd_decoder", max_rows=n, dy=self.dpred, ld_dy=4, k_dy=4, n_linear=2, hidden=h, h1=self.h1_d, dpre=self.dpre_n,
                   w2t_hi=hi, w2t_lo=lo, want_dx=1, kx=h, w1t_hi=hi1, w1t_lo=lo1, dx0=dx, ld_dx0=h, k0=h)
         self._wgrad(self.dpred, 4, self.h1_d, h, n, None, dim + 1, h, md["b"].weight.grad, 0, db=md["b"].bias.grad)
         self._wgrad(self.dpre_n, h, xl, h, n, None, h, h, md["a"].weight.grad, 0, db=md["a"].bias.grad)
@@ -489,7 +490,7 @@ class TrainEngine:
         self._bwd(tag="bwd_node_encoder", max_rows=n, dy=self.dy2_n, ld_dy=h, k_dy=h, n_linear=2, hidden=h, h1=a["h1"], dpre=self.dpre_n,
                   w2t_hi=hi, w2t_lo=lo, want_dx=0)
         self._wgrad(self.dy2_n, h, a["h1"], h, n, None, h, h, m["b"].weight.grad, 0, db=m["b"].bias.grad)
-        self._wgrad(self.dpre_n, h, self.nf, self.k_node, n, None, h, self.k_node, m["a"].weight.grad, 0, db=m["a"].bias.grad)
+        self._wgrad(self.dpre_n, h, self.nf, self.k_node_pad, n, None, h, self.k_node, m["a"].weight.grad, 0, db=m["a"].bias.grad)
 
     def _whole_step(self):
         with self._timed("forward_backward_total"):
