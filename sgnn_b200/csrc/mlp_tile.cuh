@@ -204,12 +204,14 @@ __device__ __forceinline__ void a_tile_load_rows(void* a_tile, int col0, const f
   char* a = reinterpret_cast<char*>(a_tile);
   const int chunks = width >> 2;                   // 16-byte chunks per row
   const int total = kTileRows * chunks;
-  // four independent loads in flight per thread: one load per iteration made this loop a chain of
-  // global round trips (32 iterations x ~0.45 us for a 128-wide tile, the multi-scale kernels)
-  for (int idx0 = threadIdx.x; idx0 < total; idx0 += 4 * kThreads) {
-    float4 v[4];
+  // independent loads in flight per thread: one load per iteration made this loop a chain of global round trips
+  // (32 iterations x ~0.45 us for a 128-wide tile, the multi-scale kernels); four per iteration left sixteen round
+  // trips for the [agg | x] tile of a 128-wide node kernel (~16 of its 61 us at 4800 nodes, r02d): eight now
+  constexpr int U = 8;
+  for (int idx0 = threadIdx.x; idx0 < total; idx0 += U * kThreads) {
+    float4 v[U];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < U; ++u) {
       const int idx = idx0 + u * kThreads;
       const int r = idx / chunks, c = idx - r * chunks;
       v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -219,7 +221,7 @@ __device__ __forceinline__ void a_tile_load_rows(void* a_tile, int col0, const f
       }
     }
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < U; ++u) {
       const int idx = idx0 + u * kThreads;
       if (idx < total) {
         const int r = idx / chunks, c = idx - r * chunks;
