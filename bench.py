@@ -743,31 +743,37 @@ def run_gpu(args):
                 line["large"] = {"error": repr(ex)}
     if not args.no_extra:
         # every rank takes part (the train step and the sharded rollout have collectives); rank 0 reports
-        try:
-            tr = train_config(dev, rank, world)
-        except Exception as ex:
-            tr = {"error": repr(ex)}
+        want = set(args.sections.split(","))
+        tr = {"skipped": True}
+        if "train" in want:
+            try:
+                tr = train_config(dev, rank, world)
+            except Exception as ex:
+                tr = {"error": repr(ex)}
         ms = fp = bt = None
         if rank == 0:
-            try:
-                ms = multiscale_config(dev, rank)
-            except Exception as ex:
-                ms = {"error": repr(ex)}
-            try:
-                fp = fp32_config(dev, traj, stats, radius)
-            except Exception as ex:
-                fp = {"error": repr(ex)}
-            if world == 1:
+            if "multi_scale" in want:
+                try:
+                    ms = multiscale_config(dev, rank)
+                except Exception as ex:
+                    ms = {"error": repr(ex)}
+            if "fp32" in want:
+                try:
+                    fp = fp32_config(dev, traj, stats, radius)
+                except Exception as ex:
+                    fp = {"error": repr(ex)}
+            if world == 1 and "batched" in want:
                 try:
                     bt = batched_config(dev)
                 except Exception as ex:
                     bt = {"error": repr(ex)}
         sh = shw = None
-        if world > 1:
+        if world > 1 and "sharded" in want:
             try:
                 sh = sharded_config(dev, rank, world)
             except Exception as ex:
                 sh = {"error": repr(ex)}
+        if world > 1 and "sharded_weak" in want:
             try:
                 shw = sharded_config(dev, rank, world, weak=True, check_steps=0)
             except Exception as ex:
@@ -803,6 +809,8 @@ def main():
     ap.add_argument("--impl", default="sgnn_b200", choices=["sgnn_b200", "reference"])
     ap.add_argument("--no-large", action="store_true", help="skip the 1M-particle single-step section")
     ap.add_argument("--no-extra", action="store_true", help="skip the training and multi-scale sections")
+    ap.add_argument("--sections", default="train,multi_scale,fp32,batched,sharded,sharded_weak",
+                    help="comma list of the extra sections to run (all by default)")
     ap.add_argument("--workload", default="rollout", choices=["rollout", "train", "sharded"],
                     help="which measured workload is the headline `value` (rollout replicas by default; train and "
                          "sharded communicate, so the driver's scaling efficiency then measures the collectives)")
