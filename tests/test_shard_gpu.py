@@ -46,9 +46,10 @@ def test_sharded_rollout_equals_unsharded(regime, world, precision):
         try:
             torch.cuda.set_device(0)
             lo, hi = bounds[r]
-            results[r] = S.sharded_rollout(sims[r], pos[lo:hi, :Sw].contiguous(), nsteps, fixed_ghosts=(regime == "A"),
+            results[r] = S.sharded_rollout(sims[r], pos[lo:hi, :Sw].contiguous(), nsteps,
                                            S.ThreadComm(shared, r), n_layers=layers, refresh_every=2,
-                                           return_edges=True, use_graph=False)   # ranks are threads here
+                                           return_edges=True, use_graph=False,    # ranks are threads here
+                                           fixed_ghosts=(regime == "A"))         # both ghost plans are covered
         except Exception as ex:      # surface failures instead of dead-locking the barrier
             errors.append(ex)
             shared.barrier.abort()
