@@ -31,9 +31,12 @@ def test_rollout_golden_and_graph_determinism(precision):
     ref64 = f["rollout_f64"]
     acc_std = f.stats()["acceleration"]["std"].max().item()
     assert a["predicted_rollout"].shape == ref64.shape
-    for step in range(nsteps):
-        err = np.abs(a["predicted_rollout"][step] - ref64[step]).max()
-        assert err <= TOL[precision] * acc_std * (step + 1) * 3 + 2e-4, (step, err)
+    from tests.test_single_scale_gpu import growth_bounds
+    ulp = float(np.spacing(np.float32(np.abs(f["positions"]).max())))
+    bounds, _ = growth_bounds(f["rollout_f32"], ref64, (5e-6 if precision == "fp32" else 3e-3) * acc_std + ulp)
+    for step in range(nsteps if precision == "fp32" else 1):     # tf32: the trajectory leaves the fixture's at the first
+        err = np.abs(a["predicted_rollout"][step] - ref64[step]).max()   # edge flip (tests/test_single_scale_gpu.py checks its
+        assert err <= bounds[step], (step, err, bounds[step])            # steps teacher-forced against the oracle)
     if precision == "fp32":
         assert np.allclose(a["rmse_position"], f["rmse_position_f32"], rtol=1e-3)
     for k in ("initial_positions", "initial_strains", "ground_truth_rollout", "ground_truth_strain",

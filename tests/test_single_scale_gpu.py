@@ -17,7 +17,17 @@ from tests.util import Fixture
 
 pytestmark = pytest.mark.gpu
 
-TOL = {"fp32": 2e-4, "tf32": 3e-2}
+# bound on one network evaluation (normalised acceleration / latent entries): ~4x what a B200 run shows
+# (fp32 FFMA mode 8e-7 .. 4e-5, tf32 mode 1.3e-3; profiles/README.md r02a)
+TOL = {"fp32": 2e-4, "tf32": 5e-3}
+
+
+def growth_bounds(ref32, ref64, one_step_abs):
+    """Per-step position bound of an autoregressive rollout: the one-step bound times the error growth of the
+    reference arithmetic itself, G(k) = envelope of gap(k) / gap(0), gap(k) = max|ref_fp32(k) - ref_fp64(k)|."""
+    import numpy as np
+    gap = (torch.as_tensor(ref32).double() - torch.as_tensor(ref64).double()).abs().amax(dim=(1, 2)).numpy()
+    return one_step_abs * np.maximum.accumulate(gap / gap[0]), gap
 
 
 def make_sim(f, precision):
@@ -56,8 +66,11 @@ def test_rollout_matches_reference(name, precision):
     acc_std = f.stats()["acceleration"]["std"].max().item()
     ref32, ref64 = f.t("rollout_f32"), f.t("rollout_f64")
     gap = (ref32.double() - ref64).abs().max().item()
+    ulp = float(np.spacing(np.float32(pos.abs().max().item())))
+    bounds, gaps = growth_bounds(ref32, ref64, (5e-6 if precision == "fp32" else 3e-3) * acc_std + ulp)
     cur = pos[:, :S].contiguous()
     worst = 0.0
+    rows = []
     for step in range(nsteps):
         if precision == "fp32":
             _, ei, _ = sim._encoder_preprocessor(cur, [torch.tensor(n)], types)
@@ -65,11 +78,27 @@ def test_rollout_matches_reference(name, precision):
         nxt, strain = sim.predict_positions(cur, [torch.tensor(n)], types)
         err = (nxt.cpu().double() - ref64[step]).abs().max().item()
         worst = max(worst, err)
-        tol = TOL[precision] * acc_std * (step + 1) * 3 + 4 * gap
-        assert err <= tol, (step, err, tol)
         serr = (strain.cpu() - f.t("rollout_strain_f32")[step]).abs().max().item()
-        assert serr <= TOL[precision] * (step + 1) * 3, (step, serr)
+        if precision == "tf32":
+            # A TF32 trajectory leaves the fixture's as soon as ONE pair sits within its position error of the
+            # d^2 = r^2 boundary (here at step 1: the edge set differs and the velocity error then integrates), so
+            # the tf32 steps are checked teacher-forced: the fp64 oracle on the CUDA trajectory's own window.
+            from oracle import sgnn_oracle as O
+            sd64, st64 = O.cast_sd(f.state_dict(), torch.float64), O.cast_stats(f.stats(), torch.float64)
+            want, want_strain, oei = O.predict_positions(sd64, cur.cpu().double(), [n], types.cpu(), radius, st64)
+            _, ei, _ = sim._encoder_preprocessor(cur, [torch.tensor(n)], types)
+            assert torch.equal(ei.cpu(), oei), step
+            err = (nxt.cpu().double() - want).abs().max().item()
+            serr = (strain.cpu().double() - want_strain).abs().max().item()
+            bounds[step] = bounds[0]
+        rows.append((step, err, bounds[step], gaps[step], serr))
         cur = torch.cat([cur[:, 1:], nxt[:, None, :]], dim=1)
+    print("step  |pos - ref64|  bound      ref fp32-fp64 gap  |dstrain|")
+    for r in rows:
+        print("%4d  %.3e      %.3e  %.3e          %.3e" % r)
+    for step, err, bound, g, serr in rows:
+        assert err <= bound, (step, err, bound)
+        assert serr <= TOL[precision] * max(1.0, bound / bounds[0]), (step, serr)
     print(f"{name} {precision}: max |pos - ref64| = {worst:.3e} (fp32 ref gap {gap:.3e}, acc_std {acc_std:.3e})")
 
 
