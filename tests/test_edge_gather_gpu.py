@@ -4,6 +4,7 @@ inputs, and against the CPU oracle.  The two device paths differ only in where t
 rounded to TF32 (x before the product vs. the fp32 product Q), so they must agree far inside the
 tolerance the TF32 path has against the fp32 oracle.  Sizes cover: fewer tiles than SMs, a ragged
 last tile, and several tiles per CTA and per epilogue group (ring wrap-around, barrier phases)."""
+import numpy as np
 import pytest
 import torch
 
@@ -69,8 +70,9 @@ def test_gather_mode_matches_oracle():
     sd = {k: v.detach().cpu() for k, v in sim.state_dict().items()}
     want, want_strain, _ = O.predict_positions(sd, pos, [n], types, radius, stats)
     acc_std = stats["acceleration"]["std"].max().item()
-    assert (nxt.cpu() - want).abs().max().item() <= 3e-2 * acc_std + 1e-5
-    assert (strain.cpu() - want_strain).abs().max().item() <= 3e-2
+    # stated one-step tolerance of the tf32 path: 3e-3 of acc_std + the fp32 quantum of the position
+    assert (nxt.cpu() - want).abs().max().item() <= 3e-3 * acc_std + float(np.spacing(np.float32(pos.abs().max().item())))
+    assert (strain.cpu() - want_strain).abs().max().item() <= 3e-3
 
 
 def test_gather_mode_rollout_is_deterministic():

@@ -3,7 +3,7 @@ rollout driver) against golden fixtures generated from the unmodified reference,
 reference's own golden vectors (sgnn/multi_scale/test/test_multi_scale_graph.py:119-140,325-348).
 
 Tolerances as in tests/test_single_scale_gpu.py: fp32 mode 2e-4 on the network output, tf32 mode
-3e-2; positions scale with acc_std.  Edge sets, hierarchy indices, node features: bit-exact.
+3e-3 of acc_std per step (tf32), growing with the reference arithmetic's own fp32-vs-fp64 gap.  Edge sets, hierarchy indices, node features: bit-exact.
 """
 import numpy as np
 import pytest
@@ -13,7 +13,8 @@ from tests.util import Fixture
 
 pytestmark = pytest.mark.gpu
 
-TOL = {"fp32": 2e-4, "tf32": 3e-2}
+TOL = {"fp32": 2e-4, "tf32": 5e-3}      # one network evaluation; observed 1e-6 / 1e-3 (profiles/README.md r02a)
+ONE_STEP = {"fp32": 5e-6, "tf32": 3e-3}  # normalised acceleration after one step (tests/test_baseline_configs_gpu.py)
 FIXTURES = ["multi_ref_fixture", "multi_h128"]
 
 
@@ -114,6 +115,11 @@ def test_rollout_matches_reference(name, precision):
     acc_std = f.stats()["acceleration"]["std"].max().item()
     ref32, ref64 = f.t("rollout_f32"), f.t("rollout_f64")
     gap = (ref32.double() - ref64).abs().max().item()
+    # the static graph never changes, so the autoregressive error follows the growth of the reference arithmetic's own
+    # fp32-vs-fp64 gap from the one-step bound (+ the fp32 quantum of the stored position)
+    from tests.test_single_scale_gpu import growth_bounds
+    ulp = float(np.spacing(np.float32(pos.abs().max().item())))
+    bounds, _ = growth_bounds(ref32, ref64, ONE_STEP[precision] * acc_std + ulp)
     cur = pos[:, :S].contiguous()
     worst = 0.0
     for step in range(nsteps):
@@ -121,10 +127,9 @@ def test_rollout_matches_reference(name, precision):
         assert nxt.shape == (n, 2) and strain.shape == (n,)
         err = (nxt.cpu().double() - ref64[step]).abs().max().item()
         worst = max(worst, err)
-        tol = TOL[precision] * acc_std * (step + 1) * 3 + 4 * gap
-        assert err <= tol, (step, err, tol)
+        assert err <= bounds[step], (step, err, bounds[step])
         serr = (strain.cpu() - f.t("rollout_strain_f32")[step]).abs().max().item()
-        assert serr <= TOL[precision] * (step + 1) * 3, (step, serr)
+        assert serr <= TOL[precision] * bounds[step] / bounds[0], (step, serr)
         cur = torch.cat([cur[:, 1:], nxt[:, None, :]], dim=1)
     print(f"{name} {precision}: max |pos - ref64| = {worst:.3e} (gap {gap:.3e}, acc_std {acc_std:.3e})")
 
@@ -178,9 +183,12 @@ def test_rollout_driver(precision):
     assert np.array_equal(a["predicted_rollout"], b["predicted_rollout"])
     acc_std = f.stats()["acceleration"]["std"].max().item()
     ref64 = f["rollout_f64"]
+    from tests.test_single_scale_gpu import growth_bounds
+    ulp = float(np.spacing(np.float32(np.abs(f["positions"]).max())))
+    bounds, _ = growth_bounds(f["rollout_f32"], ref64, ONE_STEP[precision] * acc_std + ulp)
     for step in range(nsteps):
         err = np.abs(a["predicted_rollout"][step] - ref64[step]).max()
-        assert err <= TOL[precision] * acc_std * (step + 1) * 3 + 2e-4, (step, err)
+        assert err <= bounds[step], (step, err, bounds[step])
     assert a["rmse_position"].shape == (nsteps,) and a["predicted_strain"].shape == (nsteps, n)
     # save / load round trip keeps the reference's key names
     import io
