@@ -326,22 +326,42 @@ class EpdEngine:
             raise L.SgnnError(f"engine sized for {self.n} nodes, got {n}")
         last_off = (seq_len - 1) * dim * 4
         last_pos_ptr = pos_seq.data_ptr() + last_off
+        # Several edge sets (multi-scale: grid2mesh, mesh2mesh, mesh2grid): their encoders and the node encoder are
+        # independent ~45 us kernels on 38-83 CTAs each -- they run side by side on forked streams (also under graph
+        # capture) and join before the first block.  With ONE edge set the fork costs more than it hides (r01m).
+        fork = len(self.edge_enc) > 1 and not os.environ.get("SGNN_NO_FORK")
+        cur_stream = torch.cuda.current_stream()
+        side = []
+        if fork:
+            if getattr(self, "_side_streams", None) is None:
+                self._side_streams = [torch.cuda.Stream(device=self.device) for _ in range(len(self.edge_enc))]
+            side = self._side_streams
+            start = torch.cuda.Event()
+            start.record(cur_stream)
+            for st in side:
+                st.wait_event(start)
         for k, (enc, csr) in enumerate(zip(self.edge_enc, csrs)):
-            enc.launch(csr, self.e_tiles[k], pos=last_pos_ptr, pos_stride=pos_seq_stride, dim=dim,
-                       radius=radii[k],
-                       feat_out=None if edge_feat_out is None else edge_feat_out[k])
+            with torch.cuda.stream(side[k - 1] if fork and k > 0 else cur_stream):
+                enc.launch(csr, self.e_tiles[k], pos=last_pos_ptr, pos_stride=pos_seq_stride, dim=dim,
+                           radius=radii[k],
+                           feat_out=None if edge_feat_out is None else edge_feat_out[k])
         # Gather mode: the latents travel between layers only as the rounded copy in the Q half of pq
         # (node_ws.cu); the fp32 buffers x[0], x[1] are written on request (tests, A/B runs) only.
         keep_x = (not self.gather) or bool(os.environ.get("SGNN_KEEP_X") or os.environ.get("SGNN_NODE_FAST")
                                            or os.environ.get("SGNN_NODE_GENERIC"))
         x_cur = 0
-        self.node_enc.launch(
-            n, pos_seq=pos_seq, pos_seq_stride=pos_seq_stride, seq_len=seq_len, dim=dim,
-            vel_mean=vel_mean, vel_std=vel_std, wall_offset=2.0, wall_max=wall_max, wall_div=wall_div,
-            types=types if emb is not None else None, emb=emb,
-            emb_dim=0 if emb is None else emb.shape[1], n_types=0 if emb is None else emb.shape[0],
-            feat_out=feat_out,
-            x_out=self.x[x_cur] if keep_x else None, pq_out=self.pq)
+        with torch.cuda.stream(side[-1] if fork else cur_stream):
+            self.node_enc.launch(
+                n, pos_seq=pos_seq, pos_seq_stride=pos_seq_stride, seq_len=seq_len, dim=dim,
+                vel_mean=vel_mean, vel_std=vel_std, wall_offset=2.0, wall_max=wall_max, wall_div=wall_div,
+                types=types if emb is not None else None, emb=emb,
+                emb_dim=0 if emb is None else emb.shape[1], n_types=0 if emb is None else emb.shape[0],
+                feat_out=feat_out,
+                x_out=self.x[x_cur] if keep_x else None, pq_out=self.pq)
+        for st in side:
+            done = torch.cuda.Event()
+            done.record(st)
+            cur_stream.wait_event(done)
         for bi, (ep, npn, es) in enumerate(self.blocks):
             csr = csrs[es]
             ep.launch(csr, self.e_tiles[es], self.pq, self.agg, self.head)
