@@ -24,6 +24,7 @@ struct NodeMisc {
   uint64_t bar_w, bar_mma, bar_stream;
   uint32_t tmem_slot;
   int pad;
+  int rowptr[kTileRows + 1];     // CSR bounds of the tile's rows (AGG_X prologue)
 };
 
 struct NodeSmem {
@@ -96,37 +97,36 @@ __device__ __forceinline__ void prologue_features(const SgnnNodeParams& p, char*
   for (; k < p.k_pad; ++k) a_store_scalar<TC>(a_tile, row, k, 0.f);
 }
 
-// AGG_X prologue: cooperative, coalesced row segments
+// AGG_X prologue: cooperative, coalesced row segments.  The tile's CSR bounds are fetched ONCE into shared memory
+// (one round trip) and the agg chunks then go eight at a time: with the bounds looked up per chunk every batch of
+// four loads was two dependent round trips, 8 batches for a 128-wide agg tile (~10 of the kernel's 61 us at 4800
+// nodes, multi-scale configs[3], r02d).
 template <bool TC>
-__device__ __forceinline__ void prologue_agg_x(const SgnnNodeParams& p, char* a_tile, long row0, int nvalid) {
+__device__ __forceinline__ void prologue_agg_x(const SgnnNodeParams& p, char* a_tile, long row0, int nvalid, int* s_rowptr) {
+  for (int r = threadIdx.x; r <= kTileRows; r += kThreads) s_rowptr[r] = r <= nvalid ? __ldg(p.rowptr + row0 + r) : 0;
+  __syncthreads();
   const int chunks = p.agg_w >> 2;
   const int total = kTileRows * chunks;
-  // four rows' CSR bounds, then their four agg chunks, in flight together (see a_tile_load_rows)
-  for (int idx0 = threadIdx.x; idx0 < total; idx0 += 4 * kThreads) {
-    int beg[4], end[4];
+  constexpr int U = 8;
+  for (int idx0 = threadIdx.x; idx0 < total; idx0 += U * kThreads) {
+    float4 v[U];
+    bool has[U];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int idx = idx0 + u * kThreads;
-      const int r = idx / chunks;
-      beg[u] = end[u] = 0;
-      if (idx < total && r < nvalid) { beg[u] = __ldg(p.rowptr + row0 + r); end[u] = __ldg(p.rowptr + row0 + r + 1); }
-    }
-    float4 v[4];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < U; ++u) {
       const int idx = idx0 + u * kThreads;
       const int r = idx / chunks, c = idx - r * chunks;
       v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (end[u] > beg[u]) v[u] = __ldg(reinterpret_cast<const float4*>(p.agg + (row0 + r) * p.agg_w) + c);
+      has[u] = idx < total && r < nvalid && s_rowptr[r + 1] > s_rowptr[r];     // no edges: the edge kernel never wrote the row
+      if (has[u]) v[u] = __ldg(reinterpret_cast<const float4*>(p.agg + (row0 + r) * p.agg_w) + c);
     }
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < U; ++u) {
       const int idx = idx0 + u * kThreads;
       if (idx >= total) continue;
       const int r = idx / chunks, c = idx - r * chunks;
       float4 t = v[u];
-      if (end[u] > beg[u]) {
-        const int t0 = beg[u] >> 7, t1 = (end[u] - 1) >> 7;
+      if (has[u]) {
+        const int t0 = s_rowptr[r] >> 7, t1 = (s_rowptr[r + 1] - 1) >> 7;
         for (int tt = t0 + 1; tt <= t1; ++tt) {          // CSR row straddling edge tiles
           const float4 h = __ldg(reinterpret_cast<const float4*>(p.head + (long)tt * p.agg_w) + c);
           t.x += h.x; t.y += h.y; t.z += h.z; t.w += h.w;
@@ -177,7 +177,7 @@ __global__ void __launch_bounds__(kThreads) node_kernel(const SgnnNodeParams p, 
     const bool valid = tid < nvalid;
     // previous tile's MMAs (async proxy) have completed (gemm_wait); its TMEM reads retired below
     if (p.prologue == SGNN_PRO_FEATURES) prologue_features<TC>(p, a_tile, i, valid);
-    else if (p.prologue == SGNN_PRO_AGG_X) prologue_agg_x<TC>(p, a_tile, row0, nvalid);
+    else if (p.prologue == SGNN_PRO_AGG_X) prologue_agg_x<TC>(p, a_tile, row0, nvalid, misc->rowptr);
     else prologue_rows<TC>(p, a_tile, row0, nvalid);
 
     int x_width = p.k_pad;       // width of the tail's input held in the A tile
