@@ -590,6 +590,46 @@ def batched_config(dev, batches=(8, 32), steps=5):
     return out
 
 
+def config1_gpu(dev, steps=5):
+    """BASELINE configs[0] exactly, on the GPU: ONE train step (batch 1, N=4800: forward + backward + Adam as one CUDA
+    graph) and a 10-step rollout -- the same work `cpu_baseline.legs` times on the host cores."""
+    from sgnn_b200 import train_engine, training
+    from sgnn_b200.single_scale import evaluate as EV
+    batch, stats, radius = make_train_batch(dev, 1, seed0=0)
+    sim = make_sim(stats, radius, dev).train()
+    eng = train_engine.TrainEngine(sim, training.make_optimizer(sim.parameters(), 1e-4), batch["positions"].shape[0], dev)
+    gen = torch.Generator(device=dev).manual_seed(1)
+    for _ in range(3):
+        eng.step(batch, 0.5, generator=gen)
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(steps):
+        eng.step(batch, 0.5, generator=gen)
+    b.record()
+    torch.cuda.synchronize()
+    train_ms = a.elapsed_time(b) / steps
+    traj, stats, radius = make_case(seed=0, nsteps=10)
+    sim = make_sim(stats, radius, dev)
+    n, t, dim = traj["positions"].shape
+    pos = traj["positions"].to(dev)
+    plan = EV.get_plan(sim, n, t, S, dim, "autoregressive", dev, True)
+    for _ in range(2):
+        plan.traj[:, :S].copy_(pos[:, :S])
+        plan.run()
+    torch.cuda.synchronize()
+    tot = 0.0
+    for _ in range(steps):
+        plan.traj[:, :S].copy_(pos[:, :S])
+        a.record()
+        plan.run()
+        b.record()
+        torch.cuda.synchronize()
+        tot += a.elapsed_time(b)
+    return {"train_step_ms": train_ms, "rollout_10_steps_ms": tot / steps, "particles": n,
+            "what": "configs[0]: one train step (batch 1) + 10-step rollout, device-timed"}
+
+
 def fp32_config(dev, traj, stats, radius, steps=3):
     """The headline workload in precision="fp32" (FFMA kernels: the reference's own arithmetic, the tight-parity mode)."""
     from sgnn_b200.single_scale import evaluate as EV
@@ -762,6 +802,11 @@ def run_gpu(args):
                     fp = fp32_config(dev, traj, stats, radius)
                 except Exception as ex:
                     fp = {"error": repr(ex)}
+            if "config1" in want and line is not None:
+                try:
+                    line["config1_gpu"] = config1_gpu(dev)
+                except Exception as ex:
+                    line["config1_gpu"] = {"error": repr(ex)}
             if world == 1 and "batched" in want:
                 try:
                     bt = batched_config(dev)
@@ -809,7 +854,7 @@ def main():
     ap.add_argument("--impl", default="sgnn_b200", choices=["sgnn_b200", "reference"])
     ap.add_argument("--no-large", action="store_true", help="skip the 1M-particle single-step section")
     ap.add_argument("--no-extra", action="store_true", help="skip the training and multi-scale sections")
-    ap.add_argument("--sections", default="train,multi_scale,fp32,batched,sharded,sharded_weak",
+    ap.add_argument("--sections", default="train,multi_scale,fp32,config1,batched,sharded,sharded_weak",
                     help="comma list of the extra sections to run (all by default)")
     ap.add_argument("--workload", default="rollout", choices=["rollout", "train", "sharded"],
                     help="which measured workload is the headline `value` (rollout replicas by default; train and "
