@@ -140,6 +140,12 @@ int sgnn_layer_norm_bwd_rows(const float* dy, const int* dy_index, const float* 
 int sgnn_linear_wgrad_ex(const float* dy, long ld_dy, const float* x, long ld_x, long max_rows, const int* n_rows_dev,
                          int out_features, int in_features, float* dw, long ld_dw, float scale, float* db,
                          void* workspace, size_t workspace_bytes, void* stream);
+ /* The 64 x 64 weight / bias gradients of up to SGNN_WGRAD_MAX_ITEMS Linears over one row set as ONE tcgen05 launch
+ * (csrc/train_wgrad_tc.cu; same autograd as sgnn_linear_wgrad: graph_network.py:21-58 under loss.backward()):
+ * operands staged MN-major in shared memory, TF32 products (split = 1: hi / lo-split, fp32-grade), fp32 accumulation
+ * in tensor memory, per-slab partials added in a fixed order.                                                 */
+size_t sgnn_linear_wgrad_tc_workspace_bytes(int n_items, long max_rows);
+int sgnn_linear_wgrad_tc(const SgnnWgradBatch* batch, void* stream);
 int sgnn_node_features(const float* pos_seq, long stride, int n, int seq_len, int dim,
                        const float* vel_mean, const float* vel_std, float wall_offset, float wall_max,
                        float wall_div, float* out, long ld_out, void* stream);

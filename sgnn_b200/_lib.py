@@ -81,6 +81,8 @@ def lib():
         _lib.sgnn_layer_norm_bwd_workspace_bytes.restype = C.c_size_t
         _lib.sgnn_linear_wgrad_workspace_bytes.restype = C.c_size_t
         _lib.sgnn_csr_by_source_workspace_bytes.restype = C.c_size_t
+        _lib.sgnn_linear_wgrad_tc_workspace_bytes.restype = C.c_size_t
+        _lib.sgnn_linear_wgrad_tc_workspace_bytes.argtypes = [C.c_int, C.c_long]
         # training-path entries are called ~100 times per step from Python: declared argument types spare the
         # per-call type inference of ctypes (the call sites keep passing c_void_p / c_long / ints / None)
         vp, lg, it, fl, sz = C.c_void_p, C.c_long, C.c_int, C.c_float, C.c_size_t

@@ -243,6 +243,29 @@ typedef struct {
   long dst_off;            /* float offset of the image in the hi and the lo image buffers                */
 } SgnnPackDesc;
 
+/* One 64 x 64 weight gradient of a batch (csrc/train_wgrad_tc.cu): dw[0:64, col0 .. col0+64) of a row-major
+ * gradient with row stride ld_dw = scale * dy[:, 0:64]^T x[:, 0:64], db[0:64] = column sums of dy (NULL: none).
+ * dy / x are column blocks of row-major fp32 matrices (16-byte aligned, leading dimensions multiples of 4).   */
+typedef struct {
+  const float* dy;
+  const float* x;
+  float* dw;
+  float* db;
+  long ld_dy, ld_x, ld_dw;
+  float scale;
+  int pad_;
+} SgnnWgradItem;
+#define SGNN_WGRAD_MAX_ITEMS 6
+typedef struct {
+  SgnnWgradItem item[SGNN_WGRAD_MAX_ITEMS];
+  int n_items;
+  int split;               /* 1: hi / lo-split TF32 operands (fp32-grade products), 0: plain TF32             */
+  long max_rows;           /* rows of every item: min(max_rows, *n_rows_dev) (n_rows_dev NULL: max_rows)      */
+  const int* n_rows_dev;
+  void* workspace;
+  size_t workspace_bytes;
+} SgnnWgradBatch;
+
 #ifdef __cplusplus
 }
 #endif

@@ -66,6 +66,16 @@ class PackDesc(C.Structure):
                 ("pad2_", C.c_int), ("dst_off", C.c_long)]
 
 
+class WgradItem(C.Structure):
+    _fields_ = [("dy", C.c_void_p), ("x", C.c_void_p), ("dw", C.c_void_p), ("db", C.c_void_p), ("ld_dy", C.c_long),
+                ("ld_x", C.c_long), ("ld_dw", C.c_long), ("scale", C.c_float), ("pad_", C.c_int)]
+
+
+class WgradBatch(C.Structure):
+    _fields_ = [("item", WgradItem * 6), ("n_items", C.c_int), ("split", C.c_int), ("max_rows", C.c_long),
+                ("n_rows_dev", C.c_void_p), ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t)]
+
+
 def supports(sim) -> bool:
     """True when `sim` is a single-scale LearnedSimulator this engine covers (module docstring)."""
     epd = getattr(sim, "_encode_process_decode", None)
@@ -221,14 +231,24 @@ class TrainEngine:
         self.dpred = f(n, 4)
         self.dx = [f(n, h), f(n, h)]
         self.dagg = f(n, h)
-        self.dy2_n, self.dpre_n = f(n, h), f(n, h)
-        self.dy2_e, self.dpre_e = f(cap, h), f(cap, h)
+        # One buffer per use: the weight-gradient kernels run on a side stream and may still read a layer's dy2 / dpre
+        # while the main stream is already producing the next layer's.
+        self.dy2_n_all = [f(n, h) for _ in range(nl + 1)]           # node blocks, node encoder
+        self.dpre_n_all = [f(n, h) for _ in range(nl + 2)]          # + decoder
+        self.dy2_e_all = [f(cap, h) for _ in range(nl + 1)]         # edge blocks, edge encoder
+        self.dpre_e_all = [f(cap, h) for _ in range(nl + 1)]
+        self.dpq_all = [f(n, 2 * h) for _ in range(nl)]
         self.de0 = f(cap, h)
-        self.dpq = f(n, 2 * h)
         nb = max(self.lib.sgnn_layer_norm_bwd_workspace_bytes(h),
                  self.lib.sgnn_linear_wgrad_workspace_bytes(C.c_long(cap), 2 * h, 2 * h),
                  self.lib.sgnn_linear_wgrad_workspace_bytes(C.c_long(n), 2 * h, 2 * h))
-        self.ws = torch.empty(nb, dtype=torch.uint8, device=dev)
+        self.ws = torch.empty(nb, dtype=torch.uint8, device=dev)          # LayerNorm backward (main stream)
+        nb_w = max([nb] + [self.lib.sgnn_linear_wgrad_tc_workspace_bytes(i, r) for i in range(1, 7) for r in (n, cap)])
+        self.ws_w = torch.empty(nb_w, dtype=torch.uint8, device=dev)      # weight gradients (side stream)
+        self.side = torch.cuda.Stream(device=dev)
+        self.overlap_wgrad = True      # weight / bias gradients feed nothing but the optimizer: off the critical path
+        self.tc_wgrad = precision == "tf32"
+        self._wq = []
         self._declare()
         self._plan_images()
 
@@ -345,13 +365,51 @@ class TrainEngine:
 
     def _wgrad(self, dy, ld_dy, x, ld_x, rows, rows_dev, m, k, dw: torch.Tensor, col0: int, scale: float = 1.0,
                db: Optional[torch.Tensor] = None):
-        """dW[:, col0:col0+k] = scale * dy^T x (and db = column sums of dy) into the parameter's .grad view."""
+        """Queues dW[:, col0:col0+k] = scale * dy^T x (and db = column sums of dy) into the parameter's .grad view;
+        _wgrad_flush() launches the queue."""
         ptr = lambda t: t if isinstance(t, int) else t.data_ptr()      # noqa: E731
-        with self._timed("wgrad_edges" if rows_dev is not None else "wgrad_nodes"):
-          L.check(self.lib.sgnn_linear_wgrad_ex(ptr(dy), ld_dy, ptr(x), ld_x, rows, rows_dev, m, k,
-                                              dw.data_ptr() + 4 * col0, dw.shape[1], scale,
-                                              None if db is None else db.data_ptr(), self.ws.data_ptr(),
-                                              self.ws.numel(), self._stream()), launches=2)
+        self._wq.append((ptr(dy), ld_dy, ptr(x), ld_x, rows, rows_dev, m, k, dw.data_ptr() + 4 * col0, dw.shape[1], scale,
+                         None if db is None else db.data_ptr()))
+
+    def _wgrad_flush(self):
+        """Launches the queued weight gradients: on the side stream when they overlap the backward pass, the 64 x 64
+        products of one row set as ONE tensor-core launch in TF32 mode (csrc/train_wgrad_tc.cu), the rest (and
+        everything in fp32 mode, whose gradients the parity tests pin to fp32 FFMA sums) with the split-row fp32 kernel."""
+        q, self._wq = self._wq, []
+        if not q:
+            return
+        tc, rest = {}, []
+        for w in q:
+            dy, ld_dy, x, ld_x, rows, rows_dev, m, k = w[:8]
+            if self.tc_wgrad and m == 64 and k == 64 and ld_dy % 4 == 0 and ld_x % 4 == 0 and (dy | x) % 16 == 0:
+                tc.setdefault((rows, rows_dev), []).append(w)
+            else:
+                rest.append(w)
+
+        def launch():
+            for (rows, rows_dev), ws in tc.items():
+                for i0 in range(0, len(ws), 6):
+                    b = WgradBatch()
+                    part = ws[i0:i0 + 6]
+                    b.n_items, b.split, b.max_rows, b.n_rows_dev = len(part), 0, rows, rows_dev
+                    b.workspace, b.workspace_bytes = self.ws_w.data_ptr(), self.ws_w.numel()
+                    for it, w in zip(b.item, part):
+                        it.dy, it.ld_dy, it.x, it.ld_x = w[0], w[1], w[2], w[3]
+                        it.dw, it.ld_dw, it.scale, it.db = w[8], w[9], w[10], w[11]
+                    L.check(self.lib.sgnn_linear_wgrad_tc(C.byref(b), self._stream()), launches=2)
+            for (dy, ld_dy, x, ld_x, rows, rows_dev, m, k, dw, ld_dw, scale, db) in rest:
+                L.check(self.lib.sgnn_linear_wgrad_ex(dy, ld_dy, x, ld_x, rows, rows_dev, m, k, dw, ld_dw, scale, db,
+                                                      self.ws_w.data_ptr(), self.ws_w.numel(), self._stream()), launches=2)
+
+        if not self.overlap_wgrad or self.profile is not None:
+            with self._timed("wgrad_edges" if q[0][5] is not None else "wgrad_nodes"):
+                launch()
+            return
+        ready = torch.cuda.Event()
+        ready.record(torch.cuda.current_stream())          # the operands have been launched on the main stream
+        self.side.wait_event(ready)
+        with torch.cuda.stream(self.side):
+            launch()
 
     def _ln_bwd(self, dy, index, act, ln, rows, rows_dev, dx):
         with self._timed("ln_bwd_edges" if rows_dev is not None else "ln_bwd_nodes"):
@@ -442,14 +500,19 @@ class TrainEngine:
 
         # ---- backward ----
         dx, dx_new = self.dx
+        nl = len(self.layers)
+        self.dpre_n = self.dpre_n_all[nl + 1]
         hi, lo = self._img(md["w2t"]); hi1, lo1 = self._img(md["w1t"])
         self._bwd(tag="bwd_decoder", max_rows=n, dy=self.dpred, ld_dy=4, k_dy=4, n_linear=2, hidden=h, h1=self.h1_d, dpre=self.dpre_n,
                   w2t_hi=hi, w2t_lo=lo, want_dx=1, kx=h, w1t_hi=hi1, w1t_lo=lo1, dx0=dx, ld_dx0=h, k0=h)
         self._wgrad(self.dpred, 4, self.h1_d, h, n, None, dim + 1, h, md["b"].weight.grad, 0, db=md["b"].bias.grad)
         self._wgrad(self.dpre_n, h, xl, h, n, None, h, h, md["a"].weight.grad, 0, db=md["a"].bias.grad)
+        self._wgrad_flush()
         self.de0.zero_()
         for l in reversed(range(len(self.layers))):
             me, mn, ae, an = self.mlp_e[l], self.mlp_n[l], self.act_e[l], self.act_n[l]
+            self.dy2_n, self.dpre_n, self.dy2_e, self.dpre_e, self.dpq = (self.dy2_n_all[l], self.dpre_n_all[l], self.dy2_e_all[l],
+                                                                           self.dpre_e_all[l], self.dpq_all[l])
             # node update: x' = x + LN(MLP([agg | x]))
             self._ln_bwd(dx, None, an, mn["ln"], n, None, self.dy2_n)
             hi, lo = self._img(mn["w2t"]); hi1, lo1 = self._img(mn["w1t"])
@@ -468,6 +531,7 @@ class TrainEngine:
             self._wgrad(self.dy2_e, h, ae["h1"], h, cap, ed, h, h, me["b"].weight.grad, 0, db=me["b"].bias.grad)
             self._wgrad(self.dpre_e, h, self.e0, h, cap, ed, h, h, me["a"].weight.grad, 2 * h, scale=me["scale"],
                         db=me["a"].bias.grad)
+            self._wgrad_flush()
             self._segsum(self.dpre_e, csr.rowptr, None, self.dpq.data_ptr(), 2 * h)
             self._segsum(self.dpre_e, self.rp_src, self.perm_src, self.dpq.data_ptr() + 4 * h, 2 * h)
             hi1, lo1 = self._img(me["pqt"])
@@ -475,8 +539,11 @@ class TrainEngine:
                       w1t_lo=lo1, dx0=dx_new, ld_dx0=h, k0=h, acc0=1)
             self._wgrad(self.dpq, 2 * h, self.x[l], h, n, None, h, h, me["a"].weight.grad, 0)
             self._wgrad(self.dpq.data_ptr() + 4 * h, 2 * h, self.x[l], h, n, None, h, h, me["a"].weight.grad, h)
+            self._wgrad_flush()
             dx, dx_new = dx_new, dx
         # encoders
+        self.dy2_n, self.dpre_n, self.dy2_e, self.dpre_e = (self.dy2_n_all[nl], self.dpre_n_all[nl], self.dy2_e_all[nl],
+                                                            self.dpre_e_all[nl])
         m, a = self.mlp["ee"], self.act_ee
         self._ln_bwd(self.de0, None, a, m["ln"], cap, ed, self.dy2_e)
         hi, lo = self._img(m["w2t"])
@@ -484,6 +551,7 @@ class TrainEngine:
                   dpre=self.dpre_e, w2t_hi=hi, w2t_lo=lo, want_dx=0)
         self._wgrad(self.dy2_e, h, a["h1"], h, cap, ed, h, h, m["b"].weight.grad, 0, db=m["b"].bias.grad)
         self._wgrad(self.dpre_e, h, self.ef, dim + 1, cap, ed, h, dim + 1, m["a"].weight.grad, 0, db=m["a"].bias.grad)
+        self._wgrad_flush()
         m, a = self.mlp["ne"], self.act_ne
         self._ln_bwd(dx, None, a, m["ln"], n, None, self.dy2_n)
         hi, lo = self._img(m["w2t"])
@@ -491,6 +559,11 @@ class TrainEngine:
                   w2t_hi=hi, w2t_lo=lo, want_dx=0)
         self._wgrad(self.dy2_n, h, a["h1"], h, n, None, h, h, m["b"].weight.grad, 0, db=m["b"].bias.grad)
         self._wgrad(self.dpre_n, h, self.nf, self.k_node_pad, n, None, h, self.k_node, m["a"].weight.grad, 0, db=m["a"].bias.grad)
+        self._wgrad_flush()
+        if self.overlap_wgrad and self.profile is None:         # every gradient is in the flat buffer before allreduce / Adam
+            done = torch.cuda.Event()
+            done.record(self.side)
+            torch.cuda.current_stream().wait_event(done)
 
     def _whole_step(self):
         with self._timed("forward_backward_total"):

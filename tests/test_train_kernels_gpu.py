@@ -1,6 +1,7 @@
 """The C entries of the hand-written training step, each called through the C ABI on its own and compared with
 torch in fp64: sgnn_csr_by_source, sgnn_train_pack + sgnn_train_mlp_fwd / _bwd (hi/lo-split and plain TF32),
-sgnn_layer_norm_bwd_rows (gathered rows, device-side row count), sgnn_linear_wgrad_ex (column blocks, scale).
+sgnn_layer_norm_bwd_rows (gathered rows, device-side row count), sgnn_linear_wgrad_ex (column blocks, scale),
+sgnn_linear_wgrad_tc (batched 64 x 64 products on tcgen05, MN-major operands).
 Reference semantics: the autograd of build_mlp + LayerNorm (sgnn/single_scale/graph_network.py:21-58,139-147) and
 of PyG's propagate gathers (graph_network.py:173)."""
 import ctypes as C
@@ -159,3 +160,50 @@ def test_layer_norm_bwd_rows_and_wgrad_ex():
     assert (dw[:, H:2 * H].double() - want).abs().max().item() <= 1e-5 * want.abs().max().item()
     assert (db.double() - dy_wide[:rows, :H].double().sum(0)).abs().max().item() <= 1e-4
     assert torch.all(dw[:, :H] == 5.0) and torch.all(dw[:, 2 * H:] == 5.0)
+
+
+@pytest.mark.parametrize("split,tol", [(1, 3e-6), (0, 3e-3)])
+@pytest.mark.parametrize("rows,live", [(5000, 4321), (96, 96), (40, 0), (70000, 65537)])
+def test_linear_wgrad_tc_batch(split, tol, rows, live):
+    """Three 64 x 64 products over one row set in one tcgen05 launch: column-block operands, a scaled result written
+    into a column block of a wider gradient, a missing bias gradient, the row count read on the device, rows past
+    it (stale, here NaN) never read into the sums; bit-repeatable."""
+    from sgnn_b200 import train_engine as TE
+    L, lib = _lib()
+    torch.manual_seed(rows + split)
+    wide = torch.randn(rows, 2 * H, device="cuda")
+    xs = [torch.randn(rows, H, device="cuda") for _ in range(2)]
+    wide[live:] = float("nan")
+    for x in xs:
+        x[live:] = float("nan")
+    live_dev = torch.tensor([live], dtype=torch.int32, device="cuda")
+    ws = torch.empty(lib.sgnn_linear_wgrad_tc_workspace_bytes(3, rows), dtype=torch.uint8, device="cuda")
+
+    def call():
+        dw = torch.full((H, 3 * H), 7.0, device="cuda")
+        dbs = [torch.full((H,), 7.0, device="cuda") for _ in range(2)]
+        b = TE.WgradBatch()
+        b.n_items, b.split, b.max_rows, b.n_rows_dev = 3, split, rows, live_dev.data_ptr()
+        b.workspace, b.workspace_bytes = ws.data_ptr(), ws.numel()
+        spec = [(wide[:, :H], xs[0], 0, 1.0, dbs[0]), (wide[:, H:], xs[0], H, 0.25, None), (wide[:, H:], xs[1], 2 * H, 1.0, dbs[1])]
+        for it, (dy, x, col0, scale, db) in zip(b.item, spec):
+            it.dy, it.ld_dy, it.x, it.ld_x = dy.data_ptr(), dy.stride(0), x.data_ptr(), x.stride(0)
+            it.dw, it.ld_dw, it.scale, it.db = dw.data_ptr() + 4 * col0, dw.stride(0), scale, None if db is None else db.data_ptr()
+        L.check(lib.sgnn_linear_wgrad_tc(C.byref(b), L.stream_ptr()))
+        torch.cuda.synchronize()
+        return dw, dbs, spec
+
+    dw, dbs, spec = call()
+    for dy, x, col0, scale, db in spec:
+        want = scale * (dy[:live].double().T @ x[:live].double())
+        mag = float((dy[:live].double().abs().T @ x[:live].double().abs()).max()) if live else 0.0
+        assert float((dw[:, col0:col0 + H].double() - want).abs().max()) <= tol * scale * mag + 1e-30
+        if db is not None:
+            wb = dy[:live].double().sum(0)
+            assert float((db.double() - wb).abs().max()) <= tol * float(dy[:live].double().abs().sum(0).max() if live else 0.0) + 1e-30
+    dw2, dbs2, _ = call()
+    assert torch.equal(dw, dw2) and all(torch.equal(a, c) for a, c in zip(dbs, dbs2))
+    with pytest.raises(L.SgnnError):
+        b = TE.WgradBatch()
+        b.n_items, b.max_rows = 7, rows
+        L.check(lib.sgnn_linear_wgrad_tc(C.byref(b), L.stream_ptr()))
