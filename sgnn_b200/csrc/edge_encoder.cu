@@ -17,6 +17,7 @@ struct EncMisc {
   uint64_t bar_w, bar_mma, bar_stream;
   uint32_t tmem_slot;
   int pad;
+  float xch[2 * kMaxParts * kTileRows];     // LayerNorm moments between the parts of a row
 };
 
 struct EdgeEncSmem {
@@ -41,10 +42,9 @@ __host__ inline bool edge_enc_streamed(int blob_bytes, int hidden, int out, bool
 constexpr int kMaxEdgeFeat = 8;
 
 template <bool TC>
-__global__ void __launch_bounds__(kThreads) edge_encoder_kernel(const SgnnEdgeEncoderParams p,
+__global__ void __launch_bounds__(kThreads * kMaxParts) edge_encoder_kernel(const SgnnEdgeEncoderParams p,
                                                                 const int streamed) {
   pdl_launch_dependents();
-  pdl_wait();
   char* smem = smem_base_1024();
   const int hidden = p.mlp.hidden, out = p.mlp.out;
   const int w = hidden > out ? hidden : out;
@@ -52,18 +52,26 @@ __global__ void __launch_bounds__(kThreads) edge_encoder_kernel(const SgnnEdgeEn
   const float* blob_f = reinterpret_cast<const float*>(smem);
   char* hid = smem + L.hid;
   EncMisc* misc = reinterpret_cast<EncMisc*>(smem + L.misc);
-  const int tid = threadIdx.x;
+  const int tid = t_row();
+  const bool t0 = threadIdx.x == 0, part0 = t_part() == 0;
 
-  const int n_edges = p.rowptr ? p.rowptr[p.n_nodes] : p.n_nodes;   // rowptr NULL: n_nodes = E
-  const int n_tiles = (n_edges + kTileRows - 1) / kTileRows;
-  if ((int)blockIdx.x >= n_tiles) return;
-
+  // the blob is constant: staged (and the first streamed image put in flight) ahead of griddepcontrol.wait
   WeightStage ws;
   weights_setup(ws, p.blob, p.blob_bytes, smem, smem + L.wbuf, &misc->bar_w, &misc->bar_stream, streamed);
   TileAcc<TC> acc;
   acc_setup<TC>(acc, TC ? pow2_cols(2 * w) : pow2_cols(w), &misc->bar_mma, &misc->tmem_slot,
                 reinterpret_cast<float*>(smem + L.simt));
+  const int n_out16 = (out + 15) & ~15;
+  weights_prefetch<TC>(ws, p.mlp.w_off[1], hidden, p.mlp.n_hidden > 1 ? hidden : n_out16);
+  pdl_wait();
+  const int n_edges = p.rowptr ? p.rowptr[p.n_nodes] : p.n_nodes;   // rowptr NULL: n_nodes = E
+  const int n_tiles = (n_edges + kTileRows - 1) / kTileRows;
   mbar_wait(&misc->bar_w, 0);
+  if ((int)blockIdx.x >= n_tiles) {
+    weights_prefetch_drain(ws);
+    acc_teardown<TC>(acc);
+    return;
+  }
   const int tile_bytes = kTileRows * out * 4;
 
   for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -86,14 +94,14 @@ __global__ void __launch_bounds__(kThreads) edge_encoder_kernel(const SgnnEdgeEn
         }
         f[p.dim] = sqrtf(sq);
       }
-      if (p.feat_out)
+      if (p.feat_out && part0)
         for (int k = 0; k < p.k_in; ++k) p.feat_out[(long)eidx * p.k_in + k] = f[k];
     }
     // ---- layer 0 (k_in -> hidden) in fp32 FFMA, ReLU ----
     {
       const float* w0 = blob_f + p.w0_off;
       const float* b0 = blob_f + p.mlp.b_off[0];
-      for (int c = 0; c < hidden; c += 32) {
+      SGNN_FOR_MY_CHUNKS(c, hidden) {
         float v[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
@@ -104,11 +112,13 @@ __global__ void __launch_bounds__(kThreads) edge_encoder_kernel(const SgnnEdgeEn
         a_tile_store32<TC>(hid, c, v);
       }
     }
-    const int acc_col = mlp_run_rest<TC>(acc, ws, hid, p.mlp, w, 1);
+    const int acc_col = tile + (int)gridDim.x < n_tiles
+                            ? mlp_run_rest<TC>(acc, ws, hid, p.mlp, w, 1, p.mlp.w_off[1], hidden, p.mlp.n_hidden > 1 ? hidden : n_out16)
+                            : mlp_run_rest<TC>(acc, ws, hid, p.mlp, w, 1);
     // ---- LayerNorm -> tile (A-operand layout) staged in `hid`, then one TMA bulk store ----
     float mean = 0.f, rstd = 1.f;
-    if (p.mlp.has_ln) row_ln_stats<TC>(acc, acc_col, out, blob_f + p.mlp.b_off[p.mlp.n_hidden], mean, rstd);
-    for (int c = 0; c < out; c += 32) {
+    if (p.mlp.has_ln) row_ln_stats<TC>(acc, acc_col, out, blob_f + p.mlp.b_off[p.mlp.n_hidden], mean, rstd, misc->xch);
+    SGNN_FOR_MY_CHUNKS(c, out) {
       float v[32];
       mlp_out_chunk<TC>(acc, acc_col, c, blob_f, p.mlp, mean, rstd, v);
       if (!valid) {
@@ -120,13 +130,14 @@ __global__ void __launch_bounds__(kThreads) edge_encoder_kernel(const SgnnEdgeEn
     fence_proxy_async_smem();
     if constexpr (TC) tc_fence_before_sync();
     __syncthreads();
-    if (tid == 0) {
+    if (t0) {
       tma_bulk_s2g(reinterpret_cast<char*>(p.e_tiles) + (long)tile * tile_bytes, hid, (uint32_t)tile_bytes);
       tma_store_wait_read();       // `hid` is rewritten by the next tile's layer 0
     }
     __syncthreads();
   }
-  if (tid == 0) tma_store_wait_all();
+  if (t0) tma_store_wait_all();
+  weights_prefetch_drain(ws);
   acc_teardown<TC>(acc);
 }
 
@@ -162,12 +173,13 @@ extern "C" int sgnn_edge_encoder_fwd(const SgnnEdgeEncoderParams* p, int use_ten
   SGNN_CHECK_ARG(smem <= 227 * 1024, "edge_encoder: needs %d bytes of shared memory (> 227 KB)", smem);
   if (grid > p->max_tiles) grid = p->max_tiles;
   if (grid < 1) grid = 1;
+  const int threads = kThreads * sgnn_tile_parts(p->mlp.hidden > p->mlp.out ? p->mlp.hidden : p->mlp.out);
   if (use_tensor_cores) {
     SGNN_ENSURE_SMEM(edge_encoder_kernel<true>, smem);
-    SGNN_CUDA(sgnn_launch((edge_encoder_kernel<true>), dim3(grid), dim3(kThreads), smem, (cudaStream_t)stream, *p, streamed));
+    SGNN_CUDA(sgnn_launch((edge_encoder_kernel<true>), dim3(grid), dim3(threads), smem, (cudaStream_t)stream, *p, streamed));
   } else {
     SGNN_ENSURE_SMEM(edge_encoder_kernel<false>, smem);
-    SGNN_CUDA(sgnn_launch((edge_encoder_kernel<false>), dim3(grid), dim3(kThreads), smem, (cudaStream_t)stream, *p, streamed));
+    SGNN_CUDA(sgnn_launch((edge_encoder_kernel<false>), dim3(grid), dim3(threads), smem, (cudaStream_t)stream, *p, streamed));
   }
   SGNN_LAUNCH_CHECK();
   return SGNN_OK;

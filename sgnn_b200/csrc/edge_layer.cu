@@ -29,6 +29,7 @@ struct EdgeMisc {
   int piece_tgt[8];
   int piece_flag[8];            // [2g] head piece of warp g (1 = exists, 3 = runs through), [2g+1] tail
   float pieces[8 * 128];
+  float xch[2 * kMaxParts * kTileRows];     // LayerNorm moments between the parts of a row
 };
 
 struct EdgeLayerSmem {
@@ -57,10 +58,9 @@ __device__ __forceinline__ float m_tile_read(const float* m, int row, int col, i
 }
 
 template <bool TC>
-__global__ void __launch_bounds__(kThreads) edge_layer_kernel(const SgnnEdgeLayerParams p,
+__global__ void __launch_bounds__(kThreads * kMaxParts) edge_layer_kernel(const SgnnEdgeLayerParams p,
                                                               const int streamed) {
   pdl_launch_dependents();
-  pdl_wait();
   char* smem = smem_base_1024();
   const int hidden = p.mlp.hidden, out = p.mlp.out, he = p.he, nh = p.mlp.n_hidden;
   const int w = hidden > out ? hidden : out;
@@ -69,24 +69,33 @@ __global__ void __launch_bounds__(kThreads) edge_layer_kernel(const SgnnEdgeLaye
   char* e_tile = smem + L.e_tile;
   char* hid = smem + L.hid;
   EdgeMisc* misc = reinterpret_cast<EdgeMisc*>(smem + L.misc);
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tid = t_row(), lane = threadIdx.x & 31, warp = (threadIdx.x >> 5) & 3;   // row; lane; warp within its part
+  const int part = t_part();
+  const bool t0 = threadIdx.x == 0;
   const int tile_bytes = kTileRows * he * 4;
 
-  const int n_edges = p.rowptr[p.n_nodes];
-  const int n_tiles = (n_edges + kTileRows - 1) / kTileRows;
-  if ((int)blockIdx.x >= n_tiles) return;   // uniform per CTA, before any barrier/TMEM use
-
+  // the blob is constant: its vector region and (streamed weights) the first image are in flight before
+  // griddepcontrol.wait; the edge count and the e0 tiles come from the kernels before this one
   WeightStage ws;
-  if (tid == 0) mbar_init(&misc->bar_e, 1);
+  if (t0) mbar_init(&misc->bar_e, 1);
   weights_setup(ws, p.blob, p.blob_bytes, smem + L.blob, smem + L.wbuf, &misc->bar_w,
                 &misc->bar_stream, streamed);
-  if (tid == 0)
-    tma_load_span(e_tile, reinterpret_cast<const char*>(p.e_tiles) + (long)blockIdx.x * tile_bytes,
-                  tile_bytes, &misc->bar_e);
   TileAcc<TC> acc;
   acc_setup<TC>(acc, TC ? pow2_cols(2 * w) : pow2_cols(w), &misc->bar_mma, &misc->tmem_slot,
                 reinterpret_cast<float*>(smem + L.simt));
+  weights_prefetch<TC>(ws, p.mlp.w_off[0], he, hidden);
+  pdl_wait();
+  const int n_edges = p.rowptr[p.n_nodes];
+  const int n_tiles = (n_edges + kTileRows - 1) / kTileRows;
   mbar_wait(&misc->bar_w, 0);
+  if ((int)blockIdx.x >= n_tiles) {         // uniform per CTA
+    weights_prefetch_drain(ws);
+    acc_teardown<TC>(acc);
+    return;
+  }
+  if (t0)
+    tma_load_span(e_tile, reinterpret_cast<const char*>(p.e_tiles) + (long)blockIdx.x * tile_bytes,
+                  tile_bytes, &misc->bar_e);
   uint32_t phase_e = 0;
 
   for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -95,26 +104,27 @@ __global__ void __launch_bounds__(kThreads) edge_layer_kernel(const SgnnEdgeLaye
     const int eidx = e0 + tid;
     const int s = tid < nvalid ? p.src[eidx] : -1;
     const int t = tid < nvalid ? p.tgt[eidx] : -3;
-    misc->tgt_s[1 + tid] = t;
-    if (tid == 0) {
+    if (part == 0) misc->tgt_s[1 + tid] = t;
+    if (t0) {
       misc->tgt_s[0] = tile > 0 ? p.tgt[e0 - 1] : -2;
       misc->tgt_s[1 + kTileRows] = e0 + kTileRows < n_edges ? p.tgt[e0 + kTileRows] : -3;
     }
-    if (tid < 8) misc->piece_flag[tid] = 0;
+    if (threadIdx.x < 8) misc->piece_flag[threadIdx.x] = 0;
 
     // ---- stage 0: e0 (2^l W1c)^T, then + P[tgt] + Q[src], ReLU ----
     mbar_wait(&misc->bar_e, phase_e);
     phase_e ^= 1u;
     gemm_weights<TC>(acc, ws, e_tile, p.mlp.w_off[0], he, hidden, 0, false);
     gemm_weights_wait<TC>(acc, ws);
+    weights_prefetch<TC>(ws, p.mlp.w_off[1], hidden, nh > 1 ? hidden : out);
     if constexpr (!TC) __syncthreads();      // every thread has finished reading the e0 tile
-    if (tid == 0 && tile + (int)gridDim.x < n_tiles)
+    if (t0 && tile + (int)gridDim.x < n_tiles)
       tma_load_span(e_tile, reinterpret_cast<const char*>(p.e_tiles) +
                                 (long)(tile + gridDim.x) * tile_bytes, tile_bytes, &misc->bar_e);
     {
       const float* prow = p.pq + (long)(t < 0 ? 0 : t) * 2 * hidden;
       const float* qrow = p.pq + (long)(s < 0 ? 0 : s) * 2 * hidden + hidden;
-      for (int c = 0; c < hidden; c += 32) {
+      SGNN_FOR_MY_CHUNKS(c, hidden) {
         float v[32];
         acc_load32<TC>(acc, c, v);
         if (tid < nvalid) {
@@ -138,8 +148,9 @@ __global__ void __launch_bounds__(kThreads) edge_layer_kernel(const SgnnEdgeLaye
       region ^= 1;
       gemm_weights<TC>(acc, ws, hid, p.mlp.w_off[l], hidden, hidden, region * w, false);
       gemm_weights_wait<TC>(acc, ws);
+      weights_prefetch<TC>(ws, p.mlp.w_off[l + 1], hidden, l + 1 < nh ? hidden : out);
       const float* b = blob_f + p.mlp.b_off[l];
-      for (int c = 0; c < hidden; c += 32) {
+      SGNN_FOR_MY_CHUNKS(c, hidden) {
         float v[32];
         acc_load32<TC>(acc, region * w + c, v);
 #pragma unroll
@@ -152,14 +163,15 @@ __global__ void __launch_bounds__(kThreads) edge_layer_kernel(const SgnnEdgeLaye
     region ^= 1;
     gemm_weights<TC>(acc, ws, hid, p.mlp.w_off[nh], hidden, out, region * w, false);
     gemm_weights_wait<TC>(acc, ws);
+    if (tile + (int)gridDim.x < n_tiles) weights_prefetch<TC>(ws, p.mlp.w_off[0], he, hidden);
     float* m_tile = reinterpret_cast<float*>(hid);
     {
       const float* b = blob_f + p.mlp.b_off[nh];
       const float* gam = blob_f + p.mlp.gamma_off;
       const float* bet = blob_f + p.mlp.beta_off;
       float mean, rstd;
-      row_ln_stats<TC>(acc, region * w, out, b, mean, rstd);
-      for (int c = 0; c < out; c += 32) {
+      row_ln_stats<TC>(acc, region * w, out, b, mean, rstd, misc->xch);
+      SGNN_FOR_MY_CHUNKS(c, out) {
         float v[32];
         acc_load32<TC>(acc, region * w + c, v);
 #pragma unroll
@@ -177,11 +189,15 @@ __global__ void __launch_bounds__(kThreads) edge_layer_kernel(const SgnnEdgeLaye
     if constexpr (TC) tc_fence_before_sync();
     __syncthreads();   // tgt_s / piece_flag visible; all TMEM reads of this tile retired
 
-    // ---- segmented sums over the receiver-sorted rows: warp g owns rows 32g..32g+31, lane
-    //      owns out/32 consecutive columns; control flow is warp-uniform ----
-    const int cpl = out >> 5;                  // columns per lane: 1, 2 or 4
+    // ---- segmented sums over the receiver-sorted rows: warp g of part q owns rows 32g..32g+31 and the columns
+    //      [q out/nq, (q+1) out/nq), a lane cpl consecutive ones of them; control flow is warp-uniform ----
+    const int cpl_w = out >> 5;                // columns per lane over the full width: 1, 2, 3 or 4
+    int nq = t_parts();
+    while (cpl_w % nq) nq >>= 1;               // parts that take a share of the columns
+    const int cpl = cpl_w / nq;
+    const int colb = part * (out / nq) + lane * cpl;
     const int r0 = warp * 32;
-    if (r0 < nvalid) {
+    if (r0 < nvalid && part < nq) {
       const int rend = r0 + 32 < nvalid ? r0 + 32 : nvalid;
       int cur = misc->tgt_s[1 + r0];
       const bool first_cont = misc->tgt_s[r0] == cur;
@@ -191,31 +207,31 @@ __global__ void __launch_bounds__(kThreads) edge_layer_kernel(const SgnnEdgeLaye
         const int tr = misc->tgt_s[1 + row];
         if (tr != cur) {
           if (first_seg && first_cont) {
-            for (int j = 0; j < cpl; ++j) misc->pieces[(2 * warp) * 128 + lane * cpl + j] = sum[j];
-            if (lane == 0) { misc->piece_tgt[2 * warp] = cur; misc->piece_flag[2 * warp] = 1; }
+            for (int j = 0; j < cpl; ++j) misc->pieces[(2 * warp) * 128 + colb + j] = sum[j];
+            if (lane == 0 && part == 0) { misc->piece_tgt[2 * warp] = cur; misc->piece_flag[2 * warp] = 1; }
           } else {
-            for (int j = 0; j < cpl; ++j) p.agg[(long)cur * out + lane * cpl + j] = sum[j];
+            for (int j = 0; j < cpl; ++j) p.agg[(long)cur * out + colb + j] = sum[j];
           }
           first_seg = false;
           cur = tr;
           sum[0] = sum[1] = sum[2] = sum[3] = 0.f;
         }
-        for (int j = 0; j < cpl; ++j) sum[j] += m_tile_read(m_tile, row, lane * cpl + j, out);
+        for (int j = 0; j < cpl; ++j) sum[j] += m_tile_read(m_tile, row, colb + j, out);
       }
       const bool cont_next = misc->tgt_s[1 + rend] == cur;
       if (first_seg && first_cont) {
-        for (int j = 0; j < cpl; ++j) misc->pieces[(2 * warp) * 128 + lane * cpl + j] = sum[j];
-        if (lane == 0) { misc->piece_tgt[2 * warp] = cur; misc->piece_flag[2 * warp] = cont_next ? 3 : 1; }
+        for (int j = 0; j < cpl; ++j) misc->pieces[(2 * warp) * 128 + colb + j] = sum[j];
+        if (lane == 0 && part == 0) { misc->piece_tgt[2 * warp] = cur; misc->piece_flag[2 * warp] = cont_next ? 3 : 1; }
       } else if (cont_next) {
-        for (int j = 0; j < cpl; ++j) misc->pieces[(2 * warp + 1) * 128 + lane * cpl + j] = sum[j];
-        if (lane == 0) { misc->piece_tgt[2 * warp + 1] = cur; misc->piece_flag[2 * warp + 1] = 1; }
+        for (int j = 0; j < cpl; ++j) misc->pieces[(2 * warp + 1) * 128 + colb + j] = sum[j];
+        if (lane == 0 && part == 0) { misc->piece_tgt[2 * warp + 1] = cur; misc->piece_flag[2 * warp + 1] = 1; }
       } else {
-        for (int j = 0; j < cpl; ++j) p.agg[(long)cur * out + lane * cpl + j] = sum[j];
+        for (int j = 0; j < cpl; ++j) p.agg[(long)cur * out + colb + j] = sum[j];
       }
     }
     __syncthreads();
     // ---- stitch the pieces of rows that straddle warp groups / tiles (warp 0) ----
-    if (warp == 0) {
+    if (threadIdx.x < 32) {
       float carry[4] = {0.f, 0.f, 0.f, 0.f};
       bool has = false, from_prev = false;
       int ctgt = -1;
@@ -224,25 +240,26 @@ __global__ void __launch_bounds__(kThreads) edge_layer_kernel(const SgnnEdgeLaye
         if (f0) {
           if (!has) { has = true; from_prev = true; ctgt = misc->piece_tgt[2 * g];
                       carry[0] = carry[1] = carry[2] = carry[3] = 0.f; }
-          for (int j = 0; j < cpl; ++j) carry[j] += misc->pieces[(2 * g) * 128 + lane * cpl + j];
+          for (int j = 0; j < cpl_w; ++j) carry[j] += misc->pieces[(2 * g) * 128 + lane * cpl_w + j];
           if (!(f0 & 2)) {
             float* dst = from_prev ? p.head + (long)tile * out : p.agg + (long)ctgt * out;
-            for (int j = 0; j < cpl; ++j) dst[lane * cpl + j] = carry[j];
+            for (int j = 0; j < cpl_w; ++j) dst[lane * cpl_w + j] = carry[j];
             has = false;
           }
         }
         if (misc->piece_flag[2 * g + 1]) {
           has = true; from_prev = false; ctgt = misc->piece_tgt[2 * g + 1];
-          for (int j = 0; j < cpl; ++j) carry[j] = misc->pieces[(2 * g + 1) * 128 + lane * cpl + j];
+          for (int j = 0; j < cpl_w; ++j) carry[j] = misc->pieces[(2 * g + 1) * 128 + lane * cpl_w + j];
         }
       }
       if (has) {   // the row continues into the next tile: its remainder arrives as that tile's head
         float* dst = from_prev ? p.head + (long)tile * out : p.agg + (long)ctgt * out;
-        for (int j = 0; j < cpl; ++j) dst[lane * cpl + j] = carry[j];
+        for (int j = 0; j < cpl_w; ++j) dst[lane * cpl_w + j] = carry[j];
       }
     }
     // next iteration's first __syncthreads (a_tile_publish) orders the piece buffers
   }
+  weights_prefetch_drain(ws);
   acc_teardown<TC>(acc);
 }
 
@@ -290,12 +307,13 @@ extern "C" int sgnn_edge_layer_fwd(const SgnnEdgeLayerParams* p, int use_tensor_
   SGNN_CHECK_ARG(p->blob_bytes >= SGNN_VEC_REGION_BYTES, "edge_layer: blob lacks the vector region");
   if (grid > p->max_tiles) grid = p->max_tiles;
   if (grid < 1) grid = 1;
+  const int threads = kThreads * sgnn_tile_parts(p->mlp.hidden > p->mlp.out ? p->mlp.hidden : p->mlp.out);
   if (use_tensor_cores) {
     SGNN_ENSURE_SMEM(edge_layer_kernel<true>, smem);
-    SGNN_CUDA(sgnn_launch((edge_layer_kernel<true>), dim3(grid), dim3(kThreads), smem, (cudaStream_t)stream, *p, streamed));
+    SGNN_CUDA(sgnn_launch((edge_layer_kernel<true>), dim3(grid), dim3(threads), smem, (cudaStream_t)stream, *p, streamed));
   } else {
     SGNN_ENSURE_SMEM(edge_layer_kernel<false>, smem);
-    SGNN_CUDA(sgnn_launch((edge_layer_kernel<false>), dim3(grid), dim3(kThreads), smem, (cudaStream_t)stream, *p, streamed));
+    SGNN_CUDA(sgnn_launch((edge_layer_kernel<false>), dim3(grid), dim3(threads), smem, (cudaStream_t)stream, *p, streamed));
   }
   SGNN_LAUNCH_CHECK();
   return SGNN_OK;

@@ -20,11 +20,27 @@
 
 namespace sgnn {
 
+// optional in-kernel timeline (SGNN_TIMELINE builds; profiles/node_generic_timeline.py): %globaltimer stamps of
+// CTA 0 / thread 0, slots 0..15 for PQ / plain tails, 16..31 for the DECODE tail
+__device__ unsigned long long* g_node_generic_timeline = nullptr;
+__device__ __forceinline__ void gstamp(const SgnnNodeParams& p, int slot) {
+#ifdef SGNN_TIMELINE
+  if (g_node_generic_timeline != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    g_node_generic_timeline[slot + (p.tail == SGNN_TAIL_DECODE ? 16 : 0)] = t;
+  }
+#else
+  (void)p; (void)slot;
+#endif
+}
+
 struct NodeMisc {
   uint64_t bar_w, bar_mma, bar_stream;
   uint32_t tmem_slot;
   int pad;
   int rowptr[kTileRows + 1];     // CSR bounds of the tile's rows (AGG_X prologue)
+  float xch[2 * kMaxParts * kTileRows];     // LayerNorm moments / decoder partial sums between the parts of a row
 };
 
 struct NodeSmem {
@@ -65,10 +81,11 @@ __device__ __forceinline__ void a_store_scalar(char* a_tile, int row, int col, f
   *reinterpret_cast<float*>(a_tile + sw128_offset(row, col, kTileRows)) = v;
 }
 
-// FEATURES prologue: thread == row
+// FEATURES prologue: one thread per row (part 0)
 template <bool TC>
 __device__ __forceinline__ void prologue_features(const SgnnNodeParams& p, char* a_tile, long i, bool valid) {
-  const int row = threadIdx.x;
+  if (t_part() != 0) return;
+  const int row = t_row();
   int k = 0;
   if (valid) {
     const float* ps = p.pos_seq + i * p.pos_seq_stride;
@@ -103,46 +120,34 @@ __device__ __forceinline__ void prologue_features(const SgnnNodeParams& p, char*
 // nodes, multi-scale configs[3], r02d).
 template <bool TC>
 __device__ __forceinline__ void prologue_agg_x(const SgnnNodeParams& p, char* a_tile, long row0, int nvalid, int* s_rowptr) {
-  for (int r = threadIdx.x; r <= kTileRows; r += kThreads) s_rowptr[r] = r <= nvalid ? __ldg(p.rowptr + row0 + r) : 0;
+  for (int r = threadIdx.x; r <= kTileRows; r += blockDim.x) s_rowptr[r] = r <= nvalid ? __ldg(p.rowptr + row0 + r) : 0;
   __syncthreads();
-  const int chunks = p.agg_w >> 2;
-  const int total = kTileRows * chunks;
-  constexpr int U = 8;
-  for (int idx0 = threadIdx.x; idx0 < total; idx0 += U * kThreads) {
-    float4 v[U];
-    bool has[U];
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int idx = idx0 + u * kThreads;
-      const int r = idx / chunks, c = idx - r * chunks;
-      v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-      has[u] = idx < total && r < nvalid && s_rowptr[r + 1] > s_rowptr[r];     // no edges: the edge kernel never wrote the row
-      if (has[u]) v[u] = __ldg(reinterpret_cast<const float4*>(p.agg + (row0 + r) * p.agg_w) + c);
-    }
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int idx = idx0 + u * kThreads;
-      if (idx >= total) continue;
-      const int r = idx / chunks, c = idx - r * chunks;
-      float4 t = v[u];
-      if (has[u]) {
-        const int t0 = s_rowptr[r] >> 7, t1 = (s_rowptr[r + 1] - 1) >> 7;
-        for (int tt = t0 + 1; tt <= t1; ++tt) {          // CSR row straddling edge tiles
-          const float4 h = __ldg(reinterpret_cast<const float4*>(p.head + (long)tt * p.agg_w) + c);
-          t.x += h.x; t.y += h.y; t.z += h.z; t.w += h.w;
-        }
+  // every chunk of the [agg | x] tile in flight at once (cp.async): the register version walked the tile in 16
+  // dependent round trips of 8 loads per thread, 17.6 of the kernel's 46 us at 4800 nodes and 128-wide latents
+  // (profiles/node_generic_timeline.py, r02f).  Receivers without edges: the edge kernel never wrote the row.
+  a_tile_load_rows_async(a_tile, 0, p.agg, p.agg_w, p.agg_w, nvalid,
+                         [=](int r) { return s_rowptr[r + 1] > s_rowptr[r] ? row0 + r : -1L; });
+  a_tile_load_rows_async(a_tile, p.agg_w, p.x_in, p.x_w, p.x_w, nvalid, [=](int r) { return row0 + r; });
+  cp_async_commit();
+  cp_async_wait_all();
+  const float* head = p.head;
+  const int agg_w = p.agg_w;
+  a_tile_fix_own<TC>(a_tile, 0, p.agg_w, [=](int r, int c, float4& t) {
+    if (r < nvalid && s_rowptr[r + 1] > s_rowptr[r]) {
+      const int t0 = s_rowptr[r] >> 7, t1 = (s_rowptr[r + 1] - 1) >> 7;
+      for (int tt = t0 + 1; tt <= t1; ++tt) {          // CSR row straddling edge tiles
+        const float4 h = __ldg(reinterpret_cast<const float4*>(head + (long)tt * agg_w) + c);
+        t.x += h.x; t.y += h.y; t.z += h.z; t.w += h.w;
       }
-      if constexpr (TC) t = make_float4(to_tf32(t.x), to_tf32(t.y), to_tf32(t.z), to_tf32(t.w));
-      *reinterpret_cast<float4*>(a_tile + sw128_chunk_offset(r, c, kTileRows)) = t;
     }
-  }
-  a_tile_load_rows<TC>(a_tile, p.agg_w, p.x_in, p.x_w, p.x_w, nvalid, [row0](int r) { return row0 + r; });
+  });
+  if constexpr (TC) a_tile_fix_own<TC>(a_tile, p.agg_w, p.x_w, [](int, int, float4&) {});
 }
 
 // ROWS prologue: arbitrary width / leading dimension (scalar, coalesced along the row)
 template <bool TC>
 __device__ __forceinline__ void prologue_rows(const SgnnNodeParams& p, char* a_tile, long row0, int nvalid) {
-  for (int idx = threadIdx.x; idx < kTileRows * p.k_pad; idx += kThreads) {
+  for (int idx = threadIdx.x; idx < kTileRows * p.k_pad; idx += blockDim.x) {
     const int r = idx / p.k_pad, c = idx - r * p.k_pad;
     float v = 0.f;
     if (r < nvalid && c < p.k_in) v = __ldg(p.rows_in + (row0 + r) * p.rows_ld + c);
@@ -151,15 +156,15 @@ __device__ __forceinline__ void prologue_rows(const SgnnNodeParams& p, char* a_t
 }
 
 template <bool TC>
-__global__ void __launch_bounds__(kThreads) node_kernel(const SgnnNodeParams p, const int streamed) {
+__global__ void __launch_bounds__(kThreads * kMaxParts) node_kernel(const SgnnNodeParams p, const int streamed) {
   pdl_launch_dependents();
-  pdl_wait();
+  gstamp(p, 0);
   char* smem = smem_base_1024();
   const NodeSmem L = node_smem(p, TC, streamed != 0);
   const float* blob_f = reinterpret_cast<const float*>(smem);
   char* a_tile = smem + L.a;
   NodeMisc* misc = reinterpret_cast<NodeMisc*>(smem + L.misc);
-  const int tid = threadIdx.x;
+  const int tid = t_row();       // the row this thread works on
   const int n_tiles = (p.n_rows + kTileRows - 1) / kTileRows;
   if ((int)blockIdx.x >= n_tiles) return;
 
@@ -167,8 +172,23 @@ __global__ void __launch_bounds__(kThreads) node_kernel(const SgnnNodeParams p, 
   weights_setup(ws, p.blob, p.blob_bytes, smem, smem + L.wbuf, &misc->bar_w, &misc->bar_stream, streamed);
   TileAcc<TC> acc;
   acc_setup<TC>(acc, L.acc_cols, &misc->bar_mma, &misc->tmem_slot, reinterpret_cast<float*>(smem + L.simt));
-  mbar_wait(&misc->bar_w, 0);
   const int w = p.has_mlp ? imax(p.mlp.hidden, (p.mlp.out + 15) & ~15) : 32;
+  // streamed weights: the first image of a tile is in flight before the tile's rows are (the blob is constant: it
+  // may be read ahead of griddepcontrol.wait)
+  const int first_off = p.has_mlp ? p.mlp.w_off[0] : (p.tail == SGNN_TAIL_PQ ? p.wp_off : p.tail == SGNN_TAIL_DECODE ? p.dec.w_off[0] : -1);
+  const int first_n = p.has_mlp ? p.mlp.hidden : (p.tail == SGNN_TAIL_PQ ? p.pq_hidden : p.dec.hidden);
+  if (first_off >= 0) weights_prefetch<TC>(ws, first_off, p.k_pad, first_n);
+  // Staging tile for coalesced row I/O: the A-tile K-blocks behind the columns the later GEMMs read, free once
+  // GEMM 0 has consumed the input tile (thread-per-row 16-byte stores ran the 64 KB x' tile out in 7.6 us and the
+  // 128 KB P | Q tile in 5.7 us at 4800 nodes, r02f).
+  const int used_cols = p.has_mlp ? imax(imax(p.mlp.hidden, p.mlp.out), p.tail == SGNN_TAIL_DECODE ? p.dec.hidden : 0) : 0;
+  const int stage_w = p.has_mlp ? imax(p.mlp.out, p.tail == SGNN_TAIL_PQ ? p.pq_hidden : 0) : 0;
+  char* stage = a_tile + kTileRows * used_cols * 4;
+  const bool staged = p.has_mlp && (L.misc - L.a) - kTileRows * used_cols * 4 >= kTileRows * stage_w * 4;
+  gstamp(p, 1);
+  pdl_wait();
+  mbar_wait(&misc->bar_w, 0);
+  gstamp(p, 2);
 
   for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const long row0 = (long)tile * kTileRows;
@@ -180,15 +200,23 @@ __global__ void __launch_bounds__(kThreads) node_kernel(const SgnnNodeParams p, 
     else if (p.prologue == SGNN_PRO_AGG_X) prologue_agg_x<TC>(p, a_tile, row0, nvalid, misc->rowptr);
     else prologue_rows<TC>(p, a_tile, row0, nvalid);
 
+    gstamp(p, 3);
     int x_width = p.k_pad;       // width of the tail's input held in the A tile
     if (p.has_mlp) {
       const int hidden = p.mlp.hidden, out = p.mlp.out;
       a_tile_publish<TC>();
       gemm_weights<TC>(acc, ws, a_tile, p.mlp.w_off[0], p.k_pad, hidden, 0, false);
       gemm_weights_wait<TC>(acc, ws);
+      weights_prefetch<TC>(ws, p.mlp.w_off[1], hidden, p.mlp.n_hidden > 1 ? hidden : (out + 15) & ~15);
+      if (staged && p.residual) {            // the K-blocks behind `stage` are free now: raw residual rows, coalesced
+        if constexpr (!TC) __syncthreads();  // FFMA mode: every thread is done with its row of the input tile
+        SGNN_FOR_MY_CHUNKS(c, out) stage_load_block_async(stage, p.x_in, p.x_w, out, row0, nvalid, c);
+        cp_async_commit();
+      }
+      gstamp(p, 4);
       {
         const float* b = blob_f + p.mlp.b_off[0];
-        for (int c = 0; c < hidden; c += 32) {
+        SGNN_FOR_MY_CHUNKS(c, hidden) {
           float v[32];
           acc_load32<TC>(acc, c, v);
 #pragma unroll
@@ -196,13 +224,38 @@ __global__ void __launch_bounds__(kThreads) node_kernel(const SgnnNodeParams p, 
           a_tile_store32<TC>(a_tile, c, v);
         }
       }
-      const int acc_col = mlp_run_rest<TC>(acc, ws, a_tile, p.mlp, w, 0);
+      gstamp(p, 5);
+      const bool more = tile + (int)gridDim.x < n_tiles;
+      const int acc_col = p.tail == SGNN_TAIL_PQ       ? mlp_run_rest<TC>(acc, ws, a_tile, p.mlp, w, 0, p.wp_off, out, p.pq_hidden)
+                          : p.tail == SGNN_TAIL_DECODE ? mlp_run_rest<TC>(acc, ws, a_tile, p.mlp, w, 0, p.dec.w_off[0], out, p.dec.hidden)
+                          : more                       ? mlp_run_rest<TC>(acc, ws, a_tile, p.mlp, w, 0, p.mlp.w_off[0], p.k_pad, hidden)
+                                                       : mlp_run_rest<TC>(acc, ws, a_tile, p.mlp, w, 0);
+      gstamp(p, 6);
       float mean = 0.f, rstd = 1.f;
-      if (p.mlp.has_ln) row_ln_stats<TC>(acc, acc_col, out, blob_f + p.mlp.b_off[p.mlp.n_hidden], mean, rstd);
-      for (int c = 0; c < out; c += 32) {
+      if (p.mlp.has_ln) row_ln_stats<TC>(acc, acc_col, out, blob_f + p.mlp.b_off[p.mlp.n_hidden], mean, rstd, misc->xch);
+      gstamp(p, 7);
+      if (staged) {
+        cp_async_wait_all();
+        __syncwarp();
+      }
+      SGNN_FOR_MY_CHUNKS(c, out) {
         float v[32];
         mlp_out_chunk<TC>(acc, acc_col, c, blob_f, p.mlp, mean, rstd, v);
-        if (valid) {
+        if (staged) {                 // residual from / result into the staging tile; the block leaves as row segments
+          if (valid && p.residual) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 x = *stage_chunk(stage, tid, (c >> 2) + j, out);
+              v[4 * j] += x.x; v[4 * j + 1] += x.y; v[4 * j + 2] += x.z; v[4 * j + 3] += x.w;
+            }
+          }
+          if (p.x_out) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              *stage_chunk(stage, tid, (c >> 2) + j, out) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            stage_store_block(stage, p.x_out, out, out, row0, nvalid, c);
+          }
+        } else if (valid) {
           if (p.residual) {
             const float4* xr = reinterpret_cast<const float4*>(p.x_in + i * p.x_w + c);
 #pragma unroll
@@ -221,6 +274,7 @@ __global__ void __launch_bounds__(kThreads) node_kernel(const SgnnNodeParams p, 
       }
       x_width = out;
     }
+    gstamp(p, 8);
 
     if (p.tail == SGNN_TAIL_PQ) {
       const int hq = p.pq_hidden;
@@ -229,7 +283,9 @@ __global__ void __launch_bounds__(kThreads) node_kernel(const SgnnNodeParams p, 
         gemm_weights<TC>(acc, ws, a_tile, p.wp_off, x_width, hq, 0, false);
         gemm_weights<TC>(acc, ws, a_tile, p.wq_off, x_width, hq, hq, false);
         gemm_weights_wait<TC>(acc, ws);
+        if (first_off >= 0 && tile + (int)gridDim.x < n_tiles) weights_prefetch<TC>(ws, first_off, p.k_pad, first_n);
       }
+      gstamp(p, 9);
       const float* b1 = blob_f + p.pq_bias_off;
       for (int half = 0; half < 2; ++half) {
         if constexpr (!TC) {      // one accumulator region: P, then Q
@@ -237,14 +293,19 @@ __global__ void __launch_bounds__(kThreads) node_kernel(const SgnnNodeParams p, 
           gemm_weights_wait<TC>(acc, ws);
         }
         const int base = TC ? half * hq : 0;
-        for (int c = 0; c < hq; c += 32) {
+        SGNN_FOR_MY_CHUNKS(c, hq) {
           float v[32];
           acc_load32<TC>(acc, base + c, v);
           if (half == 0) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] += b1[c + j];
           }
-          if (valid) {
+          if (staged) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              *stage_chunk(stage, tid, (c >> 2) + j, hq) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            stage_store_block(stage, p.pq_out + half * hq, 2 * hq, hq, row0, nvalid, c);
+          } else if (valid) {
             float4* dst = reinterpret_cast<float4*>(p.pq_out + i * 2 * hq + half * hq + c);
 #pragma unroll
             for (int j = 0; j < 8; ++j) dst[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
@@ -259,10 +320,12 @@ __global__ void __launch_bounds__(kThreads) node_kernel(const SgnnNodeParams p, 
         region ^= 1;
         gemm_weights<TC>(acc, ws, a_tile, p.dec.w_off[l], kin, hd, region * hd, false);
         gemm_weights_wait<TC>(acc, ws);
+        if (l + 1 < p.dec.n_hidden) weights_prefetch<TC>(ws, p.dec.w_off[l + 1], hd, hd);
+        else if (first_off >= 0 && tile + (int)gridDim.x < n_tiles) weights_prefetch<TC>(ws, first_off, p.k_pad, first_n);
         kin = hd;
         if (l + 1 < p.dec.n_hidden) {
           const float* b = blob_f + p.dec.b_off[l];
-          for (int c = 0; c < hd; c += 32) {
+          SGNN_FOR_MY_CHUNKS(c, hd) {
             float v[32];
             acc_load32<TC>(acc, region * hd + c, v);
 #pragma unroll
@@ -278,7 +341,7 @@ __global__ void __launch_bounds__(kThreads) node_kernel(const SgnnNodeParams p, 
       const float* bh = blob_f + p.dec.b_off[p.dec.n_hidden - 1];
 #pragma unroll
       for (int k = 0; k < 8; ++k) o[k] = 0.f;
-      for (int c = 0; c < hd; c += 32) {
+      SGNN_FOR_MY_CHUNKS(c, hd) {
         float v[32];
         acc_load32<TC>(acc, region * hd + c, v);
 #pragma unroll
@@ -290,7 +353,18 @@ __global__ void __launch_bounds__(kThreads) node_kernel(const SgnnNodeParams p, 
           o[k] = a;
         }
       }
-      if (valid) {
+      if (t_parts() > 1) {        // partial dot products of the parts, added in part order (the A tile is free: the
+        float* xo = reinterpret_cast<float*>(a_tile);       // MMAs that read it have completed)
+        for (int k = 0; k < nout; ++k) xo[(t_part() * 8 + k) * kTileRows + tid] = o[k];
+        __syncthreads();
+        if (t_part() == 0)
+          for (int k = 0; k < nout; ++k) {
+            float a = 0.f;
+            for (int q = 0; q < t_parts(); ++q) a += xo[(q * 8 + k) * kTileRows + tid];
+            o[k] = a;
+          }
+      }
+      if (valid && t_part() == 0) {
         for (int k = 0; k < nout; ++k) o[k] += bl[k];
         if (p.dec_out)
           for (int k = 0; k < nout; ++k) p.dec_out[i * nout + k] = o[k];
@@ -306,15 +380,24 @@ __global__ void __launch_bounds__(kThreads) node_kernel(const SgnnNodeParams p, 
         }
       }
     }
+    gstamp(p, 10);
     if constexpr (TC) tc_fence_before_sync();
     __syncthreads();     // TMEM reads and A-tile reads of this tile retired before the next prologue
   }
+  weights_prefetch_drain(ws);
   acc_teardown<TC>(acc);
+  gstamp(p, 11);
 }
 
 }  // namespace sgnn
 
 using namespace sgnn;
+
+// debug: device buffer of >= 32 uint64 receiving the stamps of node_kernel (NULL = off); SGNN_TIMELINE builds
+extern "C" int sgnn_debug_node_generic_timeline(unsigned long long* buf) {
+  SGNN_CUDA(cudaMemcpyToSymbol(g_node_generic_timeline, &buf, sizeof(buf)));
+  return SGNN_OK;
+}
 
 extern "C" size_t sgnn_node_smem_bytes(const SgnnNodeParams* p, int tc) {
   return (size_t)node_smem(*p, tc != 0, node_streamed(*p, tc != 0)).total;
@@ -361,12 +444,14 @@ extern "C" int sgnn_node_fwd(const SgnnNodeParams* p, int use_tensor_cores, int 
   const int n_tiles = sgnn_ceil_div(p->n_rows, kTileRows);
   if (grid > n_tiles) grid = n_tiles;
   if (grid < 1) grid = 1;
+  const int width = p->has_mlp ? imax(p->mlp.hidden, p->mlp.out) : (p->tail == SGNN_TAIL_PQ ? p->pq_hidden : p->dec.hidden);
+  const int threads = kThreads * sgnn_tile_parts(width);
   if (use_tensor_cores) {
     SGNN_ENSURE_SMEM(node_kernel<true>, L.total);
-    SGNN_CUDA(sgnn_launch((node_kernel<true>), dim3(grid), dim3(kThreads), L.total, (cudaStream_t)stream, *p, streamed));
+    SGNN_CUDA(sgnn_launch((node_kernel<true>), dim3(grid), dim3(threads), L.total, (cudaStream_t)stream, *p, streamed));
   } else {
     SGNN_ENSURE_SMEM(node_kernel<false>, L.total);
-    SGNN_CUDA(sgnn_launch((node_kernel<false>), dim3(grid), dim3(kThreads), L.total, (cudaStream_t)stream, *p, streamed));
+    SGNN_CUDA(sgnn_launch((node_kernel<false>), dim3(grid), dim3(threads), L.total, (cudaStream_t)stream, *p, streamed));
   }
   SGNN_LAUNCH_CHECK();
   return SGNN_OK;
