@@ -29,10 +29,23 @@ plan.traj[:, :S].copy_(pos[:, :S])
 plan.launch_steps(0, 2)
 torch.cuda.synchronize()
 buf = torch.zeros(32, dtype=torch.int64, device=dev)
+ebuf = torch.zeros(16, dtype=torch.int64, device=dev)
 L.check(L.lib().sgnn_debug_node_generic_timeline(C.c_void_p(buf.data_ptr())), 0)
+L.check(L.lib().sgnn_debug_edge_generic_timeline(C.c_void_p(ebuf.data_ptr())), 0)
 plan.launch_steps(2, 3)
 torch.cuda.synchronize()
 L.check(L.lib().sgnn_debug_node_generic_timeline(None), 0)
+L.check(L.lib().sgnn_debug_edge_generic_timeline(None), 0)
+e = ebuf.cpu().tolist()
+enames = ["entry", "setup + tmem alloc + first prefetch", "pdl wait + edge count + vectors", "e0 tile + GEMM 0", "P[tgt] + Q[src] + ReLU",
+          "hidden GEMMs and epilogues", "output GEMM", "LayerNorm -> message tile", "segmented sums", "stitch + teardown"]
+print("last edge_layer_kernel of the step")
+for k in range(1, 10):
+    print(f"  {enames[k]:40s} +{(e[k] - e[k - 1]) / 1e3:7.2f} us")
+print(f"  total {(e[9] - e[0]) / 1e3:.2f} us")
+if e[10]:
+    print(f"  inside the sums (thread 0): messages in registers +{(e[10] - e[7]) / 1e3:.2f}, walk + stores +{(e[11] - e[10]) / 1e3:.2f}, "
+          f"barrier +{(e[8] - e[11]) / 1e3:.2f} us")
 t = buf.cpu().tolist()
 names = ["entry", "setup + tmem alloc + first prefetch", "pdl wait + vectors landed", "prologue (agg | x rows)",
          "GEMM 0 (K = 256)", "epilogue 0", "hidden + output GEMMs and epilogues", "LayerNorm moments", "affine + residual + store",

@@ -173,7 +173,7 @@ extern "C" int sgnn_edge_encoder_fwd(const SgnnEdgeEncoderParams* p, int use_ten
   SGNN_CHECK_ARG(smem <= 227 * 1024, "edge_encoder: needs %d bytes of shared memory (> 227 KB)", smem);
   if (grid > p->max_tiles) grid = p->max_tiles;
   if (grid < 1) grid = 1;
-  const int threads = kThreads * sgnn_tile_parts(p->mlp.hidden > p->mlp.out ? p->mlp.hidden : p->mlp.out);
+  const int threads = kThreads * sgnn_tile_parts(p->mlp.hidden > p->mlp.out ? p->mlp.hidden : p->mlp.out, use_tensor_cores != 0);
   if (use_tensor_cores) {
     SGNN_ENSURE_SMEM(edge_encoder_kernel<true>, smem);
     SGNN_CUDA(sgnn_launch((edge_encoder_kernel<true>), dim3(grid), dim3(threads), smem, (cudaStream_t)stream, *p, streamed));

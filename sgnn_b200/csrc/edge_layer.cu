@@ -57,10 +57,25 @@ __device__ __forceinline__ float m_tile_read(const float* m, int row, int col, i
   return m[row * width + ((((col >> 2) ^ (row & 7))) << 2) + (col & 3)];
 }
 
+// optional in-kernel timeline (SGNN_TIMELINE builds; profiles/node_generic_timeline.py): %globaltimer stamps of CTA 0
+__device__ unsigned long long* g_edge_generic_timeline = nullptr;
+__device__ __forceinline__ void estamp(int slot) {
+#ifdef SGNN_TIMELINE
+  if (g_edge_generic_timeline != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    g_edge_generic_timeline[slot] = t;
+  }
+#else
+  (void)slot;
+#endif
+}
+
 template <bool TC>
 __global__ void __launch_bounds__(kThreads * kMaxParts) edge_layer_kernel(const SgnnEdgeLayerParams p,
                                                               const int streamed) {
   pdl_launch_dependents();
+  estamp(0);
   char* smem = smem_base_1024();
   const int hidden = p.mlp.hidden, out = p.mlp.out, he = p.he, nh = p.mlp.n_hidden;
   const int w = hidden > out ? hidden : out;
@@ -84,10 +99,12 @@ __global__ void __launch_bounds__(kThreads * kMaxParts) edge_layer_kernel(const 
   acc_setup<TC>(acc, TC ? pow2_cols(2 * w) : pow2_cols(w), &misc->bar_mma, &misc->tmem_slot,
                 reinterpret_cast<float*>(smem + L.simt));
   weights_prefetch<TC>(ws, p.mlp.w_off[0], he, hidden);
+  estamp(1);
   pdl_wait();
   const int n_edges = p.rowptr[p.n_nodes];
   const int n_tiles = (n_edges + kTileRows - 1) / kTileRows;
   mbar_wait(&misc->bar_w, 0);
+  estamp(2);
   if ((int)blockIdx.x >= n_tiles) {         // uniform per CTA
     weights_prefetch_drain(ws);
     acc_teardown<TC>(acc);
@@ -117,6 +134,7 @@ __global__ void __launch_bounds__(kThreads * kMaxParts) edge_layer_kernel(const 
     gemm_weights<TC>(acc, ws, e_tile, p.mlp.w_off[0], he, hidden, 0, false);
     gemm_weights_wait<TC>(acc, ws);
     weights_prefetch<TC>(ws, p.mlp.w_off[1], hidden, nh > 1 ? hidden : out);
+    estamp(3);
     if constexpr (!TC) __syncthreads();      // every thread has finished reading the e0 tile
     if (t0 && tile + (int)gridDim.x < n_tiles)
       tma_load_span(e_tile, reinterpret_cast<const char*>(p.e_tiles) +
@@ -141,6 +159,7 @@ __global__ void __launch_bounds__(kThreads * kMaxParts) edge_layer_kernel(const 
         a_tile_store32<TC>(hid, c, v);
       }
     }
+    estamp(4);
     // ---- hidden -> hidden stages (nmlp_layers > 1) ----
     int region = 0;
     for (int l = 1; l < nh; ++l) {
@@ -158,12 +177,14 @@ __global__ void __launch_bounds__(kThreads * kMaxParts) edge_layer_kernel(const 
         a_tile_store32<TC>(hid, c, v);
       }
     }
+    estamp(5);
     // ---- output stage + LayerNorm -> message tile M (aliases hid) ----
     a_tile_publish<TC>();
     region ^= 1;
     gemm_weights<TC>(acc, ws, hid, p.mlp.w_off[nh], hidden, out, region * w, false);
     gemm_weights_wait<TC>(acc, ws);
     if (tile + (int)gridDim.x < n_tiles) weights_prefetch<TC>(ws, p.mlp.w_off[0], he, hidden);
+    estamp(6);
     float* m_tile = reinterpret_cast<float*>(hid);
     {
       const float* b = blob_f + p.mlp.b_off[nh];
@@ -188,6 +209,7 @@ __global__ void __launch_bounds__(kThreads * kMaxParts) edge_layer_kernel(const 
     }
     if constexpr (TC) tc_fence_before_sync();
     __syncthreads();   // tgt_s / piece_flag visible; all TMEM reads of this tile retired
+    estamp(7);
 
     // ---- segmented sums over the receiver-sorted rows: warp g of part q owns rows 32g..32g+31 and the columns
     //      [q out/nq, (q+1) out/nq), a lane cpl consecutive ones of them; control flow is warp-uniform ----
@@ -198,38 +220,53 @@ __global__ void __launch_bounds__(kThreads * kMaxParts) edge_layer_kernel(const 
     const int colb = part * (out / nq) + lane * cpl;
     const int r0 = warp * 32;
     if (r0 < nvalid && part < nq) {
-      const int rend = r0 + 32 < nvalid ? r0 + 32 : nvalid;
-      int cur = misc->tgt_s[1 + r0];
-      const bool first_cont = misc->tgt_s[r0] == cur;
-      bool first_seg = true;
-      float sum[4] = {0.f, 0.f, 0.f, 0.f};
-      for (int row = r0; row < rend; ++row) {
-        const int tr = misc->tgt_s[1 + row];
-        if (tr != cur) {
-          if (first_seg && first_cont) {
-            for (int j = 0; j < cpl; ++j) misc->pieces[(2 * warp) * 128 + colb + j] = sum[j];
-            if (lane == 0 && part == 0) { misc->piece_tgt[2 * warp] = cur; misc->piece_flag[2 * warp] = 1; }
-          } else {
-            for (int j = 0; j < cpl; ++j) p.agg[(long)cur * out + colb + j] = sum[j];
+      // The receivers of the warp's 32 rows sit in its lanes (segment starts as one ballot mask) and a column's 32
+      // messages are fetched up front, so the walk over the rows is register arithmetic under warp-uniform branches
+      // (the row-by-row version -- shared-memory loads of receiver and message, a dynamically indexed sum[] in local
+      // memory -- took 7.5 of the kernel's 21 us at 128-wide messages, r02f).  Additions in row order, as before.
+      const int nr = r0 + 32 < nvalid ? 32 : nvalid - r0;
+      const int my_t = misc->tgt_s[1 + r0 + lane];
+      const unsigned start = __ballot_sync(0xffffffffu, my_t != misc->tgt_s[r0 + lane]);   // bit r: row r0 + r opens a receiver
+      const bool first_cont = !(start & 1u);
+      const int last_t = __shfl_sync(0xffffffffu, my_t, nr - 1);
+      const bool cont_next = misc->tgt_s[1 + r0 + nr] == last_t;
+      const bool flagger = lane == 0 && part == 0;
+      for (int j = 0; j < cpl; ++j) {
+        const int col = colb + j;
+        float sum = 0.f, nxt = m_tile_read(m_tile, r0, col, out);
+        bool first_seg = true;
+        estamp(10);
+#pragma unroll 1
+        for (int r = 0; r < nr; ++r) {
+          const float mv = nxt;
+          if (r + 1 < nr) nxt = m_tile_read(m_tile, r0 + r + 1, col, out);
+          if (r > 0 && ((start >> r) & 1u)) {          // the receiver of rows .. r - 1 is complete within this warp
+            const int cur = __shfl_sync(0xffffffffu, my_t, r - 1);
+            if (first_seg && first_cont) {
+              misc->pieces[(2 * warp) * 128 + col] = sum;
+              if (flagger && j == 0) { misc->piece_tgt[2 * warp] = cur; misc->piece_flag[2 * warp] = 1; }
+            } else {
+              p.agg[(long)cur * out + col] = sum;
+            }
+            first_seg = false;
+            sum = 0.f;
           }
-          first_seg = false;
-          cur = tr;
-          sum[0] = sum[1] = sum[2] = sum[3] = 0.f;
+          sum += mv;
         }
-        for (int j = 0; j < cpl; ++j) sum[j] += m_tile_read(m_tile, row, colb + j, out);
+        if (first_seg && first_cont) {
+          misc->pieces[(2 * warp) * 128 + col] = sum;
+          if (flagger && j == 0) { misc->piece_tgt[2 * warp] = last_t; misc->piece_flag[2 * warp] = cont_next ? 3 : 1; }
+        } else if (cont_next) {
+          misc->pieces[(2 * warp + 1) * 128 + col] = sum;
+          if (flagger && j == 0) { misc->piece_tgt[2 * warp + 1] = last_t; misc->piece_flag[2 * warp + 1] = 1; }
+        } else {
+          p.agg[(long)last_t * out + col] = sum;
+        }
       }
-      const bool cont_next = misc->tgt_s[1 + rend] == cur;
-      if (first_seg && first_cont) {
-        for (int j = 0; j < cpl; ++j) misc->pieces[(2 * warp) * 128 + colb + j] = sum[j];
-        if (lane == 0 && part == 0) { misc->piece_tgt[2 * warp] = cur; misc->piece_flag[2 * warp] = cont_next ? 3 : 1; }
-      } else if (cont_next) {
-        for (int j = 0; j < cpl; ++j) misc->pieces[(2 * warp + 1) * 128 + colb + j] = sum[j];
-        if (lane == 0 && part == 0) { misc->piece_tgt[2 * warp + 1] = cur; misc->piece_flag[2 * warp + 1] = 1; }
-      } else {
-        for (int j = 0; j < cpl; ++j) p.agg[(long)cur * out + colb + j] = sum[j];
-      }
+      estamp(11);
     }
     __syncthreads();
+    estamp(8);
     // ---- stitch the pieces of rows that straddle warp groups / tiles (warp 0) ----
     if (threadIdx.x < 32) {
       float carry[4] = {0.f, 0.f, 0.f, 0.f};
@@ -261,9 +298,16 @@ __global__ void __launch_bounds__(kThreads * kMaxParts) edge_layer_kernel(const 
   }
   weights_prefetch_drain(ws);
   acc_teardown<TC>(acc);
+  estamp(9);
 }
 
 }  // namespace sgnn
+
+// debug: device buffer of >= 16 uint64 receiving the stamps of edge_layer_kernel (NULL = off); SGNN_TIMELINE builds
+extern "C" int sgnn_debug_edge_generic_timeline(unsigned long long* buf) {
+  SGNN_CUDA(cudaMemcpyToSymbol(sgnn::g_edge_generic_timeline, &buf, sizeof(buf)));
+  return SGNN_OK;
+}
 
 using namespace sgnn;
 
@@ -307,7 +351,7 @@ extern "C" int sgnn_edge_layer_fwd(const SgnnEdgeLayerParams* p, int use_tensor_
   SGNN_CHECK_ARG(p->blob_bytes >= SGNN_VEC_REGION_BYTES, "edge_layer: blob lacks the vector region");
   if (grid > p->max_tiles) grid = p->max_tiles;
   if (grid < 1) grid = 1;
-  const int threads = kThreads * sgnn_tile_parts(p->mlp.hidden > p->mlp.out ? p->mlp.hidden : p->mlp.out);
+  const int threads = kThreads * sgnn_tile_parts(p->mlp.hidden > p->mlp.out ? p->mlp.hidden : p->mlp.out, use_tensor_cores != 0);
   if (use_tensor_cores) {
     SGNN_ENSURE_SMEM(edge_layer_kernel<true>, smem);
     SGNN_CUDA(sgnn_launch((edge_layer_kernel<true>), dim3(grid), dim3(threads), smem, (cudaStream_t)stream, *p, streamed));

@@ -26,13 +26,17 @@ constexpr int kMaxParts = 4;
 __device__ __forceinline__ int t_row() { return threadIdx.x & (kTileRows - 1); }
 __device__ __forceinline__ int t_part() { return threadIdx.x >> 7; }
 __device__ __forceinline__ int t_parts() { return blockDim.x >> 7; }
-// parts for a layer whose widest row is `width` columns: one per 32-column chunk, at most kMaxParts
-// (SGNN_GENERIC_PARTS=1|2|4 overrides: 1 is the one-thread-per-row mapping)
-__host__ inline int sgnn_tile_parts(int width) {
-  int parts = width >= 128 ? 4 : (width >= 64 ? 2 : 1);
+// Parts for a layer whose widest row is `width` columns: four at 128 columns (the multi-scale network).  Narrower
+// tensor-core layers keep one thread per row: that mapping adds the LayerNorm moments in the order of the 64-wide
+// throughput kernels, so which of the two runs a layer does not change a bit of the result
+// (tests/test_edge_fast_gpu.py); the FFMA parity mode has no TF32 rounding to amplify the reordering and takes two.
+// SGNN_GENERIC_PARTS=1|2|4 overrides (capped by the width).
+__host__ inline int sgnn_tile_parts(int width, bool tc) {
+  int parts = width >= 128 ? 4 : (width >= 64 && !tc ? 2 : 1);
+  const int cap = width >= 128 ? 4 : (width >= 64 ? 2 : 1);
   if (const char* e = getenv("SGNN_GENERIC_PARTS")) {
     const int v = atoi(e);
-    if (v == 1 || v == 2 || v == 4) parts = v < parts ? v : parts;
+    if (v == 1 || v == 2 || v == 4) parts = v < cap ? v : cap;
   }
   return parts;
 }
@@ -130,6 +134,12 @@ constexpr int kWbufBytesTc = 65536;     // tensor-core mode: up to 4 K-blocks of
 constexpr int kWbufBytesSimt = 16384;   // FFMA parity mode: shared memory also holds the accumulators
 __host__ __device__ inline int wbuf_bytes(bool tc) { return tc ? kWbufBytesTc : kWbufBytesSimt; }
 
+// K-blocks of an n-row image that fit the stage buffer: wbuf / (128 n), without the ~40-instruction integer division
+// on the path of every GEMM (n <= 256 and a multiple of 16: the quotient's fraction is a multiple of 1 / 256)
+__device__ __forceinline__ int stage_kblocks(bool tc, int n) {
+  return (int)(__fdividef((float)(wbuf_bytes(tc) / kKBlockBytes), (float)n) + 0.001f);
+}
+
 struct WeightStage {
   const char* gblob;   // the blob in global memory
   char* smem_blob;     // shared copy: whole blob (resident) or the vector region (streamed)
@@ -156,7 +166,7 @@ __device__ __forceinline__ void weights_prefetch(WeightStage& ws, int w_off, int
   if (!ws.streamed || ws.busy || ws.pf_off >= 0) return;
   if constexpr (!TC) __syncthreads();       // FFMA mode: every thread is done with wbuf
   const int kb_total = k / kKBlock;
-  int kb_chunk = wbuf_bytes(TC) / (n * kKBlockBytes);
+  int kb_chunk = stage_kblocks(TC, n);
   if (kb_chunk > kb_total) kb_chunk = kb_total;
   if (threadIdx.x == 0) {
     const int bytes = kb_chunk * n * kKBlockBytes;
@@ -178,6 +188,8 @@ __device__ __forceinline__ void weights_prefetch_drain(WeightStage& ws) {
 
 // D[128 x n] (+)= A[128 x k] * W^T with W the image at byte offset w_off of the blob.
 // All threads call (uniform control flow).  Completion is observed with gemm_wait().
+// (Inlined on purpose: as one shared __noinline__ copy the kernels shrank from 278 / 121 KB to 142 / 73 KB of SASS but
+// the multi-scale step got 10 % slower -- acc / ws then live in local memory; r02f.)
 template <bool TC>
 __device__ __forceinline__ void gemm_weights(TileAcc<TC>& acc, WeightStage& ws, const void* a_tile,
                                              int w_off, int k, int n, int acc_col, bool accumulate) {
@@ -186,7 +198,7 @@ __device__ __forceinline__ void gemm_weights(TileAcc<TC>& acc, WeightStage& ws, 
     return;
   }
   const int kb_total = k / kKBlock;
-  int kb_chunk = wbuf_bytes(TC) / (n * kKBlockBytes);
+  int kb_chunk = stage_kblocks(TC, n);
   if (kb_chunk > kb_total) kb_chunk = kb_total;
   for (int kb0 = 0; kb0 < kb_total; kb0 += kb_chunk) {
     const int nkb = kb_total - kb0 < kb_chunk ? kb_total - kb0 : kb_chunk;

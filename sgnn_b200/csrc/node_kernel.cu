@@ -445,7 +445,7 @@ extern "C" int sgnn_node_fwd(const SgnnNodeParams* p, int use_tensor_cores, int 
   if (grid > n_tiles) grid = n_tiles;
   if (grid < 1) grid = 1;
   const int width = p->has_mlp ? imax(p->mlp.hidden, p->mlp.out) : (p->tail == SGNN_TAIL_PQ ? p->pq_hidden : p->dec.hidden);
-  const int threads = kThreads * sgnn_tile_parts(width);
+  const int threads = kThreads * sgnn_tile_parts(width, use_tensor_cores != 0);
   if (use_tensor_cores) {
     SGNN_ENSURE_SMEM(node_kernel<true>, L.total);
     SGNN_CUDA(sgnn_launch((node_kernel<true>), dim3(grid), dim3(threads), L.total, (cudaStream_t)stream, *p, streamed));

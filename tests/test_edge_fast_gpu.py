@@ -36,18 +36,28 @@ def test_fast_equals_generic(regime, nx, ny, nmlp):
     a, sa = sim.predict_positions(pos[:, :11], [n], types)
     b, sb = sim.predict_positions(pos[:, :11], [n], types)
     assert torch.equal(a, b)                                   # deterministic
-    os.environ["SGNN_EDGE_GENERIC"] = "1"
-    os.environ["SGNN_NODE_GENERIC"] = "1"
-    os.environ["SGNN_ENC_GENERIC"] = "1"
-    try:
-        c, sc = sim.predict_positions(pos[:, :11], [n], types)
-    finally:
-        os.environ.pop("SGNN_EDGE_GENERIC", None)
-        os.environ.pop("SGNN_NODE_GENERIC", None)
-        os.environ.pop("SGNN_ENC_GENERIC", None)
-    torch.cuda.synchronize()
-    assert torch.isfinite(a).all()
-    err = (a - c).abs().max().item()
-    serr = (sa - sc).abs().max().item()
-    print(f"regime {regime} nmlp {nmlp}: N={n} max|fast-generic| pos {err:.3e} strain {serr:.3e}")
-    assert err <= 1e-6 * max(1.0, pos.abs().max().item()) and serr <= 1e-4
+    # The generic kernels with ONE thread per row (their default at 64-wide latents on the tensor cores) add the
+    # LayerNorm moments in the order of the throughput kernels: the same bits.  With two threads per row the moments
+    # are combined over the halves: a last-bit change before a TF32 rounding, i.e. TF32-level differences in the
+    # outputs, bounded like any TF32 result (3e-3 acceleration standard deviations, tests/test_single_scale_gpu.py).
+    acc_std = stats["acceleration"]["std"].max().item()
+    for parts, tol_pos, tol_strain in ((None, 1e-6 * max(1.0, pos.abs().max().item()), 1e-4), ("2", 3e-3 * acc_std, 3e-3)):
+        if parts:
+            os.environ["SGNN_GENERIC_PARTS"] = parts
+        try:
+            a, sa = sim.predict_positions(pos[:, :11], [n], types)     # nmlp = 2: some of its layers run on the generic kernels too
+            os.environ["SGNN_EDGE_GENERIC"] = "1"
+            os.environ["SGNN_NODE_GENERIC"] = "1"
+            os.environ["SGNN_ENC_GENERIC"] = "1"
+            c, sc = sim.predict_positions(pos[:, :11], [n], types)
+        finally:
+            os.environ.pop("SGNN_EDGE_GENERIC", None)
+            os.environ.pop("SGNN_NODE_GENERIC", None)
+            os.environ.pop("SGNN_ENC_GENERIC", None)
+            os.environ.pop("SGNN_GENERIC_PARTS", None)
+        torch.cuda.synchronize()
+        assert torch.isfinite(a).all()
+        err = (a - c).abs().max().item()
+        serr = (sa - sc).abs().max().item()
+        print(f"regime {regime} nmlp {nmlp} parts {parts or 'default'}: N={n} max|fast-generic| pos {err:.3e} strain {serr:.3e}")
+        assert err <= tol_pos and serr <= tol_strain, (parts, err, tol_pos, serr, tol_strain)
