@@ -398,8 +398,10 @@ def _train_config(dev, rank, world, steps, warmup, samples, precision):
            "particles_per_step_global": n_glob, "edges_per_rank": e, "samples_per_s": samples * world * 1e3 / ms,
            "loss_first": losses[0].item() * world, "loss_last": losses[-1].item() * world,
            "collective": "one flat fp32 gradient allreduce (NCCL) inside the captured step" if world > 1 else "none (1 GPU)",
-           "gemm": ("sgnn_b200 tcgen05, hi/lo-split TF32 operands (fp32-grade products)" if precision == "fp32"
-                    else "sgnn_b200 tcgen05, TF32 operands") + "; weight / bias gradients: sgnn_b200 split-row fp32 kernel",
+           "gemm": ("sgnn_b200 tcgen05, hi/lo-split TF32 operands (fp32-grade products); weight / bias gradients: "
+                    "sgnn_b200 split-row fp32 kernel on a forked stream of the captured step" if precision == "fp32"
+                    else "sgnn_b200 tcgen05, TF32 operands; weight / bias gradients: sgnn_b200 tcgen05 (MN-major operands, "
+                    "batched per row set) on a forked stream of the captured step"),
            "step": "ONE CUDA graph per step: weight images, neighbour search, forward, loss, backward, allreduce, Adam; no host read",
            "graph_ops": "sgnn_b200 CUDA (deterministic segment sums / LayerNorm)", "optimizer": "Adam (torch fused, capturable)",
            "breakdown_ms": {k: {"launch_groups": v[0], "total_ms": round(v[1], 4)} for k, v in sorted(prof.items())}}
