@@ -599,7 +599,8 @@ def config1_gpu(dev, steps=5):
     from sgnn_b200.single_scale import evaluate as EV
     batch, stats, radius = make_train_batch(dev, 1, seed0=0)
     sim = make_sim(stats, radius, dev).train()
-    eng = train_engine.TrainEngine(sim, training.make_optimizer(sim.parameters(), 1e-4), batch["positions"].shape[0], dev)
+    eng = train_engine.TrainEngine(sim, training.make_optimizer(sim.parameters(), 1e-4), batch["positions"].shape[0], dev,
+                                   distributed=False)       # runs on rank 0 only: no collective inside
     gen = torch.Generator(device=dev).manual_seed(1)
     for _ in range(3):
         eng.step(batch, 0.5, generator=gen)

@@ -162,7 +162,7 @@ class TrainEngine:
     learning rate (training.make_optimizer builds it)."""
 
     def __init__(self, sim, optimizer, n: int, device, precision: str = "fp32", w_pos: float = 1.0,
-                 w_strain: float = 1.0, group=None, use_graph: bool = True):
+                 w_strain: float = 1.0, group=None, use_graph: bool = True, distributed: bool = True):
         if not supports(sim):
             raise L.SgnnError("TrainEngine: unsupported model (needs single-scale, nmlp_layers=1, one particle type, "
                               "latent 64)")
@@ -173,7 +173,8 @@ class TrainEngine:
         self.precision = precision
         self.w_pos, self.w_strain = float(w_pos), float(w_strain)
         self.group = group
-        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        # distributed=False: a rank-local engine inside an initialised process group (no gradient allreduce)
+        self.world = dist.get_world_size(group) if (distributed and dist.is_initialized()) else 1
         self.use_graph = use_graph
         self.graph = None
         self.dim = sim._particle_dimensions
